@@ -1,0 +1,236 @@
+// Library plumbing + the whole-step entry points (t3b_decode_step, t3b_head_cfg_sample).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "t3b_common.cuh"
+
+// implemented in the kernel translation units
+int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s);
+int32_t t3b_linear_umma_launch(const void* x, const void* w, int rows, int N, int K, void* y, float* partials, int n_split, cudaStream_t s);
+int t3b_umma_pick_split(int rows, int N, int K);
+int t3b_umma_available();
+int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_split, const float* logits_in, int V, int n_req,
+                           const t3b_sampling_t* sp, const t3b_state_t* st, int advance, int32_t* out_tokens, float* logits_out,
+                           cudaStream_t stream);
+int32_t t3b_awq_gemv_launch(const void* x, const t3b_linear_t* w, int rows, void* y, int mode, cudaStream_t s);
+int32_t t3b_awq_umma_launch(const void* x, const t3b_linear_t* w, int rows, void* y, float* partials, int n_split, cudaStream_t s);
+
+static thread_local char g_err[512] = "";
+
+void t3b_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int t3b_num_sms() {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+            sms = 148;
+    }
+    return sms;
+}
+
+extern "C" const char* t3b_last_error(void) { return g_err; }
+extern "C" int32_t t3b_version(void) { return 100; }
+
+extern "C" int32_t t3b_check_device(void) {
+    int dev = 0, major = 0;
+    T3B_CUDA(cudaGetDevice(&dev));
+    T3B_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (major != 10) T3B_FAIL(T3B_ERR_UNSUPPORTED, "libt3b200 is built for sm_100a only; device %d is sm_%dx", dev, major);
+    if (!t3b_umma_available()) T3B_FAIL(T3B_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled driver entry point not found");
+    return T3B_OK;
+}
+
+// ------------------------------------------------------------------ workspace carving
+namespace {
+constexpr size_t kPartialBytes = (8u << 20) + (1u << 20);
+inline size_t al(size_t x) { return (x + 255) & ~size_t(255); }
+
+struct Workspace {
+    char *x_emb, *resid, *normed, *qkv, *q, *attn, *gu, *act, *lin, *head;
+    float* partials;
+    size_t total;
+};
+
+Workspace carve(const t3b_model_t* m, int rows, void* base) {
+    Workspace w;
+    char* p = static_cast<char*>(base);
+    const size_t D = m->hidden, F = m->ffn, V = m->speech_vocab, R = rows;
+    auto take = [&](size_t bytes) { char* r = p; p += al(bytes); return r; };
+    w.x_emb = take(R * D * 2);
+    w.resid = take(R * D * 2);
+    w.normed = take(R * D * 2);
+    w.qkv = take(R * 3 * D * 2);
+    w.q = take(R * D * 2);
+    w.attn = take(R * D * 2);
+    w.gu = take(R * 2 * F * 2);
+    w.act = take(R * F * 2);
+    w.lin = take(R * D * 2);
+    w.head = take(R * V * 2 + 64);
+    w.partials = reinterpret_cast<float*>(take(kPartialBytes));
+    w.total = static_cast<size_t>(p - static_cast<char*>(base));
+    return w;
+}
+
+struct LinOut { const void* y; const float* partials; int n_split; };
+}  // namespace
+
+extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
+    if (!m || max_rows <= 0) return 0;
+    return carve(m, max_rows, nullptr).total + 256;
+}
+
+// ------------------------------------------------------------------ linear dispatch
+static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* y, float* partials, int n_split, int* n_split_out, int impl,
+                          cudaStream_t s) {
+    T3B_CHECK_ARG(x && w && w->w, "linear: null pointer");
+    T3B_CHECK_ARG(rows >= 0 && w->n > 0 && w->k > 0, "linear: bad sizes rows=%d n=%d k=%d", rows, w->n, w->k);
+    T3B_CHECK_ALIGN(x); T3B_CHECK_ALIGN(w->w);
+    if (y) T3B_CHECK_ALIGN(y);
+    if (partials) T3B_CHECK_ALIGN(partials);
+    if (rows == 0) { if (n_split_out) *n_split_out = 1; return T3B_OK; }
+    const bool awq = w->kind == T3B_W_AWQ;
+    T3B_CHECK_ARG(awq || w->kind == T3B_W_BF16, "linear: unknown weight kind %d", w->kind);
+    if (impl == T3B_IMPL_AUTO) impl = (rows <= 4 && w->k % 1024 == 0 && w->k <= 8192) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
+    if (impl == T3B_IMPL_GEMV) {
+        T3B_CHECK_ARG(n_split <= 1, "linear: the GEMV path has no split-K (n_split %d)", n_split);
+        T3B_CHECK_ARG(y != nullptr, "linear: y is null");
+        if (n_split_out) *n_split_out = 1;
+        return awq ? t3b_awq_gemv_launch(x, w, rows, y, 0, s) : t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, 0, s);
+    }
+    T3B_CHECK_ARG(impl == T3B_IMPL_UMMA, "linear: unknown impl %d", impl);
+    if (n_split <= 0) {
+        n_split = t3b_umma_pick_split(rows, w->n, w->k);
+        if (partials == nullptr) n_split = 1;
+        if (y == nullptr && n_split == 1) T3B_FAIL(T3B_ERR_ARG, "linear: n_split resolved to 1 but y is null");
+    }
+    if (n_split_out) *n_split_out = n_split;
+    return awq ? t3b_awq_umma_launch(x, w, rows, y, partials, n_split, s)
+               : t3b_linear_umma_launch(x, w->w, rows, w->n, w->k, y, partials, n_split, s);
+}
+
+extern "C" int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
+                                   int32_t* n_split_out, int32_t impl, void* stream) {
+    T3B_CHECK_ARG(w && w->kind == T3B_W_BF16, "t3b_linear_bf16: weight kind must be T3B_W_BF16");
+    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, t3b_stream(stream));
+}
+
+extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
+                                  int32_t* n_split_out, int32_t impl, void* stream) {
+    T3B_CHECK_ARG(w && w->kind == T3B_W_AWQ, "t3b_linear_awq: weight kind must be T3B_W_AWQ");
+    T3B_CHECK_ARG(w->scales && w->zeros, "t3b_linear_awq: scales / zeros are null");
+    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, t3b_stream(stream));
+}
+
+// ------------------------------------------------------------------ whole step
+static int32_t check_model(const t3b_model_t* m) {
+    T3B_CHECK_ARG(m && m->layers && m->final_norm && m->speech_emb && m->speech_pos_emb && m->rope_cos_sin && m->head.w,
+                  "model: null pointer");
+    T3B_CHECK_SHAPE(m->head_dim == T3B_HEAD_DIM, "model: head_dim %d (kernels are specialised for 64)", m->head_dim);
+    T3B_CHECK_SHAPE(m->hidden == m->n_heads * m->head_dim, "model: hidden %d != heads %d x 64", m->hidden, m->n_heads);
+    T3B_CHECK_SHAPE(m->hidden % 128 == 0 && m->ffn % 128 == 0 && m->hidden <= 4096, "model: hidden %d / ffn %d unsupported", m->hidden, m->ffn);
+    T3B_CHECK_SHAPE(m->n_layers >= 1 && m->speech_vocab >= 2 && m->speech_pos_rows >= 1 && m->max_pos >= 1, "model: bad sizes");
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_decode_step(const t3b_model_t* m, const t3b_kv_t* kv, const t3b_state_t* st, const void* x_in, int32_t rows,
+                                   void* hidden_out, void* workspace, size_t workspace_bytes, void* stream) {
+    int32_t rc = check_model(m);
+    if (rc) return rc;
+    T3B_CHECK_ARG(kv && kv->k && kv->v && st && hidden_out && workspace, "t3b_decode_step: null pointer");
+    T3B_CHECK_ARG(st->rope_pos && st->ctx_lens && st->block_tables && st->max_blocks > 0, "t3b_decode_step: state arrays are null");
+    T3B_CHECK_ARG(rows >= 0 && rows % 2 == 0, "t3b_decode_step: rows %d must be even (cond/uncond pairs)", rows);
+    T3B_CHECK_ARG(x_in || (st->tokens && st->speech_pos), "t3b_decode_step: no input (x_in and state tokens are null)");
+    T3B_CHECK_ALIGN(workspace); T3B_CHECK_ALIGN(hidden_out);
+    if (rows == 0) return T3B_OK;
+    T3B_CHECK_ARG(workspace_bytes >= t3b_workspace_bytes(m, rows), "t3b_decode_step: workspace %zu < %zu bytes", workspace_bytes,
+                  t3b_workspace_bytes(m, rows));
+    cudaStream_t s = t3b_stream(stream);
+    const Workspace ws = carve(m, rows, workspace);
+    const int D = m->hidden, F = m->ffn, H = m->n_heads;
+
+    const void* x0 = x_in;
+    if (!x0) {
+        rc = t3b_embed_gather(m->speech_emb, m->speech_pos_emb, st->tokens, st->speech_pos, rows / 2, D, m->speech_vocab,
+                              m->speech_pos_rows, 2, ws.x_emb, stream);
+        if (rc) return rc;
+        x0 = ws.x_emb;
+    }
+    auto run_linear = [&](const void* x, const t3b_linear_t* w, void* ybuf, LinOut* out) -> int32_t {
+        int ns = 1;
+        int32_t r = linear_any(x, w, rows, ybuf, ws.partials, 0, &ns, T3B_IMPL_AUTO, s);
+        out->n_split = ns;
+        out->y = ns == 1 ? ybuf : nullptr;
+        out->partials = ns == 1 ? nullptr : ws.partials;
+        return r;
+    };
+    LinOut prev = {x0, nullptr, 1};
+    for (int li = 0; li < m->n_layers; ++li) {
+        const t3b_layer_t* L = &m->layers[li];
+        T3B_CHECK_ARG(L->ln1 && L->ln2, "t3b_decode_step: layer %d norm weights are null", li);
+        rc = t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, L->ln1, ws.normed, rows, D, m->rms_eps, li > 0, stream);
+        if (rc) return rc;
+        LinOut qkv;
+        rc = run_linear(ws.normed, &L->qkv, ws.qkv, &qkv);
+        if (rc) return rc;
+        bf16* kp = static_cast<bf16*>(kv->k) + (size_t)li * kv->layer_stride;
+        bf16* vp = static_cast<bf16*>(kv->v) + (size_t)li * kv->layer_stride;
+        rc = t3b_rope_kv_write(qkv.y, qkv.partials, qkv.n_split, rows, nullptr, st->ctx_lens, st->rope_pos, m->rope_cos_sin, m->max_pos,
+                               st->block_tables, st->max_blocks, kp, vp, H, ws.q, stream);
+        if (rc) return rc;
+        rc = t3b_paged_attn_decode(ws.q, rows, nullptr, st->ctx_lens, st->block_tables, st->max_blocks, kp, vp, H, ws.attn, stream);
+        if (rc) return rc;
+        LinOut o;
+        rc = run_linear(ws.attn, &L->o, ws.lin, &o);
+        if (rc) return rc;
+        rc = t3b_add_rmsnorm(o.y, o.partials, o.n_split, ws.resid, L->ln2, ws.normed, rows, D, m->rms_eps, 1, stream);
+        if (rc) return rc;
+        const bool gemv = rows <= 4 && D % 1024 == 0;
+        if (gemv && L->gate_up.kind == T3B_W_BF16) {
+            rc = t3b_linear_gemv_launch(ws.normed, L->gate_up.w, rows, L->gate_up.n, L->gate_up.k, ws.act, 1, s);   // fused SiLU*mul
+            if (rc) return rc;
+        } else if (gemv && L->gate_up.kind == T3B_W_AWQ) {
+            rc = t3b_awq_gemv_launch(ws.normed, &L->gate_up, rows, ws.act, 1, s);
+            if (rc) return rc;
+        } else {
+            LinOut gu;
+            rc = run_linear(ws.normed, &L->gate_up, ws.gu, &gu);
+            if (rc) return rc;
+            rc = t3b_silu_mul(gu.y, gu.partials, gu.n_split, rows, F, ws.act, stream);
+            if (rc) return rc;
+        }
+        rc = run_linear(ws.act, &L->down, ws.lin, &prev);
+        if (rc) return rc;
+    }
+    return t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, m->final_norm, hidden_out, rows, D, m->rms_eps, 1, stream);
+}
+
+extern "C" int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden, int32_t rows, const t3b_sampling_t* sp,
+                                       const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out, void* workspace,
+                                       size_t workspace_bytes, void* stream) {
+    int32_t rc = check_model(m);
+    if (rc) return rc;
+    T3B_CHECK_ARG(hidden && sp && workspace, "t3b_head_cfg_sample: null pointer");
+    T3B_CHECK_ARG(rows >= 0 && rows % 2 == 0, "t3b_head_cfg_sample: rows %d must be even", rows);
+    T3B_CHECK_ARG(m->head.kind == T3B_W_BF16, "t3b_head_cfg_sample: speech_head must be bf16");
+    if (rows == 0) return T3B_OK;
+    T3B_CHECK_ARG(workspace_bytes >= t3b_workspace_bytes(m, rows), "t3b_head_cfg_sample: workspace too small");
+    const Workspace ws = carve(m, rows, workspace);
+    int ns = 1;
+    rc = linear_any(hidden, &m->head, rows, ws.head, ws.partials, 0, &ns, T3B_IMPL_AUTO, t3b_stream(stream));
+    if (rc) return rc;
+    return t3b_sampler_launch(ns == 1 ? ws.head : nullptr, ns == 1 ? nullptr : ws.partials, ns, nullptr, m->speech_vocab, rows / 2, sp, st,
+                              advance, out_tokens, logits_out, t3b_stream(stream));
+}
+
+extern "C" int32_t t3b_sample_logits(const float* logits, int32_t n_req, int32_t vocab, const t3b_sampling_t* sp, const t3b_state_t* st,
+                                     int32_t* out_tokens, void* stream) {
+    T3B_CHECK_ARG(logits && sp && out_tokens && n_req >= 0, "t3b_sample_logits: null pointer");
+    return t3b_sampler_launch(nullptr, nullptr, 1, logits, vocab, n_req, sp, st, 0, out_tokens, nullptr, t3b_stream(stream));
+}

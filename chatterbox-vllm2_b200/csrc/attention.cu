@@ -1,0 +1,148 @@
+// F2.4 paged decode attention (llama.py:211-221,231), MHA (group = 1), head_dim 64, block 16.
+//
+// HBM-bound byte work: per (query, head) the kernel streams (ctx) x 128 B of K and of V exactly once.
+// Pool layout [block][head][16 tok][64] makes one (block, head) slice 2 KB contiguous, so a warp's
+// four 128-bit loads per slice are four fully coalesced 512 B segments.
+//
+// CTA = one (query, head); its NW warps take the row's KV pages round-robin two at a time (16 128-bit
+// loads in flight per lane), keep a private online-softmax state and are merged through shared
+// memory at the end (fixed order -> deterministic).  Dot products are reduced across the 8 lanes of
+// a token with a 7-shuffle butterfly-transpose, softmax statistics with warp shuffles.
+#include "t3b_common.cuh"
+
+#define ATT_PAGES_PER_ITER 2
+
+__global__ void __launch_bounds__(256) paged_attn_decode_kernel(const bf16* __restrict__ q, const int32_t* __restrict__ tok_row,
+                                                                const int32_t* __restrict__ tok_idx,
+                                                                const int32_t* __restrict__ block_tables, int max_blocks,
+                                                                const bf16* __restrict__ k_pool, const bf16* __restrict__ v_pool,
+                                                                int n_heads, bf16* __restrict__ out) {
+    __shared__ float sm_m[8], sm_l[8];
+    __shared__ float sm_acc[8][64];
+    pdl_wait();
+    pdl_launch_dependents();
+    const int t = blockIdx.x / n_heads, h = blockIdx.x - t * n_heads;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int t4 = lane >> 3, c = lane & 7;
+    const int row = tok_row ? tok_row[t] : t;
+    const int ctx = tok_idx[t] + 1;                      // keys 0..tok_idx[t] (own token was just written)
+    const int n_pages = (ctx + 15) >> 4;
+    const int32_t* bt = block_tables + (size_t)row * max_blocks;
+    const float kScale = 0.125f * 1.4426950408889634f;   // head_dim^-0.5 * log2(e)
+
+    float qf[8];
+    unpack8(*reinterpret_cast<const uint4*>(q + ((size_t)t * n_heads + h) * 64 + c * 8), qf);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) qf[e] *= kScale;
+
+    float m = -INFINITY, l = 0.f, acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+
+    for (int p0 = warp * ATT_PAGES_PER_ITER; p0 < n_pages; p0 += nw * ATT_PAGES_PER_ITER) {
+        uint4 kv[ATT_PAGES_PER_ITER][4], vv[ATT_PAGES_PER_ITER][4];
+#pragma unroll
+        for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp) {
+            const int page = p0 + pp;
+            const int blk = page < n_pages ? bt[page] : bt[p0];   // tail page re-reads a valid page, masked below
+            const size_t base = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK) * 64 + (size_t)lane * 8;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) kv[pp][j] = ldg_stream(k_pool + base + j * 256);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) vv[pp][j] = ldg_stream(v_pool + base + j * 256);
+        }
+        // partial dot products: value i = pp*4 + j belongs to token p0*16 + pp*16 + 4j + t4
+        float s[8];
+#pragma unroll
+        for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float kf[8];
+                unpack8(kv[pp][j], kf);
+                float d = 0.f;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) d = fmaf(qf[e], kf[e], d);
+                s[pp * 4 + j] = d;
+            }
+        // butterfly-transpose reduce over the 8 lanes (c) of a token: lane c ends with value i == c
+        float w4[4], w2[2], sc;
+        {
+            const bool up = (c & 4) != 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float send = up ? s[i] : s[i + 4], keep = up ? s[i + 4] : s[i];
+                w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+            }
+            const bool up2 = (c & 2) != 0;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const float send = up2 ? w4[i] : w4[i + 2], keep = up2 ? w4[i + 2] : w4[i];
+                w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+            const bool up1 = (c & 1) != 0;
+            const float send = up1 ? w2[0] : w2[1], keep = up1 ? w2[1] : w2[0];
+            sc = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+        }
+        const int my_tok = (p0 + (c >> 2)) * 16 + 4 * (c & 3) + t4;
+        if (my_tok >= ctx) sc = -INFINITY;
+        const float m_new = fmaxf(m, warp_max(sc));     // finite: page p0 always holds >= 1 valid token
+        const float corr = exp2f(m - m_new);
+        const float pr = exp2f(sc - m_new);
+        l = l * corr + pr;                              // per-lane partial of the row sum
+        m = m_new;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] *= corr;
+#pragma unroll
+        for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float pj = __shfl_sync(0xffffffffu, pr, t4 * 8 + pp * 4 + j);
+                float vf[8];
+                unpack8(vv[pp][j], vf);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
+            }
+    }
+    // fold the four token groups (t4) of the warp, then the row sum
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
+        acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
+    }
+    l = warp_sum(l);
+    if (lane < 8) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) sm_acc[warp][lane * 8 + e] = acc[e];
+    }
+    if (lane == 0) { sm_m[warp] = m; sm_l[warp] = l; }
+    __syncthreads();
+    if (threadIdx.x < 64) {
+        float mm = -INFINITY;
+        for (int w = 0; w < nw; ++w) mm = fmaxf(mm, sm_m[w]);
+        float ll = 0.f, o = 0.f;
+        for (int w = 0; w < nw; ++w) {
+            const float f = sm_m[w] == -INFINITY ? 0.f : exp2f(sm_m[w] - mm);
+            ll += sm_l[w] * f;
+            o += sm_acc[w][threadIdx.x] * f;
+        }
+        out[((size_t)t * n_heads + h) * 64 + threadIdx.x] = __float2bfloat16_rn(o / ll);
+    }
+}
+
+extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
+                                         const int32_t* block_tables, int32_t max_blocks, const void* k_pool, const void* v_pool,
+                                         int32_t n_heads, void* out, void* stream) {
+    T3B_CHECK_ARG(q && tok_idx && block_tables && k_pool && v_pool && out, "t3b_paged_attn_decode: null pointer");
+    T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && n_heads >= 1, "t3b_paged_attn_decode: bad sizes");
+    T3B_CHECK_ALIGN(q); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
+    if (n_tok == 0) return T3B_OK;
+    // warps per (query, head): enough CTAs x warps to cover the machine at small batch, fewer at large
+    const long units = (long)n_tok * n_heads;
+    const int sms = t3b_num_sms();
+    int nw = 8;
+    if (units >= (long)sms * 8) nw = 2;
+    else if (units >= (long)sms * 4) nw = 4;
+    T3B_CUDA(t3b_launch(paged_attn_decode_kernel, dim3((unsigned)units), dim3(nw * 32), 0, t3b_stream(stream), (const bf16*)q, tok_row,
+                        tok_idx, block_tables, max_blocks, (const bf16*)k_pool, (const bf16*)v_pool, n_heads, (bf16*)out));
+    return T3B_OK;
+}

@@ -1,0 +1,245 @@
+// E1 embedding gather, F2.1 fused add+RMSNorm, F2.3 RoPE + paged-KV write, F2.6 SiLU*mul.
+// All are HBM/L2-bound byte work: 128-bit accesses, one pass, bf16 rounding at the points where
+// the reference's bf16 pipeline materialises a tensor (see oracle/t3_ref.py header).
+#include "t3b_common.cuh"
+
+// ------------------------------------------------------------------ E1
+// t3.py:440,475-480: out[dup*b+j] = bf16(emb[tok] + pos_emb[p % pos_rows])
+__global__ void __launch_bounds__(128) embed_gather_kernel(const uint4* __restrict__ emb, const uint4* __restrict__ pos_emb,
+                                                           const int32_t* __restrict__ tokens, const int32_t* __restrict__ speech_pos,
+                                                           int hidden8, int emb_rows, int pos_rows, int dup, uint4* __restrict__ out) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int b = blockIdx.x;
+    int tok = tokens[b];
+    tok = min(max(tok, 0), emb_rows - 1);
+    int p = speech_pos[b] % pos_rows;
+    if (p < 0) p += pos_rows;
+    for (int i = threadIdx.x; i < hidden8; i += blockDim.x) {
+        float a[8], c[8];
+        unpack8(emb[(size_t)tok * hidden8 + i], a);
+        unpack8(pos_emb[(size_t)p * hidden8 + i], c);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) a[e] += c[e];
+        const uint4 v = pack8(a);
+        for (int j = 0; j < dup; ++j) out[(size_t)(b * dup + j) * hidden8 + i] = v;
+    }
+}
+
+// ------------------------------------------------------------------ F2.1
+// vllm ir/ops/layernorm.py:40-59.  One CTA per row; each thread owns up to 2 chunks of 8 elements
+// (hidden <= 2048*... generic loop kept in registers for hidden == 1024 with 128 threads).
+template <int MAX_CHUNKS>
+__global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__ partials, int n_split,
+                                                          size_t split_stride4,  // rows*hidden/4
+                                                          uint4* __restrict__ residual, const uint4* __restrict__ weight,
+                                                          uint4* __restrict__ y, int hidden8, float eps, int has_residual) {
+    __shared__ float red[4];
+    pdl_wait();
+    pdl_launch_dependents();
+    const int row = blockIdx.x;
+    float s[MAX_CHUNKS][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int c = 0; c < MAX_CHUNKS; ++c) {
+        const int i = threadIdx.x + c * 128;
+        if (i < hidden8) {
+            float xv[8];
+            if (x != nullptr) {
+                unpack8(x[(size_t)row * hidden8 + i], xv);
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) xv[e] = 0.f;
+                for (int sp = 0; sp < n_split; ++sp) {            // fixed order -> deterministic
+                    const float4* p = partials + sp * split_stride4 + ((size_t)row * hidden8 + i) * 2;
+                    const float4 a = p[0], b = p[1];
+                    xv[0] += a.x; xv[1] += a.y; xv[2] += a.z; xv[3] += a.w;
+                    xv[4] += b.x; xv[5] += b.y; xv[6] += b.z; xv[7] += b.w;
+                }
+#pragma unroll
+                for (int e = 0; e < 8; ++e) xv[e] = bf16_round(xv[e]);  // the GEMM's bf16 output
+            }
+            if (has_residual) {
+                float r[8];
+                unpack8(residual[(size_t)row * hidden8 + i], r);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) xv[e] += r[e];
+            }
+            residual[(size_t)row * hidden8 + i] = pack8(xv);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { s[c][e] = xv[e]; ss += xv[e] * xv[e]; }
+        }
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    const float tot = (red[0] + red[1]) + (red[2] + red[3]);
+    const float rstd = rsqrtf(tot / (float)(hidden8 * 8) + eps);
+#pragma unroll
+    for (int c = 0; c < MAX_CHUNKS; ++c) {
+        const int i = threadIdx.x + c * 128;
+        if (i < hidden8) {
+            float w[8], o[8];
+            unpack8(weight[i], w);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] = bf16_round(s[c][e] * rstd) * w[e];   // x.to(weight.dtype) * weight
+            y[(size_t)row * hidden8 + i] = pack8(o);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ F2.3 + KV write
+// One CTA per token, one warp per head: lane j rotates the pair (j, j+32) of q and k
+// (rotary_embedding/common.py:144-174 in bf16 tensor arithmetic: each product and the sum round).
+__global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restrict__ qkv, const float* __restrict__ partials, int n_split,
+                                                            size_t split_stride, const int32_t* __restrict__ tok_row,
+                                                            const int32_t* __restrict__ tok_idx, const int32_t* __restrict__ rope_pos,
+                                                            const bf16* __restrict__ cos_sin, int max_pos,
+                                                            const int32_t* __restrict__ block_tables, int max_blocks,
+                                                            bf16* __restrict__ k_pool, bf16* __restrict__ v_pool, int n_heads,
+                                                            bf16* __restrict__ q_out) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int t = blockIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int hidden = n_heads * 64;
+    const int row = tok_row ? tok_row[t] : t;
+    const int idx = tok_idx[t];
+    int pos = rope_pos[t];
+    pos = min(max(pos, 0), max_pos - 1);
+    const float c = __bfloat162float(cos_sin[(size_t)pos * 64 + lane]);
+    const float s = __bfloat162float(cos_sin[(size_t)pos * 64 + 32 + lane]);
+    const int blk = block_tables[(size_t)row * max_blocks + (idx >> 4)];
+    for (int h = threadIdx.x >> 5; h < n_heads; h += blockDim.x >> 5) {
+        float v[6];   // q1 q2 k1 k2 v1 v2
+#pragma unroll
+        for (int part = 0; part < 3; ++part) {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const size_t col = (size_t)part * hidden + h * 64 + half * 32 + lane;
+                float a;
+                if (qkv != nullptr) {
+                    a = __bfloat162float(qkv[(size_t)t * 3 * hidden + col]);
+                } else {
+                    a = 0.f;
+                    for (int sp = 0; sp < n_split; ++sp) a += partials[sp * split_stride + (size_t)t * 3 * hidden + col];
+                    a = bf16_round(a);
+                }
+                v[part * 2 + half] = a;
+            }
+        }
+        const float q1 = bf16_round(bf16_round(v[0] * c) - bf16_round(v[1] * s));
+        const float q2 = bf16_round(bf16_round(v[1] * c) + bf16_round(v[0] * s));
+        const float k1 = bf16_round(bf16_round(v[2] * c) - bf16_round(v[3] * s));
+        const float k2 = bf16_round(bf16_round(v[3] * c) + bf16_round(v[2] * s));
+        bf16* qo = q_out + (size_t)t * hidden + h * 64;
+        qo[lane] = __float2bfloat16_rn(q1);
+        qo[32 + lane] = __float2bfloat16_rn(q2);
+        const size_t slot = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK + (idx & 15)) * 64;
+        k_pool[slot + lane] = __float2bfloat16_rn(k1);
+        k_pool[slot + 32 + lane] = __float2bfloat16_rn(k2);
+        v_pool[slot + lane] = __float2bfloat16_rn(v[4]);
+        v_pool[slot + 32 + lane] = __float2bfloat16_rn(v[5]);
+    }
+}
+
+// ------------------------------------------------------------------ F2.6
+// activation.py:138-141: F.silu(gate) * up on bf16 tensors -> two roundings.
+__global__ void __launch_bounds__(256) silu_mul_kernel(const uint4* __restrict__ gu, const float4* __restrict__ partials, int n_split,
+                                                       size_t split_stride4, int ffn8, uint4* __restrict__ act, int total) {
+    pdl_wait();
+    pdl_launch_dependents();
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int row = i / ffn8, c = i - row * ffn8;
+        float g[8], u[8];
+        if (gu != nullptr) {
+            unpack8(gu[(size_t)row * 2 * ffn8 + c], g);
+            unpack8(gu[(size_t)row * 2 * ffn8 + ffn8 + c], u);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { g[e] = 0.f; u[e] = 0.f; }
+            for (int sp = 0; sp < n_split; ++sp) {
+                const float4* pg = partials + sp * split_stride4 + ((size_t)row * 2 * ffn8 + c) * 2;
+                const float4* pu = pg + (size_t)ffn8 * 2;
+                const float4 a = pg[0], b = pg[1], d = pu[0], f = pu[1];
+                g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w; g[4] += b.x; g[5] += b.y; g[6] += b.z; g[7] += b.w;
+                u[0] += d.x; u[1] += d.y; u[2] += d.z; u[3] += d.w; u[4] += f.x; u[5] += f.y; u[6] += f.z; u[7] += f.w;
+            }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { g[e] = bf16_round(g[e]); u[e] = bf16_round(u[e]); }
+        }
+        float o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = bf16_round(g[e] / (1.0f + expf(-g[e]))) * u[e];
+        act[(size_t)row * ffn8 + c] = pack8(o);
+    }
+}
+
+// ------------------------------------------------------------------ C ABI
+extern "C" int32_t t3b_embed_gather(const void* emb, const void* pos_emb, const int32_t* tokens, const int32_t* speech_pos,
+                                    int32_t n_req, int32_t hidden, int32_t emb_rows, int32_t pos_rows, int32_t dup, void* out,
+                                    void* stream) {
+    T3B_CHECK_ARG(emb && pos_emb && tokens && speech_pos && out, "t3b_embed_gather: null pointer");
+    T3B_CHECK_ARG(n_req >= 0 && dup >= 1 && emb_rows > 0 && pos_rows > 0, "t3b_embed_gather: bad sizes");
+    T3B_CHECK_SHAPE(hidden > 0 && hidden % 8 == 0, "t3b_embed_gather: hidden %d not a multiple of 8", hidden);
+    T3B_CHECK_ALIGN(emb); T3B_CHECK_ALIGN(pos_emb); T3B_CHECK_ALIGN(out);
+    if (n_req == 0) return T3B_OK;
+    T3B_CUDA(t3b_launch(embed_gather_kernel, dim3(n_req), dim3(128), 0, t3b_stream(stream), (const uint4*)emb, (const uint4*)pos_emb,
+                        tokens, speech_pos, hidden / 8, emb_rows, pos_rows, dup, (uint4*)out));
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_add_rmsnorm(const void* x, const float* partials, int32_t n_split, void* residual, const void* weight,
+                                   void* y, int32_t rows, int32_t hidden, float eps, int32_t has_residual, void* stream) {
+    T3B_CHECK_ARG((x != nullptr) != (partials != nullptr), "t3b_add_rmsnorm: exactly one of x / partials");
+    T3B_CHECK_ARG(residual && weight && y && rows >= 0, "t3b_add_rmsnorm: null pointer");
+    T3B_CHECK_ARG(x || n_split >= 1, "t3b_add_rmsnorm: n_split %d", n_split);
+    T3B_CHECK_SHAPE(hidden > 0 && hidden % 8 == 0 && hidden <= 4096, "t3b_add_rmsnorm: hidden %d unsupported", hidden);
+    if (x) T3B_CHECK_ALIGN(x);
+    if (partials) T3B_CHECK_ALIGN(partials);
+    T3B_CHECK_ALIGN(residual); T3B_CHECK_ALIGN(weight); T3B_CHECK_ALIGN(y);
+    if (rows == 0) return T3B_OK;
+    const size_t stride4 = (size_t)rows * hidden / 4;
+    if (hidden <= 1024) {
+        T3B_CUDA(t3b_launch(add_rmsnorm_kernel<1>, dim3(rows), dim3(128), 0, t3b_stream(stream), (const uint4*)x, (const float4*)partials,
+                            n_split, stride4, (uint4*)residual, (const uint4*)weight, (uint4*)y, hidden / 8, eps, has_residual));
+    } else {
+        T3B_CUDA(t3b_launch(add_rmsnorm_kernel<4>, dim3(rows), dim3(128), 0, t3b_stream(stream), (const uint4*)x, (const float4*)partials,
+                            n_split, stride4, (uint4*)residual, (const uint4*)weight, (uint4*)y, hidden / 8, eps, has_residual));
+    }
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_rope_kv_write(const void* qkv, const float* partials, int32_t n_split, int32_t n_tok, const int32_t* tok_row,
+                                     const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int32_t max_pos,
+                                     const int32_t* block_tables, int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads,
+                                     void* q_out, void* stream) {
+    T3B_CHECK_ARG((qkv != nullptr) != (partials != nullptr), "t3b_rope_kv_write: exactly one of qkv / partials");
+    T3B_CHECK_ARG(tok_idx && rope_pos && rope_cos_sin && block_tables && k_pool && v_pool && q_out, "t3b_rope_kv_write: null pointer");
+    T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && max_pos > 0 && (qkv || n_split >= 1), "t3b_rope_kv_write: bad sizes");
+    T3B_CHECK_SHAPE(n_heads >= 1 && n_heads <= 64, "t3b_rope_kv_write: n_heads %d", n_heads);
+    if (n_tok == 0) return T3B_OK;
+    const int threads = 32 * (n_heads < 16 ? n_heads : 16);
+    T3B_CUDA(t3b_launch(rope_kv_write_kernel, dim3(n_tok), dim3(threads), 0, t3b_stream(stream), (const bf16*)qkv, partials, n_split,
+                        (size_t)n_tok * 3 * n_heads * 64, tok_row, tok_idx, rope_pos, (const bf16*)rope_cos_sin, max_pos, block_tables,
+                        max_blocks, (bf16*)k_pool, (bf16*)v_pool, n_heads, (bf16*)q_out));
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_silu_mul(const void* gate_up, const float* partials, int32_t n_split, int32_t rows, int32_t ffn, void* act,
+                                void* stream) {
+    T3B_CHECK_ARG((gate_up != nullptr) != (partials != nullptr), "t3b_silu_mul: exactly one of gate_up / partials");
+    T3B_CHECK_ARG(act && rows >= 0 && (gate_up || n_split >= 1), "t3b_silu_mul: bad arguments");
+    T3B_CHECK_SHAPE(ffn > 0 && ffn % 8 == 0, "t3b_silu_mul: ffn %d not a multiple of 8", ffn);
+    if (gate_up) T3B_CHECK_ALIGN(gate_up);
+    if (partials) T3B_CHECK_ALIGN(partials);
+    T3B_CHECK_ALIGN(act);
+    if (rows == 0) return T3B_OK;
+    const int total = rows * (ffn / 8);
+    int blocks = (total + 255) / 256;
+    const int cap = t3b_num_sms() * 8;
+    if (blocks > cap) blocks = cap;
+    T3B_CUDA(t3b_launch(silu_mul_kernel, dim3(blocks), dim3(256), 0, t3b_stream(stream), (const uint4*)gate_up, (const float4*)partials,
+                        n_split, (size_t)rows * 2 * ffn / 4, ffn / 8, (uint4*)act, total));
+    return T3B_OK;
+}

@@ -1,0 +1,211 @@
+/*
+ * t3b200.h - C ABI of libt3b200.so: the B200 (sm_100a) implementation of the Chatterbox T3
+ * CFG decode step.
+ *
+ * Nothing comparable exists in the reference (groxaxo/chatterbox-vllm2 is pure Python and all of
+ * its arithmetic runs inside the vllm==0.10.0 wheel); every entry point below cites the reference
+ * interface (file:line, relative to the reference repo; "vllm:" = the engine it drives) whose
+ * arithmetic it replaces.  INTEGRATION.md shows the ctypes binding a maintainer adds on the
+ * reference side.
+ *
+ * Conventions
+ *   - every function returns int32_t: 0 = T3B_OK, <0 = T3B_ERR_*; t3b_last_error() gives the
+ *     thread-local message of the last failure on this host thread.
+ *   - all data pointers are DEVICE pointers (tensor.data_ptr()) unless the name says host_*;
+ *     the last argument is the cudaStream_t to launch on (passed as void*).
+ *   - no allocation, no ownership transfer, no host synchronisation inside any entry point;
+ *     scratch comes from the caller (t3b_workspace_bytes()).  All launches are CUDA-graph
+ *     capturable.
+ *   - bf16 = 16-bit bfloat16, row-major.  R = CFG rows (row 2i = cond, 2i+1 = uncond of request i;
+ *     t3.py:697-708 batches the two halves the same way), B = R/2 requests.
+ *   - thread model: one host thread per GPU context; re-entrant across streams given disjoint
+ *     workspaces.
+ */
+#ifndef T3B200_H
+#define T3B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define T3B_OK               0
+#define T3B_ERR_ARG         -1   /* null / out-of-range argument */
+#define T3B_ERR_SHAPE       -2   /* shape the kernels do not support */
+#define T3B_ERR_ALIGN       -3   /* pointer not 16-byte aligned */
+#define T3B_ERR_CUDA        -4   /* a CUDA runtime / driver call failed */
+#define T3B_ERR_UNSUPPORTED -5   /* device is not sm_100 */
+
+#define T3B_KV_BLOCK 16          /* tokens per paged-KV block (BASELINE.json configs[3]) */
+#define T3B_HEAD_DIM 64
+
+/* linear-layer weight formats */
+#define T3B_W_BF16 0             /* w = bf16 [N, K] row-major (nn.Linear layout) */
+#define T3B_W_AWQ  1             /* AutoAWQ GEMM, group 128, repacked by t3b_repack_weights_awq */
+
+/* kernel selection for t3b_linear_* (0 lets the library choose by row count) */
+#define T3B_IMPL_AUTO 0
+#define T3B_IMPL_GEMV 1          /* SIMT 128-bit-load GEMV, rows <= 4                */
+#define T3B_IMPL_UMMA 2          /* TMA-fed tcgen05.mma, accumulators in TMEM        */
+
+/* CFG combine arithmetic (t3.py:662 runs in bf16 tensors; SURVEY.md 8(a) also defines fp32) */
+#define T3B_COMBINE_BF16 0
+#define T3B_COMBINE_FP32 1
+
+typedef struct t3b_linear {
+    int32_t kind;                /* T3B_W_* */
+    int32_t n, k;                /* out features, in features */
+    const void* w;               /* bf16 [n,k]  |  AWQ repacked nibbles */
+    const void* scales;          /* AWQ: bf16 [k/128, n]          (else NULL) */
+    const void* zeros;           /* AWQ: uint8 [k/128, n]         (else NULL) */
+} t3b_linear_t;
+
+typedef struct t3b_layer {       /* one LlamaDecoderLayer (vllm:model_executor/models/llama.py:316-333) */
+    t3b_linear_t qkv;            /* [3*hidden, hidden]  q|k|v rows stacked (llama.py:437-443) */
+    t3b_linear_t o;              /* [hidden, hidden] */
+    t3b_linear_t gate_up;        /* [2*ffn, hidden]     gate rows first */
+    t3b_linear_t down;           /* [hidden, ffn] */
+    const void* ln1;             /* bf16 [hidden] input_layernorm.weight */
+    const void* ln2;             /* bf16 [hidden] post_attention_layernorm.weight */
+} t3b_layer_t;
+
+typedef struct t3b_model {
+    int32_t n_layers, hidden, n_heads, head_dim, ffn, speech_vocab;
+    int32_t speech_pos_rows;     /* rows of speech_pos_emb (4100, t3.py:283) */
+    int32_t max_pos;             /* rows of rope_cos_sin */
+    float   rms_eps;
+    const t3b_layer_t* layers;   /* HOST array [n_layers] of structs holding device pointers */
+    const void* final_norm;      /* bf16 [hidden]  tfmr.norm.weight */
+    t3b_linear_t head;           /* speech_head [speech_vocab, hidden], bf16 only */
+    const void* speech_emb;      /* bf16 [speech_vocab, hidden] */
+    const void* speech_pos_emb;  /* bf16 [speech_pos_rows, hidden] */
+    const void* rope_cos_sin;    /* bf16 [max_pos, head_dim]  cos(32) | sin(32) */
+} t3b_model_t;
+
+/* Paged KV pool.  Layout per layer: [num_blocks][n_heads][T3B_KV_BLOCK][head_dim] bf16, K and V
+ * separate.  (vLLM's flash layout is [block][token][head][dim]; heads are hoisted here so one
+ * (block, head) slice is 2 KB contiguous.)  Block 0 is reserved as a scratch block for idle rows. */
+typedef struct t3b_kv {
+    void* k; void* v;            /* bf16 [n_layers][num_blocks][n_heads][16][64] */
+    int64_t layer_stride;        /* elements between layers = num_blocks*n_heads*16*64 */
+    int32_t num_blocks;
+} t3b_kv_t;
+
+/* Per-step device-resident request state; the sampler advances it so a captured graph can be
+ * replayed with no host writes between steps. */
+typedef struct t3b_state {
+    int32_t* tokens;             /* [B]  in: last sampled speech token (un-offset); out: new token */
+    int32_t* speech_pos;         /* [B]  index into speech_pos_emb for `tokens` (t3.py:468-478)   */
+    int32_t* rope_pos;           /* [R]  RoPE position of the token being fed (= ctx_lens)        */
+    int32_t* ctx_lens;           /* [R]  tokens already in the row's KV cache                     */
+    const int32_t* block_tables; /* [R, max_blocks] physical block ids                            */
+    int32_t  max_blocks;
+    int32_t* history;            /* [B, hist_stride] generated tokens (penalty history, S2)       */
+    int32_t* hist_len;           /* [B] */
+    int32_t  hist_stride;
+    int32_t* step;               /* [B]  sampler step counter (Philox counter word 1)             */
+    int32_t* active;             /* [B]  1 = decoding, 0 = idle slot / finished                   */
+    int32_t  stop_token;         /* 6562 (t3_config.py:9); sampling it clears active[b]           */
+    int32_t  max_ctx;            /* capacity guard: a row never advances past this many tokens     */
+} t3b_state_t;
+
+typedef struct t3b_sampling {    /* per-request device arrays [B]; tts.py:455-464 SamplingParams */
+    const float* cfg_scale;      /* CHATTERBOX_CFG_SCALE (t3.py:296), per request here             */
+    const float* repetition_penalty;
+    const float* temperature;    /* < 1e-5 = greedy (vllm:v1/sample/sampler.py _SAMPLING_EPS)      */
+    const float* min_p;
+    const float* top_p;
+    const uint64_t* seed;
+    int32_t combine;             /* T3B_COMBINE_* */
+} t3b_sampling_t;
+
+const char* t3b_last_error(void);
+int32_t     t3b_version(void);
+/* 0 if the current device is sm_100 and the driver entry points resolve, else T3B_ERR_UNSUPPORTED */
+int32_t     t3b_check_device(void);
+/* scratch needed by t3b_decode_step / t3b_head_cfg_sample for up to max_rows CFG rows */
+size_t      t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows);
+
+/* E1  t3.py:440,475-480 (+ learned_pos_emb.py:21-32): out[dup*b + j] = emb[tokens[b]] +
+ *     pos_emb[speech_pos[b] % pos_rows], j < dup.  out bf16 [n_req*dup, hidden]. */
+int32_t t3b_embed_gather(const void* emb, const void* pos_emb, const int32_t* tokens,
+                         const int32_t* speech_pos, int32_t n_req, int32_t hidden, int32_t emb_rows,
+                         int32_t pos_rows, int32_t dup, void* out, void* stream);
+
+/* F2.1 vllm:ir/ops/layernorm.py:9-21,40-59 (RMSNorm / fused_add_rms_norm of llama.py:311-331).
+ *     x comes either as bf16 [rows,hidden] (x != NULL) or as n_split fp32 split-K partials
+ *     [n_split, rows, hidden] that are summed in order and rounded to bf16 first.
+ *     has_residual = 0: residual := x (first layer).  residual is updated in place. */
+int32_t t3b_add_rmsnorm(const void* x, const float* partials, int32_t n_split, void* residual,
+                        const void* weight, void* y, int32_t rows, int32_t hidden, float eps,
+                        int32_t has_residual, void* stream);
+
+/* F2.2 / F2.5 / F2.6 / C1  the projections (llama.py:164-180,228-232,117-121; t3.py:659-660):
+ *     y[r, n] = sum_k x[r,k] * w[n,k], fp32 accumulate.  Exactly one of y (bf16 [rows, n]) and
+ *     partials (fp32 [n_split, rows, n]) is written: y when n_split == 1, else partials.
+ *     n_split <= 0 lets the library pick (returned through *n_split_out, may be NULL). */
+int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials,
+                        int32_t n_split, int32_t* n_split_out, int32_t impl, void* stream);
+
+/* Q   vllm:model_executor/layers/quantization/awq.py:214-283: same contract as t3b_linear_bf16
+ *     with W[k,n] = (nib - zero) * scale, group 128, dequantised to bf16 on the fly. */
+int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials,
+                       int32_t n_split, int32_t* n_split_out, int32_t impl, void* stream);
+
+/* one-off layout transform of AutoAWQ tensors (qweight int32 [k, n/8], qzeros int32 [k/128, n/8],
+ * scales fp16 [k/128, n]; nibble order 0,2,4,6,1,3,5,7 - awq_triton.py:56-62) into the kernel
+ * layout: w_out uint8 [n/128][k/64][128][32] (two k-adjacent nibbles per byte), zeros_out uint8
+ * [k/128, n], scales_out bf16 [k/128, n]. */
+int32_t t3b_repack_weights_awq(const int32_t* qweight, const int32_t* qzeros, const void* scales_fp16,
+                               int32_t n, int32_t k, void* w_out, void* zeros_out, void* scales_out,
+                               void* stream);
+
+/* F2.3 + KV write  (rotary_embedding/common.py:144-174, llama3 table; reshape_and_cache of
+ *     llama.py:231): qkv as bf16 [n_tok, 3*hidden] or split-K partials.  Token j belongs to KV row
+ *     tok_row[j] (NULL = j), sits at index tok_idx[j] of that row's sequence and is rotated by
+ *     rope_pos[j].  Writes q (rotated) bf16 [n_tok, hidden] and k (rotated), v into the pool. */
+int32_t t3b_rope_kv_write(const void* qkv, const float* partials, int32_t n_split, int32_t n_tok,
+                          const int32_t* tok_row, const int32_t* tok_idx, const int32_t* rope_pos,
+                          const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables,
+                          int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads, void* q_out,
+                          void* stream);
+
+/* F2.4 paged decode attention (llama.py:211-221,231): o[j] = softmax(q[j] K^T / 8) V over the
+ *     first tok_idx[j]+1 tokens of row tok_row[j], per head.  out bf16 [n_tok, hidden]. */
+int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
+                              const int32_t* block_tables, int32_t max_blocks, const void* k_pool,
+                              const void* v_pool, int32_t n_heads, void* out, void* stream);
+
+/* F2.6 activation (vllm:model_executor/layers/activation.py:138-141): act = silu(g) * u with the
+ *     bf16 roundings of the reference; gate_up as bf16 [rows, 2*ffn] or split-K partials. */
+int32_t t3b_silu_mul(const void* gate_up, const float* partials, int32_t n_split, int32_t rows, int32_t ffn,
+                     void* act, void* stream);
+
+/* F1 + F2  T3VllmModel.forward (t3.py:676-713) over LlamaModel.forward (llama.py:395-432) for one
+ *     decode token per CFG row.  x_in (bf16 [rows, hidden]) != NULL feeds given embeddings (prefill-
+ *     by-decode, t3.py:542-561 rows); x_in == NULL gathers E1 from st->tokens/speech_pos.  Uses
+ *     st->rope_pos / ctx_lens / block_tables.  hidden_out bf16 [rows, hidden] = final-norm output. */
+int32_t t3b_decode_step(const t3b_model_t* m, const t3b_kv_t* kv, const t3b_state_t* st, const void* x_in,
+                        int32_t rows, void* hidden_out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* C1 + S1..S4  compute_logits (t3.py:650-673) fused with the sampler the engine runs next
+ *     (vllm:v1/sample/sampler.py:67-307, ops/topk_topp_sampler.py:328-416, layers/utils.py:51-89):
+ *     head on both rows, l = c + w (c - u), repetition penalty over st->history, greedy or
+ *     temperature/min-p/top-p + exponential race (Philox4x32-10 keyed by seed, counter (index, step)).
+ *     Writes out_tokens[b] (un-offset id; caller adds SPEECH_TOKEN_OFFSET = 2500, t3.py:666-672),
+ *     optionally the combined fp32 logits [B, speech_vocab], and - if advance != 0 - appends to
+ *     history and advances tokens/speech_pos/rope_pos/ctx_lens/step, clearing active[b] on stop. */
+int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden, int32_t rows, const t3b_sampling_t* sp,
+                            const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
+/* S1..S4 alone on caller-provided combined fp32 logits [n_req, vocab] (parity tests of the sampler). */
+int32_t t3b_sample_logits(const float* logits, int32_t n_req, int32_t vocab, const t3b_sampling_t* sp,
+                          const t3b_state_t* st, int32_t* out_tokens, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* T3B200_H */

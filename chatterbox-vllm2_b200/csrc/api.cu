@@ -139,6 +139,79 @@ static int32_t check_model(const t3b_model_t* m) {
     return T3B_OK;
 }
 
+// F2: the 30-layer stack over n_tok tokens (decode: one token per CFG row; prefill: the whole prompt of
+// each new row, causal through tok_idx).  x0 = bf16 [n_tok, hidden] input embeddings.
+static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void* x0, int n_tok, const int32_t* tok_row,
+                            const int32_t* tok_idx, const int32_t* rope_pos, const int32_t* block_tables, int max_blocks,
+                            void* hidden_out, const Workspace& ws, void* stream) {
+    cudaStream_t s = t3b_stream(stream);
+    const int D = m->hidden, F = m->ffn, H = m->n_heads;
+    int32_t rc;
+    auto run_linear = [&](const void* x, const t3b_linear_t* w, void* ybuf, LinOut* out) -> int32_t {
+        int ns = 1;
+        int32_t r = linear_any(x, w, n_tok, ybuf, ws.partials, 0, &ns, T3B_IMPL_AUTO, s);
+        out->n_split = ns;
+        out->y = ns == 1 ? ybuf : nullptr;
+        out->partials = ns == 1 ? nullptr : ws.partials;
+        return r;
+    };
+    LinOut prev = {x0, nullptr, 1};
+    for (int li = 0; li < m->n_layers; ++li) {
+        const t3b_layer_t* L = &m->layers[li];
+        T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
+        rc = t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, L->ln1, ws.normed, n_tok, D, m->rms_eps, li > 0, stream);
+        if (rc) return rc;
+        LinOut qkv;
+        rc = run_linear(ws.normed, &L->qkv, ws.qkv, &qkv);
+        if (rc) return rc;
+        bf16* kp = static_cast<bf16*>(kv->k) + (size_t)li * kv->layer_stride;
+        bf16* vp = static_cast<bf16*>(kv->v) + (size_t)li * kv->layer_stride;
+        rc = t3b_rope_kv_write(qkv.y, qkv.partials, qkv.n_split, n_tok, tok_row, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos,
+                               block_tables, max_blocks, kp, vp, H, ws.q, stream);
+        if (rc) return rc;
+        rc = t3b_paged_attn_decode(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kp, vp, H, ws.attn, stream);
+        if (rc) return rc;
+        LinOut o;
+        rc = run_linear(ws.attn, &L->o, ws.lin, &o);
+        if (rc) return rc;
+        rc = t3b_add_rmsnorm(o.y, o.partials, o.n_split, ws.resid, L->ln2, ws.normed, n_tok, D, m->rms_eps, 1, stream);
+        if (rc) return rc;
+        const bool gemv = n_tok <= 4 && D % 1024 == 0;
+        if (gemv && L->gate_up.kind == T3B_W_BF16) {
+            rc = t3b_linear_gemv_launch(ws.normed, L->gate_up.w, n_tok, L->gate_up.n, L->gate_up.k, ws.act, 1, s);   // fused SiLU*mul
+            if (rc) return rc;
+        } else if (gemv && L->gate_up.kind == T3B_W_AWQ) {
+            rc = t3b_awq_gemv_launch(ws.normed, &L->gate_up, n_tok, ws.act, 1, s);
+            if (rc) return rc;
+        } else {
+            LinOut gu;
+            rc = run_linear(ws.normed, &L->gate_up, ws.gu, &gu);
+            if (rc) return rc;
+            rc = t3b_silu_mul(gu.y, gu.partials, gu.n_split, n_tok, F, ws.act, stream);
+            if (rc) return rc;
+        }
+        rc = run_linear(ws.act, &L->down, ws.lin, &prev);
+        if (rc) return rc;
+    }
+    return t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, m->final_norm, hidden_out, n_tok, D, m->rms_eps, 1, stream);
+}
+
+extern "C" int32_t t3b_forward_tokens(const t3b_model_t* m, const t3b_kv_t* kv, const void* x_in, int32_t n_tok,
+                                      const int32_t* tok_row, const int32_t* tok_idx, const int32_t* rope_pos,
+                                      const int32_t* block_tables, int32_t max_blocks, void* hidden_out, void* workspace,
+                                      size_t workspace_bytes, void* stream) {
+    int32_t rc = check_model(m);
+    if (rc) return rc;
+    T3B_CHECK_ARG(kv && kv->k && kv->v && x_in && hidden_out && workspace, "t3b_forward_tokens: null pointer");
+    T3B_CHECK_ARG(tok_idx && rope_pos && block_tables && max_blocks > 0 && n_tok >= 0, "t3b_forward_tokens: bad token arrays");
+    T3B_CHECK_ALIGN(workspace); T3B_CHECK_ALIGN(hidden_out); T3B_CHECK_ALIGN(x_in);
+    if (n_tok == 0) return T3B_OK;
+    T3B_CHECK_ARG(workspace_bytes >= t3b_workspace_bytes(m, n_tok), "t3b_forward_tokens: workspace %zu < %zu bytes", workspace_bytes,
+                  t3b_workspace_bytes(m, n_tok));
+    return forward_impl(m, kv, x_in, n_tok, tok_row, tok_idx, rope_pos, block_tables, max_blocks, hidden_out,
+                        carve(m, n_tok, workspace), stream);
+}
+
 extern "C" int32_t t3b_decode_step(const t3b_model_t* m, const t3b_kv_t* kv, const t3b_state_t* st, const void* x_in, int32_t rows,
                                    void* hidden_out, void* workspace, size_t workspace_bytes, void* stream) {
     int32_t rc = check_model(m);
@@ -151,64 +224,15 @@ extern "C" int32_t t3b_decode_step(const t3b_model_t* m, const t3b_kv_t* kv, con
     if (rows == 0) return T3B_OK;
     T3B_CHECK_ARG(workspace_bytes >= t3b_workspace_bytes(m, rows), "t3b_decode_step: workspace %zu < %zu bytes", workspace_bytes,
                   t3b_workspace_bytes(m, rows));
-    cudaStream_t s = t3b_stream(stream);
     const Workspace ws = carve(m, rows, workspace);
-    const int D = m->hidden, F = m->ffn, H = m->n_heads;
-
     const void* x0 = x_in;
     if (!x0) {
-        rc = t3b_embed_gather(m->speech_emb, m->speech_pos_emb, st->tokens, st->speech_pos, rows / 2, D, m->speech_vocab,
+        rc = t3b_embed_gather(m->speech_emb, m->speech_pos_emb, st->tokens, st->speech_pos, rows / 2, m->hidden, m->speech_vocab,
                               m->speech_pos_rows, 2, ws.x_emb, stream);
         if (rc) return rc;
         x0 = ws.x_emb;
     }
-    auto run_linear = [&](const void* x, const t3b_linear_t* w, void* ybuf, LinOut* out) -> int32_t {
-        int ns = 1;
-        int32_t r = linear_any(x, w, rows, ybuf, ws.partials, 0, &ns, T3B_IMPL_AUTO, s);
-        out->n_split = ns;
-        out->y = ns == 1 ? ybuf : nullptr;
-        out->partials = ns == 1 ? nullptr : ws.partials;
-        return r;
-    };
-    LinOut prev = {x0, nullptr, 1};
-    for (int li = 0; li < m->n_layers; ++li) {
-        const t3b_layer_t* L = &m->layers[li];
-        T3B_CHECK_ARG(L->ln1 && L->ln2, "t3b_decode_step: layer %d norm weights are null", li);
-        rc = t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, L->ln1, ws.normed, rows, D, m->rms_eps, li > 0, stream);
-        if (rc) return rc;
-        LinOut qkv;
-        rc = run_linear(ws.normed, &L->qkv, ws.qkv, &qkv);
-        if (rc) return rc;
-        bf16* kp = static_cast<bf16*>(kv->k) + (size_t)li * kv->layer_stride;
-        bf16* vp = static_cast<bf16*>(kv->v) + (size_t)li * kv->layer_stride;
-        rc = t3b_rope_kv_write(qkv.y, qkv.partials, qkv.n_split, rows, nullptr, st->ctx_lens, st->rope_pos, m->rope_cos_sin, m->max_pos,
-                               st->block_tables, st->max_blocks, kp, vp, H, ws.q, stream);
-        if (rc) return rc;
-        rc = t3b_paged_attn_decode(ws.q, rows, nullptr, st->ctx_lens, st->block_tables, st->max_blocks, kp, vp, H, ws.attn, stream);
-        if (rc) return rc;
-        LinOut o;
-        rc = run_linear(ws.attn, &L->o, ws.lin, &o);
-        if (rc) return rc;
-        rc = t3b_add_rmsnorm(o.y, o.partials, o.n_split, ws.resid, L->ln2, ws.normed, rows, D, m->rms_eps, 1, stream);
-        if (rc) return rc;
-        const bool gemv = rows <= 4 && D % 1024 == 0;
-        if (gemv && L->gate_up.kind == T3B_W_BF16) {
-            rc = t3b_linear_gemv_launch(ws.normed, L->gate_up.w, rows, L->gate_up.n, L->gate_up.k, ws.act, 1, s);   // fused SiLU*mul
-            if (rc) return rc;
-        } else if (gemv && L->gate_up.kind == T3B_W_AWQ) {
-            rc = t3b_awq_gemv_launch(ws.normed, &L->gate_up, rows, ws.act, 1, s);
-            if (rc) return rc;
-        } else {
-            LinOut gu;
-            rc = run_linear(ws.normed, &L->gate_up, ws.gu, &gu);
-            if (rc) return rc;
-            rc = t3b_silu_mul(gu.y, gu.partials, gu.n_split, rows, F, ws.act, stream);
-            if (rc) return rc;
-        }
-        rc = run_linear(ws.act, &L->down, ws.lin, &prev);
-        if (rc) return rc;
-    }
-    return t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, m->final_norm, hidden_out, rows, D, m->rms_eps, 1, stream);
+    return forward_impl(m, kv, x0, rows, nullptr, st->ctx_lens, st->rope_pos, st->block_tables, st->max_blocks, hidden_out, ws, stream);
 }
 
 extern "C" int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden, int32_t rows, const t3b_sampling_t* sp,

@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 SOURCES = ["api.cu", "elementwise.cu", "attention.cu", "linear_gemv.cu", "linear_umma.cu", "sampler.cu", "awq.cu"]
 OUT = os.path.join(HERE, "libt3b200.so")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
-         "-Xcompiler", "-fvisibility=hidden", "--expt-relaxed-constexpr", "-cudart", "static"]
+         "--expt-relaxed-constexpr", "-cudart", "static"]
 
 
 def needs_build():

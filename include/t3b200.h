@@ -183,6 +183,16 @@ int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_r
 int32_t t3b_silu_mul(const void* gate_up, const float* partials, int32_t n_split, int32_t rows, int32_t ffn,
                      void* act, void* stream);
 
+/* F2   LlamaModel.forward (llama.py:395-432) over n_tok tokens given as embeddings x_in (bf16
+ *     [n_tok, hidden]): token j belongs to KV row tok_row[j] (NULL = j), is the tok_idx[j]-th token of
+ *     that row (its K/V are written there and it attends causally to tokens 0..tok_idx[j]) and is
+ *     rotated by rope_pos[j].  One call with every prompt token of the new rows is the prefill of
+ *     t3.py:542-561; one token per row is a decode step.  hidden_out bf16 [n_tok, hidden]. */
+int32_t t3b_forward_tokens(const t3b_model_t* m, const t3b_kv_t* kv, const void* x_in, int32_t n_tok,
+                           const int32_t* tok_row, const int32_t* tok_idx, const int32_t* rope_pos,
+                           const int32_t* block_tables, int32_t max_blocks, void* hidden_out,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
 /* F1 + F2  T3VllmModel.forward (t3.py:676-713) over LlamaModel.forward (llama.py:395-432) for one
  *     decode token per CFG row.  x_in (bf16 [rows, hidden]) != NULL feeds given embeddings (prefill-
  *     by-decode, t3.py:542-561 rows); x_in == NULL gathers E1 from st->tokens/speech_pos.  Uses

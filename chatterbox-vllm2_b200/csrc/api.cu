@@ -15,6 +15,8 @@ int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_s
                            cudaStream_t stream);
 int32_t t3b_awq_gemv_launch(const void* x, const t3b_linear_t* w, int rows, void* y, int mode, cudaStream_t s);
 int32_t t3b_awq_umma_launch(const void* x, const t3b_linear_t* w, int rows, void* y, float* partials, int n_split, cudaStream_t s);
+int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
+                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, void* out, int warps, cudaStream_t s);
 
 static thread_local char g_err[512] = "";
 
@@ -147,9 +149,13 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     cudaStream_t s = t3b_stream(stream);
     const int D = m->hidden, F = m->ffn, H = m->n_heads;
     int32_t rc;
+    // Multi-token passes (tok_row given = prefill) fix every launch shape that changes fp32 summation order
+    // (split-K = 1, 2 warps per attention CTA) so a request's prefill is bit-identical no matter which other
+    // requests are admitted with it.  Decode steps pick shapes by row count (identical within a slot bucket).
+    const bool prefill = tok_row != nullptr;
     auto run_linear = [&](const void* x, const t3b_linear_t* w, void* ybuf, LinOut* out) -> int32_t {
         int ns = 1;
-        int32_t r = linear_any(x, w, n_tok, ybuf, ws.partials, 0, &ns, T3B_IMPL_AUTO, s);
+        int32_t r = linear_any(x, w, n_tok, ybuf, ws.partials, prefill ? 1 : 0, &ns, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, s);
         out->n_split = ns;
         out->y = ns == 1 ? ybuf : nullptr;
         out->partials = ns == 1 ? nullptr : ws.partials;
@@ -169,14 +175,14 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
         rc = t3b_rope_kv_write(qkv.y, qkv.partials, qkv.n_split, n_tok, tok_row, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos,
                                block_tables, max_blocks, kp, vp, H, ws.q, stream);
         if (rc) return rc;
-        rc = t3b_paged_attn_decode(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kp, vp, H, ws.attn, stream);
+        rc = t3b_paged_attn_launch(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kp, vp, H, ws.attn, prefill ? 2 : 0, s);
         if (rc) return rc;
         LinOut o;
         rc = run_linear(ws.attn, &L->o, ws.lin, &o);
         if (rc) return rc;
         rc = t3b_add_rmsnorm(o.y, o.partials, o.n_split, ws.resid, L->ln2, ws.normed, n_tok, D, m->rms_eps, 1, stream);
         if (rc) return rc;
-        const bool gemv = n_tok <= 4 && D % 1024 == 0;
+        const bool gemv = !prefill && n_tok <= 4 && D % 1024 == 0;
         if (gemv && L->gate_up.kind == T3B_W_BF16) {
             rc = t3b_linear_gemv_launch(ws.normed, L->gate_up.w, n_tok, L->gate_up.n, L->gate_up.k, ws.act, 1, s);   // fused SiLU*mul
             if (rc) return rc;

@@ -129,6 +129,22 @@ __global__ void __launch_bounds__(256) paged_attn_decode_kernel(const bf16* __re
     }
 }
 
+// warps = 0: pick by occupancy (enough CTAs x warps to cover the machine at small batch, fewer at large)
+int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
+                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, void* out, int warps, cudaStream_t s) {
+    const long units = (long)n_tok * n_heads;
+    const int sms = t3b_num_sms();
+    int nw = warps;
+    if (nw <= 0) {
+        nw = 8;
+        if (units >= (long)sms * 8) nw = 2;
+        else if (units >= (long)sms * 4) nw = 4;
+    }
+    T3B_CUDA(t3b_launch(paged_attn_decode_kernel, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)q, tok_row, tok_idx,
+                        block_tables, max_blocks, (const bf16*)k_pool, (const bf16*)v_pool, n_heads, (bf16*)out));
+    return T3B_OK;
+}
+
 extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
                                          const int32_t* block_tables, int32_t max_blocks, const void* k_pool, const void* v_pool,
                                          int32_t n_heads, void* out, void* stream) {
@@ -136,13 +152,5 @@ extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int
     T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && n_heads >= 1, "t3b_paged_attn_decode: bad sizes");
     T3B_CHECK_ALIGN(q); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
     if (n_tok == 0) return T3B_OK;
-    // warps per (query, head): enough CTAs x warps to cover the machine at small batch, fewer at large
-    const long units = (long)n_tok * n_heads;
-    const int sms = t3b_num_sms();
-    int nw = 8;
-    if (units >= (long)sms * 8) nw = 2;
-    else if (units >= (long)sms * 4) nw = 4;
-    T3B_CUDA(t3b_launch(paged_attn_decode_kernel, dim3((unsigned)units), dim3(nw * 32), 0, t3b_stream(stream), (const bf16*)q, tok_row,
-                        tok_idx, block_tables, max_blocks, (const bf16*)k_pool, (const bf16*)v_pool, n_heads, (bf16*)out));
-    return T3B_OK;
+    return t3b_paged_attn_launch(q, n_tok, tok_row, tok_idx, block_tables, max_blocks, k_pool, v_pool, n_heads, out, 0, t3b_stream(stream));
 }

@@ -41,6 +41,19 @@ def i32(x):
     return torch.as_tensor(x, dtype=torch.int32).to(DEV)
 
 
+_KEEP = []
+
+
+def dptr(t):
+    """Device address of a tensor that stays alive (a temporary's block would be recycled by the caching
+    allocator for the next temporary before the kernel runs)."""
+    _KEEP.append(t)
+    if len(_KEEP) > 64:
+        torch.cuda.synchronize()
+        del _KEEP[:-32]
+    return t.data_ptr()
+
+
 def ulp_diff(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
     """|a-b| in units of the bf16 ulp of max(|a|,|b|) (fp32 inputs holding bf16 values)."""
     a, b = a.float().cpu(), b.float().cpu()
@@ -57,7 +70,7 @@ def test_embed_gather_bit_exact(L, orc, n, dup):
     pos = torch.randint(0, 6000, (n,), generator=g)            # > 4100 exercises the modulo of t3.py:472
     emb, pe = bf(orc.speech_emb), bf(orc.speech_pos)
     out = torch.empty(n * dup, 1024, dtype=torch.bfloat16, device=DEV)
-    _lib.check(L.t3b_embed_gather(emb.data_ptr(), pe.data_ptr(), i32(tok).data_ptr(), i32(pos).data_ptr(), n, 1024,
+    _lib.check(L.t3b_embed_gather(emb.data_ptr(), pe.data_ptr(), dptr(i32(tok)), dptr(i32(pos)), n, 1024,
                                   emb.shape[0], pe.shape[0], dup, out.data_ptr(), sp()))
     ref = orc.embed_decode(tok.tolist(), pos.tolist()).repeat_interleave(dup, 0)
     assert torch.equal(out.float().cpu(), ref)
@@ -76,7 +89,9 @@ def test_add_rmsnorm(L, orc, rows, has_res):
     y_ref, res_ref = orc.add_rmsnorm(x.float(), r.float() if has_res else None, w.float())
     assert torch.equal(rd.float().cpu(), res_ref)                       # residual: one add, one rounding -> exact
     d = ulp_diff(y, y_ref)
-    assert d.max() <= 1.0 and (d > 0).float().mean() < 2e-3             # fp32 sum order moves rstd by <= 1 fp32 ulp
+    # fp32 sum order moves rstd by <= 1 fp32 ulp -> rare 1-ulp flips of the pre-weight cast, which the weight
+    # multiply + second rounding can stretch to 2 ulp
+    assert d.max() <= 2.0 and (d > 1).float().mean() < 1e-4 and (d > 0).float().mean() < 2e-3
 
 
 def test_add_rmsnorm_from_partials(L, orc):
@@ -105,7 +120,8 @@ def _check_linear(y, ref, K):
     small = ref.abs() < 1e-2                       # ulp of a cancelled sum is meaningless: use abs tol there
     ok = (d <= 1.0) | (small & ((y.float().cpu() - ref).abs() < 2e-4))
     assert ok.float().mean() > 0.999, f"mismatch fraction {(~ok).float().mean():.5f}, max ulp {d.max():.1f}"
-    assert torch.nn.functional.cosine_similarity(y.float().cpu().flatten(), ref.flatten(), dim=0) > 0.99999
+    # float64: an fp32 dot product over 10^5..10^6 terms is itself only good to ~1e-5
+    assert torch.nn.functional.cosine_similarity(y.double().cpu().flatten(), ref.double().flatten(), dim=0) > 0.99999
 
 
 @pytest.mark.parametrize("rows", [1, 2, 3, 4])
@@ -197,8 +213,8 @@ def test_rope_kv_write_bit_exact(L, orc):
     bt, kp, vp = _kv_setup(6, 13, 1)
     cs = bf(rope_cos_sin_table(SMALL))
     q_out = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
-    _lib.check(L.t3b_rope_kv_write(bf(qkv).data_ptr(), None, 1, n, i32(rows).data_ptr(), i32(idx).data_ptr(), i32(pos).data_ptr(),
-                                   cs.data_ptr(), SMALL.max_pos, bt.to(DEV).data_ptr(), 13, kp.data_ptr(), vp.data_ptr(), 16,
+    _lib.check(L.t3b_rope_kv_write(dptr(bf(qkv)), None, 1, n, dptr(i32(rows)), dptr(i32(idx)), dptr(i32(pos)),
+                                   cs.data_ptr(), SMALL.max_pos, dptr(bt.to(DEV)), 13, kp.data_ptr(), vp.data_ptr(), 16,
                                    q_out.data_ptr(), sp()))
     q_ref = orc.rope(qkv[:, :1024].float().reshape(n, 16, 64), pos)
     k_ref = orc.rope(qkv[:, 1024:2048].float().reshape(n, 16, 64), pos)
@@ -231,7 +247,7 @@ def test_paged_attention(L, ctxs):
     kp.copy_(kh); vp.copy_(vh)
     out = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     idx = i32([c - 1 for c in ctxs])
-    _lib.check(L.t3b_paged_attn_decode(bf(q).data_ptr(), n, None, idx.data_ptr(), bt.to(DEV).data_ptr(), mb, kp.data_ptr(),
+    _lib.check(L.t3b_paged_attn_decode(dptr(bf(q)), n, None, idx.data_ptr(), dptr(bt.to(DEV)), mb, kp.data_ptr(),
                                        vp.data_ptr(), 16, out.data_ptr(), sp()))
     for r, c in enumerate(ctxs):
         s = torch.einsum("hd,lhd->hl", q[r].float(), Ks[r].float()) * 0.125
@@ -249,7 +265,7 @@ def test_paged_attention_tail_ignores_stale_tokens(L):
     kp[bt[0, 0], :, :5, :] = 0.01
     vp[bt[0, 0], :, :5, :] = 1.0
     out = torch.empty(1, 1024, dtype=torch.bfloat16, device=DEV)
-    _lib.check(L.t3b_paged_attn_decode(bf(q).data_ptr(), 1, None, i32([4]).data_ptr(), bt.to(DEV).data_ptr(), 2, kp.data_ptr(),
+    _lib.check(L.t3b_paged_attn_decode(dptr(bf(q)), 1, None, dptr(i32([4])), dptr(bt.to(DEV)), 2, kp.data_ptr(),
                                        vp.data_ptr(), 16, out.data_ptr(), sp()))
     assert torch.equal(out.float().cpu(), torch.ones(1, 1024))
 
@@ -260,7 +276,7 @@ def test_silu_mul(L, rows):
     g = torch.Generator().manual_seed(rows)
     gu = (2 * torch.randn(rows, 8192, generator=g)).bfloat16()
     act = torch.empty(rows, 4096, dtype=torch.bfloat16, device=DEV)
-    _lib.check(L.t3b_silu_mul(bf(gu).data_ptr(), None, 1, rows, 4096, act.data_ptr(), sp()))
+    _lib.check(L.t3b_silu_mul(dptr(bf(gu)), None, 1, rows, 4096, act.data_ptr(), sp()))
     ref = (torch.nn.functional.silu(gu[:, :4096]) * gu[:, 4096:]).float()          # torch bf16 tensor arithmetic
     d = ulp_diff(act, ref)
     assert d.max() <= 1.0 and (d > 0).float().mean() < 1e-3                          # expf vs torch's sigmoid: rare 1-ulp flips
@@ -292,7 +308,7 @@ def test_sampler_greedy_with_penalty_bit_exact(L):
     rho = [2.0, 2.0, 2.0, 1.3, 2.0, 2.0, 1.0, 0.5, 2.0]
     s = _sampling(B, repetition_penalty=rho, temperature=[0.0] * B)
     out = torch.empty(B, dtype=torch.int32, device=DEV)
-    _lib.check(L.t3b_sample_logits(lg.to(DEV).data_ptr(), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
+    _lib.check(L.t3b_sample_logits(dptr(lg.to(DEV)), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
     ref = sampler_ref.sample_ref(lg, hist, repetition_penalty=rho, temperature=[0.0] * B, min_p=[0] * B, top_p=[1] * B,
                                  seeds=[0] * B, steps=[0] * B)
     assert out.cpu().tolist() == ref.tolist()
@@ -304,7 +320,7 @@ def test_sampler_greedy_tie_takes_lowest_index(L):
     lg[1, 8193] = 1.0
     s = _sampling(2, temperature=[0.0, 0.0])
     out = torch.empty(2, dtype=torch.int32, device=DEV)
-    _lib.check(L.t3b_sample_logits(lg.to(DEV).data_ptr(), 2, 8194, C.byref(s.c), None, out.data_ptr(), sp()))
+    _lib.check(L.t3b_sample_logits(dptr(lg.to(DEV)), 2, 8194, C.byref(s.c), None, out.data_ptr(), sp()))
     assert out.cpu().tolist() == [77, 8193]
 
 
@@ -324,7 +340,7 @@ def test_sampler_random_matches_oracle(L, temp, min_p, top_p):
     seeds = [42 + b for b in range(B)]
     s = _sampling(B, repetition_penalty=[2.0] * B, temperature=[temp] * B, min_p=[min_p] * B, top_p=[top_p] * B, seed=seeds)
     out = torch.empty(B, dtype=torch.int32, device=DEV)
-    _lib.check(L.t3b_sample_logits(lg.to(DEV).data_ptr(), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
+    _lib.check(L.t3b_sample_logits(dptr(lg.to(DEV)), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
     info = []
     ref = sampler_ref.sample_ref(lg, hist, repetition_penalty=[2.0] * B, temperature=[temp] * B, min_p=[min_p] * B,
                                  top_p=[top_p] * B, seeds=seeds, steps=[b * 7 for b in range(B)], info=info)
@@ -351,7 +367,7 @@ def test_sampler_philox_matches_oracle_stream(L):
     seeds = [(1 << 40) + 17 * b for b in range(B)]
     s = _sampling(B, temperature=[1.0] * B, seed=seeds)
     out = torch.empty(B, dtype=torch.int32, device=DEV)
-    _lib.check(L.t3b_sample_logits(lg.to(DEV).data_ptr(), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
+    _lib.check(L.t3b_sample_logits(dptr(lg.to(DEV)), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
     ref = [int(np.argmin(sampler_ref.exp_race_q(V, seeds[b], b * 1000))) for b in range(B)]
     assert out.cpu().tolist() == ref
 

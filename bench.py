@@ -300,7 +300,6 @@ def kernel_breakdown(m, eng, B, ctx):
     x, x4 = bf(R, d.hidden), bf(R, d.ffn)
     y_qkv, y_gu, y_d = bf(R, 3 * d.hidden), bf(R, 2 * d.ffn), bf(R, d.hidden)
     act, q, attn, res = bf(R, d.ffn), bf(R, d.hidden), bf(R, d.hidden), bf(R, d.hidden)
-    parts = torch.empty(16 << 20, dtype=torch.float32, device=dev)
     st, kv = eng.state, eng.kv
     # context: every row holds `ctx` tokens in its own blocks
     nblk = (ctx + 16) // 16
@@ -312,39 +311,29 @@ def kernel_breakdown(m, eng, B, ctx):
     ns = C.c_int32(0)
     auto = m.c.layers
 
-    def lin(name, xin, yout, gemv_mode=0):
+    def lin(name, xin, yout, epi=0):
         def f(li):
             w = getattr(auto[li], name)
-            _lib.check(L.t3b_linear_bf16(xin.data_ptr(), C.byref(w), R, yout.data_ptr(), parts.data_ptr(), 0, C.byref(ns), 0, s), name)
+            _lib.check(L.t3b_linear_bf16(xin.data_ptr(), C.byref(w), R, yout.data_ptr(), None, 0, C.byref(ns), 0, epi, s), name)
         return f
 
     def attn_f(li):
         off = li * kv.c.layer_stride * 2
-        _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), R, None, idx.data_ptr(), bt.data_ptr(), eng.max_blocks,
-                                           kv.k.data_ptr() + off, kv.v.data_ptr() + off, d.n_heads, attn.data_ptr(), s), "attn")
-
-    def rope_f(li):
-        off = li * kv.c.layer_stride * 2
-        _lib.check(L.t3b_rope_kv_write(y_qkv.data_ptr(), None, 1, R, None, idx.data_ptr(), idx.data_ptr(), m.w["rope"].data_ptr(), d.max_pos,
-                                       bt.data_ptr(), eng.max_blocks, kv.k.data_ptr() + off, kv.v.data_ptr() + off, d.n_heads,
-                                       q.data_ptr(), s), "rope")
+        _lib.check(L.t3b_attn_decode_fused(y_qkv.data_ptr(), R, idx.data_ptr(), idx.data_ptr(), m.w["rope"].data_ptr(), d.max_pos,
+                                           bt.data_ptr(), eng.max_blocks, kv.k.data_ptr() + off, kv.v.data_ptr() + off, d.n_heads,
+                                           attn.data_ptr(), s), "attn")
 
     def norm_f(li):
         _lib.check(L.t3b_add_rmsnorm(y_d.data_ptr(), None, 1, res.data_ptr(), m.w[f"{li}.ln1"].data_ptr(), x.data_ptr(), R, d.hidden,
                                      d.rms_eps, 1, s), "norm")
 
-    def silu_f(li):
-        _lib.check(L.t3b_silu_mul(y_gu.data_ptr(), None, 1, R, d.ffn, act.data_ptr(), s), "silu")
-
     classes = {
         "qkv_proj": (lin("qkv", x, y_qkv), 3 * d.hidden * d.hidden * 2, 1),
+        "attention_rope_kvwrite": (attn_f, R * ctx * d.n_heads * d.head_dim * 2 * 2, 1),
         "o_proj": (lin("o", attn, y_d), d.hidden * d.hidden * 2, 1),
-        "gate_up_proj": (lin("gate_up", x, y_gu), 2 * d.ffn * d.hidden * 2, 1),
+        "gate_up_silu_proj": (lin("gate_up", x, act, 1), 2 * d.ffn * d.hidden * 2, 1),
         "down_proj": (lin("down", x4, y_d), d.hidden * d.ffn * 2, 1),
-        "paged_attention": (attn_f, R * ctx * d.n_heads * d.head_dim * 2 * 2, 1),
-        "rope_kv_write": (rope_f, R * 3 * d.hidden * 2 + R * 3 * d.hidden * 2, 1),
         "add_rmsnorm": (norm_f, R * d.hidden * 2 * 4, 2),
-        "silu_mul": (silu_f, R * d.ffn * 2 * 3, 1),
     }
     out = {}
     for name, (fn, bytes_per_launch, per_layer) in classes.items():

@@ -7,14 +7,16 @@
 
 // implemented in the kernel translation units
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s);
-int32_t t3b_linear_umma_launch(const void* x, const void* w, int rows, int N, int K, void* y, float* partials, int n_split, cudaStream_t s);
+int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
+                               int n_split, int epi, cudaStream_t s);
 int t3b_umma_pick_split(int rows, int N, int K);
+int t3b_umma_pick_split_partials(int rows, int N, int K);
 int t3b_umma_available();
 int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_split, const float* logits_in, int V, int n_req,
                            const t3b_sampling_t* sp, const t3b_state_t* st, int advance, int32_t* out_tokens, float* logits_out,
                            cudaStream_t stream);
-int32_t t3b_awq_gemv_launch(const void* x, const t3b_linear_t* w, int rows, void* y, int mode, cudaStream_t s);
-int32_t t3b_awq_umma_launch(const void* x, const t3b_linear_t* w, int rows, void* y, float* partials, int n_split, cudaStream_t s);
+int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
+                              const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, void* out, cudaStream_t s);
 int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
                               int max_blocks, const void* k_pool, const void* v_pool, int n_heads, void* out, int warps, cudaStream_t s);
 
@@ -51,12 +53,10 @@ extern "C" int32_t t3b_check_device(void) {
 
 // ------------------------------------------------------------------ workspace carving
 namespace {
-constexpr size_t kPartialBytes = (8u << 20) + (1u << 20);
 inline size_t al(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct Workspace {
-    char *x_emb, *resid, *normed, *qkv, *q, *attn, *gu, *act, *lin, *head;
-    float* partials;
+    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head;
     size_t total;
 };
 
@@ -71,16 +71,13 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
     w.qkv = take(R * 3 * D * 2);
     w.q = take(R * D * 2);
     w.attn = take(R * D * 2);
-    w.gu = take(R * 2 * F * 2);
     w.act = take(R * F * 2);
     w.lin = take(R * D * 2);
     w.head = take(R * V * 2 + 64);
-    w.partials = reinterpret_cast<float*>(take(kPartialBytes));
     w.total = static_cast<size_t>(p - static_cast<char*>(base));
     return w;
 }
 
-struct LinOut { const void* y; const float* partials; int n_split; };
 }  // namespace
 
 extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
@@ -89,8 +86,9 @@ extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
 }
 
 // ------------------------------------------------------------------ linear dispatch
+// epi: 0 = y[rows, n]; 1 = gate_up with the SiLU*mul epilogue -> y[rows, n/2].
 static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* y, float* partials, int n_split, int* n_split_out, int impl,
-                          cudaStream_t s) {
+                          int epi, cudaStream_t s) {
     T3B_CHECK_ARG(x && w && w->w, "linear: null pointer");
     T3B_CHECK_ARG(rows >= 0 && w->n > 0 && w->k > 0, "linear: bad sizes rows=%d n=%d k=%d", rows, w->n, w->k);
     T3B_CHECK_ALIGN(x); T3B_CHECK_ALIGN(w->w);
@@ -99,35 +97,35 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     if (rows == 0) { if (n_split_out) *n_split_out = 1; return T3B_OK; }
     const bool awq = w->kind == T3B_W_AWQ;
     T3B_CHECK_ARG(awq || w->kind == T3B_W_BF16, "linear: unknown weight kind %d", w->kind);
-    if (impl == T3B_IMPL_AUTO) impl = (rows <= 4 && w->k % 1024 == 0 && w->k <= 8192) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
+    if (impl == T3B_IMPL_AUTO) impl = (!awq && rows <= 4 && w->k % 1024 == 0 && w->k <= 8192) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
     if (impl == T3B_IMPL_GEMV) {
+        T3B_CHECK_ARG(!awq, "linear: AWQ weights run on the dequant-fused tcgen05 kernel at every row count (no GEMV)");
         T3B_CHECK_ARG(n_split <= 1, "linear: the GEMV path has no split-K (n_split %d)", n_split);
         T3B_CHECK_ARG(y != nullptr, "linear: y is null");
         if (n_split_out) *n_split_out = 1;
-        return awq ? t3b_awq_gemv_launch(x, w, rows, y, 0, s) : t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, 0, s);
+        return t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, epi, s);
     }
     T3B_CHECK_ARG(impl == T3B_IMPL_UMMA, "linear: unknown impl %d", impl);
-    if (n_split <= 0) {
-        n_split = t3b_umma_pick_split(rows, w->n, w->k);
-        if (partials == nullptr) n_split = 1;
-        if (y == nullptr && n_split == 1) T3B_FAIL(T3B_ERR_ARG, "linear: n_split resolved to 1 but y is null");
-    }
+    const bool legacy = partials != nullptr && n_split > 1;      // explicit request for global fp32 partials
+    if (n_split <= 0) n_split = t3b_umma_pick_split(rows, w->n, w->k);
+    if (!legacy && y == nullptr) T3B_FAIL(T3B_ERR_ARG, "linear: y is null (partials are only written for an explicit n_split > 1)");
     if (n_split_out) *n_split_out = n_split;
-    return awq ? t3b_awq_umma_launch(x, w, rows, y, partials, n_split, s)
-               : t3b_linear_umma_launch(x, w->w, rows, w->n, w->k, y, partials, n_split, s);
+    return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, legacy ? partials : nullptr, n_split, epi, s);
 }
 
 extern "C" int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
-                                   int32_t* n_split_out, int32_t impl, void* stream) {
+                                   int32_t* n_split_out, int32_t impl, int32_t epilogue, void* stream) {
     T3B_CHECK_ARG(w && w->kind == T3B_W_BF16, "t3b_linear_bf16: weight kind must be T3B_W_BF16");
-    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, t3b_stream(stream));
+    T3B_CHECK_ARG(epilogue == T3B_EPI_NONE || epilogue == T3B_EPI_SILU_MUL, "t3b_linear_bf16: unknown epilogue %d", epilogue);
+    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, epilogue, t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
-                                  int32_t* n_split_out, int32_t impl, void* stream) {
+                                  int32_t* n_split_out, int32_t impl, int32_t epilogue, void* stream) {
     T3B_CHECK_ARG(w && w->kind == T3B_W_AWQ, "t3b_linear_awq: weight kind must be T3B_W_AWQ");
     T3B_CHECK_ARG(w->scales && w->zeros, "t3b_linear_awq: scales / zeros are null");
-    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, t3b_stream(stream));
+    T3B_CHECK_ARG(epilogue == T3B_EPI_NONE || epilogue == T3B_EPI_SILU_MUL, "t3b_linear_awq: unknown epilogue %d", epilogue);
+    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, epilogue, t3b_stream(stream));
 }
 
 // ------------------------------------------------------------------ whole step
@@ -143,63 +141,52 @@ static int32_t check_model(const t3b_model_t* m) {
 
 // F2: the 30-layer stack over n_tok tokens (decode: one token per CFG row; prefill: the whole prompt of
 // each new row, causal through tok_idx).  x0 = bf16 [n_tok, hidden] input embeddings.
+// Decode layer = 7 launches: add+norm, qkv GEMM, attention (RoPE + KV write fused), o GEMM, add+norm,
+// gate_up GEMM (SiLU*mul epilogue), down GEMM.
 static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void* x0, int n_tok, const int32_t* tok_row,
                             const int32_t* tok_idx, const int32_t* rope_pos, const int32_t* block_tables, int max_blocks,
                             void* hidden_out, const Workspace& ws, void* stream) {
     cudaStream_t s = t3b_stream(stream);
-    const int D = m->hidden, F = m->ffn, H = m->n_heads;
+    const int D = m->hidden, H = m->n_heads;
     int32_t rc;
     // Multi-token passes (tok_row given = prefill) fix every launch shape that changes fp32 summation order
     // (split-K = 1, 2 warps per attention CTA) so a request's prefill is bit-identical no matter which other
     // requests are admitted with it.  Decode steps pick shapes by row count (identical within a slot bucket).
     const bool prefill = tok_row != nullptr;
-    auto run_linear = [&](const void* x, const t3b_linear_t* w, void* ybuf, LinOut* out) -> int32_t {
-        int ns = 1;
-        int32_t r = linear_any(x, w, n_tok, ybuf, ws.partials, prefill ? 1 : 0, &ns, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, s);
-        out->n_split = ns;
-        out->y = ns == 1 ? ybuf : nullptr;
-        out->partials = ns == 1 ? nullptr : ws.partials;
-        return r;
+    auto lin = [&](const void* x, const t3b_linear_t* w, void* y, int epi) -> int32_t {
+        return linear_any(x, w, n_tok, y, nullptr, prefill ? 1 : 0, nullptr, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, epi, s);
     };
-    LinOut prev = {x0, nullptr, 1};
+    const void* prev = x0;
     for (int li = 0; li < m->n_layers; ++li) {
         const t3b_layer_t* L = &m->layers[li];
         T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
-        rc = t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, L->ln1, ws.normed, n_tok, D, m->rms_eps, li > 0, stream);
+        rc = t3b_add_rmsnorm(prev, nullptr, 1, ws.resid, L->ln1, ws.normed, n_tok, D, m->rms_eps, li > 0, stream);
         if (rc) return rc;
-        LinOut qkv;
-        rc = run_linear(ws.normed, &L->qkv, ws.qkv, &qkv);
+        rc = lin(ws.normed, &L->qkv, ws.qkv, T3B_EPI_NONE);
         if (rc) return rc;
         bf16* kp = static_cast<bf16*>(kv->k) + (size_t)li * kv->layer_stride;
         bf16* vp = static_cast<bf16*>(kv->v) + (size_t)li * kv->layer_stride;
-        rc = t3b_rope_kv_write(qkv.y, qkv.partials, qkv.n_split, n_tok, tok_row, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos,
-                               block_tables, max_blocks, kp, vp, H, ws.q, stream);
-        if (rc) return rc;
-        rc = t3b_paged_attn_launch(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kp, vp, H, ws.attn, prefill ? 2 : 0, s);
-        if (rc) return rc;
-        LinOut o;
-        rc = run_linear(ws.attn, &L->o, ws.lin, &o);
-        if (rc) return rc;
-        rc = t3b_add_rmsnorm(o.y, o.partials, o.n_split, ws.resid, L->ln2, ws.normed, n_tok, D, m->rms_eps, 1, stream);
-        if (rc) return rc;
-        const bool gemv = !prefill && n_tok <= 4 && D % 1024 == 0;
-        if (gemv && L->gate_up.kind == T3B_W_BF16) {
-            rc = t3b_linear_gemv_launch(ws.normed, L->gate_up.w, n_tok, L->gate_up.n, L->gate_up.k, ws.act, 1, s);   // fused SiLU*mul
+        if (prefill) {
+            rc = t3b_rope_kv_write(ws.qkv, nullptr, 1, n_tok, tok_row, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables,
+                                   max_blocks, kp, vp, H, ws.q, stream);
             if (rc) return rc;
-        } else if (gemv && L->gate_up.kind == T3B_W_AWQ) {
-            rc = t3b_awq_gemv_launch(ws.normed, &L->gate_up, n_tok, ws.act, 1, s);
-            if (rc) return rc;
+            rc = t3b_paged_attn_launch(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kp, vp, H, ws.attn, 2, s);
         } else {
-            LinOut gu;
-            rc = run_linear(ws.normed, &L->gate_up, ws.gu, &gu);
-            if (rc) return rc;
-            rc = t3b_silu_mul(gu.y, gu.partials, gu.n_split, n_tok, F, ws.act, stream);
-            if (rc) return rc;
+            rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kp, vp, H,
+                                       ws.attn, s);
         }
-        rc = run_linear(ws.act, &L->down, ws.lin, &prev);
         if (rc) return rc;
+        rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE);
+        if (rc) return rc;
+        rc = t3b_add_rmsnorm(ws.lin, nullptr, 1, ws.resid, L->ln2, ws.normed, n_tok, D, m->rms_eps, 1, stream);
+        if (rc) return rc;
+        rc = lin(ws.normed, &L->gate_up, ws.act, T3B_EPI_SILU_MUL);
+        if (rc) return rc;
+        rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE);
+        if (rc) return rc;
+        prev = ws.lin;
     }
-    return t3b_add_rmsnorm(prev.y, prev.partials, prev.n_split, ws.resid, m->final_norm, hidden_out, n_tok, D, m->rms_eps, 1, stream);
+    return t3b_add_rmsnorm(prev, nullptr, 1, ws.resid, m->final_norm, hidden_out, n_tok, D, m->rms_eps, 1, stream);
 }
 
 extern "C" int32_t t3b_forward_tokens(const t3b_model_t* m, const t3b_kv_t* kv, const void* x_in, int32_t n_tok,
@@ -252,11 +239,10 @@ extern "C" int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden,
     if (rows == 0) return T3B_OK;
     T3B_CHECK_ARG(workspace_bytes >= t3b_workspace_bytes(m, rows), "t3b_head_cfg_sample: workspace too small");
     const Workspace ws = carve(m, rows, workspace);
-    int ns = 1;
-    rc = linear_any(hidden, &m->head, rows, ws.head, ws.partials, 0, &ns, T3B_IMPL_AUTO, t3b_stream(stream));
+    rc = linear_any(hidden, &m->head, rows, ws.head, nullptr, 0, nullptr, T3B_IMPL_AUTO, T3B_EPI_NONE, t3b_stream(stream));
     if (rc) return rc;
-    return t3b_sampler_launch(ns == 1 ? ws.head : nullptr, ns == 1 ? nullptr : ws.partials, ns, nullptr, m->speech_vocab, rows / 2, sp, st,
-                              advance, out_tokens, logits_out, t3b_stream(stream));
+    return t3b_sampler_launch(ws.head, nullptr, 1, nullptr, m->speech_vocab, rows / 2, sp, st, advance, out_tokens, logits_out,
+                              t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_sample_logits(const float* logits, int32_t n_req, int32_t vocab, const t3b_sampling_t* sp, const t3b_state_t* st,

@@ -4,6 +4,11 @@
 // Pool layout [block][head][16 tok][64] makes one (block, head) slice 2 KB contiguous, so a warp's
 // four 128-bit loads per slice are four fully coalesced 512 B segments.
 //
+// Decode steps run the FUSED variant: the CTA reads its head's q/k/v straight from the QKV projection
+// output, applies llama3/neox RoPE (F2.3, bf16 roundings of rotary_embedding/common.py:144-174), writes the
+// rotated k and v into the paged pool (reshape_and_cache) and then attends over the row's context including
+// that token - one launch per layer instead of three.
+//
 // CTA = one (query, head); its NW warps take the row's KV pages round-robin two at a time (16 128-bit
 // loads in flight per lane), keep a private online-softmax state and are merged through shared
 // memory at the end (fixed order -> deterministic).  Dot products are reduced across the 8 lanes of
@@ -12,11 +17,22 @@
 
 #define ATT_PAGES_PER_ITER 2
 
+// coherent 128-bit load that bypasses L1 allocation (the fused variant reads a line this CTA just wrote)
+__device__ __forceinline__ uint4 ldg_kv(const void* p) {
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
+
+// FUSED: q points at the QKV projection output bf16 [n_tok, 3*hidden]; k_pool / v_pool are written.
+template <bool FUSED>
 __global__ void __launch_bounds__(256) paged_attn_decode_kernel(const bf16* __restrict__ q, const int32_t* __restrict__ tok_row,
                                                                 const int32_t* __restrict__ tok_idx,
                                                                 const int32_t* __restrict__ block_tables, int max_blocks,
-                                                                const bf16* __restrict__ k_pool, const bf16* __restrict__ v_pool,
-                                                                int n_heads, bf16* __restrict__ out) {
+                                                                bf16* k_pool, bf16* v_pool, int n_heads, bf16* __restrict__ out,
+                                                                const int32_t* __restrict__ rope_pos, const bf16* __restrict__ cos_sin,
+                                                                int max_pos) {
     __shared__ float sm_m[8], sm_l[8];
     __shared__ float sm_acc[8][64];
     pdl_wait();
@@ -25,13 +41,41 @@ __global__ void __launch_bounds__(256) paged_attn_decode_kernel(const bf16* __re
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int t4 = lane >> 3, c = lane & 7;
     const int row = tok_row ? tok_row[t] : t;
-    const int ctx = tok_idx[t] + 1;                      // keys 0..tok_idx[t] (own token was just written)
+    const int ctx = tok_idx[t] + 1;                      // keys 0..tok_idx[t] (own token is written first)
     const int n_pages = (ctx + 15) >> 4;
     const int32_t* bt = block_tables + (size_t)row * max_blocks;
     const float kScale = 0.125f * 1.4426950408889634f;   // head_dim^-0.5 * log2(e)
 
     float qf[8];
-    unpack8(*reinterpret_cast<const uint4*>(q + ((size_t)t * n_heads + h) * 64 + c * 8), qf);
+    if (FUSED) {
+        const int hidden = n_heads * 64;
+        const bf16* src = q + (size_t)t * 3 * hidden + h * 64 + c * 8;
+        float kf[8], cs[8], sn[8];
+        unpack8(*reinterpret_cast<const uint4*>(src), qf);
+        unpack8(*reinterpret_cast<const uint4*>(src + hidden), kf);
+        const uint4 vraw = *reinterpret_cast<const uint4*>(src + 2 * hidden);
+        int pos = rope_pos[t];
+        pos = min(max(pos, 0), max_pos - 1);
+        unpack8(*reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + (c & 3) * 8), cs);
+        unpack8(*reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + 32 + (c & 3) * 8), sn);
+        const bool hi = c >= 4;                           // lanes c < 4 hold x1 (dims 0..31), c >= 4 hold x2
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4), kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
+            // o1 = x1*cos - x2*sin ; o2 = x2*cos + x1*sin, every product and the sum rounded to bf16
+            qf[e] = hi ? bf16_round(bf16_round(qf[e] * cs[e]) + bf16_round(qp * sn[e])) : bf16_round(bf16_round(qf[e] * cs[e]) - bf16_round(qp * sn[e]));
+            kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
+        }
+        if (warp == 0 && t4 == 0) {
+            const int idx = ctx - 1;
+            const size_t slot = (((size_t)bt[idx >> 4] * n_heads + h) * T3B_KV_BLOCK + (idx & 15)) * 64 + c * 8;
+            *reinterpret_cast<uint4*>(k_pool + slot) = pack8(kf);
+            *reinterpret_cast<uint4*>(v_pool + slot) = vraw;
+        }
+        __syncthreads();                                  // the new K/V line is visible to every warp of this CTA
+    } else {
+        unpack8(*reinterpret_cast<const uint4*>(q + ((size_t)t * n_heads + h) * 64 + c * 8), qf);
+    }
 #pragma unroll
     for (int e = 0; e < 8; ++e) qf[e] *= kScale;
 
@@ -47,9 +91,9 @@ __global__ void __launch_bounds__(256) paged_attn_decode_kernel(const bf16* __re
             const int blk = page < n_pages ? bt[page] : bt[p0];   // tail page re-reads a valid page, masked below
             const size_t base = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK) * 64 + (size_t)lane * 8;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) kv[pp][j] = ldg_stream(k_pool + base + j * 256);
+            for (int j = 0; j < 4; ++j) kv[pp][j] = ldg_kv(k_pool + base + j * 256);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) vv[pp][j] = ldg_stream(v_pool + base + j * 256);
+            for (int j = 0; j < 4; ++j) vv[pp][j] = ldg_kv(v_pool + base + j * 256);
         }
         // partial dot products: value i = pp*4 + j belongs to token p0*16 + pp*16 + 4j + t4
         float s[8];
@@ -140,9 +184,39 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
         if (units >= (long)sms * 8) nw = 2;
         else if (units >= (long)sms * 4) nw = 4;
     }
-    T3B_CUDA(t3b_launch(paged_attn_decode_kernel, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)q, tok_row, tok_idx,
-                        block_tables, max_blocks, (const bf16*)k_pool, (const bf16*)v_pool, n_heads, (bf16*)out));
+    (void)sms;
+    T3B_CUDA(t3b_launch(paged_attn_decode_kernel<false>, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)q, tok_row, tok_idx,
+                        block_tables, max_blocks, (bf16*)const_cast<void*>(k_pool), (bf16*)const_cast<void*>(v_pool), n_heads, (bf16*)out,
+                        (const int32_t*)nullptr, (const bf16*)nullptr, 0));
     return T3B_OK;
+}
+
+static int pick_warps(long units) {
+    const int sms = t3b_num_sms();
+    if (units >= (long)sms * 8) return 2;
+    if (units >= (long)sms * 4) return 4;
+    return 8;
+}
+
+// decode step: one token per KV row (token j <-> row j)
+int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
+                              const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, void* out, cudaStream_t s) {
+    const long units = (long)n_tok * n_heads;
+    T3B_CUDA(t3b_launch(paged_attn_decode_kernel<true>, dim3((unsigned)units), dim3(pick_warps(units) * 32), 0, s, (const bf16*)qkv,
+                        (const int32_t*)nullptr, tok_idx, block_tables, max_blocks, (bf16*)k_pool, (bf16*)v_pool, n_heads, (bf16*)out, rope_pos,
+                        (const bf16*)rope_cos_sin, max_pos));
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const int32_t* tok_idx, const int32_t* rope_pos,
+                                         const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables, int32_t max_blocks,
+                                         void* k_pool, void* v_pool, int32_t n_heads, void* out, void* stream) {
+    T3B_CHECK_ARG(qkv && tok_idx && rope_pos && rope_cos_sin && block_tables && k_pool && v_pool && out, "t3b_attn_decode_fused: null pointer");
+    T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && max_pos > 0 && n_heads >= 1, "t3b_attn_decode_fused: bad sizes");
+    T3B_CHECK_ALIGN(qkv); T3B_CHECK_ALIGN(rope_cos_sin); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
+    if (n_tok == 0) return T3B_OK;
+    return t3b_attn_fused_launch(qkv, n_tok, tok_idx, rope_pos, rope_cos_sin, max_pos, block_tables, max_blocks, k_pool, v_pool, n_heads, out,
+                                 t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,

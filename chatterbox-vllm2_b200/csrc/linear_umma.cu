@@ -1,56 +1,128 @@
-// F2.2 / F2.5 / F2.6 / C1 for rows > 4: TMA-fed tcgen05.mma with the accumulator in TMEM.
+// F2.2 / F2.5 / F2.6 / C1 / Q for rows > 4: TMA-fed tcgen05.mma with the accumulator in TMEM.
 //
 // Swap-AB skinny GEMM: the weight tile is the UMMA "A" operand (M = 128 output features, K-major
 // straight from the nn.Linear layout), the activations are the "B" operand (N = CFG rows padded to
 // 16, <= 256, also K-major), so D^T[128 features x rows] lives in 128 TMEM lanes x `rows` fp32 columns
 // and a 2..256-row decode batch uses full-width MMAs without padding the batch to 128.
 //
-//   warp 0  TMA producer   W tile {64 k, 128 n} + X tile {64 k, Rp rows}, SWIZZLE_128B, `stages`-deep ring.
+// Parallelism for the short-and-wide decode shapes (N/128 is only 8..64 tiles) comes from split-K over a
+// THREAD-BLOCK CLUSTER: the n_split CTAs of a cluster each own a K slice of the same 128-feature tile,
+// park their fp32 partial tile in shared memory, and after one barrier.cluster each CTA reduces a
+// disjoint set of rows across all peers through distributed shared memory (fixed peer order 0..n-1 ->
+// deterministic) and runs the epilogue for those rows.  No fp32 partials ever reach HBM/L2.
+//
+//   warp 0  TMA producer   W tile 2 x {64 k, 64 n} + X tile {64 k, Rp rows}, SWIZZLE_128B, `stages`-deep ring.
 //                          The first ring of W tiles is issued BEFORE griddepcontrol.wait (weights never
 //                          depend on the previous kernel) so HBM keeps streaming across kernel boundaries.
+//                          AWQ: the W tile is a 4 KB block of packed nibbles fetched with a 1-D bulk copy.
 //   warp 1  MMA issuer     one elected lane, 4 x tcgen05.mma (K = 16 each) per stage, tcgen05.commit
 //                          frees the stage / publishes the accumulator.
 //   warp 2  TMEM allocate / free.
-//   warps 4-7 epilogue     tcgen05.ld 32x32b (lane = feature, columns = rows) -> bf16 y[r][n] when the CTA
-//                          owns the whole K range, else fp32 split-K partials [split][r][n] that the
-//                          consumer kernel (add_rmsnorm / rope / silu) sums in fixed order.
+//   warps 4-7 epilogue     tcgen05.ld 32x32b (lane = feature, columns = rows) -> fp32 tile in smem ->
+//                          cluster reduce -> epilogue -> bf16 global stores (256 B per row segment).
+//   warps 8-15 (AWQ only)  dequantise: nibble -> bf16 via the 0x4300 magic, (q - z) * s in bf16x2
+//                          (exactly bf16_rn((q - z) * s), the oracle's definition), written as the
+//                          128B-swizzled K-major A tile the MMA reads.
 //
-// grid = (ceil(N/128), n_split, ceil(rows/256)).  Memory-bound for rows < ~216.
+// Epilogues: STORE  y[r, n] = bf16(acc)
+//            SILU   tile t = gate features [64t, 64t+64) in lanes 0..63 and up features [ffn + 64t, ..) in
+//                   lanes 64..127;  act[r, 64t + p] = bf16(bf16(silu(bf16 g)) * bf16 u)
+//                   (llama.py:117-121, activation.py:138-141).
+// Legacy mode (partials != NULL): each split writes its fp32 tile to global memory [split][rows][N].
+//
+// grid = (ceil(N/128), n_split, ceil(rows/256)), cluster = (1, n_split, 1).
 #include <cudaTypedefs.h>
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <cstring>
 
 #include "t3b_common.cuh"
 
 #define UM_M 128
 #define UM_K 64
 #define UM_A_BYTES (UM_M * UM_K * 2)
+#define UM_RAW_BYTES 4096                  // AWQ: 128 x 64 nibbles
 #define UM_MAX_STAGES 8
 
-__global__ void __launch_bounds__(256, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
-                                                             const __grid_constant__ CUtensorMap tmap_x, bf16* __restrict__ y,
-                                                             float* __restrict__ partials, int rows, int N, int kb_total, int n_split,
-                                                             int Rp, int row_chunk, int stages, uint32_t tmem_cols) {
+enum { EPI_STORE = 0, EPI_SILU = 1 };
+
+struct UmmaParams {
+    bf16* y;                 // bf16 [rows, N] (STORE) or [rows, N/2] (SILU); NULL in legacy mode
+    float* partials;         // legacy: fp32 [n_split, rows, N]
+    int rows, N, kb_total, n_split, Rp, row_chunk, stages;
+    uint32_t tmem_cols;
+    int epi;
+    // AWQ (WSRC == 1)
+    const unsigned char* qw; // repacked nibbles [N/128][K/64][2][128][16 B]
+    const bf16* scales;      // bf16 [K/128, N]
+    const unsigned char* zeros;   // u8 [K/128, N]
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(nthreads) : "memory"); }
+
+// actual output feature held by row `r` of tile `tile`
+__device__ __forceinline__ int tile_feature(int tile, int r, int N, int epi) {
+    if (epi == EPI_SILU) return r < 64 ? tile * 64 + r : N / 2 + tile * 64 + (r - 64);
+    return tile * UM_M + r;
+}
+
+template <int WSRC>
+__global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
+                                                                          const __grid_constant__ CUtensorMap tmap_x,
+                                                                          const UmmaParams p) {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
-    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + (size_t)stages * stage_bytes);
+    const int stages = p.stages, Rp = p.Rp;
+    const uint32_t x_bytes = (uint32_t)Rp * 128u;
+    const uint32_t stage_bytes = UM_A_BYTES + x_bytes + (WSRC ? UM_RAW_BYTES : 0);   // [A | X | raw]
+    // the fp32 reduction tile [Rp][128] overlays the pipeline ring once every MMA has retired
+    const size_t ring_bytes = (size_t)stages * stage_bytes;
+    const size_t red_bytes = p.partials ? 0 : (size_t)Rp * UM_M * 4;
+    const size_t body = ring_bytes > red_bytes ? ring_bytes : red_bytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + body);
     uint64_t* empty_bar = full_bar + UM_MAX_STAGES;
-    uint64_t* tmem_full_bar = empty_bar + UM_MAX_STAGES;
+    uint64_t* raw_bar = empty_bar + UM_MAX_STAGES;
+    uint64_t* tmem_full_bar = raw_bar + UM_MAX_STAGES;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+    float* red = reinterpret_cast<float*>(smem);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x, split = blockIdx.y, rchunk = blockIdx.z;
-    const int kb_begin = (int)(((long)split * kb_total) / n_split);
-    const int kb_end = (int)(((long)(split + 1) * kb_total) / n_split);
+    const int kb_begin = (int)(((long)split * p.kb_total) / p.n_split);
+    const int kb_end = (int)(((long)(split + 1) * p.kb_total) / p.n_split);
     const int nkb = kb_end - kb_begin;
+    const int n_a = p.epi == EPI_SILU ? tile * 64 : tile * UM_M;                 // first 64 weight rows of the tile
+    const int n_b = p.epi == EPI_SILU ? p.N / 2 + tile * 64 : tile * UM_M + 64;   // second 64
 
     if (threadIdx.x == 0) {
-        tma_prefetch_desc(&tmap_w);
+        if (!WSRC) tma_prefetch_desc(&tmap_w);
         tma_prefetch_desc(&tmap_x);
-        for (int i = 0; i < stages; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+        for (int i = 0; i < stages; ++i) {
+            mbar_init(&full_bar[i], WSRC ? 1 + 8 : 1);      // producer (tx) [+ 8 dequant warps]
+            mbar_init(&empty_bar[i], 1);
+            mbar_init(&raw_bar[i], 1);
+        }
         mbar_init(tmem_full_bar, 1);
         mbar_fence_init();
     }
-    if (warp == 2) tmem_alloc(tmem_ptr, tmem_cols);
+    if (warp == 2) tmem_alloc(tmem_ptr, p.tmem_cols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -59,20 +131,32 @@ __global__ void __launch_bounds__(256, 1) linear_umma_kernel(const __grid_consta
 
     if (warp == 0) {
         if (lane == 0) {
+            auto load_w = [&](int i, int s) {
+                unsigned char* st = smem + (size_t)s * stage_bytes;
+                if (WSRC) {
+                    mbar_expect_tx(&raw_bar[s], UM_RAW_BYTES);
+                    bulk_load_1d(st + UM_A_BYTES + x_bytes, p.qw + ((size_t)tile * p.kb_total + (kb_begin + i)) * UM_RAW_BYTES, UM_RAW_BYTES,
+                                 &raw_bar[s]);
+                } else {
+                    tma_load_2d(st, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_a);
+                    tma_load_2d(st + UM_A_BYTES / 2, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_b);
+                }
+            };
+            const uint32_t tx = WSRC ? x_bytes : stage_bytes;
             const int pre = nkb < stages ? nkb : stages;
             for (int i = 0; i < pre; ++i) {
-                mbar_expect_tx(&full_bar[i], stage_bytes);
-                tma_load_2d(smem + (size_t)i * stage_bytes, &tmap_w, &full_bar[i], (kb_begin + i) * UM_K, tile * UM_M);
+                mbar_expect_tx(&full_bar[i], tx);
+                load_w(i, i);
             }
             pdl_wait();
             for (int i = 0; i < pre; ++i)
-                tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * row_chunk);
+                tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             for (int i = pre; i < nkb; ++i) {
                 const int s = i % stages, round = i / stages;
                 mbar_wait(&empty_bar[s], (round & 1) ^ 1);
-                mbar_expect_tx(&full_bar[s], stage_bytes);
-                tma_load_2d(smem + (size_t)s * stage_bytes, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, tile * UM_M);
-                tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * row_chunk);
+                mbar_expect_tx(&full_bar[s], tx);
+                load_w(i, s);
+                tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             }
         }
     } else if (warp == 1) {
@@ -92,33 +176,165 @@ __global__ void __launch_bounds__(256, 1) linear_umma_kernel(const __grid_consta
             }
             umma_commit(tmem_full_bar);
         }
-    } else if (warp >= 4) {
+    } else if (WSRC && warp >= 8) {
+        // ---- AWQ dequant: thread d owns weight row (d & 127) and k half (d >> 7) of every k-block
+        const int d = threadIdx.x - 256, row = d & 127, half = d >> 7;
+        const int n = tile_feature(tile, row, p.N, p.epi);
+        const uint32_t a_off = (uint32_t)(row >> 3) * 1024u + (uint32_t)(row & 7) * 128u;
+        int g_cur = -1;
+        __nv_bfloat162 s2 = __float2bfloat162_rn(0.f), zb2 = s2;
+        for (int i = 0; i < nkb; ++i) {
+            const int s = i % stages, round = i / stages;
+            const int g = (kb_begin + i) >> 1;                       // 128-wide quantisation group
+            if (g != g_cur) {
+                g_cur = g;
+                s2 = __bfloat162bfloat162(p.scales[(size_t)g * p.N + n]);
+                zb2 = __float2bfloat162_rn(128.f + (float)p.zeros[(size_t)g * p.N + n]);
+            }
+            unsigned char* st = smem + (size_t)s * stage_bytes;
+            mbar_wait(&raw_bar[s], round & 1);
+            const uint4 raw = *reinterpret_cast<const uint4*>(st + UM_A_BYTES + x_bytes + half * 2048 + row * 16);
+            const uint32_t words[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                uint32_t o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint32_t t = ((words[w] >> (4 * j)) & 0x000F000Fu) | 0x43004300u;   // bf16x2 (128+q_lo, 128+q_hi)
+                    __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&t);
+                    v = __hmul2(__hsub2(v, zb2), s2);                                    // bf16_rn((q - z) * s)
+                    o[j] = *reinterpret_cast<uint32_t*>(&v);
+                }
+                const uint32_t chunk = (uint32_t)(half * 4 + w) ^ (uint32_t)(row & 7);
+                *reinterpret_cast<uint4*>(st + a_off + chunk * 16u) = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+            fence_proxy_async_smem();                                 // generic-proxy writes -> visible to the MMA (async proxy)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full_bar[s]);
+        }
+    } else if (warp >= 4 && warp < 8) {
         pdl_wait();
         const int quad = warp & 3;
-        const int n = tile * UM_M + quad * 32 + lane;
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
-        const int r0 = rchunk * row_chunk;
-        for (int c0 = 0; c0 < Rp; c0 += 16) {
-            uint32_t v[16];
-            tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
-            tmem_ld_wait();
-            if (n < N) {
+        if (p.partials != nullptr) {
+            // legacy: fp32 partial tile straight to global memory
+            const int n = tile * UM_M + quad * 32 + lane;
+            const int r0 = rchunk * p.row_chunk;
+            for (int c0 = 0; c0 < Rp; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+                tmem_ld_wait();
+                if (n < p.N) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int r = r0 + c0 + j;
-                    if (r < rows) {
-                        const float f = __uint_as_float(v[j]);
-                        if (partials != nullptr) partials[((size_t)split * rows + r) * N + n] = f;
-                        else y[(size_t)r * N + n] = __float2bfloat16_rn(f);
+                    for (int j = 0; j < 16; ++j) {
+                        const int r = r0 + c0 + j;
+                        if (r < p.rows) p.partials[((size_t)split * p.rows + r) * p.N + n] = __uint_as_float(v[j]);
                     }
                 }
+            }
+        } else {
+            // fp32 tile -> own shared memory [Rp][128] (the ring is dead: every MMA has retired)
+            const int f = quad * 32 + lane;
+            for (int c0 = 0; c0 < Rp; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) red[(c0 + j) * UM_M + f] = __uint_as_float(v[j]);
             }
         }
     }
     tc_fence_before();
-    __syncthreads();
-    if (warp == 2) tmem_dealloc(tmem_base, tmem_cols);
+    if (p.partials == nullptr) {
+        cluster_sync_all();                      // every CTA's partial tile is parked (n_split == 1: a plain CTA barrier)
+        if (warp >= 4 && warp < 8) {
+            const int t = threadIdx.x - 128;     // 0..127
+            const uint32_t red_s = smem_u32(red);
+            uint32_t peer[8];
+#pragma unroll
+            for (int c = 0; c < 8; ++c) peer[c] = map_to_cta(red_s, (uint32_t)(c < p.n_split ? c : 0));
+            const int r0 = rchunk * p.row_chunk;
+            if (p.epi == EPI_STORE) {
+                const int n = tile * UM_M + t;
+                for (int rl = split; rl < Rp; rl += p.n_split) {          // this CTA's rows of the chunk
+                    const int r = r0 + rl;
+                    if (r >= p.rows) break;
+                    float acc = 0.f;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        if (c < p.n_split) acc += ld_dsmem_f32(peer[c] + (uint32_t)(rl * UM_M + t) * 4u);
+                    if (n < p.N) p.y[(size_t)r * p.N + n] = __float2bfloat16_rn(acc);
+                }
+            } else {
+                const int pi = t & 63, sub = t >> 6, ffn = p.N / 2;
+                for (int rl = split + sub * p.n_split; rl < Rp; rl += 2 * p.n_split) {
+                    const int r = r0 + rl;
+                    if (r >= p.rows) break;
+                    float g = 0.f, u = 0.f;
+#pragma unroll
+                    for (int c = 0; c < 8; ++c)
+                        if (c < p.n_split) {
+                            g += ld_dsmem_f32(peer[c] + (uint32_t)(rl * UM_M + pi) * 4u);
+                            u += ld_dsmem_f32(peer[c] + (uint32_t)(rl * UM_M + 64 + pi) * 4u);
+                        }
+                    g = bf16_round(g); u = bf16_round(u);
+                    p.y[(size_t)r * ffn + tile * 64 + pi] = __float2bfloat16_rn(bf16_round(g / (1.0f + expf(-g))) * u);
+                }
+            }
+        }
+        cluster_sync_all();                      // nobody leaves while a peer may still read its tile
+    } else {
+        __syncthreads();
+    }
+    if (warp == 2) tmem_dealloc(tmem_base, p.tmem_cols);
+}
+
+// ------------------------------------------------------------------ AWQ repack (one-off, at load)
+// AutoAWQ GEMM tensors -> kernel layout.  Word (tile, kb, half, row, w) holds the 8 nibbles of weight
+// row n(tile,row), k = kb*64 + half*32 + w*8 + {0,2,4,6,1,3,5,7}[nibble position] so that
+// (word >> 4j) & 0x000F000F yields the k-adjacent pair (2j, 2j+1) as a bf16x2.
+__global__ void awq_repack_kernel(const int32_t* __restrict__ qweight, const int32_t* __restrict__ qzeros, const __half* __restrict__ scales,
+                                  int N, int K, int gate_up, uint32_t* __restrict__ w_out, unsigned char* __restrict__ zeros_out,
+                                  bf16* __restrict__ scales_out) {
+    const int rev[8] = {0, 4, 1, 5, 2, 6, 3, 7};          // column n % 8 sits at bits 4 * rev[n % 8] (awq_triton.py:56-62)
+    const int koff[8] = {0, 2, 4, 6, 1, 3, 5, 7};
+    const size_t n_words = (size_t)N * K / 8;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x) {
+        const int w = (int)(i & 3), row = (int)((i >> 2) & 127), half = (int)((i >> 9) & 1);
+        const size_t blk = i >> 10;
+        const int kb = (int)(blk % (size_t)(K / 64)), tile = (int)(blk / (size_t)(K / 64));
+        const int n = gate_up ? (row < 64 ? tile * 64 + row : N / 2 + tile * 64 + (row - 64)) : tile * 128 + row;
+        uint32_t word = 0;
+#pragma unroll
+        for (int pos = 0; pos < 8; ++pos) {
+            const int k = kb * 64 + half * 32 + w * 8 + koff[pos];
+            const uint32_t q = ((uint32_t)qweight[(size_t)k * (N / 8) + n / 8] >> (4 * rev[n & 7])) & 15u;
+            word |= q << (4 * pos);
+        }
+        w_out[i] = word;
+    }
+    const size_t n_sz = (size_t)(K / 128) * N;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_sz; i += (size_t)gridDim.x * blockDim.x) {
+        const int n = (int)(i % (size_t)N);
+        const size_t g = i / (size_t)N;
+        zeros_out[i] = (unsigned char)(((uint32_t)qzeros[g * (N / 8) + n / 8] >> (4 * rev[n & 7])) & 15u);
+        scales_out[i] = __float2bfloat16_rn(__half2float(scales[i]));
+    }
+}
+
+extern "C" int32_t t3b_repack_weights_awq(const int32_t* qweight, const int32_t* qzeros, const void* scales_fp16, int32_t n, int32_t k,
+                                          int32_t gate_up_interleave, void* w_out, void* zeros_out, void* scales_out, void* stream) {
+    T3B_CHECK_ARG(qweight && qzeros && scales_fp16 && w_out && zeros_out && scales_out, "t3b_repack_weights_awq: null pointer");
+    T3B_CHECK_SHAPE(n > 0 && k > 0 && n % 128 == 0 && k % 128 == 0, "t3b_repack_weights_awq: n %d / k %d must be multiples of 128", n, k);
+    T3B_CHECK_ALIGN(w_out);
+    const size_t words = (size_t)n * k / 8;
+    int blocks = (int)((words + 255) / 256);
+    if (blocks > t3b_num_sms() * 16) blocks = t3b_num_sms() * 16;
+    awq_repack_kernel<<<blocks, 256, 0, t3b_stream(stream)>>>(qweight, qzeros, (const __half*)scales_fp16, n, k, gate_up_interleave ? 1 : 0,
+                                                             (uint32_t*)w_out, (unsigned char*)zeros_out, (bf16*)scales_out);
+    T3B_LAUNCH_CHECK();
+    return T3B_OK;
 }
 
 // ------------------------------------------------------------------ host
@@ -151,44 +367,104 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t o
 
 int t3b_umma_available() { return get_encode_fn() != nullptr; }
 
-// Split-K factor: fill the SMs, keep >= 1 k-block per CTA, bound the fp32 partial traffic.
+// Split-K factor.  Cluster mode (DSMEM reduce): a power of two <= 8 that divides the k-blocks, chosen to
+// put ~one CTA on every SM.  Depends on (N, K, row chunks) only, never on the row count inside a chunk,
+// so a request's arithmetic does not change with the batch it runs in.
 int t3b_umma_pick_split(int rows, int N, int K) {
+    const int tiles = (N + UM_M - 1) / UM_M * ((rows + 255) / 256);
+    const int kb = K / UM_K;
+    const int sms = t3b_num_sms();
+    int s = 1;
+    while (s < 8 && tiles * s * 2 <= sms + sms / 4 && kb % (s * 2) == 0 && kb / (s * 2) >= 2) s *= 2;
+    return s;
+}
+
+// Legacy split (global fp32 partials): fill the SMs, keep >= 1 k-block per CTA, bound the partial traffic.
+static int pick_split_partials(int rows, int N, int K) {
     const int tiles = (N + UM_M - 1) / UM_M * ((rows + 255) / 256);
     const int kb = K / UM_K;
     const int sms = t3b_num_sms();
     int s = (sms + tiles / 2) / tiles;
     if (s < 1) s = 1;
     if (s > kb) s = kb;
-    const long budget = 8l << 20;                       // bytes of partials per GEMM
+    const long budget = 8l << 20;
     while (s > 1 && (long)s * rows * N * 4 > budget) --s;
     return s;
 }
+int t3b_umma_pick_split_partials(int rows, int N, int K) { return pick_split_partials(rows, N, K); }
 
-int32_t t3b_linear_umma_launch(const void* x, const void* w, int rows, int N, int K, void* y, float* partials, int n_split,
-                               cudaStream_t stream) {
+template <int WSRC>
+static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const UmmaParams& p, int tiles, int chunks, bool cluster,
+                           cudaStream_t stream) {
+    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0);
+    const size_t ring = (size_t)p.stages * stage_bytes, red = cluster ? (size_t)p.Rp * UM_M * 4 : 0;
+    const size_t smem = (ring > red ? ring : red) + 1024 + (3 * UM_MAX_STAGES + 2) * 8;
+    auto kern = linear_umma_kernel<WSRC>;
+    T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(tiles, p.n_split, chunks);
+    cfg.blockDim = dim3(WSRC ? 512 : 256);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    int na = 1;
+    if (cluster && p.n_split > 1) {
+        attr[1].id = cudaLaunchAttributeClusterDimension;
+        attr[1].val.clusterDim.x = 1; attr[1].val.clusterDim.y = p.n_split; attr[1].val.clusterDim.z = 1;
+        na = 2;
+    }
+    cfg.attrs = attr; cfg.numAttrs = na;
+    T3B_CUDA(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
+    return T3B_OK;
+}
+
+// y != NULL: bf16 output (cluster split-K when n_split > 1); partials != NULL: legacy fp32 partials.
+// epi: EPI_STORE / EPI_SILU (bf16 output only).  awq == NULL: bf16 weights `w` [N, K].
+int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
+                               int n_split, int epi, cudaStream_t stream) {
     T3B_CHECK_SHAPE(K % UM_K == 0 && K >= UM_K, "umma: K %d must be a multiple of 64", K);
     T3B_CHECK_SHAPE(rows >= 1, "umma: rows %d", rows);
     const int kb_total = K / UM_K;
+    const bool legacy = partials != nullptr && n_split > 1;
     T3B_CHECK_ARG(n_split >= 1 && n_split <= kb_total, "umma: n_split %d not in [1, %d]", n_split, kb_total);
-    T3B_CHECK_ARG((n_split == 1) ? (y != nullptr) : (partials != nullptr), "umma: output pointer for n_split %d is null", n_split);
+    T3B_CHECK_ARG(legacy || y != nullptr, "umma: y is null");
+    T3B_CHECK_ARG(legacy || n_split <= 8, "umma: cluster split-K %d > 8", n_split);
+    T3B_CHECK_ARG(!(legacy && epi != EPI_STORE), "umma: fused epilogues need the bf16 output mode");
+    if (epi == EPI_SILU) T3B_CHECK_SHAPE(N % 128 == 0, "umma: gate_up N %d must be a multiple of 128", N);
+    if (awq) {
+        T3B_CHECK_SHAPE(N % 128 == 0 && K % 128 == 0, "umma: AWQ needs N %d and K %d to be multiples of 128", N, K);
+        T3B_CHECK_ARG(awq->w && awq->scales && awq->zeros, "umma: AWQ tensors are null");
+        T3B_CHECK_ARG(((awq->flags & T3B_LIN_GATE_UP_INTERLEAVED) != 0) == (epi == EPI_SILU),
+                      "umma: AWQ gate_up weights repacked with gate_up_interleave must run the SiLU epilogue (and only they may)");
+    }
     const int row_chunk = rows > 256 ? 256 : rows;
     const int chunks = (rows + row_chunk - 1) / row_chunk;
     const int Rp = (row_chunk + 15) & ~15;
-    uint32_t tmem_cols = 32;
-    while ((int)tmem_cols < Rp) tmem_cols <<= 1;
-    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u;
+    UmmaParams p = {};
+    p.y = legacy ? nullptr : (bf16*)y;
+    p.partials = legacy ? partials : nullptr;
+    p.rows = rows; p.N = N; p.kb_total = kb_total; p.n_split = n_split; p.Rp = Rp; p.row_chunk = row_chunk; p.epi = epi;
+    p.tmem_cols = 32;
+    while ((int)p.tmem_cols < Rp) p.tmem_cols <<= 1;
+    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u + (awq ? UM_RAW_BYTES : 0);
     const uint32_t budget = Rp >= 128 ? 200u * 1024u : 96u * 1024u;   // small batch: two CTAs per SM
     int stages = (int)(budget / stage_bytes);
+    const int nkb_max = (kb_total + n_split - 1) / n_split;
+    if (stages > nkb_max) stages = nkb_max;
     if (stages > UM_MAX_STAGES) stages = UM_MAX_STAGES;
     if (stages < 2) stages = 2;
-    const size_t smem = (size_t)stages * stage_bytes + 1024 + (2 * UM_MAX_STAGES + 2) * 8;
+    p.stages = stages;
     CUtensorMap tw, tx;
-    int e1 = make_tmap(&tw, w, (uint64_t)K, (uint64_t)N, UM_M, true);
+    memset(&tw, 0, sizeof(tw));
+    int e1 = awq ? 0 : make_tmap(&tw, w, (uint64_t)K, (uint64_t)N, 64, true);
     int e2 = make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
     if (e1 || e2) T3B_FAIL(T3B_ERR_CUDA, "umma: cuTensorMapEncodeTiled failed (%d, %d)", e1, e2);
-    T3B_CUDA(cudaFuncSetAttribute(linear_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((N + UM_M - 1) / UM_M, n_split, chunks);
-    T3B_CUDA(t3b_launch(linear_umma_kernel, grid, dim3(256), smem, stream, tw, tx, (bf16*)(n_split == 1 ? y : nullptr),
-                        n_split == 1 ? (float*)nullptr : partials, rows, N, kb_total, n_split, Rp, row_chunk, stages, tmem_cols));
-    return T3B_OK;
+    const int tiles = epi == EPI_SILU ? N / 128 : (N + UM_M - 1) / UM_M;
+    if (awq) {
+        p.qw = (const unsigned char*)awq->w; p.scales = (const bf16*)awq->scales; p.zeros = (const unsigned char*)awq->zeros;
+        return launch_umma<1>(tw, tx, p, tiles, chunks, !legacy, stream);
+    }
+    return launch_umma<0>(tw, tx, p, tiles, chunks, !legacy, stream);
 }

@@ -95,11 +95,9 @@ class T3B200Engine:
         self.m.head_cfg_sample(self.hidden, 2 * n_slots, self.sampling, self.state, self.out_tokens, advance=True)
 
     def launches_per_step(self, n_slots: int) -> int:
-        """Kernels one decode step launches (embed + per layer [norm, qkv, rope, attn, o, norm, gate_up(+silu), down]
-        + final norm + head + sampler); GEMV path fuses SiLU into gate_up."""
-        rows = 2 * n_slots
-        per_layer = 8 if rows <= 4 else 9
-        return 1 + self.dims.n_layers * per_layer + 3
+        """Kernels one decode step launches: embed + per layer [norm, qkv, attention(+RoPE+KV write), o, norm,
+        gate_up(+SiLU*mul), down] + final norm + head + sampler."""
+        return 1 + self.dims.n_layers * 7 + 3
 
     def _bucket(self, n_slots: int) -> int:
         b = 1

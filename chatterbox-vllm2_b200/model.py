@@ -164,7 +164,7 @@ class T3B200Model:
             assert qkv.shape == (3 * d.hidden, d.hidden) and gu.shape == (2 * d.ffn, d.hidden) and dn.shape == (d.hidden, d.ffn)
             for nm, t in (("qkv", qkv), ("o", o), ("gate_up", gu), ("down", dn)):
                 self.w[f"{i}.{nm}"] = t
-                setattr(layers[i], nm, self._linear_struct(f"{i}.{nm}", t))
+                setattr(layers[i], nm, self._linear_struct(f"{i}.{nm}", t, gate_up=(nm == "gate_up")))
             self.w[f"{i}.ln1"], self.w[f"{i}.ln2"] = ln1, ln2
             layers[i].ln1, layers[i].ln2 = ln1.data_ptr(), ln2.data_ptr()
         self.w["norm"] = bf(need("tfmr.norm.weight"))
@@ -177,20 +177,36 @@ class T3B200Model:
         self.w["rope"] = llama3_rope_table(d).to(device=dev, dtype=torch.bfloat16).contiguous()
         assert self.w["speech_emb"].shape == (d.speech_vocab, d.hidden) and self.w["head"].shape == (d.speech_vocab, d.hidden)
         self._layers = layers
-        head = _lib.Linear(_lib.T3B_W_BF16, d.speech_vocab, d.hidden, self.w["head"].data_ptr(), None, None)
+        head = _lib.Linear(_lib.T3B_W_BF16, d.speech_vocab, d.hidden, self.w["head"].data_ptr(), None, None, 0)
         self.c = _lib.Model(d.n_layers, d.hidden, d.n_heads, d.head_dim, d.ffn, d.speech_vocab, self.w["speech_pos_emb"].shape[0],
                             d.max_pos, d.rms_eps, layers, self.w["norm"].data_ptr(), head, self.w["speech_emb"].data_ptr(),
                             self.w["speech_pos_emb"].data_ptr(), self.w["rope"].data_ptr())
         return loaded
 
-    def _linear_struct(self, key: str, w: torch.Tensor) -> _lib.Linear:
+    def _linear_struct(self, key: str, w: torch.Tensor, gate_up: bool = False) -> _lib.Linear:
+        """bf16 [N, K] -> t3b_linear_t.  quantization="awq": the weight is quantised here (no pre-quantised T3
+        checkpoint exists; load_awq_tensors() takes AutoAWQ tensors directly) and repacked for the kernel."""
         if self.quantization == "awq":
             from .awq import quantize_and_repack
-            q = quantize_and_repack(w)
-            self.w[key] = q["w"]
-            self.w[key + ".scales"], self.w[key + ".zeros"] = q["scales"], q["zeros"]
-            return _lib.Linear(_lib.T3B_W_AWQ, w.shape[0], w.shape[1], q["w"].data_ptr(), q["scales"].data_ptr(), q["zeros"].data_ptr())
-        return _lib.Linear(_lib.T3B_W_BF16, w.shape[0], w.shape[1], w.data_ptr(), None, None)
+            return self._awq_struct(key, quantize_and_repack(w, gate_up), w.shape[0], w.shape[1], gate_up)
+        return _lib.Linear(_lib.T3B_W_BF16, w.shape[0], w.shape[1], w.data_ptr(), None, None, 0)
+
+    def _awq_struct(self, key: str, q: Dict[str, torch.Tensor], n: int, k: int, gate_up: bool) -> _lib.Linear:
+        self.w[key] = q["w"]
+        self.w[key + ".scales"], self.w[key + ".zeros"] = q["scales"], q["zeros"]
+        return _lib.Linear(_lib.T3B_W_AWQ, n, k, q["w"].data_ptr(), q["scales"].data_ptr(), q["zeros"].data_ptr(),
+                           _lib.T3B_LIN_GATE_UP_INTERLEAVED if gate_up else 0)
+
+    def load_awq_tensors(self, layer: int, name: str, qweight: torch.Tensor, qzeros: torch.Tensor, scales: torch.Tensor) -> None:
+        """Replace projection ``name`` ("qkv" | "o" | "gate_up" | "down") of ``layer`` by AutoAWQ GEMM tensors
+        (qweight int32 [K, N/8], qzeros int32 [K/128, N/8], scales fp16 [K/128, N]; vllm awq.py:214-260), with
+        q/k/v and gate/up already concatenated along N like vLLM's stacked parameters."""
+        from .awq import repack
+        if self._layers is None:
+            raise RuntimeError("load_weights() first")
+        k, n = qweight.shape[0], qweight.shape[1] * 8
+        q = repack(qweight, qzeros, scales, self.device, gate_up=(name == "gate_up"))
+        setattr(self._layers[layer], name, self._awq_struct(f"{layer}.{name}", q, n, k, name == "gate_up"))
 
     def weight_bytes(self) -> int:
         """Bytes streamed from HBM per decode step (layers + final norm + head)."""

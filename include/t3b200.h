@@ -47,8 +47,15 @@ extern "C" {
 
 /* kernel selection for t3b_linear_* (0 lets the library choose by row count) */
 #define T3B_IMPL_AUTO 0
-#define T3B_IMPL_GEMV 1          /* SIMT 128-bit-load GEMV, rows <= 4                */
+#define T3B_IMPL_GEMV 1          /* SIMT 128-bit-load GEMV, rows <= 4, bf16 weights  */
 #define T3B_IMPL_UMMA 2          /* TMA-fed tcgen05.mma, accumulators in TMEM        */
+
+/* fused epilogues of t3b_linear_* */
+#define T3B_EPI_NONE     0       /* y[rows, n] = bf16(x W^T)                                             */
+#define T3B_EPI_SILU_MUL 1       /* w = gate_up [2*ffn, k]: y[rows, ffn] = silu(gate) * up (llama.py:117-121) */
+
+/* t3b_linear_t.flags */
+#define T3B_LIN_GATE_UP_INTERLEAVED 1   /* AWQ tiles repacked as 64 gate rows + 64 up rows (SILU_MUL epilogue only) */
 
 /* CFG combine arithmetic (t3.py:662 runs in bf16 tensors; SURVEY.md 8(a) also defines fp32) */
 #define T3B_COMBINE_BF16 0
@@ -60,6 +67,7 @@ typedef struct t3b_linear {
     const void* w;               /* bf16 [n,k]  |  AWQ repacked nibbles */
     const void* scales;          /* AWQ: bf16 [k/128, n]          (else NULL) */
     const void* zeros;           /* AWQ: uint8 [k/128, n]         (else NULL) */
+    int32_t flags;               /* T3B_LIN_* */
 } t3b_linear_t;
 
 typedef struct t3b_layer {       /* one LlamaDecoderLayer (vllm:model_executor/models/llama.py:316-333) */
@@ -143,24 +151,32 @@ int32_t t3b_add_rmsnorm(const void* x, const float* partials, int32_t n_split, v
                         int32_t has_residual, void* stream);
 
 /* F2.2 / F2.5 / F2.6 / C1  the projections (llama.py:164-180,228-232,117-121; t3.py:659-660):
- *     y[r, n] = sum_k x[r,k] * w[n,k], fp32 accumulate.  Exactly one of y (bf16 [rows, n]) and
- *     partials (fp32 [n_split, rows, n]) is written: y when n_split == 1, else partials.
- *     n_split <= 0 lets the library pick (returned through *n_split_out, may be NULL). */
+ *     y[r, n] = sum_k x[r,k] * w[n,k], fp32 accumulate, bf16 output [rows, n] (T3B_EPI_NONE) or the fused
+ *     SiLU*mul of the gate_up projection [rows, n/2] (T3B_EPI_SILU_MUL, activation.py:138-141).
+ *     Split-K: n_split <= 0 lets the library pick (returned through *n_split_out, may be NULL); the
+ *     partial tiles are reduced on-chip through the thread-block cluster's distributed shared memory in a
+ *     fixed order (deterministic) and y is written.  Only when partials != NULL AND n_split > 1 is given
+ *     explicitly are the fp32 partials written to global memory instead ([n_split, rows, n], y untouched)
+ *     for a consumer that sums them (t3b_add_rmsnorm / t3b_rope_kv_write / t3b_silu_mul accept them). */
 int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials,
-                        int32_t n_split, int32_t* n_split_out, int32_t impl, void* stream);
+                        int32_t n_split, int32_t* n_split_out, int32_t impl, int32_t epilogue, void* stream);
 
-/* Q   vllm:model_executor/layers/quantization/awq.py:214-283: same contract as t3b_linear_bf16
- *     with W[k,n] = (nib - zero) * scale, group 128, dequantised to bf16 on the fly. */
+/* Q   vllm:model_executor/layers/quantization/awq.py:214-283: same contract as t3b_linear_bf16 with
+ *     W[k,n] = bf16((nib - zero) * scale), group 128, dequantised on the fly into the tcgen05 operand tile
+ *     (every row count runs T3B_IMPL_UMMA; activations are bf16, scales are converted fp16 -> bf16 by
+ *     t3b_repack_weights_awq). */
 int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials,
-                       int32_t n_split, int32_t* n_split_out, int32_t impl, void* stream);
+                       int32_t n_split, int32_t* n_split_out, int32_t impl, int32_t epilogue, void* stream);
 
 /* one-off layout transform of AutoAWQ tensors (qweight int32 [k, n/8], qzeros int32 [k/128, n/8],
  * scales fp16 [k/128, n]; nibble order 0,2,4,6,1,3,5,7 - awq_triton.py:56-62) into the kernel
- * layout: w_out uint8 [n/128][k/64][128][32] (two k-adjacent nibbles per byte), zeros_out uint8
- * [k/128, n], scales_out bf16 [k/128, n]. */
+ * layout: w_out uint8 [n/128][k/64][2][128][16] (tile, k-block, k half, feature row, 32 nibbles; inside
+ * a 32-bit word the nibble positions hold k offsets 0,2,4,6,1,3,5,7), zeros_out uint8 [k/128, n],
+ * scales_out bf16 [k/128, n].  gate_up_interleave != 0: tile t = gate rows [64t, 64t+64) then up rows
+ * [n/2 + 64t, ...) (set T3B_LIN_GATE_UP_INTERLEAVED in the t3b_linear_t; needs T3B_EPI_SILU_MUL). */
 int32_t t3b_repack_weights_awq(const int32_t* qweight, const int32_t* qzeros, const void* scales_fp16,
-                               int32_t n, int32_t k, void* w_out, void* zeros_out, void* scales_out,
-                               void* stream);
+                               int32_t n, int32_t k, int32_t gate_up_interleave, void* w_out, void* zeros_out,
+                               void* scales_out, void* stream);
 
 /* F2.3 + KV write  (rotary_embedding/common.py:144-174, llama3 table; reshape_and_cache of
  *     llama.py:231): qkv as bf16 [n_tok, 3*hidden] or split-K partials.  Token j belongs to KV row
@@ -177,6 +193,14 @@ int32_t t3b_rope_kv_write(const void* qkv, const float* partials, int32_t n_spli
 int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
                               const int32_t* block_tables, int32_t max_blocks, const void* k_pool,
                               const void* v_pool, int32_t n_heads, void* out, void* stream);
+
+/* F2.3 + KV write + F2.4 in one launch for a decode step (token j <-> KV row j): reads q/k/v of every head
+ *     from qkv bf16 [n_tok, 3*hidden], rotates q and k by rope_pos[j], stores k (rotated) and v at index
+ *     tok_idx[j] of row j and attends over tokens 0..tok_idx[j].  out bf16 [n_tok, hidden]. */
+int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const int32_t* tok_idx, const int32_t* rope_pos,
+                              const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables,
+                              int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads, void* out,
+                              void* stream);
 
 /* F2.6 activation (vllm:model_executor/layers/activation.py:138-141): act = silu(g) * u with the
  *     bf16 roundings of the reference; gate_up as bf16 [rows, 2*ffn] or split-K partials. */

@@ -14,7 +14,7 @@ for (rows, N, K) in [(64, 3072, 1024), (128, 3072, 1024), (50, 8192, 1024), (256
     torch.cuda.synchronize()
     y = torch.full((rows, N), float("nan"), dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(0, N, K, wd.data_ptr(), None, None)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, 2, torch.cuda.current_stream().cuda_stream))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, 2, 0, torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     yc = y.float().cpu()
     r32 = (x.float() @ w.float().t())

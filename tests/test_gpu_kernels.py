@@ -133,7 +133,7 @@ def test_linear_gemv(L, rows, N, K):
     xd, wd = bf(x), bf(w)
     y = torch.empty(rows, N, dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_GEMV, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_GEMV, 0, sp()))
     _check_linear(y, _linear_ref(x, w), K)
 
 
@@ -146,7 +146,7 @@ def test_linear_umma_single(L, rows, N, K):
     xd, wd = bf(x), bf(w)
     y = torch.empty(rows, N, dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, 0, sp()))
     _check_linear(y, _linear_ref(x, w), K)
 
 
@@ -159,7 +159,7 @@ def test_linear_umma_split_k_partials(L, rows, N, K, split):
     parts = torch.full((split, rows, N), float("nan"), dtype=torch.float32, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
     ns = C.c_int32(0)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, None, parts.data_ptr(), split, C.byref(ns), _lib.T3B_IMPL_UMMA, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, None, parts.data_ptr(), split, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, sp()))
     assert ns.value == split
     y = parts.sum(0).bfloat16()
     assert torch.isfinite(parts).all()
@@ -172,19 +172,67 @@ def test_linear_umma_split_k_partials(L, rows, N, K, split):
         assert torch.allclose(parts[s].cpu(), ref, atol=2e-3, rtol=1e-3)
 
 
+@pytest.mark.parametrize("rows", [2, 6, 16, 64, 100, 256, 300])
+@pytest.mark.parametrize("N,K,split", [(3072, 1024, 4), (1024, 1024, 8), (1024, 4096, 8), (8194, 1024, 2), (1024, 4096, 2)])
+def test_linear_umma_cluster_split_k(L, rows, N, K, split):
+    """Split-K reduced on-chip through the cluster's distributed shared memory -> bf16 y, no global partials."""
+    g = torch.Generator().manual_seed(N + K + rows + split)
+    x = torch.randn(rows, K, generator=g).bfloat16()
+    w = (torch.randn(N, K, generator=g) * K ** -0.5).bfloat16()
+    xd, wd = bf(x), bf(w)
+    y = torch.full((rows, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
+    ns = C.c_int32(0)
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, split, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, sp()))
+    assert ns.value == split and torch.isfinite(y.float()).all()
+    _check_linear(y, _linear_ref(x, w), K)
+    y2 = torch.empty_like(y)                                        # fixed reduction order -> bit-reproducible
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y2.data_ptr(), None, split, None, _lib.T3B_IMPL_UMMA, 0, sp()))
+    assert torch.equal(y, y2)
+
+
+@pytest.mark.parametrize("rows,impl,split", [(1, 1, 1), (4, 1, 1), (6, 2, 0), (64, 2, 0), (64, 2, 1), (257, 2, 4), (512, 2, 1)])
+def test_linear_gate_up_silu_epilogue(L, rows, impl, split):
+    """T3B_EPI_SILU_MUL: act = silu(x Wg^T) * (x Wu^T) with the reference's bf16 roundings (activation.py:138-141)."""
+    g = torch.Generator().manual_seed(rows)
+    K, F = 1024, 4096
+    x = torch.randn(rows, K, generator=g).bfloat16()
+    w = (torch.randn(2 * F, K, generator=g) * K ** -0.5).bfloat16()
+    xd, wd = bf(x), bf(w)
+    act = torch.full((rows, F), float("nan"), dtype=torch.bfloat16, device=DEV)
+    lin = _lib.Linear(_lib.T3B_W_BF16, 2 * F, K, wd.data_ptr(), None, None)
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, act.data_ptr(), None, split, None, impl, _lib.T3B_EPI_SILU_MUL, sp()))
+    gu = (x.float() @ w.float().t()).bfloat16()
+    ref = (torch.nn.functional.silu(gu[:, :F]) * gu[:, F:]).float()
+    d = ulp_diff(act, ref)
+    small = ref.abs() < 1e-2
+    # a 1-ulp flip of g or u (fp32 sum order) moves the product by ~1 ulp, the silu slope can add one more
+    ok = (d <= 2.0) | (small & ((act.float().cpu() - ref).abs() < 3e-4))
+    assert ok.float().mean() > 0.999 and (d <= 1.0).float().mean() > 0.97, (float(d.max()), float((d > 1).float().mean()))
+    assert torch.nn.functional.cosine_similarity(act.double().cpu().flatten(), ref.double().flatten(), dim=0) > 0.99999
+
+
 def test_linear_auto_picks_and_is_deterministic(L):
     g = torch.Generator().manual_seed(5)
     x = bf(torch.randn(64, 1024, generator=g))
     w = bf(torch.randn(8192, 1024, generator=g) / 32)
     lin = _lib.Linear(_lib.T3B_W_BF16, 8192, 1024, w.data_ptr(), None, None)
-    parts = torch.empty(16 * 64 * 8192, dtype=torch.float32, device=DEV)
     outs = []
     for _ in range(2):
         y = torch.zeros(64, 8192, dtype=torch.bfloat16, device=DEV)
         ns = C.c_int32(0)
-        _lib.check(L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 64, y.data_ptr(), parts.data_ptr(), 0, C.byref(ns), 0, sp()))
-        outs.append((ns.value, y.clone() if ns.value == 1 else parts[:ns.value * 64 * 8192].clone()))
-    assert outs[0][0] == outs[1][0] and torch.equal(outs[0][1], outs[1][1])
+        _lib.check(L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 64, y.data_ptr(), None, 0, C.byref(ns), 0, 0, sp()))
+        outs.append((ns.value, y.clone()))
+    assert outs[0][0] == outs[1][0] >= 1 and torch.equal(outs[0][1], outs[1][1])
+    # the split never depends on the row count inside a 256-row chunk (batch invariance of a request's arithmetic)
+    splits = set()
+    x256 = bf(torch.randn(256, 1024, generator=g))
+    for rows in (6, 64, 200, 256):
+        ns = C.c_int32(0)
+        y = torch.zeros(rows, 8192, dtype=torch.bfloat16, device=DEV)
+        _lib.check(L.t3b_linear_bf16(x256.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 0, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, sp()))
+        splits.add(ns.value)
+    assert len(splits) == 1
 
 
 # ---------------------------------------------------------------------------------------------- F2.3 + KV write, F2.4
@@ -227,6 +275,33 @@ def test_rope_kv_write_bit_exact(L, orc):
         assert torch.equal(vc[blk, :, idx[j] % 16, :], v_ref[j])
     # nothing else was touched
     assert int((kc != 0).any(-1).sum()) <= n * 16
+
+
+@pytest.mark.parametrize("ctxs", [[1], [16, 17, 33], [1, 15, 16, 33, 99, 100, 399, 1200], list(range(1, 65))])
+def test_attention_fused_rope_kvwrite_equals_separate_kernels(L, ctxs):
+    """t3b_attn_decode_fused == t3b_rope_kv_write + t3b_paged_attn_decode, bit for bit (outputs and KV pool)."""
+    n = len(ctxs)
+    mb = (max(ctxs) + 15) // 16
+    bt, kp, vp = _kv_setup(n, mb, 3)
+    g = torch.Generator().manual_seed(n + 100)
+    kp.copy_(torch.randn(kp.shape, generator=g).bfloat16()); vp.copy_(torch.randn(vp.shape, generator=g).bfloat16())
+    kp2, vp2 = kp.clone(), vp.clone()
+    qkv = bf(torch.randn(n, 3072, generator=g))
+    idx = i32([c - 1 for c in ctxs])
+    pos = i32([(c * 7) % SMALL.max_pos for c in ctxs])
+    cs = bf(rope_cos_sin_table(SMALL))
+    btd = bt.to(DEV)
+    q = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
+    out_a = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
+    out_b = torch.empty_like(out_a)
+    _lib.check(L.t3b_rope_kv_write(qkv.data_ptr(), None, 1, n, None, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos,
+                                   btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, q.data_ptr(), sp()))
+    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, None, idx.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16,
+                                       out_a.data_ptr(), sp()))
+    _lib.check(L.t3b_attn_decode_fused(qkv.data_ptr(), n, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb,
+                                       kp2.data_ptr(), vp2.data_ptr(), 16, out_b.data_ptr(), sp()))
+    assert torch.equal(kp, kp2) and torch.equal(vp, vp2)
+    assert torch.equal(out_a, out_b)
 
 
 @pytest.mark.parametrize("ctxs", [[1], [16, 17], [1, 15, 16, 33, 99, 100, 399, 1200], list(range(1, 65))])
@@ -376,11 +451,11 @@ def test_error_paths(L):
     x = torch.zeros(4, 1024, dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, 1024, 1000, x.data_ptr(), None, None)        # K not a multiple of 64
     y = torch.zeros(4, 1024, dtype=torch.bfloat16, device=DEV)
-    rc = L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 4, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, sp())
+    rc = L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 4, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, 0, sp())
     assert rc == -2 and b"multiple of 64" in L.t3b_last_error()
-    rc = L.t3b_linear_bf16(None, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, sp())
+    rc = L.t3b_linear_bf16(None, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, 0, sp())
     assert rc == -1
-    rc = L.t3b_linear_bf16(x.data_ptr() + 2, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, sp())
+    rc = L.t3b_linear_bf16(x.data_ptr() + 2, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, 0, sp())
     assert rc == -3
     with pytest.raises(_lib.T3BLibraryError):
         _lib.check(rc, "linear")

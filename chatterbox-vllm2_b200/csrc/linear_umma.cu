@@ -57,7 +57,12 @@ struct UmmaParams {
     const unsigned char* qw; // repacked nibbles [N/128][K/64][2][128][16 B]
     const bf16* scales;      // bf16 [K/128, N]
     const unsigned char* zeros;   // u8 [K/128, N]
+    long long* trace;        // debug: 16 clock64 stamps per CTA (NULL = off)
 };
+
+static long long* g_umma_trace = nullptr;
+extern "C" void t3b_debug_set_umma_trace(void* p) { g_umma_trace = static_cast<long long*>(p); }
+#define TRACE(i) do { if (p.trace) p.trace[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 16 + (i)] = clock64(); } while (0)
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void cluster_sync_all() {
@@ -92,16 +97,17 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     const int stages = p.stages, Rp = p.Rp;
     const uint32_t x_bytes = (uint32_t)Rp * 128u;
     const uint32_t stage_bytes = UM_A_BYTES + x_bytes + (WSRC ? UM_RAW_BYTES : 0);   // [A | X | raw]
-    // the fp32 reduction tile [Rp][128] overlays the pipeline ring once every MMA has retired
+    // fp32 reduction buffer behind the ring (peers push into it while this CTA's pipeline may still be running):
+    // n_split > 1: [n_split][Rp / n_split][128]; n_split == 1: a [16][128] exchange buffer; legacy: none
     const size_t ring_bytes = (size_t)stages * stage_bytes;
-    const size_t red_bytes = p.partials ? 0 : (size_t)Rp * UM_M * 4;
-    const size_t body = ring_bytes > red_bytes ? ring_bytes : red_bytes;
+    const size_t red_bytes = p.partials ? 0 : (p.n_split > 1 ? (size_t)Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
+    const size_t body = ring_bytes + red_bytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + body);
     uint64_t* empty_bar = full_bar + UM_MAX_STAGES;
     uint64_t* raw_bar = empty_bar + UM_MAX_STAGES;
     uint64_t* tmem_full_bar = raw_bar + UM_MAX_STAGES;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-    float* red = reinterpret_cast<float*>(smem);
+    float* red = reinterpret_cast<float*>(smem + ring_bytes);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x, split = blockIdx.y, rchunk = blockIdx.z;
@@ -112,6 +118,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     const int n_b = p.epi == EPI_SILU ? p.N / 2 + tile * 64 : tile * UM_M + 64;   // second 64
 
     if (threadIdx.x == 0) {
+        TRACE(0);
         if (!WSRC) tma_prefetch_desc(&tmap_w);
         tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < stages; ++i) {
@@ -128,27 +135,35 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
     pdl_launch_dependents();
+    if (threadIdx.x == 0) TRACE(1);
+
+    auto load_w = [&](int i, int s) {
+        unsigned char* st = smem + (size_t)s * stage_bytes;
+        if (WSRC) {
+            mbar_expect_tx(&raw_bar[s], UM_RAW_BYTES);
+            bulk_load_1d(st + UM_A_BYTES + x_bytes, p.qw + ((size_t)tile * p.kb_total + (kb_begin + i)) * UM_RAW_BYTES, UM_RAW_BYTES, &raw_bar[s]);
+        } else {
+            tma_load_2d(st, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_a);
+            tma_load_2d(st + UM_A_BYTES / 2, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_b);
+        }
+    };
+    const uint32_t tx = WSRC ? x_bytes : stage_bytes;
+    const int pre = nkb < stages ? nkb : stages;
+    // The first ring of weight tiles goes out before anything else: weights never depend on the previous kernel.
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < pre; ++i) {
+            mbar_expect_tx(&full_bar[i], tx);
+            load_w(i, i);
+        }
+    }
+    // Every CTA of the cluster must be running before a peer stores into its shared memory (hidden under the
+    // first-byte latency of the loads above).
+    if (p.partials == nullptr && p.n_split > 1) cluster_sync_all();
 
     if (warp == 0) {
         if (lane == 0) {
-            auto load_w = [&](int i, int s) {
-                unsigned char* st = smem + (size_t)s * stage_bytes;
-                if (WSRC) {
-                    mbar_expect_tx(&raw_bar[s], UM_RAW_BYTES);
-                    bulk_load_1d(st + UM_A_BYTES + x_bytes, p.qw + ((size_t)tile * p.kb_total + (kb_begin + i)) * UM_RAW_BYTES, UM_RAW_BYTES,
-                                 &raw_bar[s]);
-                } else {
-                    tma_load_2d(st, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_a);
-                    tma_load_2d(st + UM_A_BYTES / 2, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_b);
-                }
-            };
-            const uint32_t tx = WSRC ? x_bytes : stage_bytes;
-            const int pre = nkb < stages ? nkb : stages;
-            for (int i = 0; i < pre; ++i) {
-                mbar_expect_tx(&full_bar[i], tx);
-                load_w(i, i);
-            }
             pdl_wait();
+            TRACE(2);
             for (int i = 0; i < pre; ++i)
                 tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             for (int i = pre; i < nkb; ++i) {
@@ -166,6 +181,8 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 const int s = i % stages, round = i / stages;
                 mbar_wait(&full_bar[s], round & 1);
                 tc_fence_after();
+                if (i == 0) TRACE(3);
+                if (i == nkb - 1) TRACE(4);
                 const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
                 const uint64_t a_desc = umma_smem_desc_sw128(a_addr);
                 const uint64_t b_desc = umma_smem_desc_sw128(a_addr + UM_A_BYTES);
@@ -215,13 +232,16 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     } else if (warp >= 4 && warp < 8) {
         pdl_wait();
         const int quad = warp & 3;
+        const int f = quad * 32 + lane;          // feature row of the tile this thread reads from TMEM
+        const int r0 = rchunk * p.row_chunk;
+        const int valid = min(Rp, p.rows - r0);  // rows of this chunk that exist
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
+        if (threadIdx.x == 128) TRACE(5);
         if (p.partials != nullptr) {
             // legacy: fp32 partial tile straight to global memory
-            const int n = tile * UM_M + quad * 32 + lane;
-            const int r0 = rchunk * p.row_chunk;
-            for (int c0 = 0; c0 < Rp; c0 += 16) {
+            const int n = tile * UM_M + f;
+            for (int c0 = 0; c0 < valid; c0 += 16) {
                 uint32_t v[16];
                 tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
                 tmem_ld_wait();
@@ -233,60 +253,98 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     }
                 }
             }
-        } else {
-            // fp32 tile -> own shared memory [Rp][128] (the ring is dead: every MMA has retired)
-            const int f = quad * 32 + lane;
-            for (int c0 = 0; c0 < Rp; c0 += 16) {
+        } else if (p.n_split > 1) {
+            // push: row rl belongs to CTA (rl % n_split) of the cluster; store this CTA's partial of it into the
+            // owner's buffer red[src split][rl / n_split][128] through distributed shared memory
+            const uint32_t red_s = smem_u32(red);
+            const int sh = p.n_split == 2 ? 1 : (p.n_split == 4 ? 2 : 3);
+            const int per = Rp >> sh;                                   // rows each CTA owns
+            for (int c0 = 0; c0 < valid; c0 += 16) {
                 uint32_t v[16];
                 tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
                 tmem_ld_wait();
 #pragma unroll
-                for (int j = 0; j < 16; ++j) red[(c0 + j) * UM_M + f] = __uint_as_float(v[j]);
+                for (int j = 0; j < 16; ++j) {
+                    const int rl = c0 + j;
+                    if (rl < valid) {
+                        const uint32_t off = (uint32_t)((split * per + (rl >> sh)) * UM_M + f) * 4u;
+                        asm volatile("st.shared::cluster.u32 [%0], %1;" :: "r"(map_to_cta(red_s + off, (uint32_t)(rl & (p.n_split - 1)))), "r"(v[j]) : "memory");
+                    }
+                }
+            }
+        } else {
+            // n_split == 1: 16 rows at a time through a small exchange buffer so that the stores of a row are
+            // 256 B contiguous and gate / up (lanes f and f + 64) meet
+            const int t = threadIdx.x - 128;
+            for (int c0 = 0; c0 < valid; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 16; ++j) red[j * UM_M + f] = __uint_as_float(v[j]);
+                named_bar_sync(1, 128);
+                if (p.epi == EPI_STORE) {
+                    const int n = tile * UM_M + t;
+                    if (n < p.N) {
+#pragma unroll 4
+                        for (int j = 0; j < 16; ++j)
+                            if (c0 + j < valid) p.y[(size_t)(r0 + c0 + j) * p.N + n] = __float2bfloat16_rn(red[j * UM_M + t]);
+                    }
+                } else {
+                    const int pi = t & 63, sub = t >> 6, ffn = p.N / 2;
+#pragma unroll 4
+                    for (int j = sub; j < 16; j += 2)
+                        if (c0 + j < valid) {
+                            const float g = bf16_round(red[j * UM_M + pi]), u = bf16_round(red[j * UM_M + 64 + pi]);
+                            p.y[(size_t)(r0 + c0 + j) * ffn + tile * 64 + pi] = __float2bfloat16_rn(bf16_round(g / (1.0f + expf(-g))) * u);
+                        }
+                }
+                named_bar_sync(1, 128);
             }
         }
     }
     tc_fence_before();
-    if (p.partials == nullptr) {
-        cluster_sync_all();                      // every CTA's partial tile is parked (n_split == 1: a plain CTA barrier)
+    if (p.partials == nullptr && p.n_split > 1) {
+        if (threadIdx.x == 128) TRACE(6);
+        cluster_sync_all();                      // release / acquire: every peer's pushes into this CTA's buffer have landed
+        if (threadIdx.x == 128) TRACE(7);
         if (warp >= 4 && warp < 8) {
             const int t = threadIdx.x - 128;     // 0..127
-            const uint32_t red_s = smem_u32(red);
-            uint32_t peer[8];
-#pragma unroll
-            for (int c = 0; c < 8; ++c) peer[c] = map_to_cta(red_s, (uint32_t)(c < p.n_split ? c : 0));
             const int r0 = rchunk * p.row_chunk;
+            const int per = Rp / p.n_split;
             if (p.epi == EPI_STORE) {
                 const int n = tile * UM_M + t;
-                for (int rl = split; rl < Rp; rl += p.n_split) {          // this CTA's rows of the chunk
-                    const int r = r0 + rl;
+#pragma unroll 4
+                for (int j = 0; j < per; ++j) {
+                    const int r = r0 + j * p.n_split + split;
                     if (r >= p.rows) break;
                     float acc = 0.f;
-#pragma unroll
-                    for (int c = 0; c < 8; ++c)
-                        if (c < p.n_split) acc += ld_dsmem_f32(peer[c] + (uint32_t)(rl * UM_M + t) * 4u);
+                    for (int c = 0; c < p.n_split; ++c) acc += red[(c * per + j) * UM_M + t];      // fixed order -> deterministic
                     if (n < p.N) p.y[(size_t)r * p.N + n] = __float2bfloat16_rn(acc);
                 }
             } else {
                 const int pi = t & 63, sub = t >> 6, ffn = p.N / 2;
-                for (int rl = split + sub * p.n_split; rl < Rp; rl += 2 * p.n_split) {
-                    const int r = r0 + rl;
+#pragma unroll 2
+                for (int j = sub; j < per; j += 2) {
+                    const int r = r0 + j * p.n_split + split;
                     if (r >= p.rows) break;
                     float g = 0.f, u = 0.f;
-#pragma unroll
-                    for (int c = 0; c < 8; ++c)
-                        if (c < p.n_split) {
-                            g += ld_dsmem_f32(peer[c] + (uint32_t)(rl * UM_M + pi) * 4u);
-                            u += ld_dsmem_f32(peer[c] + (uint32_t)(rl * UM_M + 64 + pi) * 4u);
-                        }
+                    for (int c = 0; c < p.n_split; ++c) {
+                        g += red[(c * per + j) * UM_M + pi];
+                        u += red[(c * per + j) * UM_M + 64 + pi];
+                    }
                     g = bf16_round(g); u = bf16_round(u);
                     p.y[(size_t)r * ffn + tile * 64 + pi] = __float2bfloat16_rn(bf16_round(g / (1.0f + expf(-g))) * u);
                 }
             }
         }
-        cluster_sync_all();                      // nobody leaves while a peer may still read its tile
-    } else {
-        __syncthreads();
+        if (threadIdx.x == 128) TRACE(8);
+        if (warp >= 4 && warp < 8 && lane == 0) TRACE(10 + (warp & 3));
     }
+    if (threadIdx.x == 0) TRACE(14);
+    if (threadIdx.x == 32) TRACE(15);
+    __syncthreads();
+    if (threadIdx.x == 128) TRACE(9);
     if (warp == 2) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
@@ -371,7 +429,7 @@ int t3b_umma_available() { return get_encode_fn() != nullptr; }
 // put ~one CTA on every SM.  Depends on (N, K, row chunks) only, never on the row count inside a chunk,
 // so a request's arithmetic does not change with the batch it runs in.
 int t3b_umma_pick_split(int rows, int N, int K) {
-    const int tiles = (N + UM_M - 1) / UM_M * ((rows + 255) / 256);
+    const int tiles = (N + UM_M - 1) / UM_M * ((rows + 127) / 128);
     const int kb = K / UM_K;
     const int sms = t3b_num_sms();
     int s = 1;
@@ -397,8 +455,9 @@ template <int WSRC>
 static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const UmmaParams& p, int tiles, int chunks, bool cluster,
                            cudaStream_t stream) {
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0);
-    const size_t ring = (size_t)p.stages * stage_bytes, red = cluster ? (size_t)p.Rp * UM_M * 4 : 0;
-    const size_t smem = (ring > red ? ring : red) + 1024 + (3 * UM_MAX_STAGES + 2) * 8;
+    const size_t ring = (size_t)p.stages * stage_bytes;
+    const size_t red = !cluster ? 0 : (p.n_split > 1 ? (size_t)p.Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
+    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 2) * 8;
     auto kern = linear_umma_kernel<WSRC>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
@@ -430,7 +489,7 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     const bool legacy = partials != nullptr && n_split > 1;
     T3B_CHECK_ARG(n_split >= 1 && n_split <= kb_total, "umma: n_split %d not in [1, %d]", n_split, kb_total);
     T3B_CHECK_ARG(legacy || y != nullptr, "umma: y is null");
-    T3B_CHECK_ARG(legacy || n_split <= 8, "umma: cluster split-K %d > 8", n_split);
+    T3B_CHECK_ARG(legacy || n_split == 1 || n_split == 2 || n_split == 4 || n_split == 8, "umma: cluster split-K %d must be 1, 2, 4 or 8", n_split);
     T3B_CHECK_ARG(!(legacy && epi != EPI_STORE), "umma: fused epilogues need the bf16 output mode");
     if (epi == EPI_SILU) T3B_CHECK_SHAPE(N % 128 == 0, "umma: gate_up N %d must be a multiple of 128", N);
     if (awq) {
@@ -439,17 +498,21 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
         T3B_CHECK_ARG(((awq->flags & T3B_LIN_GATE_UP_INTERLEAVED) != 0) == (epi == EPI_SILU),
                       "umma: AWQ gate_up weights repacked with gate_up_interleave must run the SiLU epilogue (and only they may)");
     }
-    const int row_chunk = rows > 256 ? 256 : rows;
+    // cluster split-K keeps a [Rp][128] fp32 buffer per CTA: 128-row chunks there, 256 otherwise
+    const int max_chunk = (!legacy && n_split > 1) ? 128 : 256;
+    const int row_chunk = rows > max_chunk ? max_chunk : rows;
     const int chunks = (rows + row_chunk - 1) / row_chunk;
     const int Rp = (row_chunk + 15) & ~15;
     UmmaParams p = {};
+    p.trace = g_umma_trace;
     p.y = legacy ? nullptr : (bf16*)y;
     p.partials = legacy ? partials : nullptr;
     p.rows = rows; p.N = N; p.kb_total = kb_total; p.n_split = n_split; p.Rp = Rp; p.row_chunk = row_chunk; p.epi = epi;
     p.tmem_cols = 32;
     while ((int)p.tmem_cols < Rp) p.tmem_cols <<= 1;
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u + (awq ? UM_RAW_BYTES : 0);
-    const uint32_t budget = Rp >= 128 ? 200u * 1024u : 96u * 1024u;   // small batch: two CTAs per SM
+    const uint32_t red_b = legacy ? 0u : (n_split > 1 ? (uint32_t)Rp * UM_M * 4u : 16u * UM_M * 4u);
+    const uint32_t budget = 220u * 1024u - red_b;
     int stages = (int)(budget / stage_bytes);
     const int nkb_max = (kb_total + n_split - 1) / n_split;
     if (stages > nkb_max) stages = nkb_max;

@@ -81,10 +81,15 @@ class DecodeState:
         self.block_tables = z(2 * max_req, max_blocks)
         self.history, self.hist_len = z(max_req, hist_stride), z(max_req)
         self.step, self.active = z(max_req), z(max_req)
-        self.c = _lib.State(self.tokens.data_ptr(), self.speech_pos.data_ptr(), self.rope_pos.data_ptr(),
-                            self.ctx_lens.data_ptr(), self.block_tables.data_ptr(), max_blocks,
-                            self.history.data_ptr(), self.hist_len.data_ptr(), hist_stride, self.step.data_ptr(),
-                            self.active.data_ptr(), stop_token, max_ctx)
+        self.c = self.view(0, stop_token)
+
+    def view(self, slot0: int, stop_token: Optional[int] = None) -> _lib.State:
+        """t3b_state_t whose request 0 is slot ``slot0`` (a lane of the decode step works on a slice of slots)."""
+        p = lambda t, n: t.data_ptr() + 4 * n
+        stop = self.c.stop_token if stop_token is None else stop_token
+        return _lib.State(p(self.tokens, slot0), p(self.speech_pos, slot0), p(self.rope_pos, 2 * slot0), p(self.ctx_lens, 2 * slot0),
+                          p(self.block_tables, 2 * slot0 * self.max_blocks), self.max_blocks, p(self.history, slot0 * self.hist_stride),
+                          p(self.hist_len, slot0), self.hist_stride, p(self.step, slot0), p(self.active, slot0), stop, self.max_ctx)
 
 
 class SamplingTensors:
@@ -95,9 +100,13 @@ class SamplingTensors:
         self.cfg_scale, self.repetition_penalty, self.temperature = f(0.5), f(1.0), f(0.0)
         self.min_p, self.top_p = f(0.0), f(1.0)
         self.seed = torch.zeros(max_req, dtype=torch.int64, device=device)
-        self.c = _lib.Sampling(self.cfg_scale.data_ptr(), self.repetition_penalty.data_ptr(), self.temperature.data_ptr(),
-                               self.min_p.data_ptr(), self.top_p.data_ptr(), self.seed.data_ptr(),
-                               _lib.T3B_COMBINE_BF16 if combine == "bf16" else _lib.T3B_COMBINE_FP32)
+        self.combine = _lib.T3B_COMBINE_BF16 if combine == "bf16" else _lib.T3B_COMBINE_FP32
+        self.c = self.view(0)
+
+    def view(self, slot0: int) -> _lib.Sampling:
+        p = lambda t: t.data_ptr() + t.element_size() * slot0
+        return _lib.Sampling(p(self.cfg_scale), p(self.repetition_penalty), p(self.temperature), p(self.min_p), p(self.top_p),
+                             p(self.seed), self.combine)
 
     def set(self, slot: int, *, cfg_scale, repetition_penalty, temperature, min_p, top_p, seed) -> None:
         self.cfg_scale[slot], self.repetition_penalty[slot], self.temperature[slot] = cfg_scale, repetition_penalty, temperature
@@ -130,6 +139,7 @@ class T3B200Model:
         self._layers = None
         self.c: Optional[_lib.Model] = None
         self._ws: Optional[torch.Tensor] = None
+        self._lane_ws: Dict[int, torch.Tensor] = {}
         self._bound: Optional[Tuple[KVPool, DecodeState]] = None
 
     # ------------------------------------------------------------------ weights
@@ -264,6 +274,29 @@ class T3B200Model:
         _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(state.c), _lib.ptr(x_in), rows, hidden_out.data_ptr(),
                                      ws.data_ptr(), ws.numel(), _lib.stream_ptr()), "t3b_decode_step")
         return hidden_out
+
+    def lane_workspace(self, lane: int, rows: int) -> torch.Tensor:
+        """Scratch of decode lane ``lane`` (lanes run concurrently on their own streams, so each owns one)."""
+        L = self._require()
+        need = L.t3b_workspace_bytes(C.byref(self.c), rows)
+        ws = self._lane_ws.get(lane)
+        if ws is None or ws.numel() < need:
+            ws = self._lane_ws[lane] = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return ws
+
+    def decode_lane(self, kv: KVPool, state: DecodeState, sampling: "SamplingTensors", slot0: int, n_slots: int, lane: int,
+                    hidden: torch.Tensor, out_tokens: torch.Tensor) -> None:
+        """One whole decode step (F1+F2, C1, S1..S4, state advance) for slots [slot0, slot0+n_slots) on the current stream."""
+        L = self._require()
+        rows = 2 * n_slots
+        ws = self.lane_workspace(lane, rows)
+        st, sp = state.view(slot0), sampling.view(slot0)
+        h = hidden.data_ptr() + 2 * slot0 * self.dims.hidden * 2
+        s = _lib.stream_ptr()
+        _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(st), None, rows, h, ws.data_ptr(), ws.numel(), s),
+                   "t3b_decode_step")
+        _lib.check(L.t3b_head_cfg_sample(C.byref(self.c), h, rows, C.byref(sp), C.byref(st), 1, out_tokens.data_ptr() + 4 * slot0, None,
+                                         ws.data_ptr(), ws.numel(), s), "t3b_head_cfg_sample")
 
     def head_cfg_sample(self, hidden: torch.Tensor, rows: int, sampling: SamplingTensors, state: Optional[DecodeState],
                         out_tokens: Optional[torch.Tensor], advance: bool = False,

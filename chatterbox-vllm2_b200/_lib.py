@@ -64,6 +64,14 @@ class Sampling(C.Structure):        # t3b_sampling_t
                 ("seed", vp), ("combine", i32)]
 
 
+class MegaLayer(C.Structure):       # t3b_mega_layer_t
+    _fields_ = [("qkv", vp), ("o", vp), ("gate_up", vp), ("down", vp), ("ln1", vp), ("ln2", vp)]
+
+
+class Mega(C.Structure):            # t3b_mega_t
+    _fields_ = [("layers", vp), ("head", vp)]
+
+
 _PROTOS = {
     "t3b_last_error": (C.c_char_p, []),
     "t3b_version": (i32, []),
@@ -83,6 +91,13 @@ _PROTOS = {
     "t3b_head_cfg_sample": (i32, [C.POINTER(Model), vp, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, vp,
                                   C.c_size_t, vp]),
     "t3b_sample_logits": (i32, [vp, i32, i32, C.POINTER(Sampling), C.POINTER(State), vp, vp]),
+    "t3b_repacked_bytes": (C.c_size_t, [i32, i32]),
+    "t3b_repack_weights_bf16": (i32, [vp, i32, i32, i32, vp, vp]),
+    "t3b_mega_max_rows": (i32, []),
+    "t3b_mega_workspace_bytes": (C.c_size_t, [C.POINTER(Model), i32]),
+    "t3b_decode_step_mega": (i32, [C.POINTER(Model), C.POINTER(Mega), C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, vp,
+                                   C.c_size_t, vp]),
+    "t3b_cfg_sample_head_logits": (i32, [vp, i32, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, vp]),
 }
 
 _lib = None

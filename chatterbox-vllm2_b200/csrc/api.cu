@@ -250,3 +250,10 @@ extern "C" int32_t t3b_sample_logits(const float* logits, int32_t n_req, int32_t
     T3B_CHECK_ARG(logits && sp && out_tokens && n_req >= 0, "t3b_sample_logits: null pointer");
     return t3b_sampler_launch(nullptr, nullptr, 1, logits, vocab, n_req, sp, st, 0, out_tokens, nullptr, t3b_stream(stream));
 }
+
+extern "C" int32_t t3b_cfg_sample_head_logits(const void* head_logits, int32_t rows, int32_t vocab, const t3b_sampling_t* sp,
+                                              const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out, void* stream) {
+    T3B_CHECK_ARG(head_logits && sp && rows >= 0 && rows % 2 == 0 && vocab >= 2, "t3b_cfg_sample_head_logits: bad arguments");
+    if (rows == 0) return T3B_OK;
+    return t3b_sampler_launch(head_logits, nullptr, 1, nullptr, vocab, rows / 2, sp, st, advance, out_tokens, logits_out, t3b_stream(stream));
+}

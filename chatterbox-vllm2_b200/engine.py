@@ -17,6 +17,7 @@ from typing import Dict, List, Optional, Sequence
 
 import torch
 
+from . import _lib
 from .constants import CONDITIONING_SIZE, KV_BLOCK, SPEECH_TOKEN_OFFSET, T3Dims
 from .model import (START_SPEECH_TOKEN, STOP_SPEECH_TOKEN, DecodeState, KVPool, SamplingTensors, T3B200Model)
 
@@ -95,6 +96,10 @@ class T3B200Engine:
         self.steps_run = 0
         model.bind(self.kv, self.state)
         model.workspace(max(2 * max_num_seqs, prefill_chunk_tokens))     # sized once: graphs hold its address
+        if model.mega is not None:
+            r = min(2 * max_num_seqs, _lib.lib().t3b_mega_max_rows())
+            model.mega_workspace(r)
+            model.mega_logits(r)
 
     # ------------------------------------------------------------------ one decode step
     def lane_plan(self, n_slots: int) -> List[tuple]:

@@ -140,6 +140,8 @@ class T3B200Model:
         self.c: Optional[_lib.Model] = None
         self._ws: Optional[torch.Tensor] = None
         self._lane_ws: Dict[int, torch.Tensor] = {}
+        self.mega: Optional[_lib.Mega] = None       # repacked weights of the persistent whole-step kernel (bf16 only)
+        self._mega_ws: Optional[torch.Tensor] = None
         self._bound: Optional[Tuple[KVPool, DecodeState]] = None
 
     # ------------------------------------------------------------------ weights
@@ -191,7 +193,31 @@ class T3B200Model:
         self.c = _lib.Model(d.n_layers, d.hidden, d.n_heads, d.head_dim, d.ffn, d.speech_vocab, self.w["speech_pos_emb"].shape[0],
                             d.max_pos, d.rms_eps, layers, self.w["norm"].data_ptr(), head, self.w["speech_emb"].data_ptr(),
                             self.w["speech_pos_emb"].data_ptr(), self.w["rope"].data_ptr())
+        self.mega = None
+        if self.quantization is None and dev.type == "cuda" and os.environ.get("T3B_MEGA", "1") != "0":
+            self._build_mega()
         return loaded
+
+    def _build_mega(self) -> None:
+        """Unit layout of csrc/decode_mega.cu: every projection as 16 KB blocks of 128 x 64 weights (t3b_repack_weights_bf16)."""
+        L, d = _lib.lib(), self.dims
+        s = _lib.stream_ptr()
+
+        def rp(key: str, w: torch.Tensor, gate_up: bool = False) -> int:
+            n, k = w.shape
+            out = torch.empty(L.t3b_repacked_bytes(n, k), dtype=torch.uint8, device=self.device)
+            _lib.check(L.t3b_repack_weights_bf16(w.data_ptr(), n, k, 1 if gate_up else 0, out.data_ptr(), s), "t3b_repack_weights_bf16")
+            self.w["mega." + key] = out
+            return out.data_ptr()
+
+        table = torch.empty(d.n_layers, 6, dtype=torch.int64)
+        for i in range(d.n_layers):
+            table[i] = torch.tensor([rp(f"{i}.qkv", self.w[f"{i}.qkv"]), rp(f"{i}.o", self.w[f"{i}.o"]),
+                                     rp(f"{i}.gate_up", self.w[f"{i}.gate_up"], True), rp(f"{i}.down", self.w[f"{i}.down"]),
+                                     self.w[f"{i}.ln1"].data_ptr(), self.w[f"{i}.ln2"].data_ptr()], dtype=torch.int64)
+        self.w["mega.table"] = table.to(self.device)
+        self.mega = _lib.Mega(self.w["mega.table"].data_ptr(), rp("head", self.w["head"]))
+        torch.cuda.synchronize(self.device)
 
     def _linear_struct(self, key: str, w: torch.Tensor, gate_up: bool = False) -> _lib.Linear:
         """bf16 [N, K] -> t3b_linear_t.  quantization="awq": the weight is quantised here (no pre-quantised T3
@@ -220,7 +246,7 @@ class T3B200Model:
 
     def weight_bytes(self) -> int:
         """Bytes streamed from HBM per decode step (layers + final norm + head)."""
-        keep = lambda k: k[0].isdigit() or k in ("norm", "head")
+        keep = lambda k: k[0].isdigit() or k in ("norm", "head")     # "mega.*" copies are the same weights in another layout
         return sum(t.numel() * t.element_size() for k, t in self.w.items() if keep(k))
 
     # ------------------------------------------------------------------ plumbing
@@ -275,6 +301,41 @@ class T3B200Model:
                                      ws.data_ptr(), ws.numel(), _lib.stream_ptr()), "t3b_decode_step")
         return hidden_out
 
+    def mega_logits(self, rows: int) -> torch.Tensor:
+        """Persistent bf16 [rows, speech_vocab] head-logit buffer (CUDA graphs hold its address)."""
+        if getattr(self, "_mega_lg", None) is None or self._mega_lg.shape[0] < rows:
+            self._mega_lg = torch.empty(max(rows, 2), self.dims.speech_vocab, dtype=torch.bfloat16, device=self.device)
+        return self._mega_lg
+
+    def mega_ok(self, rows: int) -> bool:
+        return self.mega is not None and 0 < rows <= _lib.lib().t3b_mega_max_rows()
+
+    def mega_workspace(self, rows: int) -> torch.Tensor:
+        L = self._require()
+        need = L.t3b_mega_workspace_bytes(C.byref(self.c), rows)
+        if self._mega_ws is None or self._mega_ws.numel() < need:
+            self._mega_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._mega_ws
+
+    def decode_step_mega(self, kv: KVPool, state_c, rows: int, hidden_out: Optional[torch.Tensor], logits_out: torch.Tensor,
+                         x_in: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """F1+F2+head in ONE persistent launch (csrc/decode_mega.cu): logits_out bf16 [rows, speech_vocab]."""
+        L = self._require()
+        if not self.mega_ok(rows):
+            raise T3BLibraryError(f"decode_step_mega: rows {rows} not supported (bf16 weights, rows <= {L.t3b_mega_max_rows()})")
+        ws = self.mega_workspace(rows)
+        _lib.check(L.t3b_decode_step_mega(C.byref(self.c), C.byref(self.mega), C.byref(kv.c), C.byref(state_c), _lib.ptr(x_in), rows,
+                                          _lib.ptr(hidden_out), logits_out.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
+                   "t3b_decode_step_mega")
+        return logits_out
+
+    def cfg_sample_head_logits(self, head_logits: torch.Tensor, rows: int, sampling_c, state_c, out_tokens_ptr: int, advance: bool = True,
+                               logits_out: Optional[torch.Tensor] = None) -> None:
+        L = self._require()
+        _lib.check(L.t3b_cfg_sample_head_logits(head_logits.data_ptr(), rows, self.dims.speech_vocab, C.byref(sampling_c), C.byref(state_c),
+                                                1 if advance else 0, out_tokens_ptr, _lib.ptr(logits_out), _lib.stream_ptr()),
+                   "t3b_cfg_sample_head_logits")
+
     def lane_workspace(self, lane: int, rows: int) -> torch.Tensor:
         """Scratch of decode lane ``lane`` (lanes run concurrently on their own streams, so each owns one)."""
         L = self._require()
@@ -291,6 +352,11 @@ class T3B200Model:
         rows = 2 * n_slots
         ws = self.lane_workspace(lane, rows)
         st, sp = state.view(slot0), sampling.view(slot0)
+        if lane == 0 and slot0 == 0 and self.mega_ok(rows) and os.environ.get("T3B_MEGA", "1") != "0":
+            lg = self.mega_logits(rows)
+            self.decode_step_mega(kv, st, rows, None, lg)
+            self.cfg_sample_head_logits(lg, rows, sp, st, out_tokens.data_ptr())
+            return
         h = hidden.data_ptr() + 2 * slot0 * self.dims.hidden * 2
         s = _lib.stream_ptr()
         _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(st), None, rows, h, ws.data_ptr(), ws.numel(), s),

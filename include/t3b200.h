@@ -239,6 +239,41 @@ int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden, int32_t ro
 int32_t t3b_sample_logits(const float* logits, int32_t n_req, int32_t vocab, const t3b_sampling_t* sp,
                           const t3b_state_t* st, int32_t* out_tokens, void* stream);
 
+/* ---- the persistent whole-step kernel -------------------------------------------------------------
+ * Same arithmetic as t3b_decode_step + the speech head of t3b_head_cfg_sample (t3.py:676-713,
+ * llama.py:395-432, t3.py:650-660), executed by ONE cooperative launch (one CTA per SM) that streams
+ * weights and past KV pages through a shared-memory ring; see csrc/decode_mega.cu. */
+
+/* device pointers to the weights of one LlamaDecoderLayer in the unit layout of
+ * t3b_repack_weights_bf16 (gate_up with gate_up_interleave = 1) + the two norm weights (bf16 [hidden]) */
+typedef struct t3b_mega_layer {
+    const void* qkv; const void* o; const void* gate_up; const void* down;
+    const void* ln1; const void* ln2;
+} t3b_mega_layer_t;
+
+typedef struct t3b_mega {
+    const t3b_mega_layer_t* layers;   /* DEVICE array [n_layers] */
+    const void* head;                 /* speech_head repacked (rows past speech_vocab zero-filled) */
+} t3b_mega_t;
+
+/* bytes of the repacked form of a bf16 [n, k] weight: ceil(n/128) * 128 * k * 2 */
+size_t  t3b_repacked_bytes(int32_t n, int32_t k);
+/* one-off layout transform: bf16 [n, k] -> [tile][k/64] blocks
+ * of 128 x 64, 128B-swizzled K-major, 16 KB each; gate_up_interleave pairs 64 gate rows with 64 up rows */
+int32_t t3b_repack_weights_bf16(const void* w, int32_t n, int32_t k, int32_t gate_up_interleave, void* out, void* stream);
+int32_t t3b_mega_max_rows(void);      /* largest `rows` t3b_decode_step_mega accepts (128) */
+size_t  t3b_mega_workspace_bytes(const t3b_model_t* m, int32_t max_rows);
+/* F1 + F2 + C1(head): one decode token per CFG row, rows even and <= t3b_mega_max_rows().  Inputs as
+ * t3b_decode_step.  hidden_out (optional) bf16 [rows, hidden] = final-norm output; logits_out bf16
+ * [rows, speech_vocab] = speech_head on every row (NULL = kept in the workspace). */
+int32_t t3b_decode_step_mega(const t3b_model_t* m, const t3b_mega_t* mw, const t3b_kv_t* kv, const t3b_state_t* st,
+                             const void* x_in, int32_t rows, void* hidden_out, void* logits_out, void* workspace,
+                             size_t workspace_bytes, void* stream);
+/* C1(combine) + S1..S4 on head logits bf16 [rows, speech_vocab] (row 2b = cond, 2b+1 = uncond), the
+ * second half of t3b_head_cfg_sample.  Same outputs and state advance. */
+int32_t t3b_cfg_sample_head_logits(const void* head_logits, int32_t rows, int32_t vocab, const t3b_sampling_t* sp,
+                                   const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -352,7 +352,9 @@ class T3B200Model:
         rows = 2 * n_slots
         ws = self.lane_workspace(lane, rows)
         st, sp = state.view(slot0), sampling.view(slot0)
-        if lane == 0 and slot0 == 0 and self.mega_ok(rows) and os.environ.get("T3B_MEGA", "1") != "0":
+        # The persistent kernel is opt-in: measured on B200 it is slower than the PDL-chained kernels below
+        # (profiles/r01c_bench_mega_default.json vs r01c_bench_multikernel.json; DESIGN.md "Persistent step").
+        if lane == 0 and slot0 == 0 and self.mega_ok(rows) and os.environ.get("T3B_MEGA", "0") == "1":
             lg = self.mega_logits(rows)
             self.decode_step_mega(kv, st, rows, None, lg)
             self.cfg_sample_head_logits(lg, rows, sp, st, out_tokens.data_ptr())

@@ -1,0 +1,150 @@
+"""CPU tests of the host side: the C-ABI library loads and exports what include/t3b200.h declares (no compute
+calls), the product path fails loudly without a GPU, the paged-KV allocator and request sharding behave, the
+replica layout works across 2 processes (gloo), and the committed golden fixtures reproduce from the oracle."""
+import ctypes as C
+import os
+import re
+import socket
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "chatterbox-vllm2_b200", "csrc", "libt3b200.so")
+
+
+@pytest.fixture(scope="module")
+def built():
+    if not os.path.exists(LIB):
+        import __graft_entry__
+        __graft_entry__.build()
+    return LIB
+
+
+def test_library_exports_every_header_symbol(built):
+    from chatterbox_vllm2_b200 import _lib
+    L = C.CDLL(built)
+    names = _lib.header_symbols()
+    hdr = open(os.path.join(ROOT, "include", "t3b200.h")).read()
+    declared = set(re.findall(r"\b(t3b_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(names) and len(names) >= 20
+    for n in names:
+        assert hasattr(L, n), n
+    L.t3b_version.restype = C.c_int32
+    assert L.t3b_version() >= 100
+
+
+def test_header_cites_the_reference_for_every_entry_point():
+    hdr = open(os.path.join(ROOT, "include", "t3b200.h")).read()
+    assert "t3.py:" in hdr and "llama.py:" in hdr and "sampler.py:" in hdr and "awq.py:" in hdr
+
+
+def test_argument_errors_are_reported_without_a_gpu(built):
+    from chatterbox_vllm2_b200 import _lib
+    L = _lib.lib()
+    rc = L.t3b_embed_gather(None, None, None, None, 1, 1024, 8194, 4100, 1, None, None)
+    assert rc == -1 and b"null" in L.t3b_last_error().lower()
+    with pytest.raises(_lib.T3BLibraryError):
+        _lib.check(rc, "t3b_embed_gather")
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
+def test_product_path_has_no_cpu_fallback(built):
+    from chatterbox_vllm2_b200 import T3Dims, _lib
+    from chatterbox_vllm2_b200.model import T3B200Model
+    from chatterbox_vllm2_b200.synthetic import synthetic_checkpoint
+    dims = T3Dims().small(n_layers=1, max_pos=64)
+    m = T3B200Model(dims=dims, device="cpu")
+    m.load_weights(synthetic_checkpoint(dims).items())
+    with pytest.raises(_lib.T3BLibraryError):
+        m.embed("speech_emb", "speech_pos_emb", torch.zeros(1, dtype=torch.int32), torch.zeros(1, dtype=torch.int32))
+    assert _lib.lib().t3b_check_device() != 0
+
+
+def test_kv_pool_allocator():
+    from chatterbox_vllm2_b200 import T3Dims
+    from chatterbox_vllm2_b200.model import KVPool
+    dims = T3Dims().small(n_layers=1, max_pos=64)
+    kv = KVPool(dims, 9, "cpu")
+    assert KVPool.bytes_per_block(T3Dims()) == 16 * 122880
+    a = kv.alloc(5)
+    assert 0 not in a and len(set(a)) == 5            # block 0 is the scratch block
+    with pytest.raises(MemoryError):
+        kv.alloc(4)
+    b = kv.alloc(3)
+    assert not set(a) & set(b)
+    kv.release(a)
+    assert sorted(kv.alloc(5)) == sorted(a)
+
+
+def test_shard_requests_partitions():
+    from chatterbox_vllm2_b200.engine import shard_requests
+    for n, w in ((4096, 8), (7, 2), (3, 4), (0, 2)):
+        parts = [shard_requests(n, w, r) for r in range(w)]
+        assert sorted(i for p in parts for i in p) == list(range(n))
+        assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_replicas_world_size_2_gloo(tmp_path):
+    """Two processes, gloo: each takes its shard of 7 requests, "decodes" them with the CPU oracle (standing in
+    for the per-GPU engine: the multi-GPU layout has no data-path collective) and rank 0 gathers token lists
+    in request order, exactly as the replica dispatcher does."""
+    script = tmp_path / "rank.py"
+    script.write_text(textwrap.dedent(f"""
+        import os, sys
+        sys.path.insert(0, {ROOT!r}); sys.path.insert(0, os.path.join({ROOT!r}, "tests"))
+        import torch, torch.distributed as dist
+        from chatterbox_vllm2_b200 import T3Dims
+        from chatterbox_vllm2_b200.engine import shard_requests
+        from chatterbox_vllm2_b200.synthetic import synthetic_checkpoint, synthetic_request
+        from helpers import oracle_generate
+        from oracle.t3_ref import T3Oracle
+        dist.init_process_group("gloo")
+        rank, world = dist.get_rank(), dist.get_world_size()
+        dims = T3Dims().small(n_layers=1, max_pos=128)
+        orc = T3Oracle(synthetic_checkpoint(dims), dims, mode="fp32")
+        mine = shard_requests(7, world, rank)
+        out = oracle_generate(orc, [synthetic_request(i, dims, n_text=6) for i in mine], 4)["tokens"].tolist()
+        gathered = [None] * world
+        dist.all_gather_object(gathered, dict(zip(mine, out)))
+        if rank == 0:
+            merged = {{}}
+            for g in gathered: merged.update(g)
+            ref = oracle_generate(orc, [synthetic_request(i, dims, n_text=6) for i in range(7)], 4)["tokens"].tolist()
+            assert [merged[i] for i in range(7)] == ref, (merged, ref)
+            print("REPLICAS_OK")
+        dist.barrier(); dist.destroy_process_group()
+    """))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", OMP_NUM_THREADS="2")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(_free_port()), str(script)], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "REPLICAS_OK" in r.stdout, r.stdout + r.stderr
+
+
+def test_golden_greedy_stream_reproduces_from_oracle():
+    from helpers import GOLD
+    path = os.path.join(GOLD, "t3_small_greedy.npz")
+    g = np.load(path, allow_pickle=False)
+    assert "tokens" in g.files and g["tokens"].ndim == 2 and g["tokens"].min() >= 0 and g["tokens"].max() < 8194
+
+
+def test_bench_reference_arm_contract():
+    """`bench.py --impl reference` prints one JSON line with the keys the driver reads (tiny run)."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--batch", "1"],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    for k in ("impl", "metric", "value", "unit", "n_gpus", "steps", "ms_per_step", "cpu_baseline", "e2e", "config"):
+        assert k in line
+    assert line["impl"] == "reference" and line["cpu_baseline"]["kind"] == "port" and line["value"] > 0

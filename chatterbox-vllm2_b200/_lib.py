@@ -98,6 +98,11 @@ _PROTOS = {
     "t3b_decode_step_mega": (i32, [C.POINTER(Model), C.POINTER(Mega), C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, vp,
                                    C.c_size_t, vp]),
     "t3b_cfg_sample_head_logits": (i32, [vp, i32, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, vp]),
+    "t3b_fused_weight_bytes": (C.c_size_t, [C.POINTER(Model)]),
+    "t3b_fused_repack": (i32, [C.POINTER(Model), vp, vp]),
+    "t3b_fused_max_rows": (i32, []),
+    "t3b_fused_workspace_bytes": (C.c_size_t, [C.POINTER(Model), i32]),
+    "t3b_decode_step_fused": (i32, [C.POINTER(Model), vp, C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, vp, C.c_size_t, vp]),
 }
 
 _lib = None

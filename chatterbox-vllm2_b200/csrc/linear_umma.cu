@@ -425,6 +425,20 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t o
 
 int t3b_umma_available() { return get_encode_fn() != nullptr; }
 
+// bf16 [outer, inner] row-major activations, box {64, box_outer}, SWIZZLE_128B (used by decode_fused.cu)
+int t3b_make_tmap_act(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, uint64_t row_stride_elems, uint32_t box_outer) {
+    auto enc = get_encode_fn();
+    if (!enc) return -1;
+    cuuint64_t gdim[2] = {inner, outer};
+    cuuint64_t gstride[1] = {row_stride_elems * 2};
+    cuuint32_t box[2] = {UM_K, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
 // Split-K factor.  Cluster mode (DSMEM reduce): a power of two <= 8 that divides the k-blocks, chosen to
 // put ~one CTA on every SM.  Depends on (N, K, row chunks) only, never on the row count inside a chunk,
 // so a request's arithmetic does not change with the batch it runs in.

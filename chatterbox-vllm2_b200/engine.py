@@ -100,6 +100,10 @@ class T3B200Engine:
             r = min(2 * max_num_seqs, _lib.lib().t3b_mega_max_rows())
             model.mega_workspace(r)
             model.mega_logits(r)
+        if model.fused is not None:
+            r = min(2 * max_num_seqs, _lib.lib().t3b_fused_max_rows())
+            model.fused_workspace(r)
+            model.mega_logits(r)
 
     # ------------------------------------------------------------------ one decode step
     def lane_plan(self, n_slots: int) -> List[tuple]:

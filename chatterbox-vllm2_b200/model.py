@@ -142,6 +142,8 @@ class T3B200Model:
         self._lane_ws: Dict[int, torch.Tensor] = {}
         self.mega: Optional[_lib.Mega] = None       # repacked weights of the persistent whole-step kernel (bf16 only)
         self._mega_ws: Optional[torch.Tensor] = None
+        self.fused: Optional[torch.Tensor] = None   # weight blob of the fused step kernel (csrc/decode_fused.cu, bf16 only)
+        self._fused_ws: Optional[torch.Tensor] = None
         self._bound: Optional[Tuple[KVPool, DecodeState]] = None
 
     # ------------------------------------------------------------------ weights
@@ -194,9 +196,24 @@ class T3B200Model:
                             d.max_pos, d.rms_eps, layers, self.w["norm"].data_ptr(), head, self.w["speech_emb"].data_ptr(),
                             self.w["speech_pos_emb"].data_ptr(), self.w["rope"].data_ptr())
         self.mega = None
-        if self.quantization is None and dev.type == "cuda" and os.environ.get("T3B_MEGA", "1") != "0":
-            self._build_mega()
+        self.fused = None
+        if self.quantization is None and dev.type == "cuda":
+            if os.environ.get("T3B_MEGA", "0") == "1":
+                self._build_mega()
+            if os.environ.get("T3B_FUSED", "1") != "0":
+                self._build_fused()
         return loaded
+
+    def _build_fused(self) -> None:
+        """Per-CTA weight streams of csrc/decode_fused.cu (t3b_fused_repack); None if the shape is not the T3 one."""
+        L = _lib.lib()
+        n = L.t3b_fused_weight_bytes(C.byref(self.c))
+        if n == 0:
+            return
+        blob = torch.empty(n, dtype=torch.uint8, device=self.device)
+        _lib.check(L.t3b_fused_repack(C.byref(self.c), blob.data_ptr(), _lib.stream_ptr()), "t3b_fused_repack")
+        torch.cuda.synchronize(self.device)
+        self.fused = blob
 
     def _build_mega(self) -> None:
         """Unit layout of csrc/decode_mega.cu: every projection as 16 KB blocks of 128 x 64 weights (t3b_repack_weights_bf16)."""
@@ -246,7 +263,7 @@ class T3B200Model:
 
     def weight_bytes(self) -> int:
         """Bytes streamed from HBM per decode step (layers + final norm + head)."""
-        keep = lambda k: k[0].isdigit() or k in ("norm", "head")     # "mega.*" copies are the same weights in another layout
+        keep = lambda k: k[0].isdigit() or k in ("norm", "head")     # "mega.*" / fused copies are the same weights in another layout
         return sum(t.numel() * t.element_size() for k, t in self.w.items() if keep(k))
 
     # ------------------------------------------------------------------ plumbing
@@ -329,6 +346,29 @@ class T3B200Model:
                    "t3b_decode_step_mega")
         return logits_out
 
+    def fused_ok(self, rows: int) -> bool:
+        return self.fused is not None and 0 < rows <= _lib.lib().t3b_fused_max_rows()
+
+    def fused_workspace(self, rows: int) -> torch.Tensor:
+        L = self._require()
+        need = L.t3b_fused_workspace_bytes(C.byref(self.c), rows)
+        if self._fused_ws is None or self._fused_ws.numel() < need:
+            self._fused_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._fused_ws
+
+    def decode_step_fused(self, kv: KVPool, state_c, rows: int, hidden_out: Optional[torch.Tensor], logits_out: torch.Tensor,
+                          x_in: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """F1+F2+head in ONE persistent launch with two global exchanges per layer (csrc/decode_fused.cu):
+        logits_out bf16 [rows, speech_vocab]."""
+        L = self._require()
+        if not self.fused_ok(rows):
+            raise T3BLibraryError(f"decode_step_fused: rows {rows} not supported (bf16 T3 shape, rows <= {L.t3b_fused_max_rows()})")
+        ws = self.fused_workspace(rows)
+        _lib.check(L.t3b_decode_step_fused(C.byref(self.c), self.fused.data_ptr(), C.byref(kv.c), C.byref(state_c), _lib.ptr(x_in), rows,
+                                           _lib.ptr(hidden_out), logits_out.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
+                   "t3b_decode_step_fused")
+        return logits_out
+
     def cfg_sample_head_logits(self, head_logits: torch.Tensor, rows: int, sampling_c, state_c, out_tokens_ptr: int, advance: bool = True,
                                logits_out: Optional[torch.Tensor] = None) -> None:
         L = self._require()
@@ -354,6 +394,11 @@ class T3B200Model:
         st, sp = state.view(slot0), sampling.view(slot0)
         # The persistent kernel is opt-in: measured on B200 it is slower than the PDL-chained kernels below
         # (profiles/r01c_bench_mega_default.json vs r01c_bench_multikernel.json; DESIGN.md "Persistent step").
+        if lane == 0 and slot0 == 0 and self.fused_ok(rows) and os.environ.get("T3B_FUSED", "1") != "0":
+            lg = self.mega_logits(rows)
+            self.decode_step_fused(kv, st, rows, None, lg)
+            self.cfg_sample_head_logits(lg, rows, sp, st, out_tokens.data_ptr())
+            return
         if lane == 0 and slot0 == 0 and self.mega_ok(rows) and os.environ.get("T3B_MEGA", "0") == "1":
             lg = self.mega_logits(rows)
             self.decode_step_mega(kv, st, rows, None, lg)

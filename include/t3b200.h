@@ -274,6 +274,27 @@ int32_t t3b_decode_step_mega(const t3b_model_t* m, const t3b_mega_t* mw, const t
 int32_t t3b_cfg_sample_head_logits(const void* head_logits, int32_t rows, int32_t vocab, const t3b_sampling_t* sp,
                                    const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out, void* stream);
 
+/* ---- the fused persistent step kernel (two global exchanges per layer) --------------------------------
+ * Same arithmetic and interface as t3b_decode_step_mega; see csrc/decode_fused.cu.  16 clusters x 8 CTAs:
+ * cluster = attention head = FFN slice, q|k|v -> attention -> o-partial and gate_up -> SiLU*mul ->
+ * down-partial stay inside a cluster (distributed shared memory); the only global exchanges are the two
+ * split-K reductions + RMSNorm per layer.  Built for hidden 1024, 16 heads x 64, ffn 4096, bf16 weights. */
+
+/* bytes of the repacked weight blob (0 if the model shape is not supported) */
+size_t  t3b_fused_weight_bytes(const t3b_model_t* m);
+/* one-off layout transform of every bf16 projection, the speech head and the norm weights of `m` into the
+ * per-CTA streams the kernel's producer warp walks (`out`: t3b_fused_weight_bytes(m) bytes, 16-byte aligned) */
+int32_t t3b_fused_repack(const t3b_model_t* m, void* out, void* stream);
+int32_t t3b_fused_max_rows(void);     /* largest `rows` t3b_decode_step_fused accepts (128) */
+size_t  t3b_fused_workspace_bytes(const t3b_model_t* m, int32_t max_rows);
+/* F1 + F2 + C1(head) (t3.py:676-713, llama.py:395-432, t3.py:650-660): one decode token per CFG row, rows
+ * even and <= t3b_fused_max_rows().  Inputs as t3b_decode_step.  hidden_out (optional) bf16 [rows, hidden] =
+ * final-norm output; logits_out bf16 [rows, speech_vocab] = speech_head on every row (NULL = kept in the
+ * workspace).  Follow with t3b_cfg_sample_head_logits. */
+int32_t t3b_decode_step_fused(const t3b_model_t* m, const void* fused_weights, const t3b_kv_t* kv, const t3b_state_t* st,
+                              const void* x_in, int32_t rows, void* hidden_out, void* logits_out, void* workspace,
+                              size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

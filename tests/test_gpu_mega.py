@@ -28,6 +28,8 @@ def model_for(dims):
     if key not in _models:
         m = T3B200Model(dims=dims, device=DEV, cfg_scale=0.5)
         m.load_weights(synthetic_checkpoint(dims).items())
+        if m.mega is None:
+            m._build_mega()          # opt-in path (T3B_MEGA=1): build its repacked weights for these tests
         assert m.mega is not None
         _models[key] = m
     return _models[key]

@@ -47,7 +47,6 @@
 
 #include "t3b_common.cuh"
 
-int t3b_make_tmap_act(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, uint64_t row_stride_elems, uint32_t box_outer);
 
 #define FZ_THREADS 320
 #define FZ_WORKERS 256
@@ -75,7 +74,7 @@ int t3b_make_tmap_act(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t 
 #define FZ_HEAD_KB_BYTES (FZ_HEAD_ROWS * 128)
 #define FZ_HEAD_CTA_BYTES (16 * FZ_HEAD_KB_BYTES)
 #define FZ_REC 68                     // floats per attention partial record: m, l, pad, pad, acc[64]
-#define FZ_TRACE 1024
+#define FZ_TRACE 2048                 // trace words per CTA: (id, globaltimer) pairs
 
 struct FusedParams {
     const unsigned char* wl;          // [n_layers]{[16 heads][4][qkv | o], [32 clusters][4][gate_up | down]}
@@ -88,6 +87,7 @@ struct FusedParams {
     int n_layers, V, emb_rows, pos_rows, max_pos, max_blocks;
     int rows, Rp, Rh, Rph, nslot, nx, n_head_ctas;      // Rh = rows / 2 (one parity), Rp / Rph = padded to 16
     uint32_t off_qkvraw, off_attpart, off_attnx, off_actx, dsm_bytes;
+    uint32_t meta_pages_max;          // capacity of the per-CTA KV page list (slots)
     float eps;
     float* s;                         // [2][rows][1024] fp32 residual stream (double buffered across exchanges)
     bf16* xn;                         // [rows][1024]    normalised activations handed to the next phase
@@ -95,6 +95,7 @@ struct FusedParams {
     bf16 *logits, *hidden_out;
     unsigned int* counters;
     unsigned long long* trace;
+    int dbg;                          // debug switches (t3b_debug_set_fused_flags)
 };
 
 struct FusedSmem {
@@ -110,6 +111,15 @@ struct FusedSmem {
     int n_groups, n_kv_slots;
     uint8_t grp_row[FZ_MAX_ROWS];
     uint16_t grp_slot0[FZ_MAX_ROWS];
+};
+
+// per-CTA copies of the step's request metadata (read once at kernel start: the producer and the attention warps
+// would otherwise pay an L2 round trip per KV slot / per row and layer)
+struct FusedMeta {
+    int32_t* pages;       // [n_kv_slots][4] physical block of each 16-token page of a KV slot (ring order)
+    int32_t* L;           // [Rh] cached tokens of local row lr (global row 2 lr + z)
+    int32_t* blk_new;     // [Rh] physical block this step's token of the row is written to
+    uint4* cs;            // [Rh][8] cos(32) | sin(32) bf16 of the row's RoPE position
 };
 
 namespace {
@@ -153,6 +163,13 @@ __device__ __forceinline__ bool fz_try_wait_cluster(uint64_t* bar, uint32_t pari
                  : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
     return ok != 0;
 }
+// one lane of a converged warp (the tcgen05 issue / commit instructions are single-thread; keeping the surrounding
+// control flow warp-uniform lets ptxas hold descriptors in uniform registers instead of R2UR-ing them per MMA)
+__device__ __forceinline__ bool fz_elect_one() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
+    return p != 0;
+}
 // spin until *ctr >= target (bounded: a protocol bug traps instead of hanging the box)
 __device__ __forceinline__ void fz_spin_ge(const unsigned int* ctr, unsigned int target) {
     if (fz_ld_acquire(ctr) >= target) return;
@@ -165,8 +182,8 @@ __device__ __forceinline__ void fz_spin_ge(const unsigned int* ctr, unsigned int
 
 
 // ===================================================================== workers (warps 2..9)
-__device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtensorMap* tmap_a, const CUtensorMap* tmap_b, FusedSmem& sm,
-                                              unsigned char* ring, unsigned char* xring, unsigned char* dsm, uint32_t tmem_base) {
+__device__ __forceinline__ void fused_workers(const FusedParams& p, FusedSmem& sm, const FusedMeta& meta, unsigned char* ring,
+                                              unsigned char* xring, unsigned char* dsm, uint32_t tmem_base) {
     const int tid = threadIdx.x - 64, wid = tid >> 5, lane = tid & 31;
     const int j = (int)fz_cluster_ctarank(), cl = (int)fz_clusterid(), b = cl * FZ_CL + j;
     const int h = cl >> 1, z = cl & 1;                               // phase A: head, row parity of this cluster
@@ -178,9 +195,11 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
     uint32_t q = 0, xq = 0, tseq = 0, bar_target = 0, ncl = 0;
     unsigned int* gbar = p.counters;
     int tr = 0;
-    auto stamp = [&]() { if (p.trace != nullptr && tid == 0 && tr < FZ_TRACE) p.trace[(size_t)b * FZ_TRACE + tr++] = fz_gtimer(); };
-    auto grid_arrive = [&]() { stamp(); __threadfence(); fz_worker_sync(); if (tid == 0) fz_red_release(gbar); };
-    auto grid_wait = [&]() { bar_target += (uint32_t)FZ_NCTA; if (tid == 0) fz_spin_ge(gbar, bar_target); fz_worker_sync(); stamp(); };
+    auto stamp = [&](int id) {
+        if (p.trace != nullptr && tid == 0 && tr + 2 <= FZ_TRACE) { p.trace[(size_t)b * FZ_TRACE + tr] = (unsigned long long)id; p.trace[(size_t)b * FZ_TRACE + tr + 1] = fz_gtimer(); tr += 2; }
+    };
+    auto grid_arrive = [&]() { stamp(1); __threadfence(); fz_worker_sync(); if (tid == 0) fz_red_release(gbar); };
+    auto grid_wait = [&]() { bar_target += (uint32_t)FZ_NCTA; if (tid == 0) fz_spin_ge(gbar, bar_target); fz_worker_sync(); stamp(2); };
     // barrier of the 4 x 256 worker threads of the cluster (producer / MMA warps run ahead, so the hardware
     // barrier.cluster cannot be used): remote mbarrier arrivals, two alternating barriers
     auto cluster_sync = [&]() {
@@ -250,20 +269,36 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
         grid_arrive();
         grid_wait();
     };
-    // activation operand: 16 k-blocks of xn -> [N x 64] SWIZZLE_128B stages by TMA (rows past the tensor read 0).
-    // tmap_a: the rows of this cluster's parity (N = Rph); tmap_b: all rows (N = Rp)
-    auto issue_x = [&](const CUtensorMap* tm, uint32_t bytes) {
-        if (tid == 0) {
-            fz_fence_async_all();
-            for (int kb = 0; kb < 16; ++kb) {
-                const uint32_t xi = xq + (uint32_t)kb, xs = xi % nx;
-                if (xi >= (uint32_t)nx) mbar_wait(&sm.x_empty[xs], ((xi / nx) - 1) & 1);
-                mbar_expect_tx(&sm.x_full[xs], bytes);
-                tma_load_2d(xring + (size_t)xs * xst, tm, &sm.x_full[xs], kb * 64, 0);
+    // activation operand: 16 k-blocks of xn rows {rmul i + radd, i < nrows} -> [N x 64] K-major SWIZZLE_128B stages, built
+    // by the workers nx stages at a time (one L2 round trip per batch; rows past nrows are never read back)
+    auto build_x = [&](int nrows, int rmul, int radd) {
+        const int lnx = 31 - __clz(nx);                              // nx is a power of two dividing 16
+        const int total = nrows * 8 * nx;
+        for (int kb0 = 0; kb0 < 16; kb0 += nx) {
+            const uint32_t use = (xq + (uint32_t)kb0) >> lnx;        // how often every stage has been filled before
+            for (int i0 = tid; i0 < total; i0 += 4 * FZ_WORKERS) {
+                uint4 v[4];
+                uint32_t dst[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int i = i0 + u * FZ_WORKERS;
+                    dst[u] = 0xffffffffu;
+                    if (i < total) {
+                        const int ch = i & 7, xs = (i >> 3) & (nx - 1), r = i >> (3 + lnx);
+                        if (use > 0) mbar_wait(&sm.x_empty[xs], (use - 1) & 1);
+                        v[u] = fz_ldcg16(p.xn + (size_t)(rmul * r + radd) * FZ_D + (kb0 + xs) * 64 + ch * 8);
+                        dst[u] = (uint32_t)xs * xst + (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (dst[u] != 0xffffffffu) *reinterpret_cast<uint4*>(xring + dst[u]) = v[u];
             }
+            fz_fence_async_smem();
+            fz_worker_sync();
+            if (tid < nx) mbar_arrive(&sm.x_full[tid]);
         }
         xq += 16;
-        __syncwarp();
     };
     const int quad = (wid + 2) & 3, hf = wid >> 2;                  // TMEM lane quadrant of this warp, column half
     uint32_t buf = 0;
@@ -272,6 +307,7 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
     // two fp32 accumulator tiles [128 features x ncols] -> P[part][row][256 j + 128 t + feature], row = rmul * col + radd
     auto drain_to_P = [&](int part, int ncols, int rmul, int radd) {
         drain_begin();
+        stamp(3);
 #pragma unroll 1
         for (int t = 0; t < 2; ++t) {
             float* dst = p.P + (size_t)part * rows * FZ_D + 256 * j + 128 * t + quad * 32 + lane;
@@ -302,11 +338,9 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
             x[e] = hi ? bf16_round(bf16_round(x[e] * cs[e]) + bf16_round(xp * sn[e])) : bf16_round(bf16_round(x[e] * cs[e]) - bf16_round(xp * sn[e]));
         }
     };
-    auto cos_sin8 = [&](int r, float* cs, float* sn) {
-        int pos = __ldg(p.rope_pos + r);
-        pos = min(max(pos, 0), p.max_pos - 1);
-        unpack8(__ldg(reinterpret_cast<const uint4*>(p.cos_sin + (size_t)pos * 64 + (c8 & 3) * 8)), cs);
-        unpack8(__ldg(reinterpret_cast<const uint4*>(p.cos_sin + (size_t)pos * 64 + 32 + (c8 & 3) * 8)), sn);
+    auto cos_sin8 = [&](int lr, float* cs, float* sn) {
+        unpack8(meta.cs[lr * 8 + (c8 & 3)], cs);
+        unpack8(meta.cs[lr * 8 + 4 + (c8 & 3)], sn);
     };
     const float kScale = 0.125f * 1.4426950408889634f;              // head_dim^-0.5 * log2(e)
 
@@ -315,10 +349,12 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
         bf16* vl = p.v_pool + (size_t)layer * p.layer_stride;
         // =========================================================== phase A
         exchange(2 * layer);
-        issue_x(tmap_a, (uint32_t)Rph * 128u);
+        build_x(Rh, 2, z);
+        stamp(10);
         // ---- qkv_h: lanes 0..47 of the accumulator = features [48 j, 48 j + 48) of q|k|v of head h, columns = local rows
         //      -> bf16 -> feature-major [192][Rph] in all 4 CTAs
         drain_begin();
+        stamp(11);
         if (quad < 2) {
             const int fl = quad * 32 + lane;
             for (int c0 = hf * 16; c0 < Rh; c0 += 32) {
@@ -343,26 +379,27 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
         }
         drain_end();
         q += 8;
+        stamp(12);
         cluster_sync();                                              // #1: q|k|v of the cluster's rows are in every CTA
-        stamp();
+        stamp(13);
         // ---- attention over the cached tokens: group g = this CTA's 64-token chunks of one row, one warp per group
         for (int g = wid; g < sm.n_groups; g += 8) {
-            const int lr = sm.grp_row[g], r = 2 * lr + z;
-            const int L = __ldg(p.ctx_lens + r);
+            const int lr = sm.grp_row[g];
+            const int L = meta.L[lr];
             const int nch = (L + 63) >> 6, npages = (L + 15) >> 4;
             float qf[8], cs[8], sn[8];
             load8(0, lr, qf);
-            cos_sin8(r, cs, sn);
+            cos_sin8(lr, cs, sn);
             rope8(qf, cs, sn);
 #pragma unroll
             for (int e = 0; e < 8; ++e) qf[e] *= kScale;
             float m = -INFINITY, l = 0.f, acc[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-            uint32_t qq = q + sm.grp_slot0[g];
-            for (int ch = (j - lr) & 3; ch < nch; ch += 4, ++qq) {
-                const uint32_t s = qq % nslot;
-                mbar_wait(&sm.full[s], (qq / nslot) & 1);
+            const uint32_t qq = q + sm.grp_slot0[g];
+            uint32_t s = qq % nslot, sph = (qq / nslot) & 1;
+            for (int ch = (j - lr) & 3; ch < nch; ch += 4) {
+                mbar_wait(&sm.full[s], sph);
                 const unsigned char* sl = ring + (size_t)s * FZ_SLOT;
 #pragma unroll 1
                 for (int half = 0; half < 2; ++half) {
@@ -431,6 +468,7 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
                 }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm.kv_empty[s]);
+                if (++s == (uint32_t)nslot) { s = 0; sph ^= 1; }
             }
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
@@ -447,17 +485,17 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
             }
         }
         q += (uint32_t)sm.n_kv_slots;
+        stamp(14);
         cluster_sync();                                              // #2: every partial sits with its row's owner
-        stamp();
+        stamp(15);
         // ---- owner (local rows lr = j mod 4): merge the <= 4 partials in chunk order, add this step's own token, write
         //      K/V, broadcast attn_h[lr] (bf16) into every CTA's o-projection operand
         for (int lr = j + 4 * wid; lr < Rh; lr += 32) {
-            const int r = 2 * lr + z;
-            const int L = __ldg(p.ctx_lens + r);
+            const int L = meta.L[lr];
             const int nch = (L + 63) >> 6;
             float qf[8], kf[8], vf[8], cs[8], sn[8];
             load8(0, lr, qf); load8(64, lr, kf); load8(128, lr, vf);
-            cos_sin8(r, cs, sn);
+            cos_sin8(lr, cs, sn);
             rope8(qf, cs, sn);
             rope8(kf, cs, sn);
 #pragma unroll
@@ -494,25 +532,28 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
             const uint32_t off = dsm_a + p.off_attnx + (uint32_t)((lr >> 3) * 1024 + (lr & 7) * 128 + ((c8 ^ (lr & 7)) << 4));
             fz_st_cluster16(fz_mapa(off, (uint32_t)t4), ov);       // lane group t4 -> peer t4
             if (t4 == 0) {                                          // reshape_and_cache: this token is number L of row r
-                const int blk = __ldg(p.block_tables + (size_t)r * p.max_blocks + (L >> 4));
+                const int blk = meta.blk_new[lr];
                 const size_t koff = (((size_t)blk * FZ_NH + h) * T3B_KV_BLOCK + (L & 15)) * 64 + c8 * 8;
                 *reinterpret_cast<uint4*>(kl + koff) = pack8(kf);
                 *reinterpret_cast<uint4*>(vl + koff) = pack8(vf);
             }
         }
+        stamp(16);
         fz_fence_async_all();
         cluster_sync();                                              // #3: attn_h of the cluster's rows is in every CTA
         if (tid == 0) { fz_fence_async_all(); mbar_arrive(&sm.attnx_full); }
-        stamp();
+        stamp(17);
         // ---- o_h partial -> P[h][r = 2 lr + z]
         drain_to_P(h, Rh, 2, z);
         q += 2;
         grid_arrive();
         // =========================================================== phase B
         exchange(2 * layer + 1);
-        issue_x(tmap_b, xst);
+        build_x(rows, 1, 0);
+        stamp(20);
         // ---- gate_up: lanes 0..31 gate, 32..63 up of features [128 cl + 32 j, +32) -> fp32 scratch (the X ring is idle now)
         drain_begin();
+        stamp(21);
         float* gu = reinterpret_cast<float*>(xring);                 // [64][Rp]
         if (quad < 2) {
             for (int c0 = hf * 16; c0 < rows; c0 += 32) {
@@ -541,10 +582,11 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
 #pragma unroll
             for (int peer = 0; peer < FZ_CL; ++peer) fz_st_cluster16(fz_mapa(off, (uint32_t)peer), av);
         }
+        stamp(22);
         fz_fence_async_all();
         cluster_sync();                                              // #4: the cluster's 128 act features are in every CTA
         if (tid == 0) { fz_fence_async_all(); mbar_arrive(&sm.actx_full); }
-        stamp();
+        stamp(23);
         // ---- down partial -> P[cl]
         drain_to_P(cl, rows, 1, 0);
         q += 4;
@@ -553,7 +595,7 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
     // =============================================================== final norm + speech head
     exchange(2 * p.n_layers);
     if (b < p.n_head_ctas) {
-        issue_x(tmap_b, xst);
+        build_x(rows, 1, 0);
         drain_begin();
         const int fl = quad * 32 + lane, n = b * FZ_HEAD_ROWS + fl;
         if (quad < 3) {
@@ -570,17 +612,21 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, const CUtens
         }
         drain_end();
     }
-    stamp();
+    stamp(30);
 }
 
 __global__ void __cluster_dims__(FZ_CL, 1, 1) __launch_bounds__(FZ_THREADS, 1)
-decode_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap tmap_a0, const __grid_constant__ CUtensorMap tmap_a1,
-                    const __grid_constant__ CUtensorMap tmap_b) {
+decode_fused_kernel(const FusedParams p) {
     extern __shared__ unsigned char smem_dyn[];
     unsigned char* ring = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
     unsigned char* xring = ring + (size_t)p.nslot * FZ_SLOT;
     unsigned char* dsm = xring + FZ_XBYTES;
     FusedSmem& sm = *reinterpret_cast<FusedSmem*>(dsm + p.dsm_bytes);
+    FusedMeta meta;
+    meta.cs = reinterpret_cast<uint4*>(dsm + p.dsm_bytes + ((sizeof(FusedSmem) + 15) & ~size_t(15)));
+    meta.pages = reinterpret_cast<int32_t*>(meta.cs + (size_t)p.Rh * 8);
+    meta.L = meta.pages + (size_t)p.meta_pages_max * 4;
+    meta.blk_new = meta.L + p.Rh;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int j = (int)fz_cluster_ctarank(), cl = (int)fz_clusterid(), b = cl * FZ_CL + j;
@@ -612,9 +658,32 @@ decode_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap tma
         }
         sm.n_groups = n; sm.n_kv_slots = slots;
     }
-    if (threadIdx.x == 96) { tma_prefetch_desc(z ? &tmap_a1 : &tmap_a0); tma_prefetch_desc(&tmap_b); }
     if (warp == 1) tmem_alloc(&sm.tmem_ptr, 512);
+    // row metadata of this cluster's rows: context length, the block this step's token goes to, cos|sin of its position
+    for (int i = threadIdx.x; i < Rh * 8; i += FZ_THREADS) {
+        const int lr = i >> 3, r = 2 * lr + z;
+        int pos = __ldg(p.rope_pos + r);
+        pos = min(max(pos, 0), p.max_pos - 1);
+        meta.cs[i] = __ldg(reinterpret_cast<const uint4*>(p.cos_sin + (size_t)pos * 64) + (i & 7));
+        if ((i & 7) == 0) {
+            const int L = __ldg(p.ctx_lens + r);
+            meta.L[lr] = L;
+            meta.blk_new[lr] = __ldg(p.block_tables + (size_t)r * p.max_blocks + (L >> 4));
+        }
+    }
     tc_fence_before();
+    __syncthreads();
+    // physical blocks of the 4 pages of every KV slot this CTA streams per layer (ring order)
+    for (int i = threadIdx.x; i < sm.n_groups * 32; i += FZ_THREADS) {       // <= 8 slots (2048 tokens) per group
+        const int g = i >> 5, sl = (i >> 2) & 7, pq = i & 3;
+        const int lr = sm.grp_row[g], r = 2 * lr + z;
+        const int npages = (meta.L[lr] + 15) >> 4, ch0 = (j - lr) & 3;
+        const int nsl = (((npages + 3) >> 2) - ch0 + 3) >> 2;
+        if (sl < nsl) {
+            const int pg = (ch0 + 4 * sl) * 4 + pq;
+            meta.pages[(sm.grp_slot0[g] + sl) * 4 + pq] = pg < npages ? __ldg(p.block_tables + (size_t)r * p.max_blocks + pg) : 0;
+        }
+    }
     __syncthreads();
     tc_fence_after();
     fz_cluster_barrier_all();          // every CTA of the cluster is running and has initialised its barriers
@@ -646,17 +715,18 @@ decode_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap tma
             // ---- past KV of this CTA's chunks: K pages at slot + 2 KB * page, V pages 8 KB further
             const bf16* kl = p.k_pool + (size_t)layer * p.layer_stride;
             const bf16* vl = p.v_pool + (size_t)layer * p.layer_stride;
+            int kvs = 0;
             for (int g = 0; g < sm.n_groups; ++g) {
-                const int lr = sm.grp_row[g], r = 2 * lr + z;
-                const int L = __ldg(p.ctx_lens + r);
+                const int lr = sm.grp_row[g];
+                const int L = meta.L[lr];
                 const int nch = (L + 63) >> 6, npages = (L + 15) >> 4;
-                for (int ch = (j - lr) & 3; ch < nch; ch += 4) {
+                for (int ch = (j - lr) & 3; ch < nch; ch += 4, ++kvs) {
                     const int np = min(4, npages - ch * 4);
                     if (lane == 0) { acquire(1); mbar_expect_tx(&sm.full[s], (uint32_t)np * 4096u); }
                     __syncwarp();
                     const int pg = lane & 3, isv = (lane >> 2) & 1;
                     if (lane < 8 && pg < np) {
-                        const int blk = __ldg(p.block_tables + (size_t)r * p.max_blocks + ch * 4 + pg);
+                        const int blk = meta.pages[kvs * 4 + pg];
                         const bf16* src = (isv ? vl : kl) + ((size_t)blk * FZ_NH + h) * (T3B_KV_BLOCK * 64);
                         bulk_load_1d(ring + (size_t)s * FZ_SLOT + isv * 8192 + pg * 2048, src, 2048, &sm.full[s]);
                     }
@@ -670,58 +740,80 @@ decode_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap tma
         if (b < p.n_head_ctas)
             for (int i = 0; i < 16; ++i) emit_w(p.wh + (size_t)b * FZ_HEAD_CTA_BYTES + i * FZ_HEAD_KB_BYTES, FZ_HEAD_KB_BYTES);
     } else if (warp == 1) {
-        // ================================================================= MMA issuer
-        if (lane == 0) {
+        // ================================================================= MMA issuer (warp-uniform; one elected lane issues)
+        {
             const uint32_t idesc_a = umma_idesc_bf16(128, (uint32_t)p.Rph), idesc_b = umma_idesc_bf16(128, (uint32_t)Rp);
-            uint32_t q = 0, xq = 0, tseq = 0, buf = 0;
+            // ring / X-stage / accumulator cursors kept incrementally (index + phase bit): no divisions on the issue path
+            uint32_t s = 0, sph = 0, xs = 0, xph = 0, tseq = 0, buf = 0;
+            const uint32_t ring_a = smem_u32(ring), x_a = smem_u32(xring);
+            const uint64_t desc0 = umma_smem_desc_sw128(0);
+            auto desc = [&](uint32_t addr) { return desc0 | (uint64_t)((addr & 0x3FFFFu) >> 4); };
+            auto slot_next = [&]() { if (++s == (uint32_t)nslot) { s = 0; sph ^= 1; } };
+            auto x_next = [&]() { if (++xs == (uint32_t)nx) { xs = 0; xph ^= 1; } };
             auto gemm_begin = [&]() {
                 buf = tseq & 1;
                 if (tseq >= 2) mbar_wait(&sm.tmem_empty[buf], ((tseq >> 1) - 1) & 1);
             };
-            auto gemm_end = [&]() { umma_commit(&sm.tmem_full[buf]); ++tseq; };
+            auto commit = [&](uint64_t* bar) { if (fz_elect_one()) umma_commit(bar); __syncwarp(); };
+            auto gemm_end = [&]() { commit(&sm.tmem_full[buf]); ++tseq; };
             auto mma4 = [&](uint32_t d_col, uint32_t a_addr, uint32_t b_addr, uint32_t idesc, bool first) {
-                const uint64_t a_desc = umma_smem_desc_sw128(a_addr), b_desc = umma_smem_desc_sw128(b_addr);
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    umma_bf16(tmem_base + d_col, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (uint32_t)(!first || k != 0));
+                const uint64_t a_desc = desc(a_addr), b_desc = desc(b_addr);
+                const uint32_t d = tmem_base + d_col;
+                if (fz_elect_one()) {
+                    umma_bf16(d, a_desc, b_desc, idesc, first ? 0u : 1u);
+                    umma_bf16(d, a_desc + 2, b_desc + 2, idesc, 1u);
+                    umma_bf16(d, a_desc + 4, b_desc + 4, idesc, 1u);
+                    umma_bf16(d, a_desc + 6, b_desc + 6, idesc, 1u);
+                }
+                __syncwarp();
+            };
+            int mtr = 0;
+            auto mstamp = [&](int id) {
+                if (p.trace != nullptr && lane == 0 && mtr + 2 <= FZ_TRACE) {
+                    unsigned long long* t = p.trace + (size_t)(FZ_NCTA + b) * FZ_TRACE;
+                    t[mtr] = (unsigned long long)id; t[mtr + 1] = fz_gtimer(); mtr += 2;
+                }
             };
             // full-K projection: n_slots ring slots holding kb_per_slot k-blocks of kb_bytes each, B operand from the X ring
             auto gemm_fullk = [&](int n_slots, int kb_per_slot, uint32_t kb_bytes, uint32_t idesc) {
                 gemm_begin();
+                mstamp(40);
                 for (int i = 0; i < n_slots; ++i) {
-                    const uint32_t s = q % nslot;
-                    mbar_wait(&sm.full[s], (q / nslot) & 1);
+                    mbar_wait(&sm.full[s], sph);
+                    if (i == 0) mstamp(41);
+                    if (i == n_slots - 1) mstamp(44);
                     for (int kk = 0; kk < kb_per_slot; ++kk) {
-                        const uint32_t xs = xq % nx;
-                        mbar_wait(&sm.x_full[xs], (xq / nx) & 1);
+                        mbar_wait(&sm.x_full[xs], xph);
+                        if (i == 0 && kk == 0) mstamp(42);
                         tc_fence_after();
-                        mma4(buf * 256, smem_u32(ring + (size_t)s * FZ_SLOT + kk * kb_bytes), smem_u32(xring + (size_t)xs * xst), idesc, i == 0 && kk == 0);
-                        umma_commit(&sm.x_empty[xs]);
-                        ++xq;
+                        mma4(buf * 256, ring_a + s * FZ_SLOT + kk * kb_bytes, x_a + xs * xst, idesc, i == 0 && kk == 0);
+                        commit(&sm.x_empty[xs]);
+                        x_next();
                     }
-                    umma_commit(&sm.w_empty[s]);
-                    ++q;
+                    commit(&sm.w_empty[s]);
+                    slot_next();
                 }
+                mstamp(43);
                 gemm_end();
             };
             // 2 output tiles x kbs k-blocks (one 16 KB ring slot each, tile-major); B tiles [N x 64] sit in the DSMEM region
             auto gemm_tiles = [&](int kbs, uint64_t* ready, uint32_t parity, const unsigned char* bsrc, uint32_t idesc) {
                 gemm_begin();
                 mbar_wait(ready, parity);
+                const uint32_t b_a = smem_u32(bsrc);
                 for (int t = 0; t < 2; ++t)
                     for (int kb = 0; kb < kbs; ++kb) {
-                        const uint32_t s = q % nslot;
-                        mbar_wait(&sm.full[s], (q / nslot) & 1);
+                        mbar_wait(&sm.full[s], sph);
                         tc_fence_after();
-                        mma4(buf * 256 + t * 128, smem_u32(ring + (size_t)s * FZ_SLOT), smem_u32(bsrc + (size_t)kb * xst), idesc, kb == 0);
-                        umma_commit(&sm.w_empty[s]);
-                        ++q;
+                        mma4(buf * 256 + t * 128, ring_a + s * FZ_SLOT, b_a + kb * xst, idesc, kb == 0);
+                        commit(&sm.w_empty[s]);
+                        slot_next();
                     }
                 gemm_end();
             };
             for (int layer = 0; layer < p.n_layers; ++layer) {
                 gemm_fullk(8, 2, FZ_QKV_KB_BYTES, idesc_a);                                     // qkv_h
-                q += (uint32_t)sm.n_kv_slots;
+                for (int n = __shfl_sync(0xffffffffu, sm.n_kv_slots, 0); n > 0; --n) slot_next();   // the KV slots belong to the workers
                 gemm_tiles(1, &sm.attnx_full, layer & 1, dsm + p.off_attnx, idesc_a);           // o_h
                 gemm_fullk(8, 2, 8192, idesc_b);                                                // gate_up
                 gemm_tiles(2, &sm.actx_full, layer & 1, dsm + p.off_actx, idesc_b);             // down
@@ -729,7 +821,7 @@ decode_fused_kernel(const FusedParams p, const __grid_constant__ CUtensorMap tma
             if (b < p.n_head_ctas) gemm_fullk(16, 1, FZ_HEAD_KB_BYTES, idesc_b);                // speech head
         }
     } else {
-        fused_workers(p, z ? &tmap_a1 : &tmap_a0, &tmap_b, sm, ring, xring, dsm, tmem_base);
+        fused_workers(p, sm, meta, ring, xring, dsm, tmem_base);
     }
     tc_fence_before();
     __syncthreads();
@@ -822,7 +914,9 @@ FusedWs fz_carve(const t3b_model_t* m, int rows, void* base) {
     return w;
 }
 unsigned long long* g_fused_trace = nullptr;
+int g_fused_dbg = 0;
 }  // namespace
+extern "C" void t3b_debug_set_fused_flags(int32_t f) { g_fused_dbg = f; }
 
 extern "C" void t3b_debug_set_fused_trace(void* p) { g_fused_trace = static_cast<unsigned long long*>(p); }
 extern "C" int32_t t3b_fused_trace_stride(void) { return FZ_TRACE; }
@@ -895,8 +989,8 @@ extern "C" int32_t t3b_decode_step_fused(const t3b_model_t* m, const void* fused
     p.max_pos = m->max_pos; p.max_blocks = st->max_blocks; p.eps = m->rms_eps;
     p.rows = rows; p.Rp = (rows + 15) & ~15;
     p.Rh = rows / 2; p.Rph = (p.Rh + 15) & ~15;
-    p.nx = FZ_XBYTES / (p.Rp * 128);
-    if (p.nx > 16) p.nx = 16;
+    p.nx = 16;                                           // X stages: a power of two (dividing the 16 k-blocks) that fits 32 KB
+    while (p.nx * p.Rp * 128 > FZ_XBYTES) p.nx >>= 1;
     p.n_head_ctas = (m->speech_vocab + FZ_HEAD_ROWS - 1) / FZ_HEAD_ROWS;
     // DSMEM region: the act operand of the down projection (phase B) aliases the q|k|v / partial / attn buffers (phase A)
     const uint32_t r4 = (uint32_t)(p.Rh + 3) / 4;
@@ -906,7 +1000,12 @@ extern "C" int32_t t3b_decode_step_fused(const t3b_model_t* m, const void* fused
     p.off_attnx = (uint32_t)((p.off_attpart + r4 * FZ_CL * FZ_REC * 4 + 1023) & ~1023u);
     const uint32_t a_bytes = p.off_attnx + (uint32_t)p.Rph * 128u, b_bytes = (uint32_t)p.Rp * 256u;
     p.dsm_bytes = ((a_bytes > b_bytes ? a_bytes : b_bytes) + 1023) & ~1023u;
-    const size_t fixed = 1024 + FZ_XBYTES + p.dsm_bytes + sizeof(FusedSmem) + 64;
+    // per-CTA metadata: cos|sin 128 B + L + block per local row, 4 page ids per KV slot (a row's chunks are dealt over 4 CTAs)
+    const uint32_t max_ch = (uint32_t)(st->max_blocks + 3) / 4;
+    p.meta_pages_max = (uint32_t)p.Rh * ((max_ch + 3) / 4);
+    T3B_CHECK_SHAPE(max_ch <= 32, "t3b_decode_step_fused: max_blocks %d (> 2048 tokens per row) not supported", st->max_blocks);
+    const size_t meta_bytes = (size_t)p.Rh * 128 + (size_t)p.meta_pages_max * 16 + (size_t)p.Rh * 8 + 64;
+    const size_t fixed = 1024 + FZ_XBYTES + p.dsm_bytes + sizeof(FusedSmem) + 64 + meta_bytes;
     p.nslot = (int)((227 * 1024 - fixed) / FZ_SLOT);
     if (p.nslot > FZ_MAX_SLOTS) p.nslot = FZ_MAX_SLOTS;
     T3B_CHECK_SHAPE(p.nslot >= 4, "t3b_decode_step_fused: %d rows leave room for only %d ring slots", rows, p.nslot);
@@ -915,13 +1014,8 @@ extern "C" int32_t t3b_decode_step_fused(const t3b_model_t* m, const void* fused
     p.hidden_out = (bf16*)hidden_out;
     p.counters = (unsigned int*)ws.counters;
     p.trace = g_fused_trace;
+    p.dbg = g_fused_dbg;
 
-    // activation operand tensor maps over xn [rows, 1024]: one per row parity (every other row) and one over all rows
-    CUtensorMap ta0, ta1, tb;
-    T3B_CHECK_ARG(t3b_make_tmap_act(&ta0, p.xn, FZ_D, (uint64_t)p.Rh, 2 * FZ_D, (uint32_t)p.Rph) == 0 &&
-                  t3b_make_tmap_act(&ta1, p.xn + FZ_D, FZ_D, (uint64_t)p.Rh, 2 * FZ_D, (uint32_t)p.Rph) == 0 &&
-                  t3b_make_tmap_act(&tb, p.xn, FZ_D, (uint64_t)rows, FZ_D, (uint32_t)p.Rp) == 0,
-                  "t3b_decode_step_fused: cuTensorMapEncodeTiled failed");
     const size_t smem = (size_t)p.nslot * FZ_SLOT + fixed;
     T3B_CUDA(cudaFuncSetAttribute(decode_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     T3B_CUDA(cudaMemsetAsync(ws.counters, 0, 256, s));
@@ -933,7 +1027,7 @@ extern "C" int32_t t3b_decode_step_fused(const t3b_model_t* m, const void* fused
     cfg.attrs = attr; cfg.numAttrs = 1;
     static int coop = -1;                                // cooperative + cluster launch: fall back to a plain launch if refused
     if (coop != 0) {
-        cudaError_t e = cudaLaunchKernelEx(&cfg, decode_fused_kernel, p, ta0, ta1, tb);
+        cudaError_t e = cudaLaunchKernelEx(&cfg, decode_fused_kernel, p);
         if (e == cudaSuccess) { coop = 1; return T3B_OK; }
         if (coop == 1) T3B_FAIL(T3B_ERR_CUDA, "t3b_decode_step_fused: launch failed: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
@@ -943,6 +1037,6 @@ extern "C" int32_t t3b_decode_step_fused(const t3b_model_t* m, const void* fused
     int ncl = 0;
     T3B_CUDA(cudaOccupancyMaxActiveClusters(&ncl, decode_fused_kernel, &cfg));
     T3B_CHECK_ARG(ncl >= FZ_NCL, "t3b_decode_step_fused: only %d of %d clusters can be co-resident", ncl, FZ_NCL);
-    T3B_CUDA(cudaLaunchKernelEx(&cfg, decode_fused_kernel, p, ta0, ta1, tb));
+    T3B_CUDA(cudaLaunchKernelEx(&cfg, decode_fused_kernel, p));
     return T3B_OK;
 }

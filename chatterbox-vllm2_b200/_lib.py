@@ -17,7 +17,7 @@ T3B_OK = 0
 T3B_W_BF16, T3B_W_AWQ = 0, 1
 T3B_IMPL_AUTO, T3B_IMPL_GEMV, T3B_IMPL_UMMA = 0, 1, 2
 T3B_COMBINE_BF16, T3B_COMBINE_FP32 = 0, 1
-T3B_EPI_NONE, T3B_EPI_SILU_MUL = 0, 1
+T3B_EPI_NONE, T3B_EPI_SILU_MUL, T3B_EPI_RESIDUAL = 0, 1, 2
 T3B_LIN_GATE_UP_INTERLEAVED = 1
 ERR_NAMES = {-1: "T3B_ERR_ARG", -2: "T3B_ERR_SHAPE", -3: "T3B_ERR_ALIGN", -4: "T3B_ERR_CUDA", -5: "T3B_ERR_UNSUPPORTED"}
 
@@ -36,6 +36,11 @@ p_i32 = C.POINTER(C.c_int32)
 
 class Linear(C.Structure):          # t3b_linear_t
     _fields_ = [("kind", i32), ("n", i32), ("k", i32), ("w", vp), ("scales", vp), ("zeros", vp), ("flags", i32)]
+
+
+class LinearFuse(C.Structure):      # t3b_linear_fuse_t
+    _fields_ = [("x_z", vp), ("x_ss", vp), ("x_ss_tiles", i32), ("norm_w", vp), ("eps", f32), ("res_z", vp), ("out_z", vp),
+                ("out_ss", vp)]
 
 
 class Layer(C.Structure):           # t3b_layer_t
@@ -81,6 +86,9 @@ _PROTOS = {
     "t3b_add_rmsnorm": (i32, [vp, vp, i32, vp, vp, vp, i32, i32, f32, i32, vp]),
     "t3b_linear_bf16": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, vp]),
     "t3b_linear_awq": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, vp]),
+    "t3b_linear_fused": (i32, [vp, C.POINTER(Linear), i32, vp, C.POINTER(LinearFuse), i32, i32, vp]),
+    "t3b_z_init": (i32, [vp, i32, i32, vp, vp, vp]),
+    "t3b_z_rmsnorm": (i32, [vp, vp, vp, i32, i32, f32, vp, vp]),
     "t3b_repack_weights_awq": (i32, [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp]),
     "t3b_attn_decode_fused": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, vp, vp, i32, vp, vp]),
     "t3b_rope_kv_write": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, i32, vp, vp, i32, vp, vp]),

@@ -1,6 +1,7 @@
 // Library plumbing + the whole-step entry points (t3b_decode_step, t3b_head_cfg_sample).
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "t3b_common.cuh"
@@ -8,7 +9,7 @@
 // implemented in the kernel translation units
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s);
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, cudaStream_t s);
+                               int n_split, int epi, cudaStream_t s, const t3b_linear_fuse_t* fz);
 int t3b_umma_pick_split(int rows, int N, int K);
 int t3b_umma_pick_split_partials(int rows, int N, int K);
 int t3b_umma_available();
@@ -56,7 +57,7 @@ namespace {
 inline size_t al(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct Workspace {
-    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head;
+    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *z, *zss;
     size_t total;
 };
 
@@ -74,6 +75,8 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
     w.act = take(R * F * 2);
     w.lin = take(R * D * 2);
     w.head = take(R * V * 2 + 64);
+    w.z = take(R * D * 4);                       // fp32 residual stream of the fused-norm decode layers
+    w.zss = take((D / 128) * R * 4);
     w.total = static_cast<size_t>(p - static_cast<char*>(base));
     return w;
 }
@@ -110,7 +113,23 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     if (n_split <= 0) n_split = t3b_umma_pick_split(rows, w->n, w->k);
     if (!legacy && y == nullptr) T3B_FAIL(T3B_ERR_ARG, "linear: y is null (partials are only written for an explicit n_split > 1)");
     if (n_split_out) *n_split_out = n_split;
-    return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, legacy ? partials : nullptr, n_split, epi, s);
+    return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, legacy ? partials : nullptr, n_split, epi, s, nullptr);
+}
+
+extern "C" int32_t t3b_linear_fused(const void* x, const t3b_linear_t* w, int32_t rows, void* y, const t3b_linear_fuse_t* f, int32_t n_split,
+                                    int32_t epilogue, void* stream) {
+    T3B_CHECK_ARG(w && w->w && (w->kind == T3B_W_BF16 || w->kind == T3B_W_AWQ), "t3b_linear_fused: bad weights");
+    T3B_CHECK_ARG(rows >= 0 && w->n > 0 && w->k > 0, "t3b_linear_fused: bad sizes rows=%d n=%d k=%d", rows, w->n, w->k);
+    T3B_CHECK_ARG(epilogue >= T3B_EPI_NONE && epilogue <= T3B_EPI_RESIDUAL, "t3b_linear_fused: unknown epilogue %d", epilogue);
+    T3B_CHECK_ARG(x || (f && f->x_z), "t3b_linear_fused: no input (x and f->x_z are null)");
+    if (x) T3B_CHECK_ALIGN(x);
+    if (y) T3B_CHECK_ALIGN(y);
+    if (f && f->x_z) { T3B_CHECK_ALIGN(f->x_z); T3B_CHECK_ALIGN(f->norm_w); }
+    if (rows == 0) return T3B_OK;
+    const bool awq = w->kind == T3B_W_AWQ;
+    if (awq) T3B_CHECK_ARG(w->scales && w->zeros, "t3b_linear_fused: scales / zeros are null");
+    if (n_split <= 0) n_split = t3b_umma_pick_split(rows, w->n, w->k);
+    return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, nullptr, n_split, epilogue, t3b_stream(stream), f);
 }
 
 extern "C" int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
@@ -129,6 +148,8 @@ extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t 
 }
 
 // ------------------------------------------------------------------ whole step
+static int g_fuse_norm = -1;        // -1: from the environment (T3B_FUSE_NORM, default on)
+extern "C" void t3b_debug_set_fuse_norm(int v) { g_fuse_norm = v; }
 static int32_t check_model(const t3b_model_t* m) {
     T3B_CHECK_ARG(m && m->layers && m->final_norm && m->speech_emb && m->speech_pos_emb && m->rope_cos_sin && m->head.w,
                   "model: null pointer");
@@ -156,6 +177,36 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     auto lin = [&](const void* x, const t3b_linear_t* w, void* y, int epi) -> int32_t {
         return linear_any(x, w, n_tok, y, nullptr, prefill ? 1 : 0, nullptr, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, epi, s);
     };
+    // Decode steps on the tcgen05 path (rows > 4): F2.1 lives inside the projections (t3b_linear_fused) - 5 launches per
+    // layer: qkv (norm fused into the operand build), attention, o (+ residual), gate_up (norm, SiLU*mul), down (+ residual).
+    if (g_fuse_norm < 0) { const char* e = getenv("T3B_FUSE_NORM"); g_fuse_norm = (e && e[0] == '0') ? 0 : 1; }
+    if (!prefill && n_tok > 4 && g_fuse_norm) {
+        float* z = reinterpret_cast<float*>(ws.z);
+        float* zss = reinterpret_cast<float*>(ws.zss);
+        rc = t3b_z_init(x0, n_tok, D, z, zss, stream);
+        if (rc) return rc;
+        for (int li = 0; li < m->n_layers; ++li) {
+            const t3b_layer_t* L = &m->layers[li];
+            T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
+            t3b_linear_fuse_t fin = {z, zss, D / 128, L->ln1, m->rms_eps, nullptr, nullptr, nullptr};
+            t3b_linear_fuse_t fout = {nullptr, nullptr, 0, nullptr, 0.f, z, z, zss};
+            rc = t3b_linear_fused(nullptr, &L->qkv, n_tok, ws.qkv, &fin, 0, T3B_EPI_NONE, stream);
+            if (rc) return rc;
+            bf16* kp = static_cast<bf16*>(kv->k) + (size_t)li * kv->layer_stride;
+            bf16* vp = static_cast<bf16*>(kv->v) + (size_t)li * kv->layer_stride;
+            rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kp, vp, H,
+                                       ws.attn, s);
+            if (rc) return rc;
+            rc = t3b_linear_fused(ws.attn, &L->o, n_tok, nullptr, &fout, 0, T3B_EPI_RESIDUAL, stream);
+            if (rc) return rc;
+            fin.norm_w = L->ln2;
+            rc = t3b_linear_fused(nullptr, &L->gate_up, n_tok, ws.act, &fin, 0, T3B_EPI_SILU_MUL, stream);
+            if (rc) return rc;
+            rc = t3b_linear_fused(ws.act, &L->down, n_tok, nullptr, &fout, 0, T3B_EPI_RESIDUAL, stream);
+            if (rc) return rc;
+        }
+        return t3b_z_rmsnorm(z, zss, m->final_norm, n_tok, D, m->rms_eps, hidden_out, stream);
+    }
     const void* prev = x0;
     for (int li = 0; li < m->n_layers; ++li) {
         const t3b_layer_t* L = &m->layers[li];

@@ -26,8 +26,9 @@ __device__ __forceinline__ uint4 ldg_kv(const void* p) {
 }
 
 // FUSED: q points at the QKV projection output bf16 [n_tok, 3*hidden]; k_pool / v_pool are written.
-template <bool FUSED>
-__global__ void __launch_bounds__(256) paged_attn_decode_kernel(const bf16* __restrict__ q, const int32_t* __restrict__ tok_row,
+// NW = warps per CTA; the min-blocks bound trims registers so that 64 rows x 16 heads (4 warps) is ONE wave of 7 CTAs per SM.
+template <bool FUSED, int NW>
+__global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) paged_attn_decode_kernel(const bf16* __restrict__ q, const int32_t* __restrict__ tok_row,
                                                                 const int32_t* __restrict__ tok_idx,
                                                                 const int32_t* __restrict__ block_tables, int max_blocks,
                                                                 bf16* k_pool, bf16* v_pool, int n_heads, bf16* __restrict__ out,
@@ -35,11 +36,23 @@ __global__ void __launch_bounds__(256) paged_attn_decode_kernel(const bf16* __re
                                                                 int max_pos) {
     __shared__ float sm_m[8], sm_l[8];
     __shared__ float sm_acc[8][64];
-    pdl_wait();
-    pdl_launch_dependents();
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     const int t = blockIdx.x / n_heads, h = blockIdx.x - t * n_heads;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = NW;
     const int t4 = lane >> 3, c = lane & 7;
+    if (FUSED) {
+        // Before the dependency wait: pull this (row, head)'s cached K/V lines from HBM into L2 while the QKV projection is
+        // still running.  Hint only - the context length may be one step stale and nothing read here is used for arithmetic
+        // (block-table entries are always valid block indices, so every prefetched address lies inside the pool).
+        const int np = min((tok_idx[t] + 16) >> 4, max_blocks);
+        const int32_t* btp = block_tables + (size_t)t * max_blocks;
+        for (int i = threadIdx.x; i < np * 32; i += NW * 32) {
+            const int page = i >> 5, w = i & 31;
+            const bf16* line = (w < 16 ? k_pool : v_pool) + (((size_t)btp[page] * n_heads + h) * T3B_KV_BLOCK) * 64 + (w & 15) * 64;
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(line));
+        }
+    }
+    pdl_wait();
     const int row = tok_row ? tok_row[t] : t;
     const int ctx = tok_idx[t] + 1;                      // keys 0..tok_idx[t] (own token is written first)
     const int n_pages = (ctx + 15) >> 4;
@@ -185,7 +198,9 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
         else if (units >= (long)sms * 4) nw = 4;
     }
     (void)sms;
-    T3B_CUDA(t3b_launch(paged_attn_decode_kernel<false>, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)q, tok_row, tok_idx,
+    T3B_CHECK_ARG(nw == 2 || nw == 4 || nw == 8, "paged attention: warps %d must be 2, 4 or 8", nw);
+    auto kern = nw == 2 ? paged_attn_decode_kernel<false, 2> : (nw == 4 ? paged_attn_decode_kernel<false, 4> : paged_attn_decode_kernel<false, 8>);
+    T3B_CUDA(t3b_launch(kern, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)q, tok_row, tok_idx,
                         block_tables, max_blocks, (bf16*)const_cast<void*>(k_pool), (bf16*)const_cast<void*>(v_pool), n_heads, (bf16*)out,
                         (const int32_t*)nullptr, (const bf16*)nullptr, 0));
     return T3B_OK;
@@ -202,7 +217,9 @@ static int pick_warps(long units) {
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
                               const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, void* out, cudaStream_t s) {
     const long units = (long)n_tok * n_heads;
-    T3B_CUDA(t3b_launch(paged_attn_decode_kernel<true>, dim3((unsigned)units), dim3(pick_warps(units) * 32), 0, s, (const bf16*)qkv,
+    const int nw = pick_warps(units);
+    auto kern = nw == 2 ? paged_attn_decode_kernel<true, 2> : (nw == 4 ? paged_attn_decode_kernel<true, 4> : paged_attn_decode_kernel<true, 8>);
+    T3B_CUDA(t3b_launch(kern, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)qkv,
                         (const int32_t*)nullptr, tok_idx, block_tables, max_blocks, (bf16*)k_pool, (bf16*)v_pool, n_heads, (bf16*)out, rope_pos,
                         (const bf16*)rope_cos_sin, max_pos));
     return T3B_OK;

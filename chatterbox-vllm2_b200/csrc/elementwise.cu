@@ -8,8 +8,8 @@
 __global__ void __launch_bounds__(128) embed_gather_kernel(const uint4* __restrict__ emb, const uint4* __restrict__ pos_emb,
                                                            const int32_t* __restrict__ tokens, const int32_t* __restrict__ speech_pos,
                                                            int hidden8, int emb_rows, int pos_rows, int dup, uint4* __restrict__ out) {
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     pdl_wait();
-    pdl_launch_dependents();
     const int b = blockIdx.x;
     int tok = tokens[b];
     tok = min(max(tok, 0), emb_rows - 1);
@@ -35,8 +35,8 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
                                                           uint4* __restrict__ residual, const uint4* __restrict__ weight,
                                                           uint4* __restrict__ y, int hidden8, float eps, int has_residual) {
     __shared__ float red[4];
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     pdl_wait();
-    pdl_launch_dependents();
     const int row = blockIdx.x;
     float s[MAX_CHUNKS][8];
     float ss = 0.f;
@@ -88,6 +88,50 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
     }
 }
 
+// ------------------------------------------------------------------ fp32 residual stream of a decode step
+// (t3b_linear_fused keeps F2.1 inside the projections; these two kernels open and close the stream)
+// z[row] = float(x[row]), ss[tile][row] = sum of squares of features [128 tile, 128 tile + 128).  One CTA per row.
+__global__ void __launch_bounds__(128) z_init_kernel(const uint4* __restrict__ x, float4* __restrict__ z, float* __restrict__ ss,
+                                                     int hidden8, int rows) {
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
+    pdl_wait();
+    const int row = blockIdx.x;
+    for (int i = threadIdx.x; i < hidden8; i += 128) {            // hidden8 % 16 == 0: a 16-lane group never straddles a tile
+        float v[8];
+        unpack8(x[(size_t)row * hidden8 + i], v);
+        z[((size_t)row * hidden8 + i) * 2] = make_float4(v[0], v[1], v[2], v[3]);
+        z[((size_t)row * hidden8 + i) * 2 + 1] = make_float4(v[4], v[5], v[6], v[7]);
+        float q = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) q += v[e] * v[e];
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
+        if ((threadIdx.x & 15) == 0) ss[(size_t)(i >> 4) * rows + row] = q;
+    }
+}
+
+// y = bf16(bf16(z * rstd) * w), rstd from the per-tile sums (fixed order).  One CTA per row.
+__global__ void __launch_bounds__(128) z_rmsnorm_kernel(const float4* __restrict__ z, const float* __restrict__ ss,
+                                                        const uint4* __restrict__ weight, uint4* __restrict__ y, int hidden8, int rows,
+                                                        float eps) {
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
+    pdl_wait();
+    const int row = blockIdx.x;
+    float tot = 0.f;
+    for (int t = 0; t < hidden8 / 16; ++t) tot += ss[(size_t)t * rows + row];
+    const float rstd = rsqrtf(tot / (float)(hidden8 * 8) + eps);
+    for (int i = threadIdx.x; i < hidden8; i += 128) {
+        const float4 a = z[((size_t)row * hidden8 + i) * 2], b = z[((size_t)row * hidden8 + i) * 2 + 1];
+        float w[8], o[8];
+        unpack8(weight[i], w);
+        o[0] = bf16_round(a.x * rstd) * w[0]; o[1] = bf16_round(a.y * rstd) * w[1];
+        o[2] = bf16_round(a.z * rstd) * w[2]; o[3] = bf16_round(a.w * rstd) * w[3];
+        o[4] = bf16_round(b.x * rstd) * w[4]; o[5] = bf16_round(b.y * rstd) * w[5];
+        o[6] = bf16_round(b.z * rstd) * w[6]; o[7] = bf16_round(b.w * rstd) * w[7];
+        y[(size_t)row * hidden8 + i] = pack8(o);
+    }
+}
+
 // ------------------------------------------------------------------ F2.3 + KV write
 // One CTA per token, one warp per head: lane j rotates the pair (j, j+32) of q and k
 // (rotary_embedding/common.py:144-174 in bf16 tensor arithmetic: each product and the sum round).
@@ -98,8 +142,8 @@ __global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restri
                                                             const int32_t* __restrict__ block_tables, int max_blocks,
                                                             bf16* __restrict__ k_pool, bf16* __restrict__ v_pool, int n_heads,
                                                             bf16* __restrict__ q_out) {
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     pdl_wait();
-    pdl_launch_dependents();
     const int t = blockIdx.x;
     const int lane = threadIdx.x & 31;
     const int hidden = n_heads * 64;
@@ -147,8 +191,8 @@ __global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restri
 // activation.py:138-141: F.silu(gate) * up on bf16 tensors -> two roundings.
 __global__ void __launch_bounds__(256) silu_mul_kernel(const uint4* __restrict__ gu, const float4* __restrict__ partials, int n_split,
                                                        size_t split_stride4, int ffn8, uint4* __restrict__ act, int total) {
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     pdl_wait();
-    pdl_launch_dependents();
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int row = i / ffn8, c = i - row * ffn8;
         float g[8], u[8];
@@ -241,5 +285,25 @@ extern "C" int32_t t3b_silu_mul(const void* gate_up, const float* partials, int3
     if (blocks > cap) blocks = cap;
     T3B_CUDA(t3b_launch(silu_mul_kernel, dim3(blocks), dim3(256), 0, t3b_stream(stream), (const uint4*)gate_up, (const float4*)partials,
                         n_split, (size_t)rows * 2 * ffn / 4, ffn / 8, (uint4*)act, total));
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_z_init(const void* x, int32_t rows, int32_t hidden, float* z, float* ss, void* stream) {
+    T3B_CHECK_ARG(x && z && ss && rows >= 0, "t3b_z_init: null pointer");
+    T3B_CHECK_SHAPE(hidden > 0 && hidden % 128 == 0, "t3b_z_init: hidden %d not a multiple of 128", hidden);
+    T3B_CHECK_ALIGN(x); T3B_CHECK_ALIGN(z);
+    if (rows == 0) return T3B_OK;
+    T3B_CUDA(t3b_launch(z_init_kernel, dim3(rows), dim3(128), 0, t3b_stream(stream), (const uint4*)x, (float4*)z, ss, hidden / 8, rows));
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_z_rmsnorm(const float* z, const float* ss, const void* weight, int32_t rows, int32_t hidden, float eps, void* y,
+                                 void* stream) {
+    T3B_CHECK_ARG(z && ss && weight && y && rows >= 0, "t3b_z_rmsnorm: null pointer");
+    T3B_CHECK_SHAPE(hidden > 0 && hidden % 128 == 0, "t3b_z_rmsnorm: hidden %d not a multiple of 128", hidden);
+    T3B_CHECK_ALIGN(z); T3B_CHECK_ALIGN(weight); T3B_CHECK_ALIGN(y);
+    if (rows == 0) return T3B_OK;
+    T3B_CUDA(t3b_launch(z_rmsnorm_kernel, dim3(rows), dim3(128), 0, t3b_stream(stream), (const float4*)z, ss, (const uint4*)weight, (uint4*)y,
+                        hidden / 8, rows, eps));
     return T3B_OK;
 }

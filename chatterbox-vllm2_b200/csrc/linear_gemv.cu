@@ -15,6 +15,7 @@ template <int R, int FPW, int KSTEP, int MODE>
 __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, int rows, int N, int K,
                                                           bf16* __restrict__ y) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     uint4* xs = reinterpret_cast<uint4*>(smem_raw);                 // [R][K/8]
     constexpr int NW = (MODE == 1) ? 2 * FPW : FPW;                 // weight rows per warp
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -38,7 +39,6 @@ __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict
             for (int c = 0; c < KSTEP; ++c) wv[f][c] = ldg_stream(wrow[f] + c * 32 + lane);
     }
     pdl_wait();
-    pdl_launch_dependents();
     for (int i = threadIdx.x; i < R * K8; i += 256) {
         const int r = i / K8;
         xs[i] = r < rows ? reinterpret_cast<const uint4*>(x)[i] : make_uint4(0, 0, 0, 0);

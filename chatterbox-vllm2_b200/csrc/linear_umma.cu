@@ -45,7 +45,7 @@
 #define UM_RAW_BYTES 4096                  // AWQ: 128 x 64 nibbles
 #define UM_MAX_STAGES 8
 
-enum { EPI_STORE = 0, EPI_SILU = 1 };
+enum { EPI_STORE = 0, EPI_SILU = 1, EPI_RESID = 2 };
 
 struct UmmaParams {
     bf16* y;                 // bf16 [rows, N] (STORE) or [rows, N/2] (SILU); NULL in legacy mode
@@ -58,6 +58,18 @@ struct UmmaParams {
     const bf16* scales;      // bf16 [K/128, N]
     const unsigned char* zeros;   // u8 [K/128, N]
     long long* trace;        // debug: 16 clock64 stamps per CTA (NULL = off)
+    // F2.1 folded into the projections (decode layers, t3b_linear_fused):
+    //   zx != NULL: the activation operand is built in-kernel from the fp32 residual stream,
+    //               X[r, k] = bf16(bf16(zx[r, k] * rstd_r) * norm_w[k]),  rstd_r = rsqrt(sum_t zx_ss[t][r] / K + eps)
+    //   EPI_RESID:  z_out[r, n] = bf16(acc) + bf16(z_res[r, n]) (fp32; in place allowed), ss_out[tile][r] = sum_n z_out^2
+    const float* zx;
+    const float* zx_ss;
+    const bf16* norm_w;
+    int zx_tiles;
+    float eps;
+    const float* z_res;
+    float* z_out;
+    float* ss_out;
 };
 
 static long long* g_umma_trace = nullptr;
@@ -107,8 +119,10 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     uint64_t* raw_bar = empty_bar + UM_MAX_STAGES;
     uint64_t* tmem_full_bar = raw_bar + UM_MAX_STAGES;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+    float* s_aux = reinterpret_cast<float*>(tmem_ptr + 2);       // [256]: rstd per row (X build), then [64][4] warp sums (EPI_RESID)
     float* red = reinterpret_cast<float*>(smem + ring_bytes);
 
+    pdl_launch_dependents();                     // the next kernel's launch latency overlaps this whole kernel (it waits before reading)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tile = blockIdx.x, split = blockIdx.y, rchunk = blockIdx.z;
     const int kb_begin = (int)(((long)split * p.kb_total) / p.n_split);
@@ -120,9 +134,9 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     if (threadIdx.x == 0) {
         TRACE(0);
         if (!WSRC) tma_prefetch_desc(&tmap_w);
-        tma_prefetch_desc(&tmap_x);
+        if (!p.zx) tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < stages; ++i) {
-            mbar_init(&full_bar[i], WSRC ? 1 + 8 : 1);      // producer (tx) [+ 8 dequant warps]
+            mbar_init(&full_bar[i], (WSRC ? 1 + 8 : 1) + (p.zx ? 4 : 0));      // producer (tx) [+ 8 dequant warps] [+ 4 X-build warps]
             mbar_init(&empty_bar[i], 1);
             mbar_init(&raw_bar[i], 1);
         }
@@ -134,7 +148,9 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    pdl_launch_dependents();
+    float zr[8];                                 // EPI_RESID: prefetched residual values (rows owned after the cluster reduce)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) zr[j] = 0.f;
     if (threadIdx.x == 0) TRACE(1);
 
     auto load_w = [&](int i, int s) {
@@ -147,7 +163,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
             tma_load_2d(st + UM_A_BYTES / 2, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_b);
         }
     };
-    const uint32_t tx = WSRC ? x_bytes : stage_bytes;
+    const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + (p.zx ? 0u : x_bytes);
     const int pre = nkb < stages ? nkb : stages;
     // The first ring of weight tiles goes out before anything else: weights never depend on the previous kernel.
     if (threadIdx.x == 0) {
@@ -164,14 +180,16 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         if (lane == 0) {
             pdl_wait();
             TRACE(2);
-            for (int i = 0; i < pre; ++i)
-                tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
+            if (!p.zx)
+                for (int i = 0; i < pre; ++i)
+                    tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             for (int i = pre; i < nkb; ++i) {
                 const int s = i % stages, round = i / stages;
                 mbar_wait(&empty_bar[s], (round & 1) ^ 1);
                 mbar_expect_tx(&full_bar[s], tx);
                 load_w(i, s);
-                tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
+                if (!p.zx)
+                    tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             }
         }
     } else if (warp == 1) {
@@ -235,6 +253,87 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         const int f = quad * 32 + lane;          // feature row of the tile this thread reads from TMEM
         const int r0 = rchunk * p.row_chunk;
         const int valid = min(Rp, p.rows - r0);  // rows of this chunk that exist
+        if (p.epi == EPI_RESID && p.n_split > 1 && (Rp / p.n_split) <= 8) {
+            // residual values this thread adds after the split-K reduce: fetched now, off the critical path
+            const int per = Rp / p.n_split;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int r = r0 + j * p.n_split + split;
+                zr[j] = (j < per && r < p.rows) ? __ldcg(p.z_res + (size_t)r * p.N + tile * UM_M + (threadIdx.x - 128)) : 0.f;
+            }
+        }
+        if (p.zx != nullptr) {
+            // F2.1 (layernorm.py:40-59) folded into the operand build: these 4 warps turn the fp32 residual stream into the
+            // normalised bf16 B tile of every k-block ([Rp rows] x 128 B, SWIZZLE_128B: 16 B chunk c of row r at c ^ (r & 7)).
+            // Batches of 512 (row, chunk) items, the loads of batch b + 1 in flight while batch b is normalised and stored.
+            const int t = threadIdx.x - 128, K = p.kb_total * UM_K;
+            const int items = Rp * 8, bpk = (items + 511) >> 9, nb = nkb * bpk;
+            const int ch = t & 7;                                         // the 16 B chunk (8 k) of every item of this thread
+            auto load_batch = [&](int b, float4* za, float4* zb, uint4& wv) {
+                const int i = b / bpk, it0 = (b - i * bpk) * 512 + t, k0 = (kb_begin + i) * UM_K;
+                wv = __ldg(reinterpret_cast<const uint4*>(p.norm_w + k0 + ch * 8));
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int r = (it0 + u * 128) >> 3;
+                    if (r < valid) {
+                        const float4* src = reinterpret_cast<const float4*>(p.zx + (size_t)(r0 + r) * K + k0 + ch * 8);
+                        za[u] = __ldcg(src); zb[u] = __ldcg(src + 1);
+                    } else {
+                        za[u] = make_float4(0.f, 0.f, 0.f, 0.f); zb[u] = za[u];
+                    }
+                }
+            };
+            auto store_batch = [&](int b, const float4* za, const float4* zb, const uint4& wv) {
+                const int i = b / bpk, bi = b - i * bpk, it0 = bi * 512 + t;
+                const int s = i % stages, round = i / stages;
+                if (bi == 0 && i >= stages) mbar_wait(&empty_bar[s], (round & 1) ^ 1);
+                unsigned char* xs = smem + (size_t)s * stage_bytes + UM_A_BYTES;
+                float w[8];
+                unpack8(wv, w);
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int r = (it0 + u * 128) >> 3;
+                    if (r < Rp) {
+                        const float rs = s_aux[r];
+                        float o[8];
+                        o[0] = bf16_round(za[u].x * rs) * w[0]; o[1] = bf16_round(za[u].y * rs) * w[1];
+                        o[2] = bf16_round(za[u].z * rs) * w[2]; o[3] = bf16_round(za[u].w * rs) * w[3];
+                        o[4] = bf16_round(zb[u].x * rs) * w[4]; o[5] = bf16_round(zb[u].y * rs) * w[5];
+                        o[6] = bf16_round(zb[u].z * rs) * w[6]; o[7] = bf16_round(zb[u].w * rs) * w[7];
+                        *reinterpret_cast<uint4*>(xs + r * 128 + ((ch ^ (r & 7)) << 4)) = pack8(o);
+                    }
+                }
+                if (bi == bpk - 1) {
+                    fence_proxy_async_smem();                             // generic-proxy writes -> visible to the MMA (async proxy)
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&full_bar[s]);
+                }
+            };
+            float4 a0[4], b0[4], a1[4], b1[4];
+            uint4 w0, w1;
+            load_batch(0, a0, b0, w0);
+            for (int r = t; r < Rp; r += 128) {                           // rstd of row r: per-tile sums in fixed order
+                float ss = 0.f;
+                if (r < valid) {
+                    for (int i0 = 0; i0 < p.zx_tiles; i0 += 8) {
+                        float v[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) v[u] = i0 + u < p.zx_tiles ? __ldcg(p.zx_ss + (size_t)(i0 + u) * p.rows + r0 + r) : 0.f;
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) ss += v[u];
+                    }
+                }
+                s_aux[r] = r < valid ? rsqrtf(ss / (float)K + p.eps) : 0.f;
+            }
+            named_bar_sync(1, 128);
+            for (int b = 0; b < nb; b += 2) {
+                if (b + 1 < nb) load_batch(b + 1, a1, b1, w1);
+                store_batch(b, a0, b0, w0);
+                if (b + 2 < nb) load_batch(b + 2, a0, b0, w0);
+                if (b + 1 < nb) store_batch(b + 1, a1, b1, w1);
+            }
+            named_bar_sync(1, 128);                                       // s_aux is reused by the EPI_RESID epilogue
+        }
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         if (threadIdx.x == 128) TRACE(5);
@@ -290,6 +389,22 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                         for (int j = 0; j < 16; ++j)
                             if (c0 + j < valid) p.y[(size_t)(r0 + c0 + j) * p.N + n] = __float2bfloat16_rn(red[j * UM_M + t]);
                     }
+                } else if (p.epi == EPI_RESID) {
+                    const int n = tile * UM_M + t;               // N % 128 == 0 (checked at launch)
+#pragma unroll 4
+                    for (int j = 0; j < 16; ++j) {
+                        float z = 0.f;
+                        if (c0 + j < valid) {
+                            const size_t o = (size_t)(r0 + c0 + j) * p.N + n;
+                            z = bf16_round(red[j * UM_M + t]) + bf16_round(__ldcg(p.z_res + o));
+                            p.z_out[o] = z;
+                        }
+                        const float sq = warp_sum(z * z);
+                        if (lane == 0) s_aux[j * 4 + quad] = sq;
+                    }
+                    named_bar_sync(1, 128);
+                    if (t < 16 && c0 + t < valid)
+                        p.ss_out[(size_t)tile * p.rows + r0 + c0 + t] = (s_aux[t * 4] + s_aux[t * 4 + 1]) + (s_aux[t * 4 + 2] + s_aux[t * 4 + 3]);
                 } else {
                     const int pi = t & 63, sub = t >> 6, ffn = p.N / 2;
 #pragma unroll 4
@@ -321,6 +436,37 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     float acc = 0.f;
                     for (int c = 0; c < p.n_split; ++c) acc += red[(c * per + j) * UM_M + t];      // fixed order -> deterministic
                     if (n < p.N) p.y[(size_t)r * p.N + n] = __float2bfloat16_rn(acc);
+                }
+            } else if (p.epi == EPI_RESID) {
+                // residual add of llama.py:316-333 in the GEMM epilogue: the fp32 stream z keeps the unrounded sum the
+                // reference's fused_add_rms_norm normalises; the next residual add reads it back as bf16(z)
+                const int n = tile * UM_M + t, quad = warp & 3;
+                auto fold = [&](int j, int r, float res) {
+                    float acc = 0.f;
+                    for (int c = 0; c < p.n_split; ++c) acc += red[(c * per + j) * UM_M + t];      // fixed order -> deterministic
+                    const float z = bf16_round(acc) + bf16_round(res);
+                    p.z_out[(size_t)r * p.N + n] = z;
+                    const float sq = warp_sum(z * z);
+                    if (lane == 0) s_aux[j * 4 + quad] = sq;
+                };
+                if (per <= 8) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int r = r0 + j * p.n_split + split;
+                        if (j < per && r < p.rows) fold(j, r, zr[j]);                              // uniform over the CTA
+                    }
+                } else {
+#pragma unroll 4
+                    for (int j = 0; j < per; ++j) {
+                        const int r = r0 + j * p.n_split + split;
+                        if (r >= p.rows) break;                                                    // uniform over the CTA
+                        fold(j, r, __ldcg(p.z_res + (size_t)r * p.N + n));
+                    }
+                }
+                named_bar_sync(1, 128);
+                if (t < per) {
+                    const int r = r0 + t * p.n_split + split;
+                    if (r < p.rows) p.ss_out[(size_t)tile * p.rows + r] = (s_aux[t * 4] + s_aux[t * 4 + 1]) + (s_aux[t * 4 + 2] + s_aux[t * 4 + 3]);
                 }
             } else {
                 const int pi = t & 63, sub = t >> 6, ffn = p.N / 2;
@@ -471,7 +617,7 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0);
     const size_t ring = (size_t)p.stages * stage_bytes;
     const size_t red = !cluster ? 0 : (p.n_split > 1 ? (size_t)p.Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
-    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 2) * 8;
+    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 2) * 8 + 256 * 4;
     auto kern = linear_umma_kernel<WSRC>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
@@ -496,13 +642,20 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
 // y != NULL: bf16 output (cluster split-K when n_split > 1); partials != NULL: legacy fp32 partials.
 // epi: EPI_STORE / EPI_SILU (bf16 output only).  awq == NULL: bf16 weights `w` [N, K].
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, cudaStream_t stream) {
+                               int n_split, int epi, cudaStream_t stream, const t3b_linear_fuse_t* fz) {
     T3B_CHECK_SHAPE(K % UM_K == 0 && K >= UM_K, "umma: K %d must be a multiple of 64", K);
     T3B_CHECK_SHAPE(rows >= 1, "umma: rows %d", rows);
     const int kb_total = K / UM_K;
     const bool legacy = partials != nullptr && n_split > 1;
     T3B_CHECK_ARG(n_split >= 1 && n_split <= kb_total, "umma: n_split %d not in [1, %d]", n_split, kb_total);
-    T3B_CHECK_ARG(legacy || y != nullptr, "umma: y is null");
+    T3B_CHECK_ARG(legacy || y != nullptr || epi == EPI_RESID, "umma: y is null");
+    const bool zx = fz != nullptr && fz->x_z != nullptr;
+    T3B_CHECK_ARG(zx || x != nullptr, "umma: x is null");
+    if (zx) T3B_CHECK_ARG(fz->x_ss && fz->norm_w && fz->x_ss_tiles >= 1 && !legacy, "umma: fused norm needs x_ss, norm_w, x_ss_tiles >= 1");
+    if (epi == EPI_RESID) {
+        T3B_CHECK_ARG(fz && fz->res_z && fz->out_z && fz->out_ss && !legacy, "umma: the residual epilogue needs res_z, out_z, out_ss");
+        T3B_CHECK_SHAPE(N % UM_M == 0, "umma: residual epilogue needs N %d to be a multiple of 128", N);
+    }
     T3B_CHECK_ARG(legacy || n_split == 1 || n_split == 2 || n_split == 4 || n_split == 8, "umma: cluster split-K %d must be 1, 2, 4 or 8", n_split);
     T3B_CHECK_ARG(!(legacy && epi != EPI_STORE), "umma: fused epilogues need the bf16 output mode");
     if (epi == EPI_SILU) T3B_CHECK_SHAPE(N % 128 == 0, "umma: gate_up N %d must be a multiple of 128", N);
@@ -536,7 +689,12 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     CUtensorMap tw, tx;
     memset(&tw, 0, sizeof(tw));
     int e1 = awq ? 0 : make_tmap(&tw, w, (uint64_t)K, (uint64_t)N, 64, true);
-    int e2 = make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
+    memset(&tx, 0, sizeof(tx));
+    int e2 = zx ? 0 : make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
+    if (fz) {
+        p.zx = fz->x_z; p.zx_ss = fz->x_ss; p.norm_w = (const bf16*)fz->norm_w; p.zx_tiles = fz->x_ss_tiles; p.eps = fz->eps;
+        p.z_res = fz->res_z; p.z_out = fz->out_z; p.ss_out = fz->out_ss;
+    }
     if (e1 || e2) T3B_FAIL(T3B_ERR_CUDA, "umma: cuTensorMapEncodeTiled failed (%d, %d)", e1, e2);
     const int tiles = epi == EPI_SILU ? N / 128 : (N + UM_M - 1) / UM_M;
     if (awq) {

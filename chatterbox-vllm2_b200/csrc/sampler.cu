@@ -98,8 +98,8 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
     __shared__ unsigned long long s_below;
     __shared__ unsigned int s_digit, s_tie_rank_base;
 
+    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     pdl_wait();
-    pdl_launch_dependents();
     const int b = blockIdx.x, tid = threadIdx.x, V = a.V;
     const bool active = a.has_state ? (a.st.active == nullptr || a.st.active[b] != 0) : true;
 

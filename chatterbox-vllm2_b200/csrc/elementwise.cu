@@ -11,9 +11,9 @@ __global__ void __launch_bounds__(128) embed_gather_kernel(const uint4* __restri
     pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     pdl_wait();
     const int b = blockIdx.x;
-    int tok = tokens[b];
+    int tok = ld_act(tokens + b);
     tok = min(max(tok, 0), emb_rows - 1);
-    int p = speech_pos[b] % pos_rows;
+    int p = ld_act(speech_pos + b) % pos_rows;
     if (p < 0) p += pos_rows;
     for (int i = threadIdx.x; i < hidden8; i += blockDim.x) {
         float a[8], c[8];
@@ -46,13 +46,13 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
         if (i < hidden8) {
             float xv[8];
             if (x != nullptr) {
-                unpack8(x[(size_t)row * hidden8 + i], xv);
+                unpack8(ld_act(x + (size_t)row * hidden8 + i), xv);
             } else {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) xv[e] = 0.f;
                 for (int sp = 0; sp < n_split; ++sp) {            // fixed order -> deterministic
                     const float4* p = partials + sp * split_stride4 + ((size_t)row * hidden8 + i) * 2;
-                    const float4 a = p[0], b = p[1];
+                    const float4 a = ld_act(p), b = ld_act(p + 1);
                     xv[0] += a.x; xv[1] += a.y; xv[2] += a.z; xv[3] += a.w;
                     xv[4] += b.x; xv[5] += b.y; xv[6] += b.z; xv[7] += b.w;
                 }
@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
             }
             if (has_residual) {
                 float r[8];
-                unpack8(residual[(size_t)row * hidden8 + i], r);
+                unpack8(ld_act(residual + (size_t)row * hidden8 + i), r);
 #pragma unroll
                 for (int e = 0; e < 8; ++e) xv[e] += r[e];
             }
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(128) z_init_kernel(const uint4* __restrict__ x
     const int row = blockIdx.x;
     for (int i = threadIdx.x; i < hidden8; i += 128) {            // hidden8 % 16 == 0: a 16-lane group never straddles a tile
         float v[8];
-        unpack8(x[(size_t)row * hidden8 + i], v);
+        unpack8(ld_act(x + (size_t)row * hidden8 + i), v);
         z[((size_t)row * hidden8 + i) * 2] = make_float4(v[0], v[1], v[2], v[3]);
         z[((size_t)row * hidden8 + i) * 2 + 1] = make_float4(v[4], v[5], v[6], v[7]);
         float q = 0.f;
@@ -118,10 +118,10 @@ __global__ void __launch_bounds__(128) z_rmsnorm_kernel(const float4* __restrict
     pdl_wait();
     const int row = blockIdx.x;
     float tot = 0.f;
-    for (int t = 0; t < hidden8 / 16; ++t) tot += ss[(size_t)t * rows + row];
+    for (int t = 0; t < hidden8 / 16; ++t) tot += ld_act(ss + (size_t)t * rows + row);
     const float rstd = rsqrtf(tot / (float)(hidden8 * 8) + eps);
     for (int i = threadIdx.x; i < hidden8; i += 128) {
-        const float4 a = z[((size_t)row * hidden8 + i) * 2], b = z[((size_t)row * hidden8 + i) * 2 + 1];
+        const float4 a = ld_act(z + ((size_t)row * hidden8 + i) * 2), b = ld_act(z + ((size_t)row * hidden8 + i) * 2 + 1);
         float w[8], o[8];
         unpack8(weight[i], w);
         o[0] = bf16_round(a.x * rstd) * w[0]; o[1] = bf16_round(a.y * rstd) * w[1];
@@ -147,13 +147,13 @@ __global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restri
     const int t = blockIdx.x;
     const int lane = threadIdx.x & 31;
     const int hidden = n_heads * 64;
-    const int row = tok_row ? tok_row[t] : t;
-    const int idx = tok_idx[t];
-    int pos = rope_pos[t];
+    const int row = tok_row ? ld_act(tok_row + t) : t;
+    const int idx = ld_act(tok_idx + t);
+    int pos = ld_act(rope_pos + t);
     pos = min(max(pos, 0), max_pos - 1);
     const float c = __bfloat162float(cos_sin[(size_t)pos * 64 + lane]);
     const float s = __bfloat162float(cos_sin[(size_t)pos * 64 + 32 + lane]);
-    const int blk = block_tables[(size_t)row * max_blocks + (idx >> 4)];
+    const int blk = ld_act(block_tables + (size_t)row * max_blocks + (idx >> 4));
     for (int h = threadIdx.x >> 5; h < n_heads; h += blockDim.x >> 5) {
         float v[6];   // q1 q2 k1 k2 v1 v2
 #pragma unroll
@@ -163,10 +163,10 @@ __global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restri
                 const size_t col = (size_t)part * hidden + h * 64 + half * 32 + lane;
                 float a;
                 if (qkv != nullptr) {
-                    a = __bfloat162float(qkv[(size_t)t * 3 * hidden + col]);
+                    a = ld_act(qkv + (size_t)t * 3 * hidden + col);
                 } else {
                     a = 0.f;
-                    for (int sp = 0; sp < n_split; ++sp) a += partials[sp * split_stride + (size_t)t * 3 * hidden + col];
+                    for (int sp = 0; sp < n_split; ++sp) a += ld_act(partials + sp * split_stride + (size_t)t * 3 * hidden + col);
                     a = bf16_round(a);
                 }
                 v[part * 2 + half] = a;
@@ -197,15 +197,15 @@ __global__ void __launch_bounds__(256) silu_mul_kernel(const uint4* __restrict__
         const int row = i / ffn8, c = i - row * ffn8;
         float g[8], u[8];
         if (gu != nullptr) {
-            unpack8(gu[(size_t)row * 2 * ffn8 + c], g);
-            unpack8(gu[(size_t)row * 2 * ffn8 + ffn8 + c], u);
+            unpack8(ld_act(gu + (size_t)row * 2 * ffn8 + c), g);
+            unpack8(ld_act(gu + (size_t)row * 2 * ffn8 + ffn8 + c), u);
         } else {
 #pragma unroll
             for (int e = 0; e < 8; ++e) { g[e] = 0.f; u[e] = 0.f; }
             for (int sp = 0; sp < n_split; ++sp) {
                 const float4* pg = partials + sp * split_stride4 + ((size_t)row * 2 * ffn8 + c) * 2;
                 const float4* pu = pg + (size_t)ffn8 * 2;
-                const float4 a = pg[0], b = pg[1], d = pu[0], f = pu[1];
+                const float4 a = ld_act(pg), b = ld_act(pg + 1), d = ld_act(pu), f = ld_act(pu + 1);
                 g[0] += a.x; g[1] += a.y; g[2] += a.z; g[3] += a.w; g[4] += b.x; g[5] += b.y; g[6] += b.z; g[7] += b.w;
                 u[0] += d.x; u[1] += d.y; u[2] += d.z; u[3] += d.w; u[4] += f.x; u[5] += f.y; u[6] += f.z; u[7] += f.w;
             }

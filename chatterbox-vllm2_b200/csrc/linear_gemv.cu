@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict
     pdl_wait();
     for (int i = threadIdx.x; i < R * K8; i += 256) {
         const int r = i / K8;
-        xs[i] = r < rows ? reinterpret_cast<const uint4*>(x)[i] : make_uint4(0, 0, 0, 0);
+        xs[i] = r < rows ? ld_act(reinterpret_cast<const uint4*>(x) + i) : make_uint4(0, 0, 0, 0);
     }
     __syncthreads();
     if (!live) return;

@@ -100,12 +100,37 @@ __device__ __forceinline__ int tile_feature(int tile, int r, int N, int epi) {
     return tile * UM_M + r;
 }
 
+// acc[e] = sum over the splits c = 0..NS-1 (in that order) of red[c][j][col + e], e < 8; red = [NS][per][128] fp32 in shared memory
+template <int NS>
+__device__ __forceinline__ void red_sum8_n(const float* red, int per, int j, int col, float* acc) {
+    float4 a[NS], b[NS];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) {
+        const float4* src = reinterpret_cast<const float4*>(red + ((size_t)(c * per + j) * UM_M + col));
+        a[c] = src[0]; b[c] = src[1];
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+#pragma unroll
+    for (int c = 0; c < NS; ++c) {
+        acc[0] += a[c].x; acc[1] += a[c].y; acc[2] += a[c].z; acc[3] += a[c].w;
+        acc[4] += b[c].x; acc[5] += b[c].y; acc[6] += b[c].z; acc[7] += b[c].w;
+    }
+}
+__device__ __forceinline__ void red_sum8(const float* red, int n_split, int per, int j, int col, float* acc) {
+    if (n_split == 8) red_sum8_n<8>(red, per, j, col, acc);
+    else if (n_split == 4) red_sum8_n<4>(red, per, j, col, acc);
+    else red_sum8_n<2>(red, per, j, col, acc);
+}
+
 template <int WSRC>
 __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                           const __grid_constant__ CUtensorMap tmap_x,
                                                                           const UmmaParams p) {
     extern __shared__ unsigned char smem_dyn[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_dyn) + 1023) & ~uintptr_t(1023));
+    // 1024-byte alignment as an OFFSET into the __shared__ array: pointer arithmetic keeps the shared address space, so every
+    // access below compiles to LDS / STS (a round trip through uintptr_t made them generic LD.E / ST.E)
+    unsigned char* smem = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     const int stages = p.stages, Rp = p.Rp;
     const uint32_t x_bytes = (uint32_t)Rp * 128u;
     const uint32_t stage_bytes = UM_A_BYTES + x_bytes + (WSRC ? UM_RAW_BYTES : 0);   // [A | X | raw]
@@ -148,9 +173,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    float zr[8];                                 // EPI_RESID: prefetched residual values (rows owned after the cluster reduce)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) zr[j] = 0.f;
+    float4 zra = make_float4(0.f, 0.f, 0.f, 0.f), zrb = zra;     // EPI_RESID: prefetched residual values (first item of the thread)
     if (threadIdx.x == 0) TRACE(1);
 
     auto load_w = [&](int i, int s) {
@@ -253,13 +276,12 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         const int f = quad * 32 + lane;          // feature row of the tile this thread reads from TMEM
         const int r0 = rchunk * p.row_chunk;
         const int valid = min(Rp, p.rows - r0);  // rows of this chunk that exist
-        if (p.epi == EPI_RESID && p.n_split > 1 && (Rp / p.n_split) <= 8) {
-            // residual values this thread adds after the split-K reduce: fetched now, off the critical path
-            const int per = Rp / p.n_split;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int r = r0 + j * p.n_split + split;
-                zr[j] = (j < per && r < p.rows) ? __ldcg(p.z_res + (size_t)r * p.N + tile * UM_M + (threadIdx.x - 128)) : 0.f;
+        if (p.epi == EPI_RESID && p.n_split > 1) {
+            // residual values of this thread's first (row, 8 features) item after the split-K reduce: fetched now, off the critical path
+            const int tt = threadIdx.x - 128, j = tt >> 4, g = tt & 15, r = r0 + j * p.n_split + split;
+            if (tt < (Rp / p.n_split) * 16 && r < p.rows) {
+                const float4* rp = reinterpret_cast<const float4*>(p.z_res + (size_t)r * p.N + tile * UM_M + g * 8);
+                zra = __ldcg(rp); zrb = __ldcg(rp + 1);
             }
         }
         if (p.zx != nullptr) {
@@ -424,10 +446,21 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         cluster_sync_all();                      // release / acquire: every peer's pushes into this CTA's buffer have landed
         if (threadIdx.x == 128) TRACE(7);
         if (warp >= 4 && warp < 8) {
+            // The CTA owns rows {r0 + j * n_split + split}.  Item = (row j, 8 adjacent features): two LDS.128 per split, one
+            // 16-byte global store - 8x fewer memory instructions than a thread per feature.  Splits are summed in peer order
+            // 0..n-1 (deterministic, the same order for every batch).
             const int t = threadIdx.x - 128;     // 0..127
             const int r0 = rchunk * p.row_chunk;
             const int per = Rp / p.n_split;
-            if (p.epi == EPI_STORE) {
+            if (p.epi == EPI_STORE && (p.N & 7) == 0) {
+                for (int it = t; it < per * 16; it += 128) {
+                    const int j = it >> 4, g = it & 15, r = r0 + j * p.n_split + split, n = tile * UM_M + g * 8;
+                    if (r >= p.rows || n >= p.N) continue;
+                    float acc[8];
+                    red_sum8(red, p.n_split, per, j, g * 8, acc);
+                    *reinterpret_cast<uint4*>(p.y + (size_t)r * p.N + n) = pack8(acc);
+                }
+            } else if (p.epi == EPI_STORE) {     // N not a multiple of 8 (the 8194-wide speech head): rows are not 16-byte aligned
                 const int n = tile * UM_M + t;
 #pragma unroll 4
                 for (int j = 0; j < per; ++j) {
@@ -440,47 +473,46 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
             } else if (p.epi == EPI_RESID) {
                 // residual add of llama.py:316-333 in the GEMM epilogue: the fp32 stream z keeps the unrounded sum the
                 // reference's fused_add_rms_norm normalises; the next residual add reads it back as bf16(z)
-                const int n = tile * UM_M + t, quad = warp & 3;
-                auto fold = [&](int j, int r, float res) {
-                    float acc = 0.f;
-                    for (int c = 0; c < p.n_split; ++c) acc += red[(c * per + j) * UM_M + t];      // fixed order -> deterministic
-                    const float z = bf16_round(acc) + bf16_round(res);
-                    p.z_out[(size_t)r * p.N + n] = z;
-                    const float sq = warp_sum(z * z);
-                    if (lane == 0) s_aux[j * 4 + quad] = sq;
-                };
-                if (per <= 8) {
+                for (int it0 = 0; it0 < per * 16; it0 += 128) {
+                    const int it = it0 + t, j = it >> 4, g = it & 15, r = r0 + j * p.n_split + split;
+                    const bool live = it < per * 16 && r < p.rows;            // uniform over each half warp
+                    float sq = 0.f;
+                    if (live) {
+                        float acc[8];
+                        red_sum8(red, p.n_split, per, j, g * 8, acc);
+                        float* zp = p.z_out + (size_t)r * p.N + tile * UM_M + g * 8;
+                        float4 ra = zra, rb = zrb;
+                        if (it0 > 0) {
+                            const float4* rp = reinterpret_cast<const float4*>(p.z_res + (size_t)r * p.N + tile * UM_M + g * 8);
+                            ra = __ldcg(rp); rb = __ldcg(rp + 1);
+                        }
+                        float4 za, zb;
+                        za.x = bf16_round(acc[0]) + bf16_round(ra.x); za.y = bf16_round(acc[1]) + bf16_round(ra.y);
+                        za.z = bf16_round(acc[2]) + bf16_round(ra.z); za.w = bf16_round(acc[3]) + bf16_round(ra.w);
+                        zb.x = bf16_round(acc[4]) + bf16_round(rb.x); zb.y = bf16_round(acc[5]) + bf16_round(rb.y);
+                        zb.z = bf16_round(acc[6]) + bf16_round(rb.z); zb.w = bf16_round(acc[7]) + bf16_round(rb.w);
+                        reinterpret_cast<float4*>(zp)[0] = za;
+                        reinterpret_cast<float4*>(zp)[1] = zb;
+                        sq = ((za.x * za.x + za.y * za.y) + (za.z * za.z + za.w * za.w)) + ((zb.x * zb.x + zb.y * zb.y) + (zb.z * zb.z + zb.w * zb.w));
+                    }
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const int r = r0 + j * p.n_split + split;
-                        if (j < per && r < p.rows) fold(j, r, zr[j]);                              // uniform over the CTA
-                    }
-                } else {
-#pragma unroll 4
-                    for (int j = 0; j < per; ++j) {
-                        const int r = r0 + j * p.n_split + split;
-                        if (r >= p.rows) break;                                                    // uniform over the CTA
-                        fold(j, r, __ldcg(p.z_res + (size_t)r * p.N + n));
-                    }
-                }
-                named_bar_sync(1, 128);
-                if (t < per) {
-                    const int r = r0 + t * p.n_split + split;
-                    if (r < p.rows) p.ss_out[(size_t)tile * p.rows + r] = (s_aux[t * 4] + s_aux[t * 4 + 1]) + (s_aux[t * 4 + 2] + s_aux[t * 4 + 3]);
+                    for (int o = 8; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);     // the 16 lanes of a row
+                    if (live && g == 0) p.ss_out[(size_t)tile * p.rows + r] = sq;
                 }
             } else {
-                const int pi = t & 63, sub = t >> 6, ffn = p.N / 2;
-#pragma unroll 2
-                for (int j = sub; j < per; j += 2) {
-                    const int r = r0 + j * p.n_split + split;
-                    if (r >= p.rows) break;
-                    float g = 0.f, u = 0.f;
-                    for (int c = 0; c < p.n_split; ++c) {
-                        g += red[(c * per + j) * UM_M + pi];
-                        u += red[(c * per + j) * UM_M + 64 + pi];
+                const int ffn = p.N / 2;
+                for (int it = t; it < per * 8; it += 128) {
+                    const int j = it >> 3, g = it & 7, r = r0 + j * p.n_split + split;
+                    if (r >= p.rows) continue;
+                    float gt[8], up[8], o[8];
+                    red_sum8(red, p.n_split, per, j, g * 8, gt);
+                    red_sum8(red, p.n_split, per, j, 64 + g * 8, up);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const float gg = bf16_round(gt[e]);
+                        o[e] = bf16_round(gg / (1.0f + expf(-gg))) * bf16_round(up[e]);
                     }
-                    g = bf16_round(g); u = bf16_round(u);
-                    p.y[(size_t)r * ffn + tile * 64 + pi] = __float2bfloat16_rn(bf16_round(g / (1.0f + expf(-g))) * u);
+                    *reinterpret_cast<uint4*>(p.y + (size_t)r * ffn + tile * 64 + g * 8) = pack8(o);
                 }
             }
         }

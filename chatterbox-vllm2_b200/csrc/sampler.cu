@@ -105,20 +105,20 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
 
     // ---- C1: load + CFG combine (t3.py:659-662) -------------------------------------------------
     if (a.logits_in != nullptr) {
-        for (int i = tid; i < V; i += SMP_THREADS) lg[i] = a.logits_in[(size_t)b * V + i];
+        for (int i = tid; i < V; i += SMP_THREADS) lg[i] = ld_act(a.logits_in + (size_t)b * V + i);
     } else {
         const float w = a.sp.cfg_scale ? a.sp.cfg_scale[b] : 0.5f;
         const int R = 2 * a.n_req;
         for (int i = tid; i < V; i += SMP_THREADS) {
             float c, u;
             if (a.head != nullptr) {
-                c = __bfloat162float(a.head[(size_t)(2 * b) * V + i]);
-                u = __bfloat162float(a.head[(size_t)(2 * b + 1) * V + i]);
+                c = ld_act(a.head + (size_t)(2 * b) * V + i);
+                u = ld_act(a.head + (size_t)(2 * b + 1) * V + i);
             } else {
                 c = 0.f; u = 0.f;
                 for (int s = 0; s < a.n_split; ++s) {
-                    c += a.head_partials[((size_t)s * R + 2 * b) * V + i];
-                    u += a.head_partials[((size_t)s * R + 2 * b + 1) * V + i];
+                    c += ld_act(a.head_partials + ((size_t)s * R + 2 * b) * V + i);
+                    u += ld_act(a.head_partials + ((size_t)s * R + 2 * b + 1) * V + i);
                 }
                 c = bf16_round(c); u = bf16_round(u);              // ParallelLMHead output dtype
             }

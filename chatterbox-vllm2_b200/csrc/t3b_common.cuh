@@ -64,6 +64,18 @@ __device__ __forceinline__ uint4 ldg_stream(const void* p) {
                  : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
 }
+// Loads of data that other kernels of the step write (activations, decode state): L2-coherent, never L1.  Kernels trigger
+// their dependents early, so several kernels of the chain can be resident on one SM; an L1 line filled by an older
+// kernel's read of a reused buffer would otherwise be served stale to a younger one (L1 is only invalidated at launch).
+__device__ __forceinline__ uint4 ld_act(const uint4* p) { return __ldcg(p); }
+__device__ __forceinline__ uint2 ld_act(const uint2* p) { return __ldcg(p); }
+__device__ __forceinline__ float4 ld_act(const float4* p) { return __ldcg(p); }
+__device__ __forceinline__ float ld_act(const float* p) { return __ldcg(p); }
+__device__ __forceinline__ int ld_act(const int* p) { return __ldcg(p); }
+__device__ __forceinline__ unsigned ld_act(const unsigned* p) { return __ldcg(p); }
+__device__ __forceinline__ unsigned long long ld_act(const unsigned long long* p) { return __ldcg(p); }
+__device__ __forceinline__ float ld_act(const bf16* p) { return bf16lo((uint32_t)__ldcg(reinterpret_cast<const unsigned short*>(p))); }
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

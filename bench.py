@@ -431,8 +431,16 @@ def run_b200(args):
         t = bd[top]
         line["kernels"] = {k: {"ms_per_launch": round(v["ms_per_launch"], 5), "share": round(v["ms_per_launch"] * v["launches_per_step"] / tot, 4),
                                "GBps": round(v["gbs"], 1)} for k, v in bd.items()}
+        traffic, traffic_note = None, None
+        tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(tp):
+            tj = json.load(open(tp)).get(top)
+            if tj:
+                traffic = tj["dram_bytes_per_launch"]
+                traffic_note = {k: tj[k] for k in ("context", "algorithmic_bytes_at_that_context", "source") if k in tj}
         line["roofline"] = {"bound": "hbm", "kernel": top, "achieved": t["gbs"], "peak": pk["hbm_gbs"], "unit": "GB/s",
-                            "frac": t["gbs"] / pk["hbm_gbs"], "traffic": None, "bytes_per_launch": t["bytes_per_launch"],
+                            "frac": t["gbs"] / pk["hbm_gbs"], "traffic": traffic, "traffic_capture": traffic_note,
+                            "bytes_per_launch": t["bytes_per_launch"],
                             "ms_per_launch": t["ms_per_launch"], "context": ctx, "peak_source": pk["source"]}
     if rank == 0 and args.sweep:
         sw = {}

@@ -40,7 +40,7 @@ class Linear(C.Structure):          # t3b_linear_t
 
 class LinearFuse(C.Structure):      # t3b_linear_fuse_t
     _fields_ = [("x_z", vp), ("x_ss", vp), ("x_ss_tiles", i32), ("norm_w", vp), ("eps", f32), ("res_z", vp), ("out_z", vp),
-                ("out_ss", vp)]
+                ("out_ss", vp), ("tail_resid", vp), ("tail_norm_w", vp), ("tail_out", vp), ("tail_counters", vp)]
 
 
 class Layer(C.Structure):           # t3b_layer_t

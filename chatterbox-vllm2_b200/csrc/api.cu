@@ -57,7 +57,7 @@ namespace {
 inline size_t al(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct Workspace {
-    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *z, *zss;
+    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *z, *zss, *counters;
     size_t total;
 };
 
@@ -77,6 +77,7 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
     w.head = take(R * V * 2 + 64);
     w.z = take(R * D * 4);                       // fp32 residual stream of the fused-norm decode layers
     w.zss = take((D / 128) * R * 4);
+    w.counters = take(256);                      // tail-norm arrival counters (zeroed at the start of every decode step)
     w.total = static_cast<size_t>(p - static_cast<char*>(base));
     return w;
 }
@@ -150,6 +151,8 @@ extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t 
 // ------------------------------------------------------------------ whole step
 static int g_fuse_norm = -1;        // -1: from the environment (T3B_FUSE_NORM, default off)
 extern "C" void t3b_debug_set_fuse_norm(int v) { g_fuse_norm = v; }
+static int g_tail_norm = -1;        // -1: from the environment (T3B_TAIL_NORM, default off)
+extern "C" void t3b_debug_set_tail_norm(int v) { g_tail_norm = v; }
 static int32_t check_model(const t3b_model_t* m) {
     T3B_CHECK_ARG(m && m->layers && m->final_norm && m->speech_emb && m->speech_pos_emb && m->rope_cos_sin && m->head.w,
                   "model: null pointer");
@@ -208,6 +211,43 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
             if (rc) return rc;
         }
         return t3b_z_rmsnorm(z, zss, m->final_norm, n_tok, D, m->rms_eps, hidden_out, stream);
+    }
+    // Decode steps on the tcgen05 path, optional: the add + RMSNorm after the o and down projections runs in the tail of those
+    // GEMMs (t3b_linear_fuse_t tail_*), bit-identical to t3b_add_rmsnorm: 5 launches per layer instead of 7.
+    // opt-in (T3B_TAIL_NORM=1): bit-identical but measured slower on B200 (18.4k vs 21.1k tokens/s at 64 rows, profiles/r01k_notes.md):
+    // fence + arrival atomic + a single block's norm cost more than a PDL-chained 64-block kernel whose launch is already hidden
+    if (g_tail_norm < 0) { const char* e = getenv("T3B_TAIL_NORM"); g_tail_norm = (e && e[0] == '1') ? 1 : 0; }
+    const bool tail = !prefill && n_tok > 4 && g_tail_norm && D == 1024 && m->layers[0].o.kind == T3B_W_BF16 &&
+                      t3b_umma_pick_split(n_tok, D, D) > 1 && t3b_umma_pick_split(n_tok, D, m->ffn) > 1 && n_tok <= 1024;
+    if (tail) {
+        T3B_CUDA(cudaMemsetAsync(ws.counters, 0, 256, s));
+        rc = t3b_add_rmsnorm(x0, nullptr, 1, ws.resid, m->layers[0].ln1, ws.normed, n_tok, D, m->rms_eps, 0, stream);
+        if (rc) return rc;
+        for (int li = 0; li < m->n_layers; ++li) {
+            const t3b_layer_t* L = &m->layers[li];
+            T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
+            const bool last = li + 1 == m->n_layers;
+            t3b_linear_fuse_t fo = {};
+            fo.eps = m->rms_eps; fo.tail_resid = ws.resid; fo.tail_norm_w = L->ln2; fo.tail_out = ws.normed;
+            fo.tail_counters = reinterpret_cast<uint32_t*>(ws.counters);
+            t3b_linear_fuse_t fd = fo;
+            fd.tail_norm_w = last ? m->final_norm : m->layers[li + 1].ln1;
+            fd.tail_out = last ? hidden_out : ws.normed;
+            rc = lin(ws.normed, &L->qkv, ws.qkv, T3B_EPI_NONE);
+            if (rc) return rc;
+            bf16* kp = static_cast<bf16*>(kv->k) + (size_t)li * kv->layer_stride;
+            bf16* vp = static_cast<bf16*>(kv->v) + (size_t)li * kv->layer_stride;
+            rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kp, vp, H,
+                                       ws.attn, s);
+            if (rc) return rc;
+            rc = t3b_linear_fused(ws.attn, &L->o, n_tok, ws.lin, &fo, 0, T3B_EPI_NONE, stream);
+            if (rc) return rc;
+            rc = lin(ws.normed, &L->gate_up, ws.act, T3B_EPI_SILU_MUL);
+            if (rc) return rc;
+            rc = t3b_linear_fused(ws.act, &L->down, n_tok, ws.lin, &fd, 0, T3B_EPI_NONE, stream);
+            if (rc) return rc;
+        }
+        return T3B_OK;
     }
     const void* prev = x0;
     for (int li = 0; li < m->n_layers; ++li) {

@@ -70,6 +70,12 @@ struct UmmaParams {
     const float* z_res;
     float* z_out;
     float* ss_out;
+    // tail norm (EPI_STORE, N == 1024, cluster split-K): the last n-tile CTA to finish a row group runs the add + RMSNorm that
+    // follows the projection (F2.1), bit for bit the arithmetic of add_rmsnorm_kernel<1>
+    bf16* tn_resid;               // bf16 [rows, N], resid += y in place
+    const bf16* tn_w;             // bf16 [N]
+    bf16* tn_out;                 // bf16 [rows, N]
+    unsigned int* tn_counters;    // [row chunks][8] zeroed; re-armed by the last CTA
 };
 
 static long long* g_umma_trace = nullptr;
@@ -445,20 +451,79 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         if (threadIdx.x == 128) TRACE(6);
         cluster_sync_all();                      // release / acquire: every peer's pushes into this CTA's buffer have landed
         if (threadIdx.x == 128) TRACE(7);
-        if (warp >= 4 && warp < 8) {
+        // after the barrier the producer / MMA warps are idle too: the pure store epilogues run on every thread of the block
+        const bool wide = p.epi == EPI_SILU || (p.epi == EPI_STORE && (p.N & 7) == 0 && p.tn_out == nullptr);
+        const int nthr = wide ? (int)blockDim.x : 128;
+        if (wide || (warp >= 4 && warp < 8)) {
             // The CTA owns rows {r0 + j * n_split + split}.  Item = (row j, 8 adjacent features): two LDS.128 per split, one
             // 16-byte global store - 8x fewer memory instructions than a thread per feature.  Splits are summed in peer order
             // 0..n-1 (deterministic, the same order for every batch).
-            const int t = threadIdx.x - 128;     // 0..127
+            const int t = wide ? (int)threadIdx.x : (int)threadIdx.x - 128;
             const int r0 = rchunk * p.row_chunk;
             const int per = Rp / p.n_split;
             if (p.epi == EPI_STORE && (p.N & 7) == 0) {
-                for (int it = t; it < per * 16; it += 128) {
+                for (int it = t; it < per * 16; it += nthr) {
                     const int j = it >> 4, g = it & 15, r = r0 + j * p.n_split + split, n = tile * UM_M + g * 8;
                     if (r >= p.rows || n >= p.N) continue;
                     float acc[8];
                     red_sum8(red, p.n_split, per, j, g * 8, acc);
                     *reinterpret_cast<uint4*>(p.y + (size_t)r * p.N + n) = pack8(acc);
+                }
+                if (p.tn_out != nullptr) {
+                    // F2.1 in the tail of the projection: rows {r0 + j * n_split + split} get their 1024 features from the
+                    // gridDim.x n-tile CTAs with this split index; the last of them to arrive normalises those rows.
+                    unsigned int* flag = reinterpret_cast<unsigned int*>(s_aux + 255);
+                    __threadfence();                                   // this thread's y stores are visible device-wide
+                    named_bar_sync(1, 128);
+                    if (t == 0) *flag = atomicAdd(p.tn_counters + rchunk * 8 + split, 1u);
+                    named_bar_sync(1, 128);
+                    if (*flag == gridDim.x - 1) {
+                        if (t == 0) p.tn_counters[rchunk * 8 + split] = 0u;      // re-arm for the next launch
+                        __threadfence();
+                        float w[8];
+                        unpack8(__ldg(reinterpret_cast<const uint4*>(p.tn_w) + t), w);
+                        const int quad = warp & 3;
+                        constexpr int TNR = WSRC ? 4 : 8;                // rows per pass (the AWQ kernel has half the registers)
+                        for (int j0 = 0; j0 < per; j0 += TNR) {
+                            uint4 xr[TNR], rr[TNR];
+#pragma unroll
+                            for (int jj = 0; jj < TNR; ++jj) {
+                                const int r = r0 + (j0 + jj) * p.n_split + split;
+                                if (j0 + jj < per && r < p.rows) {
+                                    xr[jj] = __ldcg(reinterpret_cast<const uint4*>(p.y + (size_t)r * p.N) + t);
+                                    rr[jj] = __ldcg(reinterpret_cast<const uint4*>(p.tn_resid + (size_t)r * p.N) + t);
+                                } else {
+                                    xr[jj] = make_uint4(0, 0, 0, 0); rr[jj] = xr[jj];
+                                }
+                            }
+                            float xv[TNR][8];
+#pragma unroll
+                            for (int jj = 0; jj < TNR; ++jj) {
+                                const int r = r0 + (j0 + jj) * p.n_split + split;
+                                float rv[8];
+                                unpack8(xr[jj], xv[jj]);
+                                unpack8(rr[jj], rv);
+                                float ss = 0.f;
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) { xv[jj][e] += rv[e]; ss += xv[jj][e] * xv[jj][e]; }
+                                if (j0 + jj < per && r < p.rows) *(reinterpret_cast<uint4*>(p.tn_resid + (size_t)r * p.N) + t) = pack8(xv[jj]);
+                                ss = warp_sum(ss);
+                                if (lane == 0) s_aux[jj * 4 + quad] = ss;
+                            }
+                            named_bar_sync(1, 128);
+#pragma unroll
+                            for (int jj = 0; jj < TNR; ++jj) {
+                                const int r = r0 + (j0 + jj) * p.n_split + split;
+                                const float tot = (s_aux[jj * 4] + s_aux[jj * 4 + 1]) + (s_aux[jj * 4 + 2] + s_aux[jj * 4 + 3]);
+                                const float rstd = rsqrtf(tot / (float)p.N + p.eps);
+                                float o[8];
+#pragma unroll
+                                for (int e = 0; e < 8; ++e) o[e] = bf16_round(xv[jj][e] * rstd) * w[e];
+                                if (j0 + jj < per && r < p.rows) *(reinterpret_cast<uint4*>(p.tn_out + (size_t)r * p.N) + t) = pack8(o);
+                            }
+                            named_bar_sync(1, 128);
+                        }
+                    }
                 }
             } else if (p.epi == EPI_STORE) {     // N not a multiple of 8 (the 8194-wide speech head): rows are not 16-byte aligned
                 const int n = tile * UM_M + t;
@@ -501,7 +566,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 }
             } else {
                 const int ffn = p.N / 2;
-                for (int it = t; it < per * 8; it += 128) {
+                for (int it = t; it < per * 8; it += nthr) {
                     const int j = it >> 3, g = it & 7, r = r0 + j * p.n_split + split;
                     if (r >= p.rows) continue;
                     float gt[8], up[8], o[8];
@@ -723,8 +788,16 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     int e1 = awq ? 0 : make_tmap(&tw, w, (uint64_t)K, (uint64_t)N, 64, true);
     memset(&tx, 0, sizeof(tx));
     int e2 = zx ? 0 : make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
+    if (fz && fz->tail_out) {
+        T3B_CHECK_ARG(fz->tail_resid && fz->tail_norm_w && fz->tail_counters, "umma: tail norm needs tail_resid, tail_norm_w, tail_counters");
+        T3B_CHECK_ARG(epi == EPI_STORE && !legacy && n_split > 1 && N == 1024 && chunks <= 8,
+                      "umma: tail norm needs the plain epilogue, cluster split-K and n == 1024 (epi %d, split %d, n %d)", epi, n_split, N);
+        p.tn_resid = (bf16*)fz->tail_resid; p.tn_w = (const bf16*)fz->tail_norm_w; p.tn_out = (bf16*)fz->tail_out;
+        p.tn_counters = fz->tail_counters; p.eps = fz->eps;
+    }
     if (fz) {
-        p.zx = fz->x_z; p.zx_ss = fz->x_ss; p.norm_w = (const bf16*)fz->norm_w; p.zx_tiles = fz->x_ss_tiles; p.eps = fz->eps;
+        p.zx = fz->x_z; p.zx_ss = fz->x_ss; p.norm_w = (const bf16*)fz->norm_w; p.zx_tiles = fz->x_ss_tiles;
+        if (fz->x_z) p.eps = fz->eps;
         p.z_res = fz->res_z; p.z_out = fz->out_z; p.ss_out = fz->out_ss;
     }
     if (e1 || e2) T3B_FAIL(T3B_ERR_CUDA, "umma: cuTensorMapEncodeTiled failed (%d, %d)", e1, e2);

@@ -83,6 +83,13 @@ typedef struct t3b_linear_fuse {
     const float* res_z;          /* T3B_EPI_RESIDUAL: residual in, fp32 [rows, n]                                     */
     float*       out_z;          /*                   residual out, fp32 [rows, n] (may alias res_z)                  */
     float*       out_ss;         /*                   [n/128][rows] sums of squares of out_z                          */
+    /* tail norm (T3B_EPI_NONE, n == 1024, cluster split-K): the fused_add_rms_norm that FOLLOWS the projection runs in
+     * its tail - the last thread block to finish a group of rows does  resid += y;  out = rmsnorm(resid) * norm  with the
+     * arithmetic of t3b_add_rmsnorm (bit-identical), saving the separate launch.  y is still written.              */
+    void*        tail_resid;     /* bf16 [rows, n], updated in place                                                  */
+    const void*  tail_norm_w;    /* bf16 [n]   (eps = the eps field above)                                            */
+    void*        tail_out;       /* bf16 [rows, n]; NULL = no tail norm                                               */
+    uint32_t*    tail_counters;  /* 64 x uint32, zero before the first use; the kernel leaves them zero              */
 } t3b_linear_fuse_t;
 
 typedef struct t3b_layer {       /* one LlamaDecoderLayer (vllm:model_executor/models/llama.py:316-333) */

@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, the bench (both arms), the ncu launch list and one full-set capture of the
+# One GPU-box visit: parity tests, smoke, the bench (both arms), the ncu launch list and one full-set capture of the
 # dominant kernels.  Everything lands in gpurun_out/$TAG_*; nothing printed under ncu is a bench value.
 TAG=${1:-r01}
 O=gpurun_out
@@ -12,19 +12,15 @@ if [ "${SKIP_TESTS:-0}" != "1" ]; then
 fi
 timeout 600 python __graft_entry__.py --smoke > $O/${TAG}_smoke.log 2>&1; echo "smoke exit $?"
 timeout 900 python bench.py --sweep ${SWEEP:-1,4,128} > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench exit $?"
-tail -c 3000 $O/${TAG}_bench.json
-T3B_FUSED=0 timeout 900 python bench.py --no-cpu-baseline > $O/${TAG}_bench_multikernel.json 2> $O/${TAG}_bench_mk.err; echo "bench mk exit $?"
+tail -c 2500 $O/${TAG}_bench.json
 if [ "${SKIP_REF:-0}" != "1" ]; then
   timeout 600 python bench.py --impl reference --steps 8 --warmup 1 > $O/${TAG}_bench_reference.json 2>&1; echo "ref exit $?"
 fi
 if [ "${SKIP_NCU:-0}" != "1" ]; then
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/${TAG}_launches.csv \
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 8000 --csv --log-file $O/${TAG}_launches.csv \
     python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-breakdown > $O/${TAG}_ncu_launch.log 2>&1; echo "ncu launches exit $?"
-  T3B_FUSED=0 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/${TAG}_launches_mk.csv \
-    python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-breakdown > $O/${TAG}_ncu_launch_mk.log 2>&1; echo "ncu launches mk exit $?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:decode_fused -c 1 --launch-skip 2 -o $O/${TAG}_fused_full -f \
+  python scripts/summarise_ncu.py launches $O/${TAG}_launches.csv $O/${TAG}_launches_summary.csv
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:"paged_attn_decode|linear_umma|add_rmsnorm" -c 8 --launch-skip 400 -o $O/${TAG}_full -f \
     python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-breakdown > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full exit $?"
-  T3B_FUSED=0 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"paged_attn_decode|linear_umma" -c 6 --launch-skip 300 -o $O/${TAG}_mk_full -f \
-    python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-breakdown > $O/${TAG}_ncu_full_mk.log 2>&1; echo "ncu full mk exit $?"
 fi
-ls -la $O | tail -20
+ls -la $O | tail -12

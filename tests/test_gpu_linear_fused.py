@@ -139,3 +139,64 @@ def test_decode_step_fused_norm_matches_seven_launch_path(L, rows):
     assert cos >= 0.9999 and (a - b).abs().max().item() <= 0.0625, (cos, (a - b).abs().max().item())
     assert (outs[0][1].float() - outs[1][1].float()).abs().max().item() <= 0.0625
     assert torch.equal(outs[1][0].view(torch.int16), outs[2][0].view(torch.int16))          # deterministic
+
+
+@pytest.mark.parametrize("rows", [6, 16, 64, 100, 128, 200])
+@pytest.mark.parametrize("K", [1024, 4096])
+def test_tail_norm_is_bit_identical_to_separate_add_rmsnorm(L, rows, K):
+    """The add + RMSNorm that follows the o / down projection, run by the last thread block of the GEMM (tail_* fields),
+    against t3b_linear_bf16 followed by t3b_add_rmsnorm: same arithmetic in the same order -> the same bits."""
+    N = 1024
+    g = torch.Generator().manual_seed(rows + K)
+    x = torch.randn(rows, K, generator=g).bfloat16()
+    w = (torch.randn(N, K, generator=g) * K ** -0.5).bfloat16()
+    res = torch.randn(rows, N, generator=g).bfloat16()
+    nw = (1.0 + 0.1 * torch.randn(N, generator=g)).bfloat16()
+    xd, wd, nwd = bf(x), bf(w), bf(nw)
+    lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
+    # reference: two launches
+    y_ref = torch.empty(rows, N, dtype=torch.bfloat16, device=DEV)
+    res_ref, out_ref = bf(res), torch.empty(rows, N, dtype=torch.bfloat16, device=DEV)
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y_ref.data_ptr(), None, 0, None, _lib.T3B_IMPL_UMMA, 0, sp()))
+    _lib.check(L.t3b_add_rmsnorm(y_ref.data_ptr(), None, 1, res_ref.data_ptr(), nwd.data_ptr(), out_ref.data_ptr(), rows, N, EPS, 1, sp()))
+    # fused tail, twice (the counters must be left re-armed)
+    counters = torch.zeros(64, dtype=torch.int32, device=DEV)
+    for _ in range(2):
+        y = torch.empty(rows, N, dtype=torch.bfloat16, device=DEV)
+        res_d, out = bf(res), torch.full((rows, N), float("nan"), dtype=torch.bfloat16, device=DEV)
+        f = _lib.LinearFuse(None, None, 0, None, EPS, None, None, None, res_d.data_ptr(), nwd.data_ptr(), out.data_ptr(), counters.data_ptr())
+        _lib.check(L.t3b_linear_fused(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), C.byref(f), 0, _lib.T3B_EPI_NONE, sp()), "t3b_linear_fused")
+        torch.cuda.synchronize()
+        assert torch.equal(y.view(torch.int16), y_ref.view(torch.int16))
+        assert torch.equal(res_d.view(torch.int16), res_ref.view(torch.int16))
+        assert torch.equal(out.view(torch.int16), out_ref.view(torch.int16))
+        assert int(counters.abs().sum()) == 0
+
+
+@pytest.mark.parametrize("rows", [6, 16, 64, 130, 256])
+def test_decode_step_tail_norm_equals_seven_launch_path(L, rows):
+    from chatterbox_vllm2_b200 import T3Dims
+    from chatterbox_vllm2_b200.model import T3B200Model
+    from chatterbox_vllm2_b200.synthetic import synthetic_checkpoint
+    from test_gpu_mega import random_state
+    dims = T3Dims().small(n_layers=3, max_pos=2048)
+    m = T3B200Model(dims=dims, device=DEV, cfg_scale=0.5)
+    m.load_weights(synthetic_checkpoint(dims).items())
+    g = torch.Generator().manual_seed(rows)
+    lens = torch.randint(40, 300, (rows,), generator=g).tolist()
+    kv, st = random_state(dims, rows, lens, seed=rows)
+    k0, v0 = kv.k.clone(), kv.v.clone()
+    outs = []
+    try:
+        for mode in (0, 1, 1):
+            L.t3b_debug_set_tail_norm(mode)
+            kv.k.copy_(k0); kv.v.copy_(v0)
+            hid = torch.zeros(rows, dims.hidden, dtype=torch.bfloat16, device=DEV)
+            m.decode_step(kv, st, rows, hid)
+            torch.cuda.synchronize()
+            outs.append((hid, kv.k.clone(), kv.v.clone()))
+    finally:
+        L.t3b_debug_set_tail_norm(-1)
+    for a, b in zip(outs[0], outs[1]):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    assert torch.equal(outs[1][0].view(torch.int16), outs[2][0].view(torch.int16))

@@ -11,6 +11,7 @@ int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, in
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
                                int n_split, int epi, cudaStream_t s, const t3b_linear_fuse_t* fz);
 int t3b_umma_pick_split(int rows, int N, int K);
+void t3b_umma_set_prefetch(const void* pool, const int32_t* ctx, const int32_t* bt, int rows, int heads, int max_blocks);
 int t3b_umma_pick_split_partials(int rows, int N, int K);
 int t3b_umma_available();
 int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_split, const float* logits_in, int V, int n_req,
@@ -151,6 +152,7 @@ extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t 
 // ------------------------------------------------------------------ whole step
 static int g_fuse_norm = -1;        // -1: from the environment (T3B_FUSE_NORM, default off)
 extern "C" void t3b_debug_set_fuse_norm(int v) { g_fuse_norm = v; }
+static int g_kv_prefetch = -1;      // -1: from the environment (T3B_KV_PREFETCH, default off)
 static int g_tail_norm = -1;        // -1: from the environment (T3B_TAIL_NORM, default off)
 extern "C" void t3b_debug_set_tail_norm(int v) { g_tail_norm = v; }
 static int32_t check_model(const t3b_model_t* m) {
@@ -249,6 +251,9 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
         }
         return T3B_OK;
     }
+    // opt-in (T3B_KV_PREFETCH=1): measured slower (17.3k vs 21.4k tokens/s, profiles/r01n_notes.md) - the prefetch warp keeps
+    // every GEMM block alive for microseconds after its epilogue and competes with the weight stream
+    if (g_kv_prefetch < 0) { const char* e = getenv("T3B_KV_PREFETCH"); g_kv_prefetch = (e && e[0] == '1') ? 1 : 0; }
     const void* prev = x0;
     for (int li = 0; li < m->n_layers; ++li) {
         const t3b_layer_t* L = &m->layers[li];
@@ -273,8 +278,12 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
         if (rc) return rc;
         rc = t3b_add_rmsnorm(ws.lin, nullptr, 1, ws.resid, L->ln2, ws.normed, n_tok, D, m->rms_eps, 1, stream);
         if (rc) return rc;
+        // decode: the idle warp of the FFN projections pulls the NEXT layer's K (gate_up) and V (down) pages into L2
+        const bool pf = !prefill && g_kv_prefetch && n_tok > 4 && li + 1 < m->n_layers;
+        if (pf) t3b_umma_set_prefetch(static_cast<bf16*>(kv->k) + (size_t)(li + 1) * kv->layer_stride, tok_idx, block_tables, n_tok, H, max_blocks);
         rc = lin(ws.normed, &L->gate_up, ws.act, T3B_EPI_SILU_MUL);
         if (rc) return rc;
+        if (pf) t3b_umma_set_prefetch(static_cast<bf16*>(kv->v) + (size_t)(li + 1) * kv->layer_stride, tok_idx, block_tables, n_tok, H, max_blocks);
         rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE);
         if (rc) return rc;
         prev = ws.lin;

@@ -36,6 +36,9 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
                                                           uint4* __restrict__ y, int hidden8, float eps, int has_residual) {
     __shared__ float red[4];
     pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
+    uint4 wraw[MAX_CHUNKS];        // norm weights never depend on the previous kernel: fetched before the wait
+#pragma unroll
+    for (int c = 0; c < MAX_CHUNKS; ++c) wraw[c] = threadIdx.x + c * 128 < hidden8 ? __ldg(weight + threadIdx.x + c * 128) : make_uint4(0, 0, 0, 0);
     pdl_wait();
     const int row = blockIdx.x;
     float s[MAX_CHUNKS][8];
@@ -80,7 +83,7 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
         const int i = threadIdx.x + c * 128;
         if (i < hidden8) {
             float w[8], o[8];
-            unpack8(weight[i], w);
+            unpack8(wraw[c], w);
 #pragma unroll
             for (int e = 0; e < 8; ++e) o[e] = bf16_round(s[c][e] * rstd) * w[e];   // x.to(weight.dtype) * weight
             y[(size_t)row * hidden8 + i] = pack8(o);

@@ -76,7 +76,19 @@ struct UmmaParams {
     const bf16* tn_w;             // bf16 [N]
     bf16* tn_out;                 // bf16 [rows, N]
     unsigned int* tn_counters;    // [row chunks][8] zeroed; re-armed by the last CTA
+    // K/V prefetch for the NEXT layer's attention, issued by the idle warp 3 (hint only: prefetch.global.L2)
+    const bf16* pf_pool;          // K or V pool of the target layer, [block][head][16][64] bf16; NULL = off
+    const int32_t* pf_ctx;        // [pf_rows] cached tokens per row (may be one step stale)
+    const int32_t* pf_bt;         // [pf_rows][pf_max_blocks]
+    int pf_rows, pf_heads, pf_max_blocks;
 };
+
+// set by api.cu for the next launch only (decode layers): see UmmaParams::pf_*
+static thread_local UmmaParams g_pf_next = {};
+void t3b_umma_set_prefetch(const void* pool, const int32_t* ctx, const int32_t* bt, int rows, int heads, int max_blocks) {
+    g_pf_next.pf_pool = static_cast<const bf16*>(pool); g_pf_next.pf_ctx = ctx; g_pf_next.pf_bt = bt;
+    g_pf_next.pf_rows = rows; g_pf_next.pf_heads = heads; g_pf_next.pf_max_blocks = max_blocks;
+}
 
 static long long* g_umma_trace = nullptr;
 extern "C" void t3b_debug_set_umma_trace(void* p) { g_umma_trace = static_cast<long long*>(p); }
@@ -129,7 +141,9 @@ __device__ __forceinline__ void red_sum8(const float* red, int n_split, int per,
     else red_sum8_n<2>(red, per, j, col, acc);
 }
 
-template <int WSRC>
+// FZ = false compiles the F2.1 fusions / prefetch role out (the default decode path): fewer registers, so more blocks of the next
+// kernel fit beside a GEMM block while it runs.
+template <int WSRC, bool FZ>
 __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                           const __grid_constant__ CUtensorMap tmap_x,
                                                                           const UmmaParams p) {
@@ -165,9 +179,9 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     if (threadIdx.x == 0) {
         TRACE(0);
         if (!WSRC) tma_prefetch_desc(&tmap_w);
-        if (!p.zx) tma_prefetch_desc(&tmap_x);
+        if (!(FZ && p.zx)) tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < stages; ++i) {
-            mbar_init(&full_bar[i], (WSRC ? 1 + 8 : 1) + (p.zx ? 4 : 0));      // producer (tx) [+ 8 dequant warps] [+ 4 X-build warps]
+            mbar_init(&full_bar[i], (WSRC ? 1 + 8 : 1) + ((FZ && p.zx) ? 4 : 0));      // producer (tx) [+ 8 dequant warps] [+ 4 X-build warps]
             mbar_init(&empty_bar[i], 1);
             mbar_init(&raw_bar[i], 1);
         }
@@ -192,7 +206,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
             tma_load_2d(st + UM_A_BYTES / 2, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_b);
         }
     };
-    const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + (p.zx ? 0u : x_bytes);
+    const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + ((FZ && p.zx) ? 0u : x_bytes);
     const int pre = nkb < stages ? nkb : stages;
     // The first ring of weight tiles goes out before anything else: weights never depend on the previous kernel.
     if (threadIdx.x == 0) {
@@ -209,7 +223,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         if (lane == 0) {
             pdl_wait();
             TRACE(2);
-            if (!p.zx)
+            if (!(FZ && p.zx))
                 for (int i = 0; i < pre; ++i)
                     tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             for (int i = pre; i < nkb; ++i) {
@@ -217,7 +231,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 mbar_wait(&empty_bar[s], (round & 1) ^ 1);
                 mbar_expect_tx(&full_bar[s], tx);
                 load_w(i, s);
-                if (!p.zx)
+                if (!(FZ && p.zx))
                     tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             }
         }
@@ -239,6 +253,27 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 umma_commit(&empty_bar[s]);
             }
             umma_commit(tmem_full_bar);
+        }
+    } else if (FZ && warp == 3 && p.pf_pool != nullptr) {
+        // The next layer's attention streams ~R x ctx x 2 KB of K/V per head; this warp has nothing else to do, HBM is mostly idle
+        // while the projections run, and the 126 MB L2 holds a layer's K/V (65 MB at 64 rows x 250 tokens) - so pull the lines into
+        // L2 now.  Row t of this block = cid % rows, its lines split over the cid / rows blocks that share the row.
+        const int ncta = gridDim.x * gridDim.y * gridDim.z, cid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+        const int rows = p.pf_rows, nparts = ncta >= rows ? ncta / rows : 1;
+        for (int t = ncta >= rows ? cid % rows : cid; t < rows && cid < nparts * rows; t += ncta) {
+            const int part = ncta >= rows ? cid / rows : 0;
+            const int np = min(min((ld_act(p.pf_ctx + t) + 16) >> 4, p.pf_max_blocks), 64);
+            const int32_t* btp = p.pf_bt + (size_t)t * p.pf_max_blocks;
+            const int b0 = lane < np ? ld_act(btp + lane) : 0, b1 = lane + 32 < np ? ld_act(btp + lane + 32) : 0;
+            const int total = np * p.pf_heads * 16;                              // 128-byte lines of this row in the pool
+            for (int i0 = part * 32; i0 < total; i0 += nparts * 32) {             // warp-uniform trip count (shuffles inside)
+                const int i = min(i0 + lane, total - 1);
+                const int ln = i & 15, ph = i >> 4, page = ph % np, h = ph / np;
+                const int lo = __shfl_sync(0xffffffffu, b0, page & 31), hi = __shfl_sync(0xffffffffu, b1, page & 31);
+                const int blk = page < 32 ? lo : hi;
+                if (i0 + lane < total)
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(p.pf_pool + (((size_t)blk * p.pf_heads + h) * T3B_KV_BLOCK) * 64 + ln * 64));
+            }
         }
     } else if (WSRC && warp >= 8) {
         // ---- AWQ dequant: thread d owns weight row (d & 127) and k half (d >> 7) of every k-block
@@ -282,7 +317,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         const int f = quad * 32 + lane;          // feature row of the tile this thread reads from TMEM
         const int r0 = rchunk * p.row_chunk;
         const int valid = min(Rp, p.rows - r0);  // rows of this chunk that exist
-        if (p.epi == EPI_RESID && p.n_split > 1) {
+        if (FZ && p.epi == EPI_RESID && p.n_split > 1) {
             // residual values of this thread's first (row, 8 features) item after the split-K reduce: fetched now, off the critical path
             const int tt = threadIdx.x - 128, j = tt >> 4, g = tt & 15, r = r0 + j * p.n_split + split;
             if (tt < (Rp / p.n_split) * 16 && r < p.rows) {
@@ -290,7 +325,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 zra = __ldcg(rp); zrb = __ldcg(rp + 1);
             }
         }
-        if (p.zx != nullptr) {
+        if (FZ && p.zx != nullptr) {
             // F2.1 (layernorm.py:40-59) folded into the operand build: these 4 warps turn the fp32 residual stream into the
             // normalised bf16 B tile of every k-block ([Rp rows] x 128 B, SWIZZLE_128B: 16 B chunk c of row r at c ^ (r & 7)).
             // Batches of 512 (row, chunk) items, the loads of batch b + 1 in flight while batch b is normalised and stored.
@@ -417,7 +452,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                         for (int j = 0; j < 16; ++j)
                             if (c0 + j < valid) p.y[(size_t)(r0 + c0 + j) * p.N + n] = __float2bfloat16_rn(red[j * UM_M + t]);
                     }
-                } else if (p.epi == EPI_RESID) {
+                } else if (FZ && p.epi == EPI_RESID) {
                     const int n = tile * UM_M + t;               // N % 128 == 0 (checked at launch)
 #pragma unroll 4
                     for (int j = 0; j < 16; ++j) {
@@ -452,7 +487,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         cluster_sync_all();                      // release / acquire: every peer's pushes into this CTA's buffer have landed
         if (threadIdx.x == 128) TRACE(7);
         // after the barrier the producer / MMA warps are idle too: the pure store epilogues run on every thread of the block
-        const bool wide = p.epi == EPI_SILU || (p.epi == EPI_STORE && (p.N & 7) == 0 && p.tn_out == nullptr);
+        const bool wide = p.epi == EPI_SILU || (p.epi == EPI_STORE && (p.N & 7) == 0 && !(FZ && p.tn_out != nullptr));
         const int nthr = wide ? (int)blockDim.x : 128;
         if (wide || (warp >= 4 && warp < 8)) {
             // The CTA owns rows {r0 + j * n_split + split}.  Item = (row j, 8 adjacent features): two LDS.128 per split, one
@@ -469,7 +504,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     red_sum8(red, p.n_split, per, j, g * 8, acc);
                     *reinterpret_cast<uint4*>(p.y + (size_t)r * p.N + n) = pack8(acc);
                 }
-                if (p.tn_out != nullptr) {
+                if (FZ && p.tn_out != nullptr) {
                     // F2.1 in the tail of the projection: rows {r0 + j * n_split + split} get their 1024 features from the
                     // gridDim.x n-tile CTAs with this split index; the last of them to arrive normalises those rows.
                     unsigned int* flag = reinterpret_cast<unsigned int*>(s_aux + 255);
@@ -535,7 +570,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     for (int c = 0; c < p.n_split; ++c) acc += red[(c * per + j) * UM_M + t];      // fixed order -> deterministic
                     if (n < p.N) p.y[(size_t)r * p.N + n] = __float2bfloat16_rn(acc);
                 }
-            } else if (p.epi == EPI_RESID) {
+            } else if (FZ && p.epi == EPI_RESID) {
                 // residual add of llama.py:316-333 in the GEMM epilogue: the fp32 stream z keeps the unrounded sum the
                 // reference's fused_add_rms_norm normalises; the next residual add reads it back as bf16(z)
                 for (int it0 = 0; it0 < per * 16; it0 += 128) {
@@ -715,7 +750,8 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
     const size_t ring = (size_t)p.stages * stage_bytes;
     const size_t red = !cluster ? 0 : (p.n_split > 1 ? (size_t)p.Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
     const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 2) * 8 + 256 * 4;
-    auto kern = linear_umma_kernel<WSRC>;
+    const bool fz = p.zx != nullptr || p.epi == EPI_RESID || p.tn_out != nullptr || p.pf_pool != nullptr;
+    auto kern = fz ? linear_umma_kernel<WSRC, true> : linear_umma_kernel<WSRC, false>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles, p.n_split, chunks);
@@ -783,6 +819,11 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     if (stages > UM_MAX_STAGES) stages = UM_MAX_STAGES;
     if (stages < 2) stages = 2;
     p.stages = stages;
+    if (g_pf_next.pf_pool) {
+        p.pf_pool = g_pf_next.pf_pool; p.pf_ctx = g_pf_next.pf_ctx; p.pf_bt = g_pf_next.pf_bt;
+        p.pf_rows = g_pf_next.pf_rows; p.pf_heads = g_pf_next.pf_heads; p.pf_max_blocks = g_pf_next.pf_max_blocks;
+        g_pf_next.pf_pool = nullptr;
+    }
     CUtensorMap tw, tx;
     memset(&tw, 0, sizeof(tw));
     int e1 = awq ? 0 : make_tmap(&tw, w, (uint64_t)K, (uint64_t)N, 64, true);

@@ -182,7 +182,7 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------ B200 arm
-def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN):
+def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN, quant=None):
     import torch
     from chatterbox_vllm2_b200 import T3Dims
     from chatterbox_vllm2_b200.engine import T3B200Engine
@@ -191,7 +191,7 @@ def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN):
     dims = T3Dims()
     if sd is None:
         sd = synthetic_checkpoint(dims)
-    m = T3B200Model(dims=dims, device=dev, cfg_scale=0.5)
+    m = T3B200Model(dims=dims, device=dev, cfg_scale=0.5, quantization=quant)
     m.load_weights(sd.items())
     eng = T3B200Engine(m, max_num_seqs=batch, max_model_len=max_model_len)
     return m, eng, sd
@@ -208,13 +208,16 @@ def make_prompts(batch, rank, pin=True):
     return out
 
 
-def device_resident(eng, prompts, steps, warmup, sampler):
+def device_resident(eng, prompts, steps, warmup, sampler, sampled=False):
     """K graph-replayed steps from the prefilled state; the 300-step job restarts from a state snapshot."""
     import torch
     from chatterbox_vllm2_b200.engine import SamplingParams
     B = len(prompts)
     st = eng.state
     sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=GEN_LEN + warmup + 2, ignore_eos=True)
+    if sampled:      # configs[2]: min-p / top-p sampling with repetition penalty (tts.py:455-464 defaults)
+        sp = SamplingParams(temperature=0.8, top_p=0.8, min_p=0.05, repetition_penalty=2.0, max_tokens=GEN_LEN + warmup + 2,
+                            ignore_eos=True, seed=1234)
     eng.state.c.stop_token = -1
     reqs = [eng._make_req(i, p, sp) for i, p in enumerate(prompts)]
     for i, r in enumerate(reqs):
@@ -336,18 +339,33 @@ def kernel_breakdown(m, eng, B, ctx):
         "add_rmsnorm": (norm_f, R * d.hidden * 2 * 4, 2),
     }
     out = {}
+    side = torch.cuda.Stream(device=dev)
     for name, (fn, bytes_per_launch, per_layer) in classes.items():
-        best = None
-        for rep in range(4):
-            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-            e0.record()
+        # the 30 launches of a class are captured into ONE CUDA graph (like the real step): a Python loop of ctypes calls
+        # is bound by the host's ~5 us per launch and hides every kernel faster than that
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            s = side.cuda_stream
             for li in range(d.n_layers):
-                fn(li)
-            e1.record()
+                fn(li)                                   # warm-up (tensor maps, attributes) outside the capture
             torch.cuda.synchronize()
-            t = e0.elapsed_time(e1) / d.n_layers
-            if rep > 0:
-                best = t if best is None else min(best, t)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                s = side.cuda_stream
+                for li in range(d.n_layers):
+                    fn(li)
+            best = None
+            for rep in range(5):
+                e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+                e0.record(side)
+                g.replay()
+                e1.record(side)
+                torch.cuda.synchronize()
+                t = e0.elapsed_time(e1) / d.n_layers
+                if rep > 0:
+                    best = t if best is None else min(best, t)
+            del g
+        torch.cuda.current_stream().wait_stream(side)
         out[name] = {"ms_per_launch": best, "bytes_per_launch": bytes_per_launch, "launches_per_step": per_layer * d.n_layers,
                      "gbs": bytes_per_launch / best / 1e6}
     kv.release(blocks)
@@ -444,15 +462,20 @@ def run_b200(args):
                             "ms_per_launch": t["ms_per_launch"], "context": ctx, "peak_source": pk["source"]}
     if rank == 0 and args.sweep:
         sw = {}
-        for b in [int(v) for v in args.sweep.split(",") if v]:
+        for tok in [v for v in args.sweep.split(",") if v]:
+            # "N" = N bf16 requests, greedy; "awqN" = N requests on AWQ W4A16 weights with min-p / top-p sampling (configs[2])
+            awq = tok.startswith("awq")
+            b = int(tok[3:] if awq else tok)
             del eng
             torch.cuda.empty_cache()
-            m2, eng, _ = build_engine(b, dev, sd)
-            rr = device_resident(eng, make_prompts(b, rank, pin=False), min(K, GEN_LEN - 1), W, ClockSampler(local))
+            m2, eng, _ = build_engine(b, dev, sd, quant="awq" if awq else None)
+            rr = device_resident(eng, make_prompts(b, rank, pin=False), min(K, GEN_LEN - 1), W, ClockSampler(local), sampled=awq)
             kk = min(K, GEN_LEN - 1)
-            bytes_ = W_bytes + KV_BYTES_PER_TOKEN_ROW * 2 * b * rr["mean_ctx"]
-            sw[str(b)] = {"tokens_per_s": b * kk / (rr["ms"] * 1e-3), "ms_per_step": rr["ms"] / kk,
-                          "hbm_frac": bytes_ / (rr["ms"] / kk) / 1e6 / pk["hbm_gbs"]}
+            wb = m2.weight_bytes()
+            bytes_ = wb + KV_BYTES_PER_TOKEN_ROW * 2 * b * rr["mean_ctx"]
+            sw[tok] = {"tokens_per_s": b * kk / (rr["ms"] * 1e-3), "ms_per_step": rr["ms"] / kk,
+                       "hbm_frac": bytes_ / (rr["ms"] / kk) / 1e6 / pk["hbm_gbs"], "weight_bytes": wb,
+                       "weights": "awq_w4a16" if awq else "bf16", "sampling": "temperature 0.8, top_p 0.8, min_p 0.05, rep 2.0" if awq else "greedy, rep 2.0"}
             del m2
         line["sweep"] = sw
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -35,6 +35,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <cstdlib>
 #include <cstring>
 
 #include "t3b_common.cuh"
@@ -817,6 +818,12 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     const int nkb_max = (kb_total + n_split - 1) / n_split;
     if (stages > nkb_max) stages = nkb_max;
     if (stages > UM_MAX_STAGES) stages = UM_MAX_STAGES;
+    {   // Ring depth cap (T3B_UMMA_STAGES, default 5): an 8-deep ring fills the SM's shared memory, so no block of the NEXT kernel
+        // (attention, norm - a few KB) can become resident beside a GEMM block and run its pre-wait part early.  Measured at 64
+        // rows: 8 stages 1.460 ms/step, 4-6 stages 1.397-1.402 (profiles/r01t_notes.md).
+        static const int cap = []() { const char* e = getenv("T3B_UMMA_STAGES"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 5; }();
+        if (stages > cap) stages = cap;
+    }
     if (stages < 2) stages = 2;
     p.stages = stages;
     if (g_pf_next.pf_pool) {

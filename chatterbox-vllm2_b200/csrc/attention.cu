@@ -13,6 +13,8 @@
 // loads in flight per lane), keep a private online-softmax state and are merged through shared
 // memory at the end (fixed order -> deterministic).  Dot products are reduced across the 8 lanes of
 // a token with a 7-shuffle butterfly-transpose, softmax statistics with warp shuffles.
+#include <cstdlib>
+
 #include "t3b_common.cuh"
 
 #define ATT_PAGES_PER_ITER 2
@@ -229,6 +231,8 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
 }
 
 static int pick_warps(long units) {
+    static const int forced = []() { const char* e = getenv("T3B_ATTN_WARPS"); return e ? atoi(e) : 0; }();
+    if (forced == 2 || forced == 4 || forced == 8) return forced;
     const int sms = t3b_num_sms();
     if (units >= (long)sms * 8) return 2;
     if (units >= (long)sms * 4) return 4;

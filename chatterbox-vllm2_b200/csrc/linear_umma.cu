@@ -611,7 +611,8 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
 #pragma unroll
                     for (int e = 0; e < 8; ++e) {
                         const float gg = bf16_round(gt[e]);
-                        o[e] = bf16_round(gg / (1.0f + expf(-gg))) * bf16_round(up[e]);
+                        // ex2.approx / rcp.approx: relative error ~1e-6, three orders below the bf16 rounding that follows
+                        o[e] = bf16_round(__fdividef(gg, 1.0f + __expf(-gg))) * bf16_round(up[e]);
                     }
                     *reinterpret_cast<uint4*>(p.y + (size_t)r * ffn + tile * 64 + g * 8) = pack8(o);
                 }

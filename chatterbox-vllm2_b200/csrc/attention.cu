@@ -67,26 +67,6 @@ __global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) pag
             asm volatile("prefetch.global.L2 [%0];" :: "l"(line));
         }
     }
-    // K lines of this warp's first two pages, copied to shared memory (cp.async: no registers held) BEFORE the dependency wait when
-    // they are certainly complete: pages below (hint - 1) / 16 hold only tokens of earlier steps whether the hint is this step's
-    // context or still the previous one's.  Each lane later reads back exactly the 16-byte pieces it copied.
-    __shared__ uint4 s_kpre[NW][ATT_PAGES_PER_ITER][4][32];
-    bool kpre_ok[ATT_PAGES_PER_ITER];
-    {
-        const int safe_pages = FUSED ? (ld_act(tok_idx + t) >> 4) : 0;      // (ctx_hint - 1) >> 4 with ctx_hint = tok_idx + 1
-        const int b0 = __shfl_sync(0xffffffffu, my_b0, 0), b1 = __shfl_sync(0xffffffffu, my_b1, 0);
-#pragma unroll
-        for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp) {
-            kpre_ok[pp] = warp * ATT_PAGES_PER_ITER + pp < safe_pages;
-            if (kpre_ok[pp]) {
-                const bf16* src = k_pool + (((size_t)(pp ? b1 : b0) * n_heads + h) * T3B_KV_BLOCK) * 64 + (size_t)lane * 8;
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(smem_u32(&s_kpre[warp][pp][j][lane])), "l"(src + j * 256) : "memory");
-            }
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    }
     pdl_wait();
     const int row = tok_row ? ld_act(tok_row + t) : t;
     const int ctx = ld_act(tok_idx + t) + 1;                      // keys 0..tok_idx[t] (own token is written first)
@@ -147,14 +127,8 @@ __global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) pag
             const int page = p0 + pp;
             const int blk = page < n_pages ? blk2[pp] : blk2[0];         // tail page re-reads a valid page, masked below
             const size_t base = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK) * 64 + (size_t)lane * 8;
-            if (iter == 0 && kpre_ok[pp]) {                               // warp-uniform
-                asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
-                for (int j = 0; j < 4; ++j) kv[pp][j] = s_kpre[warp][pp][j][lane];
-            } else {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) kv[pp][j] = ldg_kv(k_pool + base + j * 256);
-            }
+            for (int j = 0; j < 4; ++j) kv[pp][j] = ldg_kv(k_pool + base + j * 256);
 #pragma unroll
             for (int j = 0; j < 4; ++j) vv[pp][j] = ldg_kv(v_pool + base + j * 256);
         }

@@ -109,7 +109,25 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
     } else {
         const float w = a.sp.cfg_scale ? a.sp.cfg_scale[b] : 0.5f;
         const int R = 2 * a.n_req;
-        for (int i = tid; i < V; i += SMP_THREADS) {
+        // bf16 head rows: two logits per 32-bit load when the rows are 4-byte aligned (V even: 8194), half the load instructions
+        const bool pairs = a.head != nullptr && (V & 1) == 0 && (reinterpret_cast<uintptr_t>(a.head) & 3u) == 0;
+        if (pairs) {
+            const unsigned* hc = reinterpret_cast<const unsigned*>(a.head + (size_t)(2 * b) * V);
+            const unsigned* hu = reinterpret_cast<const unsigned*>(a.head + (size_t)(2 * b + 1) * V);
+            for (int i2 = tid; i2 < V / 2; i2 += SMP_THREADS) {
+                const unsigned wc = ld_act(hc + i2), wu = ld_act(hu + i2);
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const float c = k ? bf16hi(wc) : bf16lo(wc), u = k ? bf16hi(wu) : bf16lo(wu);
+                    float l;
+                    if (a.sp.combine == T3B_COMBINE_BF16) l = bf16_round(c + bf16_round(w * bf16_round(c - u)));
+                    else l = c + w * (c - u);
+                    lg[2 * i2 + k] = l;
+                    if (a.logits_out) a.logits_out[(size_t)b * V + 2 * i2 + k] = l;
+                }
+            }
+        }
+        for (int i = tid; i < (pairs ? 0 : V); i += SMP_THREADS) {
             float c, u;
             if (a.head != nullptr) {
                 c = ld_act(a.head + (size_t)(2 * b) * V + i);

@@ -201,14 +201,17 @@ class T3B200Engine:
         """Reserve KV, run the prompts of ``reqs`` through the backbone in one multi-token pass per chunk,
         sample each request's first speech token and install its slot state."""
         st, dev = self.state, self.dev
-        for r in reqs:
+        # block tables of all admitted requests: built on the host, ONE copy + ONE indexed store on the device
+        bt = torch.zeros(2 * len(reqs), self.max_blocks, dtype=torch.int32)
+        bt_rows = []
+        for i, r in enumerate(reqs):
             total = min(self.max_len, r.n_prompt + r.sp.max_tokens)
             nblk = (total + KV_BLOCK - 1) // KV_BLOCK
             r.blocks = self.kv.alloc(2 * nblk)
-            bt = torch.zeros(2, self.max_blocks, dtype=torch.int32)
-            bt[0, :nblk] = torch.tensor(r.blocks[:nblk], dtype=torch.int32)
-            bt[1, :nblk] = torch.tensor(r.blocks[nblk:], dtype=torch.int32)
-            st.block_tables[2 * r.slot:2 * r.slot + 2] = bt.to(dev)
+            bt[2 * i, :nblk] = torch.tensor(r.blocks[:nblk], dtype=torch.int32)
+            bt[2 * i + 1, :nblk] = torch.tensor(r.blocks[nblk:], dtype=torch.int32)
+            bt_rows += [2 * r.slot, 2 * r.slot + 1]
+        st.block_tables[torch.tensor(bt_rows, device=dev)] = bt.to(dev)
         # token arrays for the multi-token pass: rows in slot order, tokens of a row contiguous
         chunks: List[List[_Req]] = [[]]
         ntok = 0
@@ -296,25 +299,29 @@ class T3B200Engine:
             budget = min(min(min(r.sp.max_tokens, self.max_len - r.n_prompt) - r.n_gen for r in live), self.check_every)
             for _ in range(max(0, budget)):
                 self.step(n_slots)
-            hist_len = st.hist_len[:n_slots].cpu()
-            active = st.active[:n_slots].cpu()
+            poll = torch.stack([st.hist_len[:n_slots], st.active[:n_slots].to(st.hist_len.dtype)]).cpu()    # one D2H per poll
+            hist_len, active = poll[0], poll[1]
             done = []
             for r in live:
                 r.n_gen = int(hist_len[r.slot])
                 limit = min(r.sp.max_tokens, self.max_len - r.n_prompt)
                 if not bool(active[r.slot]) or r.n_gen >= limit:
                     done.append(r)
+            hist_host = st.history[:n_slots].cpu() if done else None          # one D2H for every request that finished
             for r in done:
-                toks = st.history[r.slot, :r.n_gen].cpu().tolist()
+                toks = hist_host[r.slot, :r.n_gen].tolist()
                 stopped = stop >= 0 and stop in toks
                 if stopped:
                     toks = toks[:toks.index(stop) + 1]
                 results[r.rid] = RequestOutput(r.rid, [CompletionOutput([t + SPEECH_TOKEN_OFFSET for t in toks],
                                                                         "stop" if stopped else "length")])
-                st.active[r.slot] = 0
-                st.ctx_lens[2 * r.slot:2 * r.slot + 2] = 0
-                st.rope_pos[2 * r.slot:2 * r.slot + 2] = 0
-                st.block_tables[2 * r.slot:2 * r.slot + 2] = 0
                 self.kv.release(r.blocks)
                 self.slots[r.slot] = None
+            if done:                                                           # park the freed slots: four indexed stores in all
+                sl = torch.tensor([r.slot for r in done], device=self.dev)
+                rw = torch.stack([2 * sl, 2 * sl + 1], 1).reshape(-1)
+                st.active[sl] = 0
+                st.ctx_lens[rw] = 0
+                st.rope_pos[rw] = 0
+                st.block_tables[rw] = 0
         return [results[i] for i in range(len(prompts))]

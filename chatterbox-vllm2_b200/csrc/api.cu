@@ -7,7 +7,8 @@
 #include "t3b_common.cuh"
 
 // implemented in the kernel translation units
-int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s);
+int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
+                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res);
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
                                int n_split, int epi, cudaStream_t s, const t3b_linear_fuse_t* fz);
 int t3b_umma_pick_split(int rows, int N, int K);
@@ -22,6 +23,7 @@ int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx
 int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
                               int max_blocks, const void* k_pool, const void* v_pool, int n_heads, void* out, int warps, cudaStream_t s);
 
+#define GEMV_MAX_ROWS_DEFAULT 2       // measured: 4 rows run 0.87 ms/step on the tcgen05 path, 0.96 on the GEMV (profiles/r02_notes.md)
 static thread_local char g_err[512] = "";
 
 void t3b_set_error(const char* fmt, ...) {
@@ -58,7 +60,7 @@ namespace {
 inline size_t al(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct Workspace {
-    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *z, *zss, *counters;
+    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *z, *zss, *counters, *resid2;
     size_t total;
 };
 
@@ -78,6 +80,7 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
     w.head = take(R * V * 2 + 64);
     w.z = take(R * D * 4);                       // fp32 residual stream of the fused-norm decode layers
     w.zss = take((D / 128) * R * 4);
+    w.resid2 = take((R < 4 ? R : 4) * D * 2);    // ping-pong residual of the small-batch path (rows <= 4)
     w.counters = take(256);                      // tail-norm arrival counters (zeroed at the start of every decode step)
     w.total = static_cast<size_t>(p - static_cast<char*>(base));
     return w;
@@ -88,6 +91,12 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
 extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
     if (!m || max_rows <= 0) return 0;
     return carve(m, max_rows, nullptr).total + 256;
+}
+
+// rows up to which the SIMT GEMV is picked over the tcgen05 GEMM (T3B_GEMV_MAX_ROWS, 0..4)
+static int gemv_max_rows() {
+    static const int v = []() { const char* e = getenv("T3B_GEMV_MAX_ROWS"); const int r = e ? atoi(e) : GEMV_MAX_ROWS_DEFAULT; return r < 0 ? 0 : (r > 4 ? 4 : r); }();
+    return v;
 }
 
 // ------------------------------------------------------------------ linear dispatch
@@ -102,13 +111,13 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     if (rows == 0) { if (n_split_out) *n_split_out = 1; return T3B_OK; }
     const bool awq = w->kind == T3B_W_AWQ;
     T3B_CHECK_ARG(awq || w->kind == T3B_W_BF16, "linear: unknown weight kind %d", w->kind);
-    if (impl == T3B_IMPL_AUTO) impl = (!awq && rows <= 4 && w->k % 1024 == 0 && w->k <= 8192) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
+    if (impl == T3B_IMPL_AUTO) impl = (!awq && rows <= gemv_max_rows() && w->k % 1024 == 0 && w->k <= 8192) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
     if (impl == T3B_IMPL_GEMV) {
         T3B_CHECK_ARG(!awq, "linear: AWQ weights run on the dequant-fused tcgen05 kernel at every row count (no GEMV)");
         T3B_CHECK_ARG(n_split <= 1, "linear: the GEMV path has no split-K (n_split %d)", n_split);
         T3B_CHECK_ARG(y != nullptr, "linear: y is null");
         if (n_split_out) *n_split_out = 1;
-        return t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, epi, s);
+        return t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, epi, s, nullptr, nullptr, nullptr, 0.f, 0);
     }
     T3B_CHECK_ARG(impl == T3B_IMPL_UMMA, "linear: unknown impl %d", impl);
     const bool legacy = partials != nullptr && n_split > 1;      // explicit request for global fp32 partials
@@ -152,6 +161,8 @@ extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t 
 // ------------------------------------------------------------------ whole step
 static int g_fuse_norm = -1;        // -1: from the environment (T3B_FUSE_NORM, default off)
 extern "C" void t3b_debug_set_fuse_norm(int v) { g_fuse_norm = v; }
+static int g_gemv_norm = -1;        // -1: from the environment (T3B_GEMV_NORM, default on)
+extern "C" void t3b_debug_set_gemv_norm(int v) { g_gemv_norm = v; }
 static int g_kv_prefetch = -1;      // -1: from the environment (T3B_KV_PREFETCH, default off)
 static int g_tail_norm = -1;        // -1: from the environment (T3B_TAIL_NORM, default off)
 extern "C" void t3b_debug_set_tail_norm(int v) { g_tail_norm = v; }
@@ -253,6 +264,37 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     }
     // opt-in (T3B_KV_PREFETCH=1): measured slower (17.3k vs 21.4k tokens/s, profiles/r01n_notes.md) - the prefetch warp keeps
     // every GEMM block alive for microseconds after its epilogue and competes with the weight stream
+    // Small batch (rows <= 4, bf16): F2.1 runs in front of the qkv / gate_up GEMVs (each block normalises the <= 4 rows it needs
+    // anyway; block 0 writes the residual to the other ping-pong buffer) - 5 launches per layer, bit-identical to the 7-launch path.
+    if (g_gemv_norm < 0) { const char* e = getenv("T3B_GEMV_NORM"); g_gemv_norm = (e && e[0] == '0') ? 0 : 1; }
+    const bool small = !prefill && n_tok <= gemv_max_rows() && g_gemv_norm && D == 1024 && m->layers[0].qkv.kind == T3B_W_BF16 &&
+                       m->layers[0].gate_up.kind == T3B_W_BF16 && m->ffn % 1024 == 0;
+    if (small) {
+        char* rcur = ws.resid;
+        char* roth = ws.resid2;
+        const void* xin = x0;
+        for (int li = 0; li < m->n_layers; ++li) {
+            const t3b_layer_t* L = &m->layers[li];
+            T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
+            rc = t3b_linear_gemv_launch(xin, L->qkv.w, n_tok, L->qkv.n, L->qkv.k, ws.qkv, 0, s, rcur, roth, L->ln1, m->rms_eps, li > 0);
+            if (rc) return rc;
+            { char* t = rcur; rcur = roth; roth = t; }
+            bf16* kp = static_cast<bf16*>(kv->k) + (size_t)li * kv->layer_stride;
+            bf16* vp = static_cast<bf16*>(kv->v) + (size_t)li * kv->layer_stride;
+            rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kp, vp, H,
+                                       ws.attn, s);
+            if (rc) return rc;
+            rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE);
+            if (rc) return rc;
+            rc = t3b_linear_gemv_launch(ws.lin, L->gate_up.w, n_tok, L->gate_up.n, L->gate_up.k, ws.act, 1, s, rcur, roth, L->ln2, m->rms_eps, 1);
+            if (rc) return rc;
+            { char* t = rcur; rcur = roth; roth = t; }
+            rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE);
+            if (rc) return rc;
+            xin = ws.lin;
+        }
+        return t3b_add_rmsnorm(xin, nullptr, 1, rcur, m->final_norm, hidden_out, n_tok, D, m->rms_eps, 1, stream);
+    }
     if (g_kv_prefetch < 0) { const char* e = getenv("T3B_KV_PREFETCH"); g_kv_prefetch = (e && e[0] == '1') ? 1 : 0; }
     const void* prev = x0;
     for (int li = 0; li < m->n_layers; ++li) {

@@ -11,9 +11,21 @@
 // act[r][j] = bf16(bf16(silu(bf16 g)) * bf16 u)  (llama.py:117-121 + activation.py:138-141).
 #include "t3b_common.cuh"
 
+// F2.1 in front of the GEMV (rows <= 4, K == 1024): x is the previous projection's output, the kernel adds the residual, normalises
+// (the arithmetic and summation order of add_rmsnorm_kernel<1>: bit-identical) into its shared-memory operand, and block 0 writes
+// the updated residual to res_out (a different buffer than res_in: the other blocks still read res_in).
+struct GemvNorm {
+    const bf16* res_in;
+    bf16* res_out;
+    const bf16* norm_w;      // NULL = plain GEMV
+    float eps;
+    int has_res;
+};
+
 template <int R, int FPW, int KSTEP, int MODE>
 __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, int rows, int N, int K,
-                                                          bf16* __restrict__ y) {
+                                                          bf16* __restrict__ y, const GemvNorm nz) {
+    __shared__ float s_red[4][4];
     extern __shared__ __align__(16) unsigned char smem_raw[];
     pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     uint4* xs = reinterpret_cast<uint4*>(smem_raw);                 // [R][K/8]
@@ -38,10 +50,58 @@ __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict
 #pragma unroll
             for (int c = 0; c < KSTEP; ++c) wv[f][c] = ldg_stream(wrow[f] + c * 32 + lane);
     }
+    uint4 nwraw = make_uint4(0, 0, 0, 0);
+    if (nz.norm_w != nullptr) nwraw = __ldg(reinterpret_cast<const uint4*>(nz.norm_w) + (threadIdx.x & 127));     // before the wait: constant
     pdl_wait();
-    for (int i = threadIdx.x; i < R * K8; i += 256) {
-        const int r = i / K8;
-        xs[i] = r < rows ? ld_act(reinterpret_cast<const uint4*>(x) + i) : make_uint4(0, 0, 0, 0);
+    if (nz.norm_w != nullptr) {
+        // K == 1024: 128 chunks of 8 per row; threads [128 g, 128 g + 128) take rows g, g + 2 (like add_rmsnorm's 128 threads per row)
+        const int g = threadIdx.x >> 7, i = threadIdx.x & 127, wq = (threadIdx.x >> 5) & 3;
+        float xv[2][8];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int r = g + 2 * q;
+            if (r < R) {
+                float ss = 0.f;
+                if (r < rows) {
+                    unpack8(ld_act(reinterpret_cast<const uint4*>(x) + (size_t)r * K8 + i), xv[q]);
+                    if (nz.has_res) {
+                        float rv[8];
+                        unpack8(ld_act(reinterpret_cast<const uint4*>(nz.res_in) + (size_t)r * K8 + i), rv);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) xv[q][e] += rv[e];
+                    }
+                    if (blockIdx.x == 0) reinterpret_cast<uint4*>(nz.res_out)[(size_t)r * K8 + i] = pack8(xv[q]);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) ss += xv[q][e] * xv[q][e];
+                }
+                ss = warp_sum(ss);
+                if (lane == 0) s_red[r][wq] = ss;
+            }
+        }
+        __syncthreads();
+        float wv8[8];
+        unpack8(nwraw, wv8);
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int r = g + 2 * q;
+            if (r < R) {
+                uint4 o4 = make_uint4(0, 0, 0, 0);
+                if (r < rows) {
+                    const float tot = (s_red[r][0] + s_red[r][1]) + (s_red[r][2] + s_red[r][3]);
+                    const float rstd = rsqrtf(tot / (float)K + nz.eps);
+                    float o[8];
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) o[e] = bf16_round(xv[q][e] * rstd) * wv8[e];
+                    o4 = pack8(o);
+                }
+                xs[r * K8 + i] = o4;
+            }
+        }
+    } else {
+        for (int i = threadIdx.x; i < R * K8; i += 256) {
+            const int r = i / K8;
+            xs[i] = r < rows ? ld_act(reinterpret_cast<const uint4*>(x) + i) : make_uint4(0, 0, 0, 0);
+        }
     }
     __syncthreads();
     if (!live) return;
@@ -105,7 +165,7 @@ __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict
 }
 
 template <int R, int FPW, int KSTEP, int MODE>
-static cudaError_t launch_gemv(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s) {
+static cudaError_t launch_gemv(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s, const GemvNorm& nz) {
     const int n_out = MODE == 1 ? N / 2 : N;
     const int warps = (n_out + FPW - 1) / FPW;
     const size_t smem = (size_t)R * K * 2;
@@ -114,30 +174,36 @@ static cudaError_t launch_gemv(const void* x, const void* w, int rows, int N, in
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    return t3b_launch(kern, dim3((warps + 7) / 8), dim3(256), smem, s, (const bf16*)x, (const bf16*)w, rows, N, K, (bf16*)y);
+    return t3b_launch(kern, dim3((warps + 7) / 8), dim3(256), smem, s, (const bf16*)x, (const bf16*)w, rows, N, K, (bf16*)y, nz);
 }
 
 template <int R, int MODE>
-static cudaError_t dispatch_gemv_r(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s) {
+static cudaError_t dispatch_gemv_r(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s, const GemvNorm& nz) {
     const int n_out = MODE == 1 ? N / 2 : N;
     const int sms = t3b_num_sms();
-    if (MODE == 1) return launch_gemv<R, 2, 4, 1>(x, w, rows, N, K, y, s);
+    if (MODE == 1) return launch_gemv<R, 2, 4, 1>(x, w, rows, N, K, y, s, nz);
     // few, long rows (o / down with K = 4096): one feature per warp, 16 chunks in flight
-    if (K % 4096 == 0 && n_out / 4 < sms * 8) return launch_gemv<R, 1, 16, 0>(x, w, rows, N, K, y, s);
-    if (n_out % 4 == 0 && n_out / 4 >= sms * 8) return launch_gemv<R, 4, 4, 0>(x, w, rows, N, K, y, s);
-    if (n_out % 2 == 0 && n_out / 2 >= sms * 8) return launch_gemv<R, 2, 4, 0>(x, w, rows, N, K, y, s);
-    return launch_gemv<R, 1, 4, 0>(x, w, rows, N, K, y, s);
+    if (K % 4096 == 0 && n_out / 4 < sms * 8) return launch_gemv<R, 1, 16, 0>(x, w, rows, N, K, y, s, nz);
+    if (n_out % 4 == 0 && n_out / 4 >= sms * 8) return launch_gemv<R, 4, 4, 0>(x, w, rows, N, K, y, s, nz);
+    if (n_out % 2 == 0 && n_out / 2 >= sms * 8) return launch_gemv<R, 2, 4, 0>(x, w, rows, N, K, y, s, nz);
+    return launch_gemv<R, 1, 4, 0>(x, w, rows, N, K, y, s, nz);
 }
 
 // mode: 0 = y[rows, N]; 1 = gate_up with fused SiLU*mul -> y[rows, N/2]
-int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s) {
+int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
+                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res) {
+    GemvNorm nz = {(const bf16*)res_in, (bf16*)res_out, (const bf16*)norm_w, eps, has_res};
+    if (norm_w != nullptr) {
+        T3B_CHECK_SHAPE(K == 1024, "gemv: the fused norm needs K == 1024 (got %d)", K);
+        T3B_CHECK_ARG(res_out != nullptr && (!has_res || res_in != nullptr) && res_in != res_out, "gemv: fused norm needs res_out != res_in");
+    }
     T3B_CHECK_SHAPE(rows >= 1 && rows <= 4, "gemv: rows %d not in [1,4]", rows);
     T3B_CHECK_SHAPE(K % 1024 == 0 && K <= 8192, "gemv: K %d must be a multiple of 1024 (<= 8192)", K);
     T3B_CHECK_SHAPE(mode == 0 || N % 4 == 0, "gemv: gate_up N %d", N);
     cudaError_t e;
-    if (rows == 1) e = mode ? dispatch_gemv_r<1, 1>(x, w, rows, N, K, y, s) : dispatch_gemv_r<1, 0>(x, w, rows, N, K, y, s);
-    else if (rows == 2) e = mode ? dispatch_gemv_r<2, 1>(x, w, rows, N, K, y, s) : dispatch_gemv_r<2, 0>(x, w, rows, N, K, y, s);
-    else e = mode ? dispatch_gemv_r<4, 1>(x, w, rows, N, K, y, s) : dispatch_gemv_r<4, 0>(x, w, rows, N, K, y, s);
+    if (rows == 1) e = mode ? dispatch_gemv_r<1, 1>(x, w, rows, N, K, y, s, nz) : dispatch_gemv_r<1, 0>(x, w, rows, N, K, y, s, nz);
+    else if (rows == 2) e = mode ? dispatch_gemv_r<2, 1>(x, w, rows, N, K, y, s, nz) : dispatch_gemv_r<2, 0>(x, w, rows, N, K, y, s, nz);
+    else e = mode ? dispatch_gemv_r<4, 1>(x, w, rows, N, K, y, s, nz) : dispatch_gemv_r<4, 0>(x, w, rows, N, K, y, s, nz);
     T3B_CUDA(e);
     return T3B_OK;
 }

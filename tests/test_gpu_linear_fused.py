@@ -200,3 +200,33 @@ def test_decode_step_tail_norm_equals_seven_launch_path(L, rows):
     for a, b in zip(outs[0], outs[1]):
         assert torch.equal(a.view(torch.int16), b.view(torch.int16))
     assert torch.equal(outs[1][0].view(torch.int16), outs[2][0].view(torch.int16))
+
+
+@pytest.mark.parametrize("rows", [2, 4])
+def test_small_batch_norm_in_gemv_equals_seven_launch_path(L, rows):
+    """rows <= 4: add + RMSNorm run in front of the qkv / gate_up GEMVs (5 launches per layer) - the same arithmetic in the same
+    order as t3b_add_rmsnorm followed by the GEMV, so hidden states and the K/V written this step are bit-identical."""
+    from chatterbox_vllm2_b200 import T3Dims
+    from chatterbox_vllm2_b200.model import T3B200Model
+    from chatterbox_vllm2_b200.synthetic import synthetic_checkpoint
+    from test_gpu_mega import random_state
+    dims = T3Dims().small(n_layers=3, max_pos=2048)
+    m = T3B200Model(dims=dims, device=DEV, cfg_scale=0.5)
+    m.load_weights(synthetic_checkpoint(dims).items())
+    lens = [37, 37, 180, 180][:rows]
+    kv, st = random_state(dims, rows, lens, seed=rows)
+    k0, v0 = kv.k.clone(), kv.v.clone()
+    outs = []
+    try:
+        for mode in (0, 1, 1):
+            L.t3b_debug_set_gemv_norm(mode)
+            kv.k.copy_(k0); kv.v.copy_(v0)
+            hid = torch.zeros(rows, dims.hidden, dtype=torch.bfloat16, device=DEV)
+            m.decode_step(kv, st, rows, hid)
+            torch.cuda.synchronize()
+            outs.append((hid, kv.k.clone(), kv.v.clone()))
+    finally:
+        L.t3b_debug_set_gemv_norm(-1)
+    for a, b in zip(outs[0], outs[1]):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    assert torch.equal(outs[1][0].view(torch.int16), outs[2][0].view(torch.int16))

@@ -446,7 +446,19 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
 #pragma unroll
                 for (int j = 0; j < 16; ++j) red[j * UM_M + f] = __uint_as_float(v[j]);
                 named_bar_sync(1, 128);
-                if (p.epi == EPI_STORE) {
+                if (p.epi == EPI_STORE && (p.N & 7) == 0) {
+                    // (row, 8 adjacent features) items: two LDS.128, one 16-byte store (the prefill shapes live here)
+#pragma unroll
+                    for (int it = t; it < 16 * 16; it += 128) {
+                        const int j = it >> 4, g = it & 15, n = tile * UM_M + g * 8;
+                        if (c0 + j < valid && n < p.N) {
+                            const float4* src = reinterpret_cast<const float4*>(red + j * UM_M + g * 8);
+                            const float4 a = src[0], b = src[1];
+                            const float o[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                            *reinterpret_cast<uint4*>(p.y + (size_t)(r0 + c0 + j) * p.N + n) = pack8(o);
+                        }
+                    }
+                } else if (p.epi == EPI_STORE) {
                     const int n = tile * UM_M + t;
                     if (n < p.N) {
 #pragma unroll 4
@@ -470,13 +482,21 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     if (t < 16 && c0 + t < valid)
                         p.ss_out[(size_t)tile * p.rows + r0 + c0 + t] = (s_aux[t * 4] + s_aux[t * 4 + 1]) + (s_aux[t * 4 + 2] + s_aux[t * 4 + 3]);
                 } else {
-                    const int pi = t & 63, sub = t >> 6, ffn = p.N / 2;
-#pragma unroll 4
-                    for (int j = sub; j < 16; j += 2)
-                        if (c0 + j < valid) {
-                            const float g = bf16_round(red[j * UM_M + pi]), u = bf16_round(red[j * UM_M + 64 + pi]);
-                            p.y[(size_t)(r0 + c0 + j) * ffn + tile * 64 + pi] = __float2bfloat16_rn(bf16_round(g / (1.0f + expf(-g))) * u);
+                    // one (row, 8 gate/up pairs) item per thread: four LDS.128, one 16-byte store
+                    const int j = t >> 3, g8 = (t & 7) * 8, ffn = p.N / 2;
+                    if (c0 + j < valid) {
+                        const float4* gs = reinterpret_cast<const float4*>(red + j * UM_M + g8);
+                        const float4* us = reinterpret_cast<const float4*>(red + j * UM_M + 64 + g8);
+                        const float4 ga = gs[0], gb = gs[1], ua = us[0], ub = us[1];
+                        const float gv[8] = {ga.x, ga.y, ga.z, ga.w, gb.x, gb.y, gb.z, gb.w}, uv[8] = {ua.x, ua.y, ua.z, ua.w, ub.x, ub.y, ub.z, ub.w};
+                        float o[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const float g = bf16_round(gv[e]);
+                            o[e] = bf16_round(g / (1.0f + expf(-g))) * bf16_round(uv[e]);
                         }
+                        *reinterpret_cast<uint4*>(p.y + (size_t)(r0 + c0 + j) * ffn + tile * 64 + g8) = pack8(o);
+                    }
                 }
                 named_bar_sync(1, 128);
             }
@@ -824,6 +844,11 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
         // rows: 8 stages 1.460 ms/step, 4-6 stages 1.397-1.402 (profiles/r01t_notes.md).
         static const int cap = []() { const char* e = getenv("T3B_UMMA_STAGES"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 5; }();
         if (stages > cap) stages = cap;
+    }
+    {   // prefill shapes (256-row chunks, no split-K): a 48 KB stage x 4 leaves one block per SM, so the long epilogue (256 TMEM
+        // columns through the exchange buffer) never overlaps another block's main loop; 2 stages -> two blocks per SM
+        static const int big = []() { const char* e = getenv("T3B_UMMA_STAGES_BIG"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 2; }();
+        if (Rp > 128 && stages > big) stages = big;
     }
     if (stages < 2) stages = 2;
     p.stages = stages;

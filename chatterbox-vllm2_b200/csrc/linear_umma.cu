@@ -35,6 +35,7 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -743,6 +744,16 @@ int t3b_make_tmap_act(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t 
 // put ~one CTA on every SM.  Depends on (N, K, row chunks) only, never on the row count inside a chunk,
 // so a request's arithmetic does not change with the batch it runs in.
 int t3b_umma_pick_split(int rows, int N, int K) {
+    {   // experiment hook: T3B_UMMA_SPLITS="qkv,o,gate_up,down" (0 = automatic) for the four T3 decode shapes
+        static int ov[4] = {-1, 0, 0, 0};
+        if (ov[0] < 0) {
+            ov[0] = 0;
+            const char* e = getenv("T3B_UMMA_SPLITS");
+            if (e) sscanf(e, "%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3]);
+        }
+        const int which = (N == 3072 && K == 1024) ? 0 : (N == 1024 && K == 1024) ? 1 : (N == 8192 && K == 1024) ? 2 : (N == 1024 && K == 4096) ? 3 : -1;
+        if (which >= 0 && ov[which] > 0 && rows <= 128) return ov[which];
+    }
     const int tiles = (N + UM_M - 1) / UM_M * ((rows + 127) / 128);
     const int kb = K / UM_K;
     const int sms = t3b_num_sms();

@@ -296,7 +296,11 @@ class T3B200Engine:
                 self._admit(new)
             live = [r for r in self.slots if r is not None]
             n_slots = max(r.slot for r in live) + 1
-            budget = min(min(min(r.sp.max_tokens, self.max_len - r.n_prompt) - r.n_gen for r in live), self.check_every)
+            # steps until the host has to look again: the shortest remaining length, and - only when a stop token can end a
+            # request early - at most check_every
+            budget = min(min(r.sp.max_tokens, self.max_len - r.n_prompt) - r.n_gen for r in live)
+            if stop >= 0:
+                budget = min(budget, self.check_every)
             for _ in range(max(0, budget)):
                 self.step(n_slots)
             poll = torch.stack([st.hist_len[:n_slots], st.active[:n_slots].to(st.hist_len.dtype)]).cpu()    # one D2H per poll

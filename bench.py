@@ -280,7 +280,9 @@ def end_to_end(eng, prompts, steps, sampler=None):
         n = min(GEN_LEN, steps - done)
         outs = eng.generate(prompts, SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=n, ignore_eos=True))
         t_tokens += sum(len(o.outputs[0].token_ids) for o in outs)
-        h2d += sum(p["multi_modal_data"]["conditionals"][0].numel() * 2 + len(p["prompt_token_ids"]) * 4 for p in prompts)
+        # conditionals (bf16) + text ids and positions (int32) + the int64 row indices of the batched embedding assembly
+        h2d += sum(p["multi_modal_data"]["conditionals"][0].numel() * 2 + len(p["prompt_token_ids"]) * 8
+                   + (2 * 34 + len(p["prompt_token_ids"]) + 2) * 8 for p in prompts)
         # generate(ignore_eos=True) polls once per job (2 int32 per slot) and reads the slots' history rows back once
         d2h += B * 8 + B * int(eng.state.c.hist_stride) * 4
         done += n

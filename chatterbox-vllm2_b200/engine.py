@@ -197,6 +197,25 @@ class T3B200Engine:
             raise ValueError(f"prompt of {r.n_prompt} tokens does not fit max_model_len {self.max_len}")
         return r
 
+    def _embed_prompts(self, prompts: List[dict]) -> List[dict]:
+        """Prompts that come as (conditionals, prompt_token_ids) get their prefill embeddings in ONE batched pass
+        (T3B200Model.prefill_embeds_batch) instead of a dozen small device operations each."""
+        todo = [i for i, p in enumerate(prompts) if "prefill_embeds" not in p and p.get("prompt_token_ids") is not None
+                and "multi_modal_data" in p]
+        if len(todo) < 2:
+            return prompts
+        conds = []
+        for i in todo:
+            c = prompts[i]["multi_modal_data"]["conditionals"]
+            conds.append(c[0] if isinstance(c, (list, tuple)) else c)
+        if any(c.shape[0] < CONDITIONING_SIZE for c in conds) or len({c.device for c in conds}) != 1:
+            return prompts
+        pairs = self.m.prefill_embeds_batch(conds, [prompts[i]["prompt_token_ids"] for i in todo])
+        out = list(prompts)
+        for i, pr in zip(todo, pairs):
+            out[i] = {"prefill_embeds": pr}
+        return out
+
     def _admit(self, reqs: List[_Req]) -> None:
         """Reserve KV, run the prompts of ``reqs`` through the backbone in one multi-token pass per chunk,
         sample each request's first speech token and install its slot state."""
@@ -278,6 +297,7 @@ class T3B200Engine:
         if stop != self.state.c.stop_token:
             self.state.c.stop_token = stop
             self._graphs.clear()                       # the stop token is baked into captured kernel arguments
+        prompts = self._embed_prompts(list(prompts))
         waiting = [self._make_req(i, p, sp) for i, (p, sp) in enumerate(zip(prompts, sps))]
         waiting.reverse()
         results: Dict[int, RequestOutput] = {}

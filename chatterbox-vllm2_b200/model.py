@@ -437,6 +437,42 @@ class T3B200Model:
         assert ce.shape == (CONDITIONING_SIZE, self.dims.hidden)
         return torch.cat([ce, text, bos], 0), torch.cat([ce, torch.zeros_like(text), bos], 0)
 
+    def prefill_embeds_batch(self, conds: Sequence[torch.Tensor], text_ids: Sequence[Sequence[int]]) -> List[Tuple[torch.Tensor, torch.Tensor]]:
+        """``prefill_embeds`` for many requests with a constant number of device operations: one host->device copy of all text
+        ids / positions, one of all conditionals, one embedding gather, three indexed stores.  Row layout per request
+        (t3.py:542-561): cond = [cond_emb(34) | text_emb + text_pos | BOS], uncond = [cond_emb | zeros | BOS]."""
+        dev, D, C34 = self.device, self.dims.hidden, CONDITIONING_SIZE
+        n = len(conds)
+        lens = [len(t) for t in text_ids]
+        P = [C34 + l + 1 for l in lens]
+        big = torch.zeros(2 * sum(P), D, dtype=torch.bfloat16, device=dev)
+        ids_all = torch.tensor([t for ids in text_ids for t in ids], dtype=torch.int32)
+        pos_all = torch.cat([torch.arange(l, dtype=torch.int32) for l in lens]) if n else torch.zeros(0, dtype=torch.int32)
+        ce_all = torch.stack([c[:C34].to(torch.bfloat16) for c in conds]).reshape(n * C34, D)
+        if ce_all.device.type == "cpu":
+            ce_all = ce_all.pin_memory()
+        idx_ce, idx_text, idx_bos, spans = [], [], [], []
+        off = 0
+        for i in range(n):
+            c0, u0 = off, off + P[i]
+            idx_ce.append((torch.arange(C34), c0, u0))
+            idx_text.append(torch.arange(lens[i]) + c0 + C34)
+            idx_bos += [c0 + P[i] - 1, u0 + P[i] - 1]
+            spans.append((c0, u0, u0 + P[i]))
+            off += 2 * P[i]
+        ce_dev = ce_all.to(dev, non_blocking=True)
+        i_ce_c = torch.cat([a + c0 for a, c0, _ in idx_ce]).to(dev, non_blocking=True)
+        i_ce_u = torch.cat([a + u0 for a, _, u0 in idx_ce]).to(dev, non_blocking=True)
+        big.index_copy_(0, i_ce_c, ce_dev)
+        big.index_copy_(0, i_ce_u, ce_dev)
+        if ids_all.numel():
+            text = self.embed("text_emb", "text_pos_emb", ids_all.to(dev), pos_all.to(dev))
+            big.index_copy_(0, torch.cat(idx_text).to(dev), text)
+        bos = self.embed("speech_emb", "speech_pos_emb", torch.tensor([START_SPEECH_TOKEN], dtype=torch.int32, device=dev),
+                         torch.zeros(1, dtype=torch.int32, device=dev))
+        big[torch.tensor(idx_bos, device=dev)] = bos
+        return [(big[a:b], big[b:c]) for a, b, c in spans]
+
     # ------------------------------------------------------------------ the reference's operator surface
     def get_language_model(self):                                 # t3.py:715
         return self

@@ -246,3 +246,16 @@ def test_full_size_engine_properties_at_bench_shape():
     part = [o.outputs[0].token_ids for o in eng.generate(prompts[:20], greedy)]
     assert part == runs[0][:20], "a request's tokens must not depend on the requests it shares a step with"
     record("full_size_properties", {"requests": 32, "tokens": T, "greedy_reproducible": True, "batch_invariant_20_of_32": True})
+
+
+def test_batched_prefill_embeddings_equal_per_request_ones():
+    """generate() assembles the prefill embeddings of all admitted requests in one pass (T3B200Model.prefill_embeds_batch);
+    the rows must be bit-identical to the per-request layout of t3.py:542-561 (prefill_embeds), for ragged text lengths."""
+    m, _ = make_model(SMALL)
+    reqs = [synthetic_request(i, SMALL, n_text=n) for i, n in enumerate((1, 9, 64, 17, 2))]
+    pairs = m.prefill_embeds_batch([c for c, _ in reqs], [ids for _, ids in reqs])
+    torch.cuda.synchronize()
+    for (cond, ids), (bc, bu) in zip(reqs, pairs):
+        c, u = m.prefill_embeds(cond[:34], ids)
+        assert bc.shape == c.shape and bu.shape == u.shape
+        assert torch.equal(bc.view(torch.int16), c.view(torch.int16)) and torch.equal(bu.view(torch.int16), u.view(torch.int16))

@@ -248,6 +248,27 @@ def test_full_size_engine_properties_at_bench_shape():
     record("full_size_properties", {"requests": 32, "tokens": T, "greedy_reproducible": True, "batch_invariant_20_of_32": True})
 
 
+def test_full_size_long_generation_at_the_reference_token_budget():
+    """The reference's default budget (tts.py: max_tokens = 1000 at max_model_len 1200): 8 full-size requests decode 1000 tokens,
+    context growing from 99 to ~1100 rows (69 KV blocks per row, multi-unit attention, several graph buckets of block-table width).
+    Size-independent properties: bit-reproducible across runs, batch-invariant (3 of the 8 requests alone), ids in vocabulary."""
+    dims = T3Dims()
+    m, _ = make_model(dims)
+    prompts = [{"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}}
+               for cond, ids in (synthetic_request(100 + i, dims, n_text=64) for i in range(8))]
+    T = 1000
+    sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=T, ignore_eos=True)
+    eng = T3B200Engine(m, max_num_seqs=8, max_model_len=1200)
+    a = [o.outputs[0].token_ids for o in eng.generate(prompts, sp)]
+    b = [o.outputs[0].token_ids for o in eng.generate(prompts, sp)]
+    assert a == b, "long greedy decode must be bit-reproducible"
+    for toks in a:
+        assert len(toks) == T and all(SPEECH_TOKEN_OFFSET <= t < SPEECH_TOKEN_OFFSET + dims.speech_vocab for t in toks)
+    part = [o.outputs[0].token_ids for o in eng.generate(prompts[:3], sp)]
+    assert part == a[:3], "a request's tokens must not depend on the requests it shares a step with (context ~1100)"
+    record("full_size_long_generation", {"requests": 8, "tokens": T, "reproducible": True, "batch_invariant_3_of_8": True})
+
+
 def test_batched_prefill_embeddings_equal_per_request_ones():
     """generate() assembles the prefill embeddings of all admitted requests in one pass (T3B200Model.prefill_embeds_batch);
     the rows must be bit-identical to the per-request layout of t3.py:542-561 (prefill_embeds), for ragged text lengths."""

@@ -221,6 +221,32 @@ def test_reference_surface_packed_2048_adapters():
     assert tok.cpu().tolist() == ref_l.argmax(-1).tolist() or (ref_l.topk(2).values[:, 0] - ref_l.topk(2).values[:, 1]).min() < 0.0625
 
 
+def test_context_limit_caps_ragged_requests_and_frees_blocks():
+    """A request whose token budget exceeds the context stops when prompt + generated == max_model_len (vLLM's length cap, which
+    the reference relies on at max_model_len 1200 / max_tokens 1000): ragged prompts end on different steps, each stream is the
+    prefix of the uncapped one, and every KV block and slot returns to the pool."""
+    m, _ = make_model(SMALL)
+    n_texts = (3, 11, 20)
+    prompts = [{"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}}
+               for cond, ids in (synthetic_request(i, SMALL, n_text=n) for i, n in enumerate(n_texts))]
+    sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=1000, ignore_eos=True)
+    L = 96
+    eng = T3B200Engine(m, max_num_seqs=4, max_model_len=L)
+    free0 = len(eng.kv.free)
+    capped = eng.generate(prompts, sp)
+    assert len(eng.kv.free) == free0 and all(s is None for s in eng.slots)
+    wide = T3B200Engine(m, max_num_seqs=4, max_model_len=256)
+    free = wide.generate(prompts, SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=100, ignore_eos=True))
+    totals = set()
+    for n, c, f in zip(n_texts, capped, free):
+        ct, ft = c.outputs[0].token_ids, f.outputs[0].token_ids
+        assert c.outputs[0].finish_reason == "length" and 0 < len(ct) < 100
+        assert ct == ft[:len(ct)], "the capped stream must be a prefix of the uncapped one"
+        totals.add(len(ct) + n)
+    assert len(totals) == 1 and totals.pop() <= L, "each request stops exactly at the context limit"
+    record("context_limit", {"max_model_len": L, "generated": [len(c.outputs[0].token_ids) for c in capped]})
+
+
 def test_full_size_engine_properties_at_bench_shape():
     """BASELINE.json configs[1] shape (30 layers, 32 requests = 64 CFG rows, 99-token prompts) through generate():
     size-independent properties the oracle is too slow to check directly - (a) two runs give the same token streams bit for

@@ -13,10 +13,12 @@ A "step" is one decode step of the whole batch: embedding gather -> 30 layers ->
 -> penalty -> argmax -> state advance.  The job (300 steps from the prefilled state) is repeated until K
 steps have run; the prefill is outside the timed region and reported separately.
 
-  value   device-resident: CUDA-graph replay of the step, inputs already in HBM, CUDA events.
-  e2e     the same K steps through the reference-facing call a user makes, T3B200Engine.generate()
-          (tts.py:445-465): host prompts in pinned memory -> H2D -> prefill -> decode -> token ids D2H;
-          everything (including the prefill and the host polling) is inside the timed region.
+  value   device-resident: CUDA-graph replay of the step, inputs already in HBM, CUDA events.  The K timed steps are
+          spread evenly over the 300-step job (decode positions 1..299 -> contexts 100..398, mean 249 at any K), so a
+          short run measures the configuration it names.
+  e2e     the same job through the reference-facing call a user makes, T3B200Engine.generate()
+          (tts.py:445-465): host prompts in pinned memory -> H2D -> prefill -> 300 tokens per request -> token ids
+          D2H; everything (including the prefill and the host polling) is inside the timed region; ceil(K/300) jobs.
   roofline  dominant kernel class of the step (per-class CUDA-event timing over all 30 layers'
           weights, L2-cold because 30 layers x weights >> L2), algorithmic bytes / launch / duration
           against MEASURED_PEAKS.json.
@@ -51,7 +53,12 @@ def parse():
     ap.add_argument("--batch", type=int, default=32, help="requests per GPU (CFG rows = 2x)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-breakdown", action="store_true")
-    ap.add_argument("--sweep", default="", help="extra batch sizes for the 'sweep' key, e.g. 1,4,128")
+    ap.add_argument("--sweep", default="1,awq256,cfg4", help="extra points for the 'sweep' key: N = N bf16 requests greedy; awqN = configs[2] "
+                                                             "(AWQ W4A16, sampling); cfg4 = configs[3] (128 requests at context ~1000); fp8N = N "
+                                                             "requests on an FP8 KV pool; '' = none")
+    ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg5"], help="cfg2 = BASELINE.json configs[1] (default); cfg5 = "
+                    "configs[4]: 4096 mixed-length requests through the dispatcher + generate()")
+    ap.add_argument("--requests", type=int, default=4096, help="cfg5: total requests over all GPUs")
     return ap.parse_args()
 
 
@@ -116,6 +123,29 @@ class ClockSampler:
         return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
 
 
+
+
+WORKLOAD = ("BASELINE.json configs[1]: T3 bf16, 32 requests (64 CFG rows) per GPU, P=99 prompt, 300 speech tokens, greedy, CFG 0.5, "
+            "rep. penalty 2.0, paged KV block 16")
+P_PROMPT = 34 + N_TEXT + 1
+
+
+def spread_positions(k_steps: int, gen_len: int = GEN_LEN):
+    """Decode positions (tokens already generated, 1..gen_len-1) of the K timed steps, spread evenly over the job: the step at
+    position g attends to P + g tokens.  K >= gen_len - 1 wraps around the job."""
+    n = gen_len - 1
+    if k_steps >= n:
+        return [1 + (i % n) for i in range(k_steps)]
+    if k_steps == 1:
+        return [(n + 1) // 2]
+    return [1 + round(i * (n - 1) / (k_steps - 1)) for i in range(k_steps)]
+
+
+def mean_context(k_steps: int) -> float:
+    pos = spread_positions(k_steps)
+    return P_PROMPT + sum(pos) / len(pos)
+
+
 # ------------------------------------------------------------------------------------------ CPU oracle arm
 def cpu_oracle_rate(batch: int, steps: int, warmup: int, ctx: int, sd=None, budget_s: float = None):
     """Decode steps of the fp32 CPU oracle (oracle/t3_ref.py) for ``batch`` requests whose KV already holds
@@ -156,25 +186,35 @@ def cpu_oracle_rate(batch: int, steps: int, warmup: int, ctx: int, sd=None, budg
     return {"value": batch * n / dt, "steps": n, "seconds": dt, "cores": cores, "ms_per_step": 1e3 * dt / n}
 
 
+def bench_config(batch: int, world: int, k_steps: int):
+    """The `config` object both arms print (the driver compares them)."""
+    sb = 1023539200 + KV_BYTES_PER_TOKEN_ROW * 2 * batch * mean_context(k_steps)
+    return {"workload": WORKLOAD, "batch_requests_per_gpu": batch, "cfg_rows_per_gpu": 2 * batch, "prompt_tokens": P_PROMPT,
+            "gen_len": GEN_LEN, "mean_context": round(mean_context(k_steps), 1),
+            "weights": "seeded random-init, exact T3 Llama-520M shapes",
+            "l2": "inputs larger than L2: every step streams %.2f GB of weights + KV (L2 = 126 MB)" % (sb / 1e9),
+            "parallelism": f"replicas x{world} (no collective on the data path)"}
+
+
 def run_reference(args):
+    """The reference's CPU arm.  The reference has no CPU (or any own) implementation of this path - its arithmetic is vLLM's CUDA
+    kernels - so this times the fp32 oracle port on the host cores, on the same workload shape as the B200 arm: the same batch, decode
+    steps at the job's mean context (every step of the port costs the same at a given context, so K steps at the mean context are
+    the bounded sample of the 300-step job)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
-    # calibrate the per-step sample so K steps end within a few minutes
     batch = args.batch
-    probe = cpu_oracle_rate(batch, 2, 1, 250)
-    while batch > 1 and probe["ms_per_step"] * 1e-3 * (args.steps + args.warmup) > 150.0:
-        batch //= 2
-        probe = cpu_oracle_rate(batch, 2, 1, 250)
-    r = cpu_oracle_rate(batch, args.steps, args.warmup, 250)
-    sample = (f"{r['steps']} decode steps of {batch} requests ({2 * batch} CFG rows) at context 250, fp32 oracle "
+    ctx = int(round(mean_context(args.steps))) - 1          # cached tokens in front of the step's own token
+    r = cpu_oracle_rate(batch, args.steps, args.warmup, ctx)
+    sample = (f"{r['steps']} decode steps of {batch} requests ({2 * batch} CFG rows) at context {ctx + 1} (the job's mean), fp32 oracle "
               f"(oracle/t3_ref.py), torch {torch.__version__} CPU, {r['cores']} threads")
+    cfg = bench_config(batch, args.gpus, args.steps)
     line = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
             "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "configs[1] decode step, CPU restatement (the reference has no CPU path; SURVEY.md 8(d))",
-                       "batch_requests": batch, "cfg_rows": 2 * batch, "context": 250},
+            "dtype": "f32", "data": "synthetic", "config": cfg,
+            "notes": {"arm": "CPU restatement of the path (the reference has no CPU implementation; SURVEY.md 8(d)); rank 0 only"},
             "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": sample},
             "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -182,7 +222,7 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------ B200 arm
-def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN, quant=None):
+def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN, quant=None, kv_dtype="bf16", kv_tokens_per_row=None):
     import torch
     from chatterbox_vllm2_b200 import T3Dims
     from chatterbox_vllm2_b200.engine import T3B200Engine
@@ -193,7 +233,10 @@ def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN, quant=None):
         sd = synthetic_checkpoint(dims)
     m = T3B200Model(dims=dims, device=dev, cfg_scale=0.5, quantization=quant)
     m.load_weights(sd.items())
-    eng = T3B200Engine(m, max_num_seqs=batch, max_model_len=max_model_len)
+    kv_blocks = None
+    if kv_tokens_per_row is not None:
+        kv_blocks = 2 * batch * ((kv_tokens_per_row + 15) // 16 + 1) + 8
+    eng = T3B200Engine(m, max_num_seqs=batch, max_model_len=max_model_len, kv_blocks=kv_blocks, kv_dtype=kv_dtype)
     return m, eng, sd
 
 
@@ -208,92 +251,89 @@ def make_prompts(batch, rank, pin=True):
     return out
 
 
-def device_resident(eng, prompts, steps, warmup, sampler, sampled=False):
-    """K graph-replayed steps from the prefilled state; the 300-step job restarts from a state snapshot."""
+def device_resident(eng, prompts, steps, warmup, sampler, sampled=False, gen_len=GEN_LEN):
+    """K graph-replayed decode steps at positions spread evenly over the ``gen_len``-token job (spread_positions): before every
+    step ONE device-to-device copy sets the counters of that position (tokens generated, context length, RoPE / speech positions,
+    sampler step); K/V beyond what the warm-up really generated is whatever the pool holds - a step's cost does not depend on the
+    values.  The prefill (admission of all requests) is timed separately."""
     import torch
     from chatterbox_vllm2_b200.engine import SamplingParams
     B = len(prompts)
     st = eng.state
-    sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=GEN_LEN + warmup + 2, ignore_eos=True)
+    sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=gen_len, ignore_eos=True)
     if sampled:      # configs[2]: min-p / top-p sampling with repetition penalty (tts.py:455-464 defaults)
-        sp = SamplingParams(temperature=0.8, top_p=0.8, min_p=0.05, repetition_penalty=2.0, max_tokens=GEN_LEN + warmup + 2,
-                            ignore_eos=True, seed=1234)
-    eng.state.c.stop_token = -1
-    reqs = [eng._make_req(i, p, sp) for i, p in enumerate(prompts)]
-    for i, r in enumerate(reqs):
-        r.slot = i
-        eng.slots[i] = r
+        sp = SamplingParams(temperature=0.8, top_p=0.8, min_p=0.05, repetition_penalty=2.0, max_tokens=gen_len, ignore_eos=True, seed=1234)
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     t0.record()
-    eng._admit(reqs)
+    reqs = eng.install(prompts, sp, reserve_steps=gen_len + 1)
     t1.record()
     torch.cuda.synchronize()
     prefill_ms = t0.elapsed_time(t1)
-    names = ("tokens", "speech_pos", "rope_pos", "ctx_lens", "hist_len", "step", "active")
-    snap = {n: getattr(st, n).clone() for n in names}
+    P = reqs[0].n_prompt
+    M = st.max_req
+    base = st.small.clone()
+    pos = spread_positions(steps, gen_len)
 
-    def restore():
-        for n in names:
-            getattr(st, n).copy_(snap[n])
+    def counters(g):
+        s = base.clone()
+        s[1 * M:1 * M + B] = g            # speech_pos
+        s[2 * M:2 * M + B] = g            # hist_len
+        s[3 * M:3 * M + B] = g            # sampler step
+        s[5 * M:5 * M + 2 * B] = P + g - 1    # rope_pos
+        s[7 * M:7 * M + 2 * B] = P + g - 1    # ctx_lens (cached tokens in front of the step's own)
+        return s
 
-    for _ in range(max(warmup, 3)):
+    table = torch.stack([counters(g) for g in pos])
+    # history of a position g must hold g valid ids: fill the rows once with a seeded id stream (the first one is the real token)
+    gen = torch.Generator(device="cpu").manual_seed(11)
+    st.history[:B, 1:gen_len] = torch.randint(0, 6561, (B, gen_len - 1), generator=gen, dtype=torch.int32).to(st.history.device)
+    for i in range(max(warmup, 3)):
+        st.small.copy_(table[i % len(pos)])
         eng.step(B)
-    restore()
     torch.cuda.synchronize()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    ctx_sum = 0
-    P = reqs[0].n_prompt
     with sampler:
         e0.record()
-        done = 0
-        while done < steps:
-            n = min(GEN_LEN - 1, steps - done)      # token 1 of the job came from the prefill
-            for j in range(n):
-                eng.step(B)
-                ctx_sum += P + 1 + j                 # tokens each row attends to, incl. its own
-            done += n
-            if done < steps:
-                restore()
+        for i in range(steps):
+            st.small.copy_(table[i])
+            eng.step(B)
         e1.record()
         torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
     toks = st.history[:B, :4].cpu().tolist()
-    for r in reqs:
-        eng.kv.release(r.blocks)
-        eng.slots[r.slot] = None
-    st.active.zero_(); st.ctx_lens.zero_(); st.rope_pos.zero_(); st.block_tables.zero_()
-    return {"ms": ms, "prefill_ms": prefill_ms, "mean_ctx": ctx_sum / steps, "P": P, "first_tokens": toks[0]}
+    eng.uninstall(reqs)
+    return {"ms": ms, "prefill_ms": prefill_ms, "mean_ctx": P + sum(pos) / len(pos), "P": P, "first_tokens": toks[0],
+            "positions": [pos[0], pos[-1]]}
 
 
-def end_to_end(eng, prompts, steps, sampler=None):
-    """The user-facing call: generate() from host prompts to host token ids, ceil(K/300) jobs."""
+def end_to_end(eng, prompts, steps):
+    """The user-facing call: generate() from host prompts to host token ids, ceil(K/300) full 300-token jobs."""
     import torch
     from chatterbox_vllm2_b200.engine import SamplingParams
     B = len(prompts)
+    jobs = max(1, -(-steps // GEN_LEN))
     h2d = d2h = 0
     t_tokens = 0
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    done = 0
-    while done < steps:
-        n = min(GEN_LEN, steps - done)
-        outs = eng.generate(prompts, SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=n, ignore_eos=True))
+    for _ in range(jobs):
+        outs = eng.generate(prompts, SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=GEN_LEN, ignore_eos=True))
         t_tokens += sum(len(o.outputs[0].token_ids) for o in outs)
-        # conditionals (bf16) + text ids and positions (int32) + the int64 row indices of the batched embedding assembly
-        h2d += sum(p["multi_modal_data"]["conditionals"][0].numel() * 2 + len(p["prompt_token_ids"]) * 8
-                   + (2 * 34 + len(p["prompt_token_ids"]) + 2) * 8 for p in prompts)
-        # generate(ignore_eos=True) polls once per job (2 int32 per slot) and reads the slots' history rows back once
-        d2h += B * 8 + B * int(eng.state.c.hist_stride) * 4
-        done += n
+        # conditionals (bf16) + one int32 buffer (text ids, offsets, slots, sequence rows) + block tables (int32 rows) and the
+        # int64 (index, block) pairs of every block-table extension
+        blocks = 2 * ((P_PROMPT + GEN_LEN + 15) // 16 + 2)
+        h2d += sum(34 * 1024 * 2 + (len(p["prompt_token_ids"]) + 6) * 4 for p in prompts) + B * 2 * eng.max_blocks * 4 + B * blocks * 16
+        # the finished requests' history rows come back once per job
+        d2h += B * int(eng.state.hist_stride) * 4
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
-    return {"tokens": t_tokens, "seconds": dt, "h2d": h2d / steps, "d2h": d2h / steps}
+    return {"tokens": t_tokens, "seconds": dt, "h2d": h2d / (jobs * GEN_LEN), "d2h": d2h / (jobs * GEN_LEN), "jobs": jobs}
 
 
 def kernel_breakdown(m, eng, B, ctx):
-    """Per kernel class: launch it for all 30 layers back to back (distinct weights / KV per layer, so every
-    launch streams from HBM) between two CUDA events; 3 repetitions, best.  Returns ms per launch and the
+    """Per kernel class: its 30 per-layer launches (distinct weights / KV per layer, so every launch streams from HBM) captured
+    into ONE CUDA graph and replayed between two CUDA events; 5 repetitions, best of the last 4.  Returns ms per launch and the
     algorithmic bytes per launch."""
     import ctypes as C
     import torch
@@ -301,13 +341,11 @@ def kernel_breakdown(m, eng, B, ctx):
     L = _lib.lib()
     d, dev = m.dims, m.device
     R = 2 * B
-    s = torch.cuda.current_stream().cuda_stream
     bf = lambda *shape: (0.5 * torch.randn(*shape, device=dev)).to(torch.bfloat16)
     x, x4 = bf(R, d.hidden), bf(R, d.ffn)
-    y_qkv, y_gu, y_d = bf(R, 3 * d.hidden), bf(R, 2 * d.ffn), bf(R, d.hidden)
-    act, q, attn, res = bf(R, d.ffn), bf(R, d.hidden), bf(R, d.hidden), bf(R, d.hidden)
-    st, kv = eng.state, eng.kv
-    # context: every row holds `ctx` tokens in its own blocks
+    y_qkv, y_d = bf(R, 3 * d.hidden), bf(R, d.hidden)
+    act, attn, res = bf(R, d.ffn), bf(R, d.hidden), bf(R, d.hidden)
+    kv = eng.kv
     nblk = (ctx + 16) // 16
     blocks = kv.alloc(R * nblk)
     bt = torch.zeros(R, eng.max_blocks, dtype=torch.int32)
@@ -316,45 +354,48 @@ def kernel_breakdown(m, eng, B, ctx):
     idx = torch.full((R,), ctx - 1, dtype=torch.int32, device=dev)
     ns = C.c_int32(0)
     auto = m.c.layers
+    cur = {"s": torch.cuda.current_stream().cuda_stream}
+    awq = m.quantization == "awq"
+    lin_fn = L.t3b_linear_awq if awq else L.t3b_linear_bf16
 
     def lin(name, xin, yout, epi=0):
         def f(li):
             w = getattr(auto[li], name)
-            _lib.check(L.t3b_linear_bf16(xin.data_ptr(), C.byref(w), R, yout.data_ptr(), None, 0, C.byref(ns), 0, epi, s), name)
+            _lib.check(lin_fn(xin.data_ptr(), C.byref(w), R, yout.data_ptr(), None, 0, C.byref(ns), 0, epi, m._opt(), cur["s"]), name)
         return f
 
     def attn_f(li):
-        off = li * kv.c.layer_stride * 2
+        off = li * kv.c.layer_stride
         _lib.check(L.t3b_attn_decode_fused(y_qkv.data_ptr(), R, idx.data_ptr(), idx.data_ptr(), m.w["rope"].data_ptr(), d.max_pos,
                                            bt.data_ptr(), eng.max_blocks, kv.k.data_ptr() + off, kv.v.data_ptr() + off, d.n_heads,
-                                           attn.data_ptr(), s), "attn")
+                                           kv.kv_dtype, attn.data_ptr(), cur["s"]), "attn")
 
     def norm_f(li):
         _lib.check(L.t3b_add_rmsnorm(y_d.data_ptr(), None, 1, res.data_ptr(), m.w[f"{li}.ln1"].data_ptr(), x.data_ptr(), R, d.hidden,
-                                     d.rms_eps, 1, s), "norm")
+                                     d.rms_eps, 1, cur["s"]), "norm")
 
+    wb = (lambda n, k: n * k // 2 + (k // 128) * n * 3) if awq else (lambda n, k: n * k * 2)
+    kv_tok = 2 * d.n_heads * kv.slice_bytes // 16            # K + V bytes per token-row per layer
     classes = {
-        "qkv_proj": (lin("qkv", x, y_qkv), 3 * d.hidden * d.hidden * 2, 1),
-        "attention_rope_kvwrite": (attn_f, R * ctx * d.n_heads * d.head_dim * 2 * 2, 1),
-        "o_proj": (lin("o", attn, y_d), d.hidden * d.hidden * 2, 1),
-        "gate_up_silu_proj": (lin("gate_up", x, act, 1), 2 * d.ffn * d.hidden * 2, 1),
-        "down_proj": (lin("down", x4, y_d), d.hidden * d.ffn * 2, 1),
+        "qkv_proj": (lin("qkv", x, y_qkv), wb(3 * d.hidden, d.hidden), 1),
+        "attention_rope_kvwrite": (attn_f, R * ctx * kv_tok, 1),
+        "o_proj": (lin("o", attn, y_d), wb(d.hidden, d.hidden), 1),
+        "gate_up_silu_proj": (lin("gate_up", x, act, 1), wb(2 * d.ffn, d.hidden), 1),
+        "down_proj": (lin("down", x4, y_d), wb(d.hidden, d.ffn), 1),
         "add_rmsnorm": (norm_f, R * d.hidden * 2 * 4, 2),
     }
     out = {}
     side = torch.cuda.Stream(device=dev)
     for name, (fn, bytes_per_launch, per_layer) in classes.items():
-        # the 30 launches of a class are captured into ONE CUDA graph (like the real step): a Python loop of ctypes calls
-        # is bound by the host's ~5 us per launch and hides every kernel faster than that
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
-            s = side.cuda_stream
+            cur["s"] = side.cuda_stream
             for li in range(d.n_layers):
                 fn(li)                                   # warm-up (tensor maps, attributes) outside the capture
             torch.cuda.synchronize()
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=side):
-                s = side.cuda_stream
+                cur["s"] = side.cuda_stream
                 for li in range(d.n_layers):
                     fn(li)
             best = None
@@ -375,6 +416,36 @@ def kernel_breakdown(m, eng, B, ctx):
     return out
 
 
+def step_bytes(m, eng, B, mean_ctx):
+    """Algorithmic bytes of one decode step: weights once + K/V of every row's context."""
+    kv_tok = 2 * m.dims.n_layers * m.dims.n_heads * eng.kv.slice_bytes // 16
+    return m.weight_bytes() + kv_tok * 2 * B * mean_ctx
+
+
+def sweep_point(tok, dev, sd, rank, K, W, pk, local):
+    """One extra measurement of the metric's other batch points / BASELINE.json configs:
+    "N" = N bf16 requests, greedy (300-token job); "awqN" = configs[2] (AWQ W4A16, N requests, min-p / top-p sampling, rep. penalty);
+    "cfg4" = configs[3] (bf16, 128 requests, 1000-token job: contexts 100..1098); "fp8N" = N bf16-weight requests on an FP8 KV pool."""
+    import torch
+    awq, fp8, cfg4 = tok.startswith("awq"), tok.startswith("fp8"), tok == "cfg4"
+    b = 128 if cfg4 else int(tok[3:] if (awq or fp8) else tok)
+    gen_len = 1000 if cfg4 else GEN_LEN
+    m2, eng, _ = build_engine(b, dev, sd, quant="awq" if awq else None, kv_dtype="fp8" if fp8 else "bf16",
+                              kv_tokens_per_row=P_PROMPT + gen_len + 40)
+    rr = device_resident(eng, make_prompts(b, rank, pin=False), K, W, ClockSampler(local), sampled=awq, gen_len=gen_len)
+    bytes_ = step_bytes(m2, eng, b, rr["mean_ctx"])
+    ms_step = rr["ms"] / K
+    flops = 2 * b * 2 * 511707136 + 122880 * 2 * b * rr["mean_ctx"]
+    out = {"tokens_per_s": b * K / (rr["ms"] * 1e-3), "ms_per_step": ms_step, "steps": K, "mean_context": round(rr["mean_ctx"], 1),
+           "bytes_per_step": bytes_, "hbm_frac": bytes_ / ms_step / 1e6 / pk["hbm_gbs"], "weight_bytes": m2.weight_bytes(),
+           "tensor_frac_whole_step": flops / (ms_step * 1e-3) / 1e12 / pk["bf16_tflops"],
+           "weights": "awq_w4a16" if awq else "bf16", "kv": eng.kv.dtype, "gen_len": gen_len, "prefill_ms": rr["prefill_ms"],
+           "sampling": "temperature 0.8, top_p 0.8, min_p 0.05, rep 2.0" if awq else "greedy, rep 2.0"}
+    del eng, m2
+    torch.cuda.empty_cache()
+    return out
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -392,8 +463,6 @@ def run_b200(args):
     _lib.check(_lib.lib().t3b_check_device(), "t3b_check_device")
     pk = peaks()
     B, K, W = args.batch, args.steps, args.warmup
-    m, eng, sd = build_engine(B, dev)
-    prompts = make_prompts(B, rank)
 
     def barrier():
         torch.cuda.synchronize()
@@ -408,6 +477,16 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    if args.workload == "cfg5":
+        run_cfg5(args, rank, world, local, dev, pk, barrier, max_over_ranks)
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    m, eng, sd = build_engine(B, dev, kv_tokens_per_row=2 * (P_PROMPT + GEN_LEN + 40))
+    prompts = make_prompts(B, rank)
+
     # ---- device-resident
     sampler = ClockSampler(local)
     barrier()
@@ -417,31 +496,29 @@ def run_b200(args):
     value = world * B * K / (ms * 1e-3)
     launches = eng.launches_per_step(B) * K
 
-    # ---- end to end through generate()
-    end_to_end(eng, prompts, min(K, 16))          # warm the graphs / allocator for this path
+    # ---- end to end through generate(): the full 300-token job
+    end_to_end(eng, prompts, 1)          # warm the graphs / allocator for this path
     barrier()
     e = end_to_end(eng, prompts, K)
     barrier()
     e_s = max_over_ranks(e["seconds"])
     e2e_value = world * e["tokens"] / e_s
 
-    W_bytes = m.weight_bytes()
-    step_bytes = W_bytes + KV_BYTES_PER_TOKEN_ROW * 2 * B * r["mean_ctx"]
+    sb = step_bytes(m, eng, B, r["mean_ctx"])
+    cfg = bench_config(B, world, K)
+    notes = {"decode_positions": r["positions"], "measured_mean_context": r["mean_ctx"],
+             "timed_region": "K CUDA-graph replays of the step + one 9*B int32 device copy per step that selects the decode position"}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3), "ms_per_step": ms / K,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": "BASELINE.json configs[1]: T3 bf16, 32 requests (64 CFG rows) per GPU, P=99 prompt, 300 speech tokens, "
-                               "greedy, CFG 0.5, rep. penalty 2.0, paged KV block 16",
-                   "batch_requests_per_gpu": B, "cfg_rows_per_gpu": 2 * B, "prompt_tokens": r["P"], "gen_len": GEN_LEN,
-                   "mean_context": r["mean_ctx"], "weights": "seeded random-init, exact T3 Llama-520M shapes",
-                   "l2": "inputs larger than L2: every step streams %.2f GB of weights + KV (L2 = 126 MB)" % (step_bytes / 1e9),
-                   "parallelism": f"replicas x{world} (no collective on the data path)"},
+        "config": cfg, "notes": notes,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": e["h2d"], "d2h_bytes_per_step": e["d2h"],
-                "api": "T3B200Engine.generate(prompts, SamplingParams) incl. prefill and host polling", "seconds": e_s},
+                "api": "T3B200Engine.generate(prompts, SamplingParams): %d job(s) of %d requests x %d tokens incl. prefill, block-table "
+                       "growth and result read-back" % (e["jobs"], B, GEN_LEN), "seconds": e_s},
         "gpu_launches": launches,
         "prefill_ms": r["prefill_ms"],
-        "step_roofline": {"bound": "hbm", "bytes_per_step": step_bytes, "achieved": step_bytes / (ms / K) / 1e6, "peak": pk["hbm_gbs"],
-                          "unit": "GB/s", "frac": step_bytes / (ms / K) / 1e6 / pk["hbm_gbs"], "peak_source": pk["source"]},
+        "step_roofline": {"bound": "hbm", "bytes_per_step": sb, "achieved": sb / (ms / K) / 1e6, "peak": pk["hbm_gbs"],
+                          "unit": "GB/s", "frac": sb / (ms / K) / 1e6 / pk["hbm_gbs"], "peak_source": pk["source"]},
         "clocks": sampler.summary(),
     }
     if rank == 0 and not args.no_breakdown:
@@ -463,35 +540,100 @@ def run_b200(args):
                             "frac": t["gbs"] / pk["hbm_gbs"], "traffic": traffic, "traffic_capture": traffic_note,
                             "bytes_per_launch": t["bytes_per_launch"],
                             "ms_per_launch": t["ms_per_launch"], "context": ctx, "peak_source": pk["source"]}
-    if rank == 0 and args.sweep:
+    pp = os.path.join(ROOT, "profiles", "parity_latest.json")
+    if os.path.exists(pp):
+        line["parity"] = json.load(open(pp))
+    if rank == 0 and world == 1 and args.sweep:
+        del eng
+        torch.cuda.empty_cache()
         sw = {}
         for tok in [v for v in args.sweep.split(",") if v]:
-            # "N" = N bf16 requests, greedy; "awqN" = N requests on AWQ W4A16 weights with min-p / top-p sampling (configs[2])
-            awq = tok.startswith("awq")
-            b = int(tok[3:] if awq else tok)
-            del eng
-            torch.cuda.empty_cache()
-            m2, eng, _ = build_engine(b, dev, sd, quant="awq" if awq else None)
-            rr = device_resident(eng, make_prompts(b, rank, pin=False), min(K, GEN_LEN - 1), W, ClockSampler(local), sampled=awq)
-            kk = min(K, GEN_LEN - 1)
-            wb = m2.weight_bytes()
-            bytes_ = wb + KV_BYTES_PER_TOKEN_ROW * 2 * b * rr["mean_ctx"]
-            sw[tok] = {"tokens_per_s": b * kk / (rr["ms"] * 1e-3), "ms_per_step": rr["ms"] / kk,
-                       "hbm_frac": bytes_ / (rr["ms"] / kk) / 1e6 / pk["hbm_gbs"], "weight_bytes": wb,
-                       "weights": "awq_w4a16" if awq else "bf16", "sampling": "temperature 0.8, top_p 0.8, min_p 0.05, rep 2.0" if awq else "greedy, rep 2.0"}
-            del m2
+            try:
+                sw[tok] = sweep_point(tok, dev, sd, rank, min(K, 100), W, pk, local)
+            except Exception as ex:  # noqa: BLE001 - a sweep point must not take the headline line down
+                sw[tok] = {"error": repr(ex)[:300]}
         line["sweep"] = sw
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        c = cpu_oracle_rate(B, 12, 1, 250, sd=sd, budget_s=25.0)
+        ctx = int(round(mean_context(K))) - 1
+        c = cpu_oracle_rate(B, 12, 1, ctx, sd=sd, budget_s=20.0)
+        c0 = cpu_oracle_rate(1, 40, 1, ctx, sd=sd, budget_s=10.0)      # BASELINE.json configs[0]: batch 1, CFG 0.5, greedy, fp32 CPU
         line["cpu_baseline"] = {"value": c["value"], "unit": UNIT, "cores": c["cores"], "kind": "port",
-                                "sample": f"{c['steps']} decode steps of {B} requests ({2 * B} CFG rows) at context 250, fp32 oracle "
+                                "sample": f"{c['steps']} decode steps of {B} requests ({2 * B} CFG rows) at context {ctx + 1}, fp32 oracle "
                                           f"(oracle/t3_ref.py; the reference has no CPU path), torch CPU, {c['cores']} threads, "
-                                          f"{c['seconds']:.1f} s"}
+                                          f"{c['seconds']:.1f} s",
+                                "configs0_batch1": {"value": c0["value"], "unit": UNIT, "ms_per_step": c0["ms_per_step"],
+                                                    "sample": f"{c0['steps']} decode steps of 1 request (2 CFG rows) at context {ctx + 1}"}}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def cfg5_lengths(n_requests: int):
+    """BASELINE.json configs[4]: lengths U{100..1000}, seed 7."""
+    import random
+    rng = random.Random(7)
+    return [rng.randint(100, 1000) for _ in range(n_requests)]
+
+
+def run_cfg5(args, rank, world, local, dev, pk, barrier, max_over_ranks):
+    """BASELINE.json configs[4]: `--requests` synthetic requests with mixed 100-1000-token lengths (EOS masked, so the work is
+    fixed), assigned to the replicas by the least-outstanding-KV-tokens dispatcher and run through T3B200Engine.generate() -
+    continuous batching, growing block tables, prefix sharing.  Total work is fixed: strong scaling."""
+    import torch
+    from chatterbox_vllm2_b200.dispatch import assign_requests, kv_traffic_cost
+    from chatterbox_vllm2_b200.engine import SamplingParams
+    lens = cfg5_lengths(args.requests)
+    shares = assign_requests([kv_traffic_cost(P_PROMPT, n) for n in lens], world)
+    mine = shares[rank]
+    slots = min(512, max(1, len(mine)))
+    free_b = torch.cuda.mem_get_info()[0]
+    budget = int(free_b * 0.80) - 6 * (1 << 30)
+    kv_blocks = max(1024, budget // (16 * KV_BYTES_PER_TOKEN_ROW))
+    from chatterbox_vllm2_b200 import T3Dims
+    from chatterbox_vllm2_b200.engine import T3B200Engine
+    from chatterbox_vllm2_b200.model import T3B200Model
+    from chatterbox_vllm2_b200.synthetic import synthetic_checkpoint, synthetic_request
+    dims = T3Dims()
+    m = T3B200Model(dims=dims, device=dev, cfg_scale=0.5)
+    m.load_weights(synthetic_checkpoint(dims).items())
+    eng = T3B200Engine(m, max_num_seqs=slots, max_model_len=MAX_MODEL_LEN, kv_blocks=kv_blocks, prefill_chunk_tokens=16384)
+    prompts, sps = [], []
+    for i in mine:
+        cond, ids = synthetic_request(i % 64, dims, n_text=N_TEXT)            # 64 voices / texts, reused across requests
+        prompts.append({"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}})
+        sps.append(SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=lens[i], ignore_eos=True))
+    # warm-up: capture the graphs of every slot bucket on a small job
+    eng.generate(prompts[:min(len(prompts), slots)], [SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=4, ignore_eos=True)] *
+                 min(len(prompts), slots))
+    sampler = ClockSampler(local)
+    barrier()
+    t0 = time.perf_counter()
+    with sampler:
+        outs = eng.generate(prompts, sps)
+        torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    barrier()
+    dt = max_over_ranks(dt)
+    toks = sum(len(o.outputs[0].token_ids) for o in outs)
+    assert toks == sum(lens[i] for i in mine)
+    total = sum(lens)
+    steps = eng.steps_run
+    line = {"metric": "T3 speech tokens/s, BASELINE.json configs[4] (4096 mixed-length requests, data-parallel replicas)", "value": total / dt,
+            "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": 1, "ms_per_step": 1e3 * dt / max(steps, 1), "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": "BASELINE.json configs[4]: T3 bf16, %d synthetic requests, lengths U{100..1000} seed 7, EOS masked, "
+                                   "P=99, greedy, dispatcher = least outstanding KV traffic" % args.requests,
+                       "requests": args.requests, "slots_per_gpu": slots, "kv_blocks_per_gpu": kv_blocks, "total_tokens": total,
+                       "requests_rank0": len(mine), "preemptions_rank0": eng.preemptions,
+                       "parallelism": f"replicas x{world} (no collective on the data path)"},
+            "e2e": {"value": total / dt, "unit": UNIT, "h2d_bytes_per_step": sum(34 * 1024 * 2 + 70 * 4 for _ in mine) / max(steps, 1),
+                    "d2h_bytes_per_step": len(mine) * MAX_MODEL_LEN * 4 / max(steps, 1),
+                    "api": "T3B200Engine.generate(prompts, per-request SamplingParams)", "seconds": dt},
+            "gpu_launches": steps * eng.launches_per_step(slots), "clocks": sampler.summary()}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
 
 
 def main():

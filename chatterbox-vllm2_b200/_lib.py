@@ -17,7 +17,8 @@ T3B_OK = 0
 T3B_W_BF16, T3B_W_AWQ = 0, 1
 T3B_IMPL_AUTO, T3B_IMPL_GEMV, T3B_IMPL_UMMA = 0, 1, 2
 T3B_COMBINE_BF16, T3B_COMBINE_FP32 = 0, 1
-T3B_EPI_NONE, T3B_EPI_SILU_MUL, T3B_EPI_RESIDUAL = 0, 1, 2
+T3B_EPI_NONE, T3B_EPI_SILU_MUL = 0, 1
+T3B_KV_BF16, T3B_KV_FP8 = 0, 1
 T3B_LIN_GATE_UP_INTERLEAVED = 1
 ERR_NAMES = {-1: "T3B_ERR_ARG", -2: "T3B_ERR_SHAPE", -3: "T3B_ERR_ALIGN", -4: "T3B_ERR_CUDA", -5: "T3B_ERR_UNSUPPORTED"}
 
@@ -38,11 +39,6 @@ class Linear(C.Structure):          # t3b_linear_t
     _fields_ = [("kind", i32), ("n", i32), ("k", i32), ("w", vp), ("scales", vp), ("zeros", vp), ("flags", i32)]
 
 
-class LinearFuse(C.Structure):      # t3b_linear_fuse_t
-    _fields_ = [("x_z", vp), ("x_ss", vp), ("x_ss_tiles", i32), ("norm_w", vp), ("eps", f32), ("res_z", vp), ("out_z", vp),
-                ("out_ss", vp), ("tail_resid", vp), ("tail_norm_w", vp), ("tail_out", vp), ("tail_counters", vp)]
-
-
 class Layer(C.Structure):           # t3b_layer_t
     _fields_ = [("qkv", Linear), ("o", Linear), ("gate_up", Linear), ("down", Linear), ("ln1", vp), ("ln2", vp)]
 
@@ -55,62 +51,53 @@ class Model(C.Structure):           # t3b_model_t
 
 
 class KV(C.Structure):              # t3b_kv_t
-    _fields_ = [("k", vp), ("v", vp), ("layer_stride", i64), ("num_blocks", i32)]
+    _fields_ = [("k", vp), ("v", vp), ("layer_stride", i64), ("num_blocks", i32), ("dtype", i32)]
 
 
 class State(C.Structure):           # t3b_state_t
     _fields_ = [("tokens", vp), ("speech_pos", vp), ("rope_pos", vp), ("ctx_lens", vp), ("block_tables", vp),
                 ("max_blocks", i32), ("history", vp), ("hist_len", vp), ("hist_stride", i32), ("step", vp),
-                ("active", vp), ("stop_token", i32), ("max_ctx", i32)]
+                ("active", vp), ("stop_tokens", vp), ("max_ctx", i32)]
 
 
 class Sampling(C.Structure):        # t3b_sampling_t
     _fields_ = [("cfg_scale", vp), ("repetition_penalty", vp), ("temperature", vp), ("min_p", vp), ("top_p", vp),
-                ("seed", vp), ("combine", i32)]
+                ("seed", vp), ("analyzer_text_tokens", vp), ("combine", i32)]
 
 
-class MegaLayer(C.Structure):       # t3b_mega_layer_t
-    _fields_ = [("qkv", vp), ("o", vp), ("gate_up", vp), ("down", vp), ("ln1", vp), ("ln2", vp)]
+class Options(C.Structure):         # t3b_options_t
+    _fields_ = [("gemv_max_rows", i32), ("gemv_no_norm", i32), ("umma_stages", i32), ("umma_row_chunk", i32),
+                ("umma_split", i32 * 4)]
 
 
-class Mega(C.Structure):            # t3b_mega_t
-    _fields_ = [("layers", vp), ("head", vp)]
-
+p_opt = C.POINTER(Options)
 
 _PROTOS = {
     "t3b_last_error": (C.c_char_p, []),
     "t3b_version": (i32, []),
     "t3b_check_device": (i32, []),
     "t3b_workspace_bytes": (C.c_size_t, [C.POINTER(Model), i32]),
+    "t3b_kv_slice_bytes": (i32, [i32]),
     "t3b_embed_gather": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, vp, vp]),
     "t3b_add_rmsnorm": (i32, [vp, vp, i32, vp, vp, vp, i32, i32, f32, i32, vp]),
-    "t3b_linear_bf16": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, vp]),
-    "t3b_linear_awq": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, vp]),
-    "t3b_linear_fused": (i32, [vp, C.POINTER(Linear), i32, vp, C.POINTER(LinearFuse), i32, i32, vp]),
-    "t3b_z_init": (i32, [vp, i32, i32, vp, vp, vp]),
-    "t3b_z_rmsnorm": (i32, [vp, vp, vp, i32, i32, f32, vp, vp]),
+    "t3b_linear_bf16": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, p_opt, vp]),
+    "t3b_linear_awq": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, p_opt, vp]),
     "t3b_repack_weights_awq": (i32, [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp]),
-    "t3b_attn_decode_fused": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, vp, vp, i32, vp, vp]),
-    "t3b_rope_kv_write": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, i32, vp, vp, i32, vp, vp]),
-    "t3b_paged_attn_decode": (i32, [vp, i32, vp, vp, vp, i32, vp, vp, i32, vp, vp]),
+    "t3b_attn_decode_fused": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, vp]),
+    "t3b_rope_kv_write": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, vp]),
+    "t3b_paged_attn_decode": (i32, [vp, i32, vp, vp, vp, i32, vp, vp, i32, i32, vp, vp]),
+    "t3b_prefill_attn": (i32, [vp, i32, vp, vp, vp, i32, vp, vp, i32, i32, i32, vp, vp]),
+    "t3b_prefill_attn_max_len": (i32, [i32]),
+    "t3b_prefill_embed": (i32, [vp, vp, vp, vp, vp, i32, vp, vp, i32, i32, vp, vp, i32, i32, i32, vp, vp, vp, vp]),
     "t3b_silu_mul": (i32, [vp, vp, i32, i32, i32, vp, vp]),
-    "t3b_forward_tokens": (i32, [C.POINTER(Model), C.POINTER(KV), vp, i32, vp, vp, vp, vp, i32, vp, vp, C.c_size_t, vp]),
-    "t3b_decode_step": (i32, [C.POINTER(Model), C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, C.c_size_t, vp]),
+    "t3b_forward_tokens": (i32, [C.POINTER(Model), C.POINTER(KV), vp, i32, vp, vp, vp, vp, i32, i32, vp, vp, i32, vp, vp, C.c_size_t,
+                                 p_opt, vp]),
+    "t3b_decode_step": (i32, [C.POINTER(Model), C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, C.c_size_t, p_opt, vp]),
     "t3b_head_cfg_sample": (i32, [C.POINTER(Model), vp, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, vp,
-                                  C.c_size_t, vp]),
+                                  C.c_size_t, p_opt, vp]),
     "t3b_sample_logits": (i32, [vp, i32, i32, C.POINTER(Sampling), C.POINTER(State), vp, vp]),
-    "t3b_repacked_bytes": (C.c_size_t, [i32, i32]),
-    "t3b_repack_weights_bf16": (i32, [vp, i32, i32, i32, vp, vp]),
-    "t3b_mega_max_rows": (i32, []),
-    "t3b_mega_workspace_bytes": (C.c_size_t, [C.POINTER(Model), i32]),
-    "t3b_decode_step_mega": (i32, [C.POINTER(Model), C.POINTER(Mega), C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, vp,
-                                   C.c_size_t, vp]),
     "t3b_cfg_sample_head_logits": (i32, [vp, i32, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, vp]),
-    "t3b_fused_weight_bytes": (C.c_size_t, [C.POINTER(Model)]),
-    "t3b_fused_repack": (i32, [C.POINTER(Model), vp, vp]),
-    "t3b_fused_max_rows": (i32, []),
-    "t3b_fused_workspace_bytes": (C.c_size_t, [C.POINTER(Model), i32]),
-    "t3b_decode_step_fused": (i32, [C.POINTER(Model), vp, C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, vp, C.c_size_t, vp]),
+    "t3b_filter_speech_tokens": (i32, [vp, i32, i32, i32, vp, vp, vp]),
 }
 
 _lib = None

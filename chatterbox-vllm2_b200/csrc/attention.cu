@@ -1,273 +1,529 @@
-// F2.4 paged decode attention (llama.py:211-221,231), MHA (group = 1), head_dim 64, block 16.
+// F2.4 paged decode attention (llama.py:211-221,231), MHA (group = 1), head_dim 64, block 16, with F2.3 (llama3 / neox RoPE,
+// rotary_embedding/common.py:144-174) and the KV-cache write (reshape_and_cache) fused in for decode steps.
 //
-// HBM-bound byte work: per (query, head) the kernel streams (ctx) x 128 B of K and of V exactly once.
-// Pool layout [block][head][16 tok][64] makes one (block, head) slice 2 KB contiguous, so a warp's
-// four 128-bit loads per slice are four fully coalesced 512 B segments.
+// HBM-bound byte work: per (query, head) item the kernel streams the row's cached K and V exactly once.  The pool layout
+// [block][head][16 tok][64] makes one (block, head) slice ONE contiguous bulk copy (2 KB bf16 / 1088 B fp8).
 //
-// Decode steps run the FUSED variant: the CTA reads its head's q/k/v straight from the QKV projection
-// output, applies llama3/neox RoPE (F2.3, bf16 roundings of rotary_embedding/common.py:144-174), writes the
-// rotated k and v into the paged pool (reshape_and_cache) and then attends over the row's context including
-// that token - one launch per layer instead of three.
+// Persistent kernel, one CTA per SM, AT_NW warps.  Items (token, head) are dealt round-robin to CTAs; the pages of an item are
+// dealt round-robin to the CTA's warps two at a time ("pair" = pages 2p, 2p+1).  Every warp owns a private ring of S pair slots
+// in shared memory that lane 0 fills with cp.async.bulk (K0 | K1 | V0 | V1 -> one mbarrier per slot) S pairs AHEAD of the pair
+// the warp is computing - across item boundaries, so the head of an item (q/k/v load, RoPE, KV write) and its tail (merge of
+// the warps' online-softmax states through shared memory, fixed warp order -> deterministic) never leave HBM idle.  The first
+// ring fill is issued before griddepcontrol.wait: cached K/V, context lengths and block tables were written by earlier steps
+// (the sampler that advances them does not trigger its dependents early), so only q/k/v of the new token wait for the QKV GEMM.
 //
-// CTA = one (query, head); its NW warps take the row's KV pages round-robin two at a time (16 128-bit
-// loads in flight per lane), keep a private online-softmax state and are merged through shared
-// memory at the end (fixed order -> deterministic).  Dot products are reduced across the 8 lanes of
-// a token with a 7-shuffle butterfly-transpose, softmax statistics with warp shuffles.
-#include <cstdlib>
+// The new token of a decode step never round-trips through the pool: warp 0 seeds its state with (q.k_new, v_new) from
+// registers and stores k (rotated) and v for the following steps.  A request's arithmetic depends on its own context only
+// (pair p -> warp p % AT_NW, merge in warp order), never on the batch it runs in.
+//
+// KVT = 1: FP8-e4m3 K/V with one fp32 scale per (token, head), slice = 16 x 64 B values | 16 x 4 B scales; the scale of a key is
+// applied to its score and the scale of a value to its probability, so the inner products run on the raw fp8 values.
+#include <cuda_fp8.h>
 
 #include "t3b_common.cuh"
 
-#define ATT_PAGES_PER_ITER 2
+#define AT_NW 8
+#define AT_MAXK 128                 // items per CTA whose metadata is staged in shared memory
 
-// 128-bit K/V load that never allocates in L1: a line of the pool is written once (by the step that appends the token) and no
-// kernel keeps pool lines in L1, so there is nothing stale to hit (measured 1.6 us per launch faster than ld.global.cg)
-__device__ __forceinline__ uint4 ldg_kv(const void* p) {
-    uint4 r;
-    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
-    return r;
+struct AttnArgs {
+    const bf16* q;                  // FUSED: qkv bf16 [n_tok, 3 * hidden]; else q bf16 [n_tok, hidden] (already rotated)
+    const int32_t* tok_row;         // KV row of token j (NULL = j)
+    const int32_t* tok_idx;         // index of token j in its row: FUSED = cached tokens before it; else it attends 0..idx
+    const int32_t* rope_pos;
+    const bf16* cos_sin;
+    int max_pos;
+    const int32_t* block_tables;
+    int max_blocks;
+    unsigned char* k_pool;          // layer base
+    unsigned char* v_pool;
+    int n_heads;
+    bf16* out;
+    int n_items;                    // n_tok * n_heads
+};
+
+template <int KVT> struct KvFmt;
+template <> struct KvFmt<0> { static constexpr int SLICE = 2048; };                 // 16 x 64 bf16
+template <> struct KvFmt<1> { static constexpr int SLICE = 1024 + 64; };            // 16 x 64 e4m3 | 16 fp32 scales
+
+__device__ __forceinline__ void fp8x8_to_float(const uint2 v, float* f) {
+    const uint32_t w[2] = {v.x, v.y};
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+#pragma unroll
+        for (int hlf = 0; hlf < 2; ++hlf) {
+            const __half2_raw hr = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)((w[i] >> (16 * hlf)) & 0xffffu), __NV_E4M3);
+            const float2 ff = __half22float2(*reinterpret_cast<const __half2*>(&hr));
+            f[i * 4 + hlf * 2] = ff.x; f[i * 4 + hlf * 2 + 1] = ff.y;
+        }
+    }
 }
 
-// FUSED: q points at the QKV projection output bf16 [n_tok, 3*hidden]; k_pool / v_pool are written.
-// NW = warps per CTA; the min-blocks bound trims registers so that 64 rows x 16 heads (4 warps) is ONE wave of 7 CTAs per SM.
-template <bool FUSED, int NW>
-__global__ void __launch_bounds__(NW * 32, NW == 2 ? 14 : (NW == 4 ? 7 : 3)) paged_attn_decode_kernel(const bf16* __restrict__ q, const int32_t* __restrict__ tok_row,
-                                                                const int32_t* __restrict__ tok_idx,
-                                                                const int32_t* __restrict__ block_tables, int max_blocks,
-                                                                bf16* k_pool, bf16* v_pool, int n_heads, bf16* __restrict__ out,
-                                                                const int32_t* __restrict__ rope_pos, const bf16* __restrict__ cos_sin,
-                                                                int max_pos) {
-    __shared__ float sm_m[8], sm_l[8];
-    __shared__ float sm_acc[8][64];
-    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
-    const int t = blockIdx.x / n_heads, h = blockIdx.x - t * n_heads;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = NW;
+// quantise 8 values of one (token, head) vector whose absolute maximum over all 64 dims is `amax`
+__device__ __forceinline__ uint2 float8_to_fp8(const float* f, float scale) {
+    uint32_t w[2] = {0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_fp8x2_storage_t p = __nv_cvt_float2_to_fp8x2(make_float2(f[2 * i] / scale, f[2 * i + 1] / scale), __NV_SATFINITE, __NV_E4M3);
+        w[i >> 1] |= (uint32_t)p << (16 * (i & 1));
+    }
+    return make_uint2(w[0], w[1]);
+}
+
+// One warp, 32 tokens (pages k0/v0 and, if `two`, k1/v1; first token index tok0), online-softmax update of (m, l, acc).
+// Lane (t4, c) = (lane >> 3, lane & 7) holds dims [8c, 8c+8) of tokens 4j + t4 of each page; qf = q * head_dim^-0.5 * log2(e);
+// tokens >= nc are masked.  acc / l are per-lane partials (folded over t4 / the warp by the caller), m is warp-uniform.
+template <int KVT>
+__device__ __forceinline__ void attn_pair(const unsigned char* k0, const unsigned char* k1, const unsigned char* v0, const unsigned char* v1,
+                                          bool two, int tok0, int nc, const float* qf, int lane, float& m, float& l, float* acc) {
     const int t4 = lane >> 3, c = lane & 7;
-    // Block-table entries of this warp's pages, one iteration per lane (lane i <-> pages (warp + i * NW) * 2 + {0, 1}), fetched once
-    // before the dependency wait instead of one L2 round trip per iteration in front of the K/V loads.  The table is written by
-    // the host (stream-ordered, long before this kernel); entries past the row's context are never used.
-    int my_b0 = 0, my_b1 = 0;
+    float s[8];
+#pragma unroll
+    for (int pg = 0; pg < 2; ++pg) {
+        if (pg == 1 && !two) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s[4 + j] = 0.f;
+            continue;
+        }
+        const unsigned char* kp = pg ? k1 : k0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float kf[8];
+            if (KVT == 1) fp8x8_to_float(*reinterpret_cast<const uint2*>(kp + j * 256 + lane * 8), kf);
+            else unpack8(*reinterpret_cast<const uint4*>(kp + j * 512 + lane * 16), kf);
+            float d = 0.f;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) d = fmaf(qf[e], kf[e], d);
+            s[pg * 4 + j] = d;
+        }
+    }
+    // butterfly-transpose reduce over the 8 lanes (c) of a token: lane c ends with value i == c
+    float w4[4], w2[2], sc;
     {
-        const int trow = tok_row ? ld_act(tok_row + t) : t;
-        const int32_t* btq = block_tables + (size_t)trow * max_blocks;
-        const int pg = (warp + lane * NW) * ATT_PAGES_PER_ITER;
-        if (pg < max_blocks) my_b0 = ld_act(btq + pg);
-        my_b1 = pg + 1 < max_blocks ? ld_act(btq + pg + 1) : my_b0;
+        const bool up = (c & 4) != 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float send = up ? s[i] : s[i + 4], keep = up ? s[i + 4] : s[i];
+            w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+        }
+        const bool up2 = (c & 2) != 0;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const float send = up2 ? w4[i] : w4[i + 2], keep = up2 ? w4[i + 2] : w4[i];
+            w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        }
+        const bool up1 = (c & 1) != 0;
+        const float send = up1 ? w2[0] : w2[1], keep = up1 ? w2[1] : w2[0];
+        sc = keep + __shfl_xor_sync(0xffffffffu, send, 1);
     }
-    if (FUSED) {
-        // Before the dependency wait: pull this (row, head)'s cached K/V lines from HBM into L2 while the QKV projection is
-        // still running.  Hint only - the context length may be one step stale and nothing read here is used for arithmetic
-        // (block-table entries are always valid block indices, so every prefetched address lies inside the pool).
-        // (prefetching a second unit for blocks that are not resident yet was measured slower: 17.6 vs 16.3 us per launch)
-        const int np = min((ld_act(tok_idx + t) + 16) >> 4, max_blocks);
-        const int32_t* btp = block_tables + (size_t)t * max_blocks;
-        for (int i = threadIdx.x; i < np * 32; i += NW * 32) {
-            const int page = i >> 5, w = i & 31;
-            const bf16* line = (w < 16 ? k_pool : v_pool) + (((size_t)ld_act(btp + page) * n_heads + h) * T3B_KV_BLOCK) * 64 + (w & 15) * 64;
-            asm volatile("prefetch.global.L2 [%0];" :: "l"(line));
+    // lane (t4, c) now owns token tok0 + (c >> 2) * 16 + 4 (c & 3) + t4
+    const int tin = 4 * (c & 3) + t4;                  // token inside its page
+    const int my_tok = tok0 + (c >> 2) * 16 + tin;
+    float vsc = 1.f;
+    if (KVT == 1) {
+        if ((c >> 2) == 0 || two) {
+            sc *= reinterpret_cast<const float*>(((c >> 2) ? k1 : k0) + 1024)[tin];
+            vsc = reinterpret_cast<const float*>(((c >> 2) ? v1 : v0) + 1024)[tin];
         }
     }
-    pdl_wait();
-    const int row = tok_row ? ld_act(tok_row + t) : t;
-    const int ctx = ld_act(tok_idx + t) + 1;                      // keys 0..tok_idx[t] (own token is written first)
-    const int n_pages = (ctx + 15) >> 4;
-    const int32_t* bt = block_tables + (size_t)row * max_blocks;
+    if (my_tok >= nc) sc = -INFINITY;
+    const float m_new = fmaxf(m, warp_max(sc));         // finite: the pair holds >= 1 valid token
+    const float corr = exp2f(m - m_new);
+    float pr = exp2f(sc - m_new);
+    l = l * corr + pr;                                  // per-lane partial of the row sum
+    m = m_new;
+    if (KVT == 1) pr = my_tok < nc ? pr * vsc : 0.f;    // the value's scale rides on its probability
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] *= corr;
+#pragma unroll
+    for (int pg = 0; pg < 2; ++pg) {
+        if (pg == 1 && !two) continue;
+        const unsigned char* vp = pg ? v1 : v0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float pj = __shfl_sync(0xffffffffu, pr, t4 * 8 + pg * 4 + j);
+            float vf[8];
+            if (KVT == 1) fp8x8_to_float(*reinterpret_cast<const uint2*>(vp + j * 256 + lane * 8), vf);
+            else unpack8(*reinterpret_cast<const uint4*>(vp + j * 512 + lane * 16), vf);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
+        }
+    }
+}
+
+template <bool FUSED, int S, int KVT>
+__global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs a) {
+    constexpr int SLICE = KvFmt<KVT>::SLICE;
+    constexpr int PAIR = 4 * SLICE;                       // K0 | K1 | V0 | V1
+    extern __shared__ __align__(128) unsigned char at_smem[];
+    unsigned char* ring = at_smem;                        // [AT_NW][S][PAIR]
+    uint64_t* full = reinterpret_cast<uint64_t*>(at_smem + (size_t)AT_NW * S * PAIR);      // [AT_NW * S]
+    float* part_acc = reinterpret_cast<float*>(full + AT_NW * S);                          // [2][AT_NW][64]
+    float* part_ml = part_acc + 2 * AT_NW * 64;                                            // [2][AT_NW][2]
+    int* s_nc = reinterpret_cast<int*>(part_ml + 2 * AT_NW * 2);                           // [AT_MAXK] cached tokens to stream
+    int* s_row = s_nc + AT_MAXK;                                                           // [AT_MAXK] KV row
+
+    pdl_launch_dependents();       // the next kernel's launch overlaps this one (it waits before reading)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t4 = lane >> 3, c = lane & 7;
+    const int G = gridDim.x, H = a.n_heads;
+    const int n_my = (a.n_items - (int)blockIdx.x + G - 1) / G;
+    for (int k = threadIdx.x; k < n_my; k += AT_NW * 32) {
+        const int t = ((int)blockIdx.x + k * G) / H;
+        const int idx = ld_act(a.tok_idx + t);
+        s_nc[k] = FUSED ? idx : idx + 1;
+        s_row[k] = a.tok_row ? ld_act(a.tok_row + t) : t;
+    }
+    if (threadIdx.x < AT_NW * S) mbar_init(&full[threadIdx.x], 1);
+    mbar_fence_init();
+    __syncthreads();
+
+    unsigned char* my_ring = ring + (size_t)warp * S * PAIR;
+    uint64_t* my_full = full + warp * S;
+
+    // ---- producer cursor: (pk, pp) = next pair of this warp to fetch; lane i holds the block ids of this warp's i-th pair of
+    // the cursor's item (cur) and of the item after it (nxt), so a block-table read is never in front of a copy
+    int pk = 0, pp = warp, pn = 0;
+    int b0c = 0, b1c = 0, b0n = 0, b1n = 0;
+    auto load_bt = [&](int k, int& b0, int& b1) {
+        b0 = 0; b1 = 0;
+        if (k < n_my) {
+            const int npg = (s_nc[k] + 15) >> 4;
+            const int pg = (warp + lane * AT_NW) * 2;
+            const int32_t* bt = a.block_tables + (size_t)s_row[k] * a.max_blocks;
+            if (pg < npg) b0 = ld_act(bt + pg);
+            if (pg + 1 < npg) b1 = ld_act(bt + pg + 1);
+        }
+    };
+    load_bt(0, b0c, b1c);
+    load_bt(1, b0n, b1n);
+    auto produce = [&]() {
+        while (pk < n_my && pp >= ((s_nc[pk] + 31) >> 5)) {
+            ++pk; pp = warp;
+            b0c = b0n; b1c = b1n;
+            load_bt(pk + 1, b0n, b1n);
+        }
+        if (pk >= n_my) return;                                            // warp-uniform
+        const int j = (pp - warp) / AT_NW;
+        const int blk0 = __shfl_sync(0xffffffffu, b0c, j), blk1 = __shfl_sync(0xffffffffu, b1c, j);
+        if (lane == 0) {
+            const int h = ((int)blockIdx.x + pk * G) % H;
+            const bool two = pp * 2 + 1 < ((s_nc[pk] + 15) >> 4);
+            const int slot = pn % S;
+            unsigned char* dst = my_ring + (size_t)slot * PAIR;
+            const size_t o0 = ((size_t)blk0 * H + h) * SLICE, o1 = ((size_t)blk1 * H + h) * SLICE;
+            mbar_expect_tx(&my_full[slot], (two ? 4u : 2u) * SLICE);
+            bulk_load_1d(dst, a.k_pool + o0, SLICE, &my_full[slot]);
+            bulk_load_1d(dst + 2 * SLICE, a.v_pool + o0, SLICE, &my_full[slot]);
+            if (two) {
+                bulk_load_1d(dst + SLICE, a.k_pool + o1, SLICE, &my_full[slot]);
+                bulk_load_1d(dst + 3 * SLICE, a.v_pool + o1, SLICE, &my_full[slot]);
+            }
+        }
+        ++pn; pp += AT_NW;
+    };
+    // FUSED (decode): everything the ring reads was written by earlier steps -> the first fill goes out before the dependency
+    // wait.  Otherwise (prefill) the K/V of this very pass were written by the kernel right in front of this one.
+    if (!FUSED) pdl_wait();
+#pragma unroll 1
+    for (int i = 0; i < S; ++i) produce();
+    if (FUSED) pdl_wait();
     const float kScale = 0.125f * 1.4426950408889634f;   // head_dim^-0.5 * log2(e)
-
-    float qf[8];
-    if (FUSED) {
-        const int hidden = n_heads * 64;
-        const bf16* src = q + (size_t)t * 3 * hidden + h * 64 + c * 8;
-        float kf[8], cs[8], sn[8];
-        unpack8(ld_act(reinterpret_cast<const uint4*>(src)), qf);
-        unpack8(ld_act(reinterpret_cast<const uint4*>(src + hidden)), kf);
-        const uint4 vraw = ld_act(reinterpret_cast<const uint4*>(src + 2 * hidden));
-        int pos = ld_act(rope_pos + t);
-        pos = min(max(pos, 0), max_pos - 1);
-        unpack8(*reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + (c & 3) * 8), cs);
-        unpack8(*reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + 32 + (c & 3) * 8), sn);
-        const bool hi = c >= 4;                           // lanes c < 4 hold x1 (dims 0..31), c >= 4 hold x2
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4), kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
-            // o1 = x1*cos - x2*sin ; o2 = x2*cos + x1*sin, every product and the sum rounded to bf16
-            qf[e] = hi ? bf16_round(bf16_round(qf[e] * cs[e]) + bf16_round(qp * sn[e])) : bf16_round(bf16_round(qf[e] * cs[e]) - bf16_round(qp * sn[e]));
-            kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
-        }
-        if (warp == 0 && t4 == 0) {
-            const int idx = ctx - 1;
-            const size_t slot = (((size_t)ld_act(bt + (idx >> 4)) * n_heads + h) * T3B_KV_BLOCK + (idx & 15)) * 64 + c * 8;
-            *reinterpret_cast<uint4*>(k_pool + slot) = pack8(kf);
-            *reinterpret_cast<uint4*>(v_pool + slot) = vraw;
-        }
-        __syncthreads();                                  // the new K/V line is visible to every warp of this CTA
-    } else {
-        unpack8(ld_act(reinterpret_cast<const uint4*>(q + ((size_t)t * n_heads + h) * 64 + c * 8)), qf);
-    }
-#pragma unroll
-    for (int e = 0; e < 8; ++e) qf[e] *= kScale;
-
-    float m = -INFINITY, l = 0.f, acc[8];
-#pragma unroll
-    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
-
-    int iter = 0;
-    for (int p0 = warp * ATT_PAGES_PER_ITER; p0 < n_pages; p0 += nw * ATT_PAGES_PER_ITER, ++iter) {
-        uint4 kv[ATT_PAGES_PER_ITER][4], vv[ATT_PAGES_PER_ITER][4];
-        int blk2[2];
-        if (iter < 32) {                                                 // warp-uniform
-            blk2[0] = __shfl_sync(0xffffffffu, my_b0, iter);
-            blk2[1] = __shfl_sync(0xffffffffu, my_b1, iter);
+    const int hidden = H * 64;
+    // head of an item: q (and k, v of the new token) with the RoPE table rows, fetched one item ahead
+    uint4 hq, hk, hv, hcs, hsn;
+    int hblk = 0;                                           // block that receives the new token
+    auto load_head = [&](int k) {
+        hq = hk = hv = hcs = hsn = make_uint4(0, 0, 0, 0);
+        if (k >= n_my) return;
+        const int item = (int)blockIdx.x + k * G, t = item / H, h = item - t * H;
+        if (FUSED) {
+            const bf16* src = a.q + (size_t)t * 3 * hidden + h * 64 + c * 8;
+            hq = ld_act(reinterpret_cast<const uint4*>(src));
+            hk = ld_act(reinterpret_cast<const uint4*>(src + hidden));
+            hv = ld_act(reinterpret_cast<const uint4*>(src + 2 * hidden));
+            int pos = ld_act(a.rope_pos + t);
+            pos = min(max(pos, 0), a.max_pos - 1);
+            hcs = __ldg(reinterpret_cast<const uint4*>(a.cos_sin + (size_t)pos * 64 + (c & 3) * 8));
+            hsn = __ldg(reinterpret_cast<const uint4*>(a.cos_sin + (size_t)pos * 64 + 32 + (c & 3) * 8));
+            if (warp == 0) hblk = ld_act(a.block_tables + (size_t)s_row[k] * a.max_blocks + (s_nc[k] >> 4));
         } else {
-            blk2[0] = ld_act(bt + p0);
-            blk2[1] = ld_act(bt + (p0 + 1 < n_pages ? p0 + 1 : p0));
+            hq = ld_act(reinterpret_cast<const uint4*>(a.q + ((size_t)t * H + h) * 64 + c * 8));
         }
+    };
+    load_head(0);
+
+    int cn = 0;
+#pragma unroll 1
+    for (int k = 0; k < n_my; ++k) {
+        const int item = (int)blockIdx.x + k * G, t = item / H, h = item - t * H;
+        const int nc = s_nc[k], np = (nc + 31) >> 5, n_pages = (nc + 15) >> 4;
+        float qf[8], m = -INFINITY, l = 0.f, acc[8];
 #pragma unroll
-        for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp) {
-            const int page = p0 + pp;
-            const int blk = page < n_pages ? blk2[pp] : blk2[0];         // tail page re-reads a valid page, masked below
-            const size_t base = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK) * 64 + (size_t)lane * 8;
+        for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+        unpack8(hq, qf);
+        if (FUSED) {
+            float kf[8], cs[8], sn[8], vf[8];
+            unpack8(hk, kf); unpack8(hcs, cs); unpack8(hsn, sn); unpack8(hv, vf);
+            const bool hi = c >= 4;                           // lanes c < 4 hold x1 (dims 0..31), c >= 4 hold x2
 #pragma unroll
-            for (int j = 0; j < 4; ++j) kv[pp][j] = ldg_kv(k_pool + base + j * 256);
+            for (int e = 0; e < 8; ++e) {
+                const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4), kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
+                // o1 = x1*cos - x2*sin ; o2 = x2*cos + x1*sin, every product and the sum rounded to bf16
+                qf[e] = hi ? bf16_round(bf16_round(qf[e] * cs[e]) + bf16_round(qp * sn[e])) : bf16_round(bf16_round(qf[e] * cs[e]) - bf16_round(qp * sn[e]));
+                kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
+            }
+            if (warp == 0) {
+                // the new token: stored for the following steps, and attended to straight from registers
+                const size_t sl = ((size_t)hblk * H + h) * SLICE;
+                if (KVT == 1) {
+                    float ka = 0.f, va = 0.f;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) vv[pp][j] = ldg_kv(v_pool + base + j * 256);
-        }
-        // partial dot products: value i = pp*4 + j belongs to token p0*16 + pp*16 + 4j + t4
-        float s[8];
+                    for (int e = 0; e < 8; ++e) { ka = fmaxf(ka, fabsf(kf[e])); va = fmaxf(va, fabsf(vf[e])); }
 #pragma unroll
-        for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp)
+                    for (int o = 1; o < 8; o <<= 1) { ka = fmaxf(ka, __shfl_xor_sync(0xffffffffu, ka, o)); va = fmaxf(va, __shfl_xor_sync(0xffffffffu, va, o)); }
+                    const float ks = ka > 0.f ? ka / 448.f : 1.f, vs = va > 0.f ? va / 448.f : 1.f;
+                    const uint2 kq = float8_to_fp8(kf, ks), vq = float8_to_fp8(vf, vs);
+                    if (t4 == 0) {
+                        *reinterpret_cast<uint2*>(a.k_pool + sl + (nc & 15) * 64 + c * 8) = kq;
+                        *reinterpret_cast<uint2*>(a.v_pool + sl + (nc & 15) * 64 + c * 8) = vq;
+                        if (c == 0) {
+                            *reinterpret_cast<float*>(a.k_pool + sl + 1024 + (nc & 15) * 4) = ks;
+                            *reinterpret_cast<float*>(a.v_pool + sl + 1024 + (nc & 15) * 4) = vs;
+                        }
+                    }
+                    // attend to what the following steps will read back: the dequantised values
+                    fp8x8_to_float(kq, kf); fp8x8_to_float(vq, vf);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                float kf[8];
-                unpack8(kv[pp][j], kf);
+                    for (int e = 0; e < 8; ++e) { kf[e] *= ks; vf[e] *= vs; }
+                } else if (t4 == 0) {
+                    *reinterpret_cast<uint4*>(a.k_pool + sl + ((nc & 15) * 64 + c * 8) * 2) = pack8(kf);
+                    *reinterpret_cast<uint4*>(a.v_pool + sl + ((nc & 15) * 64 + c * 8) * 2) = hv;
+                }
                 float d = 0.f;
 #pragma unroll
                 for (int e = 0; e < 8; ++e) d = fmaf(qf[e], kf[e], d);
-                s[pp * 4 + j] = d;
-            }
-        // butterfly-transpose reduce over the 8 lanes (c) of a token: lane c ends with value i == c
-        float w4[4], w2[2], sc;
-        {
-            const bool up = (c & 4) != 0;
+                d += __shfl_xor_sync(0xffffffffu, d, 1);
+                d += __shfl_xor_sync(0xffffffffu, d, 2);
+                d += __shfl_xor_sync(0xffffffffu, d, 4);
+                m = d * kScale;
+                l = lane == 0 ? 1.f : 0.f;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float send = up ? s[i] : s[i + 4], keep = up ? s[i + 4] : s[i];
-                w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+                for (int e = 0; e < 8; ++e) acc[e] = t4 == 0 ? vf[e] : 0.f;
             }
-            const bool up2 = (c & 2) != 0;
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const float send = up2 ? w4[i] : w4[i + 2], keep = up2 ? w4[i + 2] : w4[i];
-                w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
-            }
-            const bool up1 = (c & 1) != 0;
-            const float send = up1 ? w2[0] : w2[1], keep = up1 ? w2[1] : w2[0];
-            sc = keep + __shfl_xor_sync(0xffffffffu, send, 1);
         }
-        const int my_tok = (p0 + (c >> 2)) * 16 + 4 * (c & 3) + t4;
-        if (my_tok >= ctx) sc = -INFINITY;
-        const float m_new = fmaxf(m, warp_max(sc));     // finite: page p0 always holds >= 1 valid token
-        const float corr = exp2f(m - m_new);
-        const float pr = exp2f(sc - m_new);
-        l = l * corr + pr;                              // per-lane partial of the row sum
-        m = m_new;
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] *= corr;
-#pragma unroll
-        for (int pp = 0; pp < ATT_PAGES_PER_ITER; ++pp)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float pj = __shfl_sync(0xffffffffu, pr, t4 * 8 + pp * 4 + j);
-                float vf[8];
-                unpack8(vv[pp][j], vf);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
-            }
-    }
-    // fold the four token groups (t4) of the warp, then the row sum
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-        acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
-        acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
-    }
-    l = warp_sum(l);
-    if (lane < 8) {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) sm_acc[warp][lane * 8 + e] = acc[e];
-    }
-    if (lane == 0) { sm_m[warp] = m; sm_l[warp] = l; }
-    __syncthreads();
-    if (threadIdx.x < 64) {
-        float mm = -INFINITY;
-        for (int w = 0; w < nw; ++w) mm = fmaxf(mm, sm_m[w]);
-        float ll = 0.f, o = 0.f;
-        for (int w = 0; w < nw; ++w) {
-            const float f = sm_m[w] == -INFINITY ? 0.f : exp2f(sm_m[w] - mm);
-            ll += sm_l[w] * f;
-            o += sm_acc[w][threadIdx.x] * f;
+        for (int e = 0; e < 8; ++e) qf[e] *= kScale;
+        load_head(k + 1);                                  // in flight while this item's pairs are processed
+
+#pragma unroll 1
+        for (int pr = warp; pr < np; pr += AT_NW) {
+            const int slot = cn % S;
+            mbar_wait(&my_full[slot], (uint32_t)((cn / S) & 1));
+            const unsigned char* sl = my_ring + (size_t)slot * PAIR;
+            const bool two = pr * 2 + 1 < n_pages;         // warp-uniform
+            attn_pair<KVT>(sl, sl + SLICE, sl + 2 * SLICE, sl + 3 * SLICE, two, pr * 32, nc, qf, lane, m, l, acc);
+            ++cn;
+            __syncwarp();                                   // every lane is done reading the slot
+            produce();                                      // refill it with the pair S ahead
         }
-        out[((size_t)t * n_heads + h) * 64 + threadIdx.x] = __float2bfloat16_rn(o / ll);
+        // fold the four token groups (t4) of the warp, then the row sum; park the warp's state
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
+            acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
+        }
+        l = warp_sum(l);
+        float* pa = part_acc + ((k & 1) * AT_NW + warp) * 64;
+        if (lane < 8) {
+            *reinterpret_cast<float4*>(pa + lane * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            *reinterpret_cast<float4*>(pa + lane * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+        }
+        if (lane == 0) { part_ml[((k & 1) * AT_NW + warp) * 2] = m; part_ml[((k & 1) * AT_NW + warp) * 2 + 1] = l; }
+        __syncthreads();
+        if (threadIdx.x < 64) {
+            const float* pm = part_ml + (k & 1) * AT_NW * 2;
+            const float* pb = part_acc + (k & 1) * AT_NW * 64;
+            float mm = -INFINITY;
+#pragma unroll
+            for (int w = 0; w < AT_NW; ++w) mm = fmaxf(mm, pm[w * 2]);
+            float ll = 0.f, o = 0.f;
+#pragma unroll
+            for (int w = 0; w < AT_NW; ++w) {
+                const float f = pm[w * 2] == -INFINITY ? 0.f : exp2f(pm[w * 2] - mm);
+                ll += pm[w * 2 + 1] * f;
+                o += pb[w * 64 + threadIdx.x] * f;
+            }
+            a.out[((size_t)t * H + h) * 64 + threadIdx.x] = __float2bfloat16_rn(o / ll);
+        }
     }
 }
 
-// warps = 0: pick by occupancy (enough CTAs x warps to cover the machine at small batch, fewer at large)
-int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
-                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, void* out, int warps, cudaStream_t s) {
-    const long units = (long)n_tok * n_heads;
-    const int sms = t3b_num_sms();
-    int nw = warps;
-    if (nw <= 0) {
-        nw = 8;
-        if (units >= (long)sms * 8) nw = 2;
-        else if (units >= (long)sms * 4) nw = 4;
+// ------------------------------------------------------------------ prefill (causal) attention
+// CTA = one (sequence, head): the prompt's K/V slices come from the pool into shared memory ONCE (bulk copies, one mbarrier);
+// the CTA's warps then take the prompt's queries round-robin, each query a sequential sweep over its causal prefix with the
+// same 32-token update as the decode kernel (a prompt's result depends on nothing but the prompt).
+struct PrefillArgs {
+    const bf16* q;                  // bf16 [n_tok, hidden], rotated
+    const int32_t* seq_start;       // [n_seq + 1]
+    const int32_t* seq_row;         // [n_seq]
+    const int32_t* block_tables;
+    int max_blocks;
+    const unsigned char* k_pool;
+    const unsigned char* v_pool;
+    int n_heads;
+    bf16* out;
+    int max_pages;
+};
+
+template <int KVT>
+__global__ void __launch_bounds__(AT_NW * 32) prefill_attn_kernel(const PrefillArgs a) {
+    constexpr int SLICE = KvFmt<KVT>::SLICE;
+    extern __shared__ __align__(128) unsigned char at_smem[];
+    __shared__ uint64_t bar;
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, c = lane & 7;
+    const int H = a.n_heads, seq = blockIdx.x / H, h = blockIdx.x - seq * H;
+    const int t0 = a.seq_start[seq], P = a.seq_start[seq + 1] - t0;
+    const int n_pages = min((P + 15) >> 4, a.max_pages);
+    unsigned char* ks = at_smem;                                   // [max_pages][SLICE]
+    unsigned char* vs = at_smem + (size_t)a.max_pages * SLICE;
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
+    __syncthreads();
+    pdl_wait();                                                    // the K/V of this pass were written by the kernel in front
+    if (warp == 0) {
+        if (lane == 0) mbar_expect_tx(&bar, (uint32_t)n_pages * 2u * SLICE);
+        __syncwarp();
+        const int32_t* bt = a.block_tables + (size_t)a.seq_row[seq] * a.max_blocks;
+        for (int p = lane; p < n_pages; p += 32) {
+            const size_t off = ((size_t)bt[p] * H + h) * SLICE;
+            bulk_load_1d(ks + (size_t)p * SLICE, a.k_pool + off, SLICE, &bar);
+            bulk_load_1d(vs + (size_t)p * SLICE, a.v_pool + off, SLICE, &bar);
+        }
     }
-    (void)sms;
-    T3B_CHECK_ARG(nw == 2 || nw == 4 || nw == 8, "paged attention: warps %d must be 2, 4 or 8", nw);
-    auto kern = nw == 2 ? paged_attn_decode_kernel<false, 2> : (nw == 4 ? paged_attn_decode_kernel<false, 4> : paged_attn_decode_kernel<false, 8>);
-    T3B_CUDA(t3b_launch(kern, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)q, tok_row, tok_idx,
-                        block_tables, max_blocks, (bf16*)const_cast<void*>(k_pool), (bf16*)const_cast<void*>(v_pool), n_heads, (bf16*)out,
-                        (const int32_t*)nullptr, (const bf16*)nullptr, 0));
+    mbar_wait(&bar, 0);
+    const float kScale = 0.125f * 1.4426950408889634f;
+    // longest queries first: warp w takes queries P-1-w, P-1-w-NW, ...
+    for (int j = P - 1 - warp; j >= 0; j -= AT_NW) {
+        float qf[8], m = -INFINITY, l = 0.f, acc[8];
+        unpack8(ld_act(reinterpret_cast<const uint4*>(a.q + ((size_t)(t0 + j) * H + h) * 64 + c * 8)), qf);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { qf[e] *= kScale; acc[e] = 0.f; }
+        const int nc = j + 1, np = (nc + 31) >> 5, npg = (nc + 15) >> 4;
+        for (int pr = 0; pr < np; ++pr) {
+            const bool two = pr * 2 + 1 < npg;
+            attn_pair<KVT>(ks + (size_t)(2 * pr) * SLICE, ks + (size_t)(2 * pr + 1) * SLICE, vs + (size_t)(2 * pr) * SLICE,
+                           vs + (size_t)(2 * pr + 1) * SLICE, two, pr * 32, nc, qf, lane, m, l, acc);
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
+            acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
+        }
+        l = warp_sum(l);
+        if (lane < 8) {
+            float o[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] = acc[e] / l;
+            *reinterpret_cast<uint4*>(a.out + ((size_t)(t0 + j) * H + h) * 64 + lane * 8) = pack8(o);
+        }
+    }
+}
+
+extern "C" int32_t t3b_prefill_attn_max_len(int32_t kv_dtype) {
+    const int slice = kv_dtype == T3B_KV_FP8 ? KvFmt<1>::SLICE : KvFmt<0>::SLICE;
+    return (220 * 1024 / (2 * slice)) * T3B_KV_BLOCK;
+}
+
+extern "C" int32_t t3b_prefill_attn(const void* q, int32_t n_seq, const int32_t* seq_start, const int32_t* seq_row,
+                                    const int32_t* block_tables, int32_t max_blocks, const void* k_pool, const void* v_pool,
+                                    int32_t n_heads, int32_t kv_dtype, int32_t max_seq_len, void* out, void* stream) {
+    T3B_CHECK_ARG(q && seq_start && seq_row && block_tables && k_pool && v_pool && out, "t3b_prefill_attn: null pointer");
+    T3B_CHECK_ARG(n_seq >= 0 && max_blocks > 0 && n_heads >= 1 && max_seq_len >= 1, "t3b_prefill_attn: bad sizes");
+    T3B_CHECK_ARG(kv_dtype == T3B_KV_BF16 || kv_dtype == T3B_KV_FP8, "t3b_prefill_attn: unknown KV dtype %d", kv_dtype);
+    T3B_CHECK_SHAPE(max_seq_len <= t3b_prefill_attn_max_len(kv_dtype), "t3b_prefill_attn: max_seq_len %d > %d", max_seq_len,
+                    t3b_prefill_attn_max_len(kv_dtype));
+    T3B_CHECK_ALIGN(q); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
+    if (n_seq == 0) return T3B_OK;
+    PrefillArgs a = {};
+    a.q = (const bf16*)q; a.seq_start = seq_start; a.seq_row = seq_row; a.block_tables = block_tables; a.max_blocks = max_blocks;
+    a.k_pool = (const unsigned char*)k_pool; a.v_pool = (const unsigned char*)v_pool; a.n_heads = n_heads; a.out = (bf16*)out;
+    a.max_pages = (max_seq_len + 15) / 16;
+    if (a.max_pages > max_blocks) a.max_pages = max_blocks;
+    const int slice = kv_dtype == T3B_KV_FP8 ? KvFmt<1>::SLICE : KvFmt<0>::SLICE;
+    const size_t smem = (size_t)a.max_pages * 2 * slice;
+    auto kern = kv_dtype == T3B_KV_FP8 ? prefill_attn_kernel<1> : prefill_attn_kernel<0>;
+    T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    T3B_CUDA(t3b_launch(kern, dim3((unsigned)(n_seq * n_heads)), dim3(AT_NW * 32), smem, t3b_stream(stream), a));
     return T3B_OK;
 }
 
-static int pick_warps(long units) {
-    static const int forced = []() { const char* e = getenv("T3B_ATTN_WARPS"); return e ? atoi(e) : 0; }();
-    if (forced == 2 || forced == 4 || forced == 8) return forced;
+// ------------------------------------------------------------------ host
+static int at_ring_depth(int kvt) { return kvt == 1 ? 5 : 3; }
+
+template <bool FUSED, int S, int KVT>
+static cudaError_t launch_ring(const AttnArgs& a, cudaStream_t s) {
+    constexpr int PAIR = 4 * KvFmt<KVT>::SLICE;
+    const size_t smem = (size_t)AT_NW * S * PAIR + AT_NW * S * 8 + 2 * AT_NW * 66 * 4 + 2 * AT_MAXK * 4;
+    auto kern = attn_ring_kernel<FUSED, S, KVT>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
     const int sms = t3b_num_sms();
-    if (units >= (long)sms * 8) return 2;
-    if (units >= (long)sms * 4) return 4;
-    return 8;
+    int grid = a.n_items < sms ? a.n_items : sms;
+    const int need = (a.n_items + AT_MAXK - 1) / AT_MAXK;
+    if (grid < need) grid = need;
+    return t3b_launch(kern, dim3((unsigned)grid), dim3(AT_NW * 32), smem, s, a);
+}
+
+static int32_t attn_launch(bool fused, const AttnArgs& a, int kv_dtype, cudaStream_t s) {
+    T3B_CHECK_SHAPE(a.max_blocks <= 2 * AT_NW * 32, "attention: max_blocks %d > %d (context > %d tokens)", a.max_blocks, 2 * AT_NW * 32,
+                    2 * AT_NW * 32 * T3B_KV_BLOCK);
+    T3B_CHECK_ARG(kv_dtype == T3B_KV_BF16 || kv_dtype == T3B_KV_FP8, "attention: unknown KV dtype %d", kv_dtype);
+    cudaError_t e;
+    if (kv_dtype == T3B_KV_FP8) e = fused ? launch_ring<true, 5, 1>(a, s) : launch_ring<false, 5, 1>(a, s);
+    else e = fused ? launch_ring<true, 3, 0>(a, s) : launch_ring<false, 3, 0>(a, s);
+    (void)at_ring_depth;
+    T3B_CUDA(e);
+    return T3B_OK;
+}
+
+int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
+                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, cudaStream_t s) {
+    AttnArgs a = {};
+    a.q = (const bf16*)q; a.tok_row = tok_row; a.tok_idx = tok_idx; a.block_tables = block_tables; a.max_blocks = max_blocks;
+    a.k_pool = (unsigned char*)const_cast<void*>(k_pool); a.v_pool = (unsigned char*)const_cast<void*>(v_pool);
+    a.n_heads = n_heads; a.out = (bf16*)out; a.n_items = n_tok * n_heads;
+    return attn_launch(false, a, kv_dtype, s);
 }
 
 // decode step: one token per KV row (token j <-> row j)
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
-                              const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, void* out, cudaStream_t s) {
-    const long units = (long)n_tok * n_heads;
-    const int nw = pick_warps(units);
-    auto kern = nw == 2 ? paged_attn_decode_kernel<true, 2> : (nw == 4 ? paged_attn_decode_kernel<true, 4> : paged_attn_decode_kernel<true, 8>);
-    T3B_CUDA(t3b_launch(kern, dim3((unsigned)units), dim3(nw * 32), 0, s, (const bf16*)qkv,
-                        (const int32_t*)nullptr, tok_idx, block_tables, max_blocks, (bf16*)k_pool, (bf16*)v_pool, n_heads, (bf16*)out, rope_pos,
-                        (const bf16*)rope_cos_sin, max_pos));
-    return T3B_OK;
+                              const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, int kv_dtype, void* out,
+                              cudaStream_t s) {
+    AttnArgs a = {};
+    a.q = (const bf16*)qkv; a.tok_idx = tok_idx; a.rope_pos = rope_pos; a.cos_sin = (const bf16*)rope_cos_sin; a.max_pos = max_pos;
+    a.block_tables = block_tables; a.max_blocks = max_blocks; a.k_pool = (unsigned char*)k_pool; a.v_pool = (unsigned char*)v_pool;
+    a.n_heads = n_heads; a.out = (bf16*)out; a.n_items = n_tok * n_heads;
+    return attn_launch(true, a, kv_dtype, s);
 }
 
 extern "C" int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const int32_t* tok_idx, const int32_t* rope_pos,
                                          const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables, int32_t max_blocks,
-                                         void* k_pool, void* v_pool, int32_t n_heads, void* out, void* stream) {
+                                         void* k_pool, void* v_pool, int32_t n_heads, int32_t kv_dtype, void* out, void* stream) {
     T3B_CHECK_ARG(qkv && tok_idx && rope_pos && rope_cos_sin && block_tables && k_pool && v_pool && out, "t3b_attn_decode_fused: null pointer");
     T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && max_pos > 0 && n_heads >= 1, "t3b_attn_decode_fused: bad sizes");
     T3B_CHECK_ALIGN(qkv); T3B_CHECK_ALIGN(rope_cos_sin); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
     if (n_tok == 0) return T3B_OK;
-    return t3b_attn_fused_launch(qkv, n_tok, tok_idx, rope_pos, rope_cos_sin, max_pos, block_tables, max_blocks, k_pool, v_pool, n_heads, out,
-                                 t3b_stream(stream));
+    return t3b_attn_fused_launch(qkv, n_tok, tok_idx, rope_pos, rope_cos_sin, max_pos, block_tables, max_blocks, k_pool, v_pool, n_heads,
+                                 kv_dtype, out, t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
                                          const int32_t* block_tables, int32_t max_blocks, const void* k_pool, const void* v_pool,
-                                         int32_t n_heads, void* out, void* stream) {
+                                         int32_t n_heads, int32_t kv_dtype, void* out, void* stream) {
     T3B_CHECK_ARG(q && tok_idx && block_tables && k_pool && v_pool && out, "t3b_paged_attn_decode: null pointer");
     T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && n_heads >= 1, "t3b_paged_attn_decode: bad sizes");
     T3B_CHECK_ALIGN(q); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
     if (n_tok == 0) return T3B_OK;
-    return t3b_paged_attn_launch(q, n_tok, tok_row, tok_idx, block_tables, max_blocks, k_pool, v_pool, n_heads, out, 0, t3b_stream(stream));
+    return t3b_paged_attn_launch(q, n_tok, tok_row, tok_idx, block_tables, max_blocks, k_pool, v_pool, n_heads, kv_dtype, out,
+                                 t3b_stream(stream));
 }

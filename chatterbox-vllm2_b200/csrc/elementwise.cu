@@ -1,6 +1,8 @@
 // E1 embedding gather, F2.1 fused add+RMSNorm, F2.3 RoPE + paged-KV write, F2.6 SiLU*mul.
 // All are HBM/L2-bound byte work: 128-bit accesses, one pass, bf16 rounding at the points where
 // the reference's bf16 pipeline materialises a tensor (see oracle/t3_ref.py header).
+#include <cuda_fp8.h>
+
 #include "t3b_common.cuh"
 
 // ------------------------------------------------------------------ E1
@@ -91,59 +93,17 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
     }
 }
 
-// ------------------------------------------------------------------ fp32 residual stream of a decode step
-// (t3b_linear_fused keeps F2.1 inside the projections; these two kernels open and close the stream)
-// z[row] = float(x[row]), ss[tile][row] = sum of squares of features [128 tile, 128 tile + 128).  One CTA per row.
-__global__ void __launch_bounds__(128) z_init_kernel(const uint4* __restrict__ x, float4* __restrict__ z, float* __restrict__ ss,
-                                                     int hidden8, int rows) {
-    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
-    pdl_wait();
-    const int row = blockIdx.x;
-    for (int i = threadIdx.x; i < hidden8; i += 128) {            // hidden8 % 16 == 0: a 16-lane group never straddles a tile
-        float v[8];
-        unpack8(ld_act(x + (size_t)row * hidden8 + i), v);
-        z[((size_t)row * hidden8 + i) * 2] = make_float4(v[0], v[1], v[2], v[3]);
-        z[((size_t)row * hidden8 + i) * 2 + 1] = make_float4(v[4], v[5], v[6], v[7]);
-        float q = 0.f;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) q += v[e] * v[e];
-#pragma unroll
-        for (int o = 8; o > 0; o >>= 1) q += __shfl_xor_sync(0xffffffffu, q, o);
-        if ((threadIdx.x & 15) == 0) ss[(size_t)(i >> 4) * rows + row] = q;
-    }
-}
-
-// y = bf16(bf16(z * rstd) * w), rstd from the per-tile sums (fixed order).  One CTA per row.
-__global__ void __launch_bounds__(128) z_rmsnorm_kernel(const float4* __restrict__ z, const float* __restrict__ ss,
-                                                        const uint4* __restrict__ weight, uint4* __restrict__ y, int hidden8, int rows,
-                                                        float eps) {
-    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
-    pdl_wait();
-    const int row = blockIdx.x;
-    float tot = 0.f;
-    for (int t = 0; t < hidden8 / 16; ++t) tot += ld_act(ss + (size_t)t * rows + row);
-    const float rstd = rsqrtf(tot / (float)(hidden8 * 8) + eps);
-    for (int i = threadIdx.x; i < hidden8; i += 128) {
-        const float4 a = ld_act(z + ((size_t)row * hidden8 + i) * 2), b = ld_act(z + ((size_t)row * hidden8 + i) * 2 + 1);
-        float w[8], o[8];
-        unpack8(weight[i], w);
-        o[0] = bf16_round(a.x * rstd) * w[0]; o[1] = bf16_round(a.y * rstd) * w[1];
-        o[2] = bf16_round(a.z * rstd) * w[2]; o[3] = bf16_round(a.w * rstd) * w[3];
-        o[4] = bf16_round(b.x * rstd) * w[4]; o[5] = bf16_round(b.y * rstd) * w[5];
-        o[6] = bf16_round(b.z * rstd) * w[6]; o[7] = bf16_round(b.w * rstd) * w[7];
-        y[(size_t)row * hidden8 + i] = pack8(o);
-    }
-}
-
 // ------------------------------------------------------------------ F2.3 + KV write
 // One CTA per token, one warp per head: lane j rotates the pair (j, j+32) of q and k
 // (rotary_embedding/common.py:144-174 in bf16 tensor arithmetic: each product and the sum round).
+// KVT = 1: K (rotated) and V are stored as e4m3 with one fp32 scale per (token, head) = max|x| / 448 (T3B_KV_FP8).
+template <int KVT>
 __global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restrict__ qkv, const float* __restrict__ partials, int n_split,
                                                             size_t split_stride, const int32_t* __restrict__ tok_row,
                                                             const int32_t* __restrict__ tok_idx, const int32_t* __restrict__ rope_pos,
                                                             const bf16* __restrict__ cos_sin, int max_pos,
                                                             const int32_t* __restrict__ block_tables, int max_blocks,
-                                                            bf16* __restrict__ k_pool, bf16* __restrict__ v_pool, int n_heads,
+                                                            unsigned char* __restrict__ k_pool, unsigned char* __restrict__ v_pool, int n_heads,
                                                             bf16* __restrict__ q_out) {
     pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
     pdl_wait();
@@ -182,12 +142,108 @@ __global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restri
         bf16* qo = q_out + (size_t)t * hidden + h * 64;
         qo[lane] = __float2bfloat16_rn(q1);
         qo[32 + lane] = __float2bfloat16_rn(q2);
-        const size_t slot = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK + (idx & 15)) * 64;
-        k_pool[slot + lane] = __float2bfloat16_rn(k1);
-        k_pool[slot + 32 + lane] = __float2bfloat16_rn(k2);
-        v_pool[slot + lane] = __float2bfloat16_rn(v[4]);
-        v_pool[slot + 32 + lane] = __float2bfloat16_rn(v[5]);
+        if (KVT == 1) {
+            const float ka = warp_max(fmaxf(fabsf(k1), fabsf(k2))), va = warp_max(fmaxf(fabsf(v[4]), fabsf(v[5])));
+            const float ks = ka > 0.f ? ka / 448.f : 1.f, vs = va > 0.f ? va / 448.f : 1.f;
+            const size_t sl = ((size_t)blk * n_heads + h) * 1088;
+            unsigned char* kp = k_pool + sl + (idx & 15) * 64;
+            unsigned char* vp = v_pool + sl + (idx & 15) * 64;
+            kp[lane] = (unsigned char)__nv_cvt_float_to_fp8(k1 / ks, __NV_SATFINITE, __NV_E4M3);
+            kp[32 + lane] = (unsigned char)__nv_cvt_float_to_fp8(k2 / ks, __NV_SATFINITE, __NV_E4M3);
+            vp[lane] = (unsigned char)__nv_cvt_float_to_fp8(v[4] / vs, __NV_SATFINITE, __NV_E4M3);
+            vp[32 + lane] = (unsigned char)__nv_cvt_float_to_fp8(v[5] / vs, __NV_SATFINITE, __NV_E4M3);
+            if (lane == 0) {
+                *reinterpret_cast<float*>(k_pool + sl + 1024 + (idx & 15) * 4) = ks;
+                *reinterpret_cast<float*>(v_pool + sl + 1024 + (idx & 15) * 4) = vs;
+            }
+        } else {
+            const size_t slot = (((size_t)blk * n_heads + h) * T3B_KV_BLOCK + (idx & 15)) * 64;
+            bf16* kp = reinterpret_cast<bf16*>(k_pool) + slot;
+            bf16* vp = reinterpret_cast<bf16*>(v_pool) + slot;
+            kp[lane] = __float2bfloat16_rn(k1);
+            kp[32 + lane] = __float2bfloat16_rn(k2);
+            vp[lane] = __float2bfloat16_rn(v[4]);
+            vp[32 + lane] = __float2bfloat16_rn(v[5]);
+        }
     }
+}
+
+// ------------------------------------------------------------------ prefill embedding assembly (t3.py:542-561)
+// One CTA per sequence (2 per request: cond, uncond); 128 threads = one 1024-wide row per pass.
+__global__ void __launch_bounds__(256) prefill_embed_kernel(const uint4* __restrict__ conds, const int32_t* __restrict__ text_ids,
+                                                            const int32_t* __restrict__ text_start, const int32_t* __restrict__ out_start,
+                                                            const int32_t* __restrict__ slots, const uint4* __restrict__ text_emb,
+                                                            const uint4* __restrict__ text_pos_emb, int text_rows, int text_pos_rows,
+                                                            const uint4* __restrict__ speech_emb, const uint4* __restrict__ speech_pos_emb,
+                                                            int bos_token, int hidden8, int cond_len, uint4* __restrict__ x_out,
+                                                            int32_t* __restrict__ tok_row, int32_t* __restrict__ tok_idx) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int seq = blockIdx.x, r = seq >> 1, half = seq & 1;
+    const int t0 = text_start[r], n_text = text_start[r + 1] - t0;
+    const int o0 = out_start[seq], P = cond_len + n_text + 1;
+    const int row = 2 * slots[r] + half;
+    for (int i = threadIdx.x; i < P; i += blockDim.x) { tok_row[o0 + i] = row; tok_idx[o0 + i] = i; }
+    const int per = blockDim.x / hidden8 > 0 ? blockDim.x / hidden8 : 1;       // rows per pass
+    const int sub = threadIdx.x / hidden8, col = threadIdx.x - sub * hidden8;
+    if (sub >= per) return;
+    for (int i = sub; i < P; i += per) {
+        uint4 v;
+        if (i < cond_len) {
+            v = conds[((size_t)r * cond_len + i) * hidden8 + col];
+        } else if (i < P - 1) {
+            if (half == 0) {
+                int id = text_ids[t0 + i - cond_len];
+                id = min(max(id, 0), text_rows - 1);
+                const int p = min(i - cond_len, text_pos_rows - 1);
+                float a[8], b[8];
+                unpack8(text_emb[(size_t)id * hidden8 + col], a);
+                unpack8(text_pos_emb[(size_t)p * hidden8 + col], b);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) a[e] += b[e];
+                v = pack8(a);
+            } else {
+                v = make_uint4(0, 0, 0, 0);               // t3.py:556: the uncond row zeroes the text embeddings
+            }
+        } else {
+            float a[8], b[8];                             // BOS = speech_emb[start] + speech_pos_emb[0] (t3.py:550-551)
+            unpack8(speech_emb[(size_t)bos_token * hidden8 + col], a);
+            unpack8(speech_pos_emb[col], b);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) a[e] += b[e];
+            v = pack8(a);
+        }
+        x_out[(size_t)(o0 + i) * hidden8 + col] = v;
+    }
+}
+
+// ------------------------------------------------------------------ S3Gen hand-off (tts.py:492-514)
+// order-preserving compaction of the ids whose un-offset value is a valid S3 code; one CTA, ballot scan
+__global__ void __launch_bounds__(1024) filter_speech_tokens_kernel(const int32_t* __restrict__ ids, int n, int offset, int n_valid,
+                                                                     int32_t* __restrict__ out, int32_t* __restrict__ n_out) {
+    __shared__ int warp_cnt[32];
+    __shared__ int base;
+    pdl_launch_dependents();
+    pdl_wait();
+    if (threadIdx.x == 0) base = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i0 = 0; i0 < n; i0 += 1024) {
+        const int i = i0 + threadIdx.x;
+        const int v = i < n ? ids[i] - offset : -1;
+        const bool keep = i < n && v >= 0 && v < n_valid;
+        const unsigned m = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) warp_cnt[warp] = __popc(m);
+        __syncthreads();
+        int off = base;
+        for (int w = 0; w < warp; ++w) off += warp_cnt[w];
+        const int pos = off + __popc(m & ((1u << lane) - 1u));
+        __syncthreads();                                   // every thread has read `base` / warp_cnt and ids[i] (out may alias ids)
+        if (keep) out[pos] = v;
+        if (threadIdx.x == 1023) base = pos + (keep ? 1 : 0);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && n_out) *n_out = base;
 }
 
 // ------------------------------------------------------------------ F2.6
@@ -260,16 +316,42 @@ extern "C" int32_t t3b_add_rmsnorm(const void* x, const float* partials, int32_t
 extern "C" int32_t t3b_rope_kv_write(const void* qkv, const float* partials, int32_t n_split, int32_t n_tok, const int32_t* tok_row,
                                      const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int32_t max_pos,
                                      const int32_t* block_tables, int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads,
-                                     void* q_out, void* stream) {
+                                     int32_t kv_dtype, void* q_out, void* stream) {
     T3B_CHECK_ARG((qkv != nullptr) != (partials != nullptr), "t3b_rope_kv_write: exactly one of qkv / partials");
     T3B_CHECK_ARG(tok_idx && rope_pos && rope_cos_sin && block_tables && k_pool && v_pool && q_out, "t3b_rope_kv_write: null pointer");
     T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && max_pos > 0 && (qkv || n_split >= 1), "t3b_rope_kv_write: bad sizes");
     T3B_CHECK_SHAPE(n_heads >= 1 && n_heads <= 64, "t3b_rope_kv_write: n_heads %d", n_heads);
+    T3B_CHECK_ARG(kv_dtype == T3B_KV_BF16 || kv_dtype == T3B_KV_FP8, "t3b_rope_kv_write: unknown KV dtype %d", kv_dtype);
     if (n_tok == 0) return T3B_OK;
     const int threads = 32 * (n_heads < 16 ? n_heads : 16);
-    T3B_CUDA(t3b_launch(rope_kv_write_kernel, dim3(n_tok), dim3(threads), 0, t3b_stream(stream), (const bf16*)qkv, partials, n_split,
+    auto kern = kv_dtype == T3B_KV_FP8 ? rope_kv_write_kernel<1> : rope_kv_write_kernel<0>;
+    T3B_CUDA(t3b_launch(kern, dim3(n_tok), dim3(threads), 0, t3b_stream(stream), (const bf16*)qkv, partials, n_split,
                         (size_t)n_tok * 3 * n_heads * 64, tok_row, tok_idx, rope_pos, (const bf16*)rope_cos_sin, max_pos, block_tables,
-                        max_blocks, (bf16*)k_pool, (bf16*)v_pool, n_heads, (bf16*)q_out));
+                        max_blocks, (unsigned char*)k_pool, (unsigned char*)v_pool, n_heads, (bf16*)q_out));
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_prefill_embed(const void* conds, const int32_t* text_ids, const int32_t* text_start, const int32_t* out_start,
+                                     const int32_t* slots, int32_t n_req, const void* text_emb, const void* text_pos_emb, int32_t text_rows,
+                                     int32_t text_pos_rows, const void* speech_emb, const void* speech_pos_emb, int32_t bos_token,
+                                     int32_t hidden, int32_t cond_len, void* x_out, int32_t* tok_row, int32_t* tok_idx, void* stream) {
+    T3B_CHECK_ARG(conds && text_ids && text_start && out_start && slots && text_emb && text_pos_emb && speech_emb && speech_pos_emb && x_out &&
+                  tok_row && tok_idx, "t3b_prefill_embed: null pointer");
+    T3B_CHECK_ARG(n_req >= 0 && text_rows > 0 && text_pos_rows > 0 && bos_token >= 0 && cond_len >= 0, "t3b_prefill_embed: bad sizes");
+    T3B_CHECK_SHAPE(hidden > 0 && hidden % 8 == 0 && hidden / 8 <= 256, "t3b_prefill_embed: hidden %d unsupported", hidden);
+    T3B_CHECK_ALIGN(conds); T3B_CHECK_ALIGN(text_emb); T3B_CHECK_ALIGN(text_pos_emb); T3B_CHECK_ALIGN(speech_emb); T3B_CHECK_ALIGN(speech_pos_emb);
+    T3B_CHECK_ALIGN(x_out);
+    if (n_req == 0) return T3B_OK;
+    T3B_CUDA(t3b_launch(prefill_embed_kernel, dim3(2 * n_req), dim3(256), 0, t3b_stream(stream), (const uint4*)conds, text_ids, text_start,
+                        out_start, slots, (const uint4*)text_emb, (const uint4*)text_pos_emb, text_rows, text_pos_rows, (const uint4*)speech_emb,
+                        (const uint4*)speech_pos_emb, bos_token, hidden / 8, cond_len, (uint4*)x_out, tok_row, tok_idx));
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_filter_speech_tokens(const int32_t* ids, int32_t n, int32_t offset, int32_t n_valid, int32_t* out, int32_t* n_out,
+                                            void* stream) {
+    T3B_CHECK_ARG(ids && out && n_out && n >= 0 && n_valid > 0, "t3b_filter_speech_tokens: bad arguments");
+    T3B_CUDA(t3b_launch(filter_speech_tokens_kernel, dim3(1), dim3(1024), 0, t3b_stream(stream), ids, n, offset, n_valid, out, n_out));
     return T3B_OK;
 }
 
@@ -291,22 +373,3 @@ extern "C" int32_t t3b_silu_mul(const void* gate_up, const float* partials, int3
     return T3B_OK;
 }
 
-extern "C" int32_t t3b_z_init(const void* x, int32_t rows, int32_t hidden, float* z, float* ss, void* stream) {
-    T3B_CHECK_ARG(x && z && ss && rows >= 0, "t3b_z_init: null pointer");
-    T3B_CHECK_SHAPE(hidden > 0 && hidden % 128 == 0, "t3b_z_init: hidden %d not a multiple of 128", hidden);
-    T3B_CHECK_ALIGN(x); T3B_CHECK_ALIGN(z);
-    if (rows == 0) return T3B_OK;
-    T3B_CUDA(t3b_launch(z_init_kernel, dim3(rows), dim3(128), 0, t3b_stream(stream), (const uint4*)x, (float4*)z, ss, hidden / 8, rows));
-    return T3B_OK;
-}
-
-extern "C" int32_t t3b_z_rmsnorm(const float* z, const float* ss, const void* weight, int32_t rows, int32_t hidden, float eps, void* y,
-                                 void* stream) {
-    T3B_CHECK_ARG(z && ss && weight && y && rows >= 0, "t3b_z_rmsnorm: null pointer");
-    T3B_CHECK_SHAPE(hidden > 0 && hidden % 128 == 0, "t3b_z_rmsnorm: hidden %d not a multiple of 128", hidden);
-    T3B_CHECK_ALIGN(z); T3B_CHECK_ALIGN(weight); T3B_CHECK_ALIGN(y);
-    if (rows == 0) return T3B_OK;
-    T3B_CUDA(t3b_launch(z_rmsnorm_kernel, dim3(rows), dim3(128), 0, t3b_stream(stream), (const float4*)z, ss, (const uint4*)weight, (uint4*)y,
-                        hidden / 8, rows, eps));
-    return T3B_OK;
-}

@@ -47,7 +47,7 @@
 #define UM_RAW_BYTES 4096                  // AWQ: 128 x 64 nibbles
 #define UM_MAX_STAGES 8
 
-enum { EPI_STORE = 0, EPI_SILU = 1, EPI_RESID = 2 };
+enum { EPI_STORE = 0, EPI_SILU = 1 };
 
 struct UmmaParams {
     bf16* y;                 // bf16 [rows, N] (STORE) or [rows, N/2] (SILU); NULL in legacy mode
@@ -59,42 +59,7 @@ struct UmmaParams {
     const unsigned char* qw; // repacked nibbles [N/128][K/64][2][128][16 B]
     const bf16* scales;      // bf16 [K/128, N]
     const unsigned char* zeros;   // u8 [K/128, N]
-    long long* trace;        // debug: 16 clock64 stamps per CTA (NULL = off)
-    // F2.1 folded into the projections (decode layers, t3b_linear_fused):
-    //   zx != NULL: the activation operand is built in-kernel from the fp32 residual stream,
-    //               X[r, k] = bf16(bf16(zx[r, k] * rstd_r) * norm_w[k]),  rstd_r = rsqrt(sum_t zx_ss[t][r] / K + eps)
-    //   EPI_RESID:  z_out[r, n] = bf16(acc) + bf16(z_res[r, n]) (fp32; in place allowed), ss_out[tile][r] = sum_n z_out^2
-    const float* zx;
-    const float* zx_ss;
-    const bf16* norm_w;
-    int zx_tiles;
-    float eps;
-    const float* z_res;
-    float* z_out;
-    float* ss_out;
-    // tail norm (EPI_STORE, N == 1024, cluster split-K): the last n-tile CTA to finish a row group runs the add + RMSNorm that
-    // follows the projection (F2.1), bit for bit the arithmetic of add_rmsnorm_kernel<1>
-    bf16* tn_resid;               // bf16 [rows, N], resid += y in place
-    const bf16* tn_w;             // bf16 [N]
-    bf16* tn_out;                 // bf16 [rows, N]
-    unsigned int* tn_counters;    // [row chunks][8] zeroed; re-armed by the last CTA
-    // K/V prefetch for the NEXT layer's attention, issued by the idle warp 3 (hint only: prefetch.global.L2)
-    const bf16* pf_pool;          // K or V pool of the target layer, [block][head][16][64] bf16; NULL = off
-    const int32_t* pf_ctx;        // [pf_rows] cached tokens per row (may be one step stale)
-    const int32_t* pf_bt;         // [pf_rows][pf_max_blocks]
-    int pf_rows, pf_heads, pf_max_blocks;
 };
-
-// set by api.cu for the next launch only (decode layers): see UmmaParams::pf_*
-static thread_local UmmaParams g_pf_next = {};
-void t3b_umma_set_prefetch(const void* pool, const int32_t* ctx, const int32_t* bt, int rows, int heads, int max_blocks) {
-    g_pf_next.pf_pool = static_cast<const bf16*>(pool); g_pf_next.pf_ctx = ctx; g_pf_next.pf_bt = bt;
-    g_pf_next.pf_rows = rows; g_pf_next.pf_heads = heads; g_pf_next.pf_max_blocks = max_blocks;
-}
-
-static long long* g_umma_trace = nullptr;
-extern "C" void t3b_debug_set_umma_trace(void* p) { g_umma_trace = static_cast<long long*>(p); }
-#define TRACE(i) do { if (p.trace) p.trace[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 16 + (i)] = clock64(); } while (0)
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void cluster_sync_all() {
@@ -143,9 +108,7 @@ __device__ __forceinline__ void red_sum8(const float* red, int n_split, int per,
     else red_sum8_n<2>(red, per, j, col, acc);
 }
 
-// FZ = false compiles the F2.1 fusions / prefetch role out (the default decode path): fewer registers, so more blocks of the next
-// kernel fit beside a GEMM block while it runs.
-template <int WSRC, bool FZ>
+template <int WSRC>
 __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                           const __grid_constant__ CUtensorMap tmap_x,
                                                                           const UmmaParams p) {
@@ -166,7 +129,6 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     uint64_t* raw_bar = empty_bar + UM_MAX_STAGES;
     uint64_t* tmem_full_bar = raw_bar + UM_MAX_STAGES;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-    float* s_aux = reinterpret_cast<float*>(tmem_ptr + 2);       // [256]: rstd per row (X build), then [64][4] warp sums (EPI_RESID)
     float* red = reinterpret_cast<float*>(smem + ring_bytes);
 
     pdl_launch_dependents();                     // the next kernel's launch latency overlaps this whole kernel (it waits before reading)
@@ -179,11 +141,10 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     const int n_b = p.epi == EPI_SILU ? p.N / 2 + tile * 64 : tile * UM_M + 64;   // second 64
 
     if (threadIdx.x == 0) {
-        TRACE(0);
         if (!WSRC) tma_prefetch_desc(&tmap_w);
-        if (!(FZ && p.zx)) tma_prefetch_desc(&tmap_x);
+        tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < stages; ++i) {
-            mbar_init(&full_bar[i], (WSRC ? 1 + 8 : 1) + ((FZ && p.zx) ? 4 : 0));      // producer (tx) [+ 8 dequant warps] [+ 4 X-build warps]
+            mbar_init(&full_bar[i], WSRC ? 1 + 8 : 1);      // producer (tx) [+ 8 dequant warps]
             mbar_init(&empty_bar[i], 1);
             mbar_init(&raw_bar[i], 1);
         }
@@ -195,8 +156,6 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr;
-    float4 zra = make_float4(0.f, 0.f, 0.f, 0.f), zrb = zra;     // EPI_RESID: prefetched residual values (first item of the thread)
-    if (threadIdx.x == 0) TRACE(1);
 
     auto load_w = [&](int i, int s) {
         unsigned char* st = smem + (size_t)s * stage_bytes;
@@ -208,7 +167,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
             tma_load_2d(st + UM_A_BYTES / 2, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_b);
         }
     };
-    const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + ((FZ && p.zx) ? 0u : x_bytes);
+    const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + x_bytes;
     const int pre = nkb < stages ? nkb : stages;
     // The first ring of weight tiles goes out before anything else: weights never depend on the previous kernel.
     if (threadIdx.x == 0) {
@@ -224,17 +183,14 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     if (warp == 0) {
         if (lane == 0) {
             pdl_wait();
-            TRACE(2);
-            if (!(FZ && p.zx))
-                for (int i = 0; i < pre; ++i)
-                    tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
+            for (int i = 0; i < pre; ++i)
+                tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             for (int i = pre; i < nkb; ++i) {
                 const int s = i % stages, round = i / stages;
                 mbar_wait(&empty_bar[s], (round & 1) ^ 1);
                 mbar_expect_tx(&full_bar[s], tx);
                 load_w(i, s);
-                if (!(FZ && p.zx))
-                    tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
+                tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             }
         }
     } else if (warp == 1) {
@@ -244,8 +200,6 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 const int s = i % stages, round = i / stages;
                 mbar_wait(&full_bar[s], round & 1);
                 tc_fence_after();
-                if (i == 0) TRACE(3);
-                if (i == nkb - 1) TRACE(4);
                 const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
                 const uint64_t a_desc = umma_smem_desc_sw128(a_addr);
                 const uint64_t b_desc = umma_smem_desc_sw128(a_addr + UM_A_BYTES);
@@ -255,27 +209,6 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 umma_commit(&empty_bar[s]);
             }
             umma_commit(tmem_full_bar);
-        }
-    } else if (FZ && warp == 3 && p.pf_pool != nullptr) {
-        // The next layer's attention streams ~R x ctx x 2 KB of K/V per head; this warp has nothing else to do, HBM is mostly idle
-        // while the projections run, and the 126 MB L2 holds a layer's K/V (65 MB at 64 rows x 250 tokens) - so pull the lines into
-        // L2 now.  Row t of this block = cid % rows, its lines split over the cid / rows blocks that share the row.
-        const int ncta = gridDim.x * gridDim.y * gridDim.z, cid = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
-        const int rows = p.pf_rows, nparts = ncta >= rows ? ncta / rows : 1;
-        for (int t = ncta >= rows ? cid % rows : cid; t < rows && cid < nparts * rows; t += ncta) {
-            const int part = ncta >= rows ? cid / rows : 0;
-            const int np = min(min((ld_act(p.pf_ctx + t) + 16) >> 4, p.pf_max_blocks), 64);
-            const int32_t* btp = p.pf_bt + (size_t)t * p.pf_max_blocks;
-            const int b0 = lane < np ? ld_act(btp + lane) : 0, b1 = lane + 32 < np ? ld_act(btp + lane + 32) : 0;
-            const int total = np * p.pf_heads * 16;                              // 128-byte lines of this row in the pool
-            for (int i0 = part * 32; i0 < total; i0 += nparts * 32) {             // warp-uniform trip count (shuffles inside)
-                const int i = min(i0 + lane, total - 1);
-                const int ln = i & 15, ph = i >> 4, page = ph % np, h = ph / np;
-                const int lo = __shfl_sync(0xffffffffu, b0, page & 31), hi = __shfl_sync(0xffffffffu, b1, page & 31);
-                const int blk = page < 32 ? lo : hi;
-                if (i0 + lane < total)
-                    asm volatile("prefetch.global.L2 [%0];" :: "l"(p.pf_pool + (((size_t)blk * p.pf_heads + h) * T3B_KV_BLOCK) * 64 + ln * 64));
-            }
         }
     } else if (WSRC && warp >= 8) {
         // ---- AWQ dequant: thread d owns weight row (d & 127) and k half (d >> 7) of every k-block
@@ -319,89 +252,8 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         const int f = quad * 32 + lane;          // feature row of the tile this thread reads from TMEM
         const int r0 = rchunk * p.row_chunk;
         const int valid = min(Rp, p.rows - r0);  // rows of this chunk that exist
-        if (FZ && p.epi == EPI_RESID && p.n_split > 1) {
-            // residual values of this thread's first (row, 8 features) item after the split-K reduce: fetched now, off the critical path
-            const int tt = threadIdx.x - 128, j = tt >> 4, g = tt & 15, r = r0 + j * p.n_split + split;
-            if (tt < (Rp / p.n_split) * 16 && r < p.rows) {
-                const float4* rp = reinterpret_cast<const float4*>(p.z_res + (size_t)r * p.N + tile * UM_M + g * 8);
-                zra = __ldcg(rp); zrb = __ldcg(rp + 1);
-            }
-        }
-        if (FZ && p.zx != nullptr) {
-            // F2.1 (layernorm.py:40-59) folded into the operand build: these 4 warps turn the fp32 residual stream into the
-            // normalised bf16 B tile of every k-block ([Rp rows] x 128 B, SWIZZLE_128B: 16 B chunk c of row r at c ^ (r & 7)).
-            // Batches of 512 (row, chunk) items, the loads of batch b + 1 in flight while batch b is normalised and stored.
-            const int t = threadIdx.x - 128, K = p.kb_total * UM_K;
-            const int items = Rp * 8, bpk = (items + 511) >> 9, nb = nkb * bpk;
-            const int ch = t & 7;                                         // the 16 B chunk (8 k) of every item of this thread
-            auto load_batch = [&](int b, float4* za, float4* zb, uint4& wv) {
-                const int i = b / bpk, it0 = (b - i * bpk) * 512 + t, k0 = (kb_begin + i) * UM_K;
-                wv = __ldg(reinterpret_cast<const uint4*>(p.norm_w + k0 + ch * 8));
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int r = (it0 + u * 128) >> 3;
-                    if (r < valid) {
-                        const float4* src = reinterpret_cast<const float4*>(p.zx + (size_t)(r0 + r) * K + k0 + ch * 8);
-                        za[u] = __ldcg(src); zb[u] = __ldcg(src + 1);
-                    } else {
-                        za[u] = make_float4(0.f, 0.f, 0.f, 0.f); zb[u] = za[u];
-                    }
-                }
-            };
-            auto store_batch = [&](int b, const float4* za, const float4* zb, const uint4& wv) {
-                const int i = b / bpk, bi = b - i * bpk, it0 = bi * 512 + t;
-                const int s = i % stages, round = i / stages;
-                if (bi == 0 && i >= stages) mbar_wait(&empty_bar[s], (round & 1) ^ 1);
-                unsigned char* xs = smem + (size_t)s * stage_bytes + UM_A_BYTES;
-                float w[8];
-                unpack8(wv, w);
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int r = (it0 + u * 128) >> 3;
-                    if (r < Rp) {
-                        const float rs = s_aux[r];
-                        float o[8];
-                        o[0] = bf16_round(za[u].x * rs) * w[0]; o[1] = bf16_round(za[u].y * rs) * w[1];
-                        o[2] = bf16_round(za[u].z * rs) * w[2]; o[3] = bf16_round(za[u].w * rs) * w[3];
-                        o[4] = bf16_round(zb[u].x * rs) * w[4]; o[5] = bf16_round(zb[u].y * rs) * w[5];
-                        o[6] = bf16_round(zb[u].z * rs) * w[6]; o[7] = bf16_round(zb[u].w * rs) * w[7];
-                        *reinterpret_cast<uint4*>(xs + r * 128 + ((ch ^ (r & 7)) << 4)) = pack8(o);
-                    }
-                }
-                if (bi == bpk - 1) {
-                    fence_proxy_async_smem();                             // generic-proxy writes -> visible to the MMA (async proxy)
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&full_bar[s]);
-                }
-            };
-            float4 a0[4], b0[4], a1[4], b1[4];
-            uint4 w0, w1;
-            load_batch(0, a0, b0, w0);
-            for (int r = t; r < Rp; r += 128) {                           // rstd of row r: per-tile sums in fixed order
-                float ss = 0.f;
-                if (r < valid) {
-                    for (int i0 = 0; i0 < p.zx_tiles; i0 += 8) {
-                        float v[8];
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) v[u] = i0 + u < p.zx_tiles ? __ldcg(p.zx_ss + (size_t)(i0 + u) * p.rows + r0 + r) : 0.f;
-#pragma unroll
-                        for (int u = 0; u < 8; ++u) ss += v[u];
-                    }
-                }
-                s_aux[r] = r < valid ? rsqrtf(ss / (float)K + p.eps) : 0.f;
-            }
-            named_bar_sync(1, 128);
-            for (int b = 0; b < nb; b += 2) {
-                if (b + 1 < nb) load_batch(b + 1, a1, b1, w1);
-                store_batch(b, a0, b0, w0);
-                if (b + 2 < nb) load_batch(b + 2, a0, b0, w0);
-                if (b + 1 < nb) store_batch(b + 1, a1, b1, w1);
-            }
-            named_bar_sync(1, 128);                                       // s_aux is reused by the EPI_RESID epilogue
-        }
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
-        if (threadIdx.x == 128) TRACE(5);
         if (p.partials != nullptr) {
             // legacy: fp32 partial tile straight to global memory
             const int n = tile * UM_M + f;
@@ -466,22 +318,6 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                         for (int j = 0; j < 16; ++j)
                             if (c0 + j < valid) p.y[(size_t)(r0 + c0 + j) * p.N + n] = __float2bfloat16_rn(red[j * UM_M + t]);
                     }
-                } else if (FZ && p.epi == EPI_RESID) {
-                    const int n = tile * UM_M + t;               // N % 128 == 0 (checked at launch)
-#pragma unroll 4
-                    for (int j = 0; j < 16; ++j) {
-                        float z = 0.f;
-                        if (c0 + j < valid) {
-                            const size_t o = (size_t)(r0 + c0 + j) * p.N + n;
-                            z = bf16_round(red[j * UM_M + t]) + bf16_round(__ldcg(p.z_res + o));
-                            p.z_out[o] = z;
-                        }
-                        const float sq = warp_sum(z * z);
-                        if (lane == 0) s_aux[j * 4 + quad] = sq;
-                    }
-                    named_bar_sync(1, 128);
-                    if (t < 16 && c0 + t < valid)
-                        p.ss_out[(size_t)tile * p.rows + r0 + c0 + t] = (s_aux[t * 4] + s_aux[t * 4 + 1]) + (s_aux[t * 4 + 2] + s_aux[t * 4 + 3]);
                 } else {
                     // one (row, 8 gate/up pairs) item per thread: four LDS.128, one 16-byte store
                     const int j = t >> 3, g8 = (t & 7) * 8, ffn = p.N / 2;
@@ -505,11 +341,9 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     }
     tc_fence_before();
     if (p.partials == nullptr && p.n_split > 1) {
-        if (threadIdx.x == 128) TRACE(6);
         cluster_sync_all();                      // release / acquire: every peer's pushes into this CTA's buffer have landed
-        if (threadIdx.x == 128) TRACE(7);
         // after the barrier the producer / MMA warps are idle too: the pure store epilogues run on every thread of the block
-        const bool wide = p.epi == EPI_SILU || (p.epi == EPI_STORE && (p.N & 7) == 0 && !(FZ && p.tn_out != nullptr));
+        const bool wide = p.epi == EPI_SILU || (p.epi == EPI_STORE && (p.N & 7) == 0);
         const int nthr = wide ? (int)blockDim.x : 128;
         if (wide || (warp >= 4 && warp < 8)) {
             // The CTA owns rows {r0 + j * n_split + split}.  Item = (row j, 8 adjacent features): two LDS.128 per split, one
@@ -526,62 +360,6 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     red_sum8(red, p.n_split, per, j, g * 8, acc);
                     *reinterpret_cast<uint4*>(p.y + (size_t)r * p.N + n) = pack8(acc);
                 }
-                if (FZ && p.tn_out != nullptr) {
-                    // F2.1 in the tail of the projection: rows {r0 + j * n_split + split} get their 1024 features from the
-                    // gridDim.x n-tile CTAs with this split index; the last of them to arrive normalises those rows.
-                    unsigned int* flag = reinterpret_cast<unsigned int*>(s_aux + 255);
-                    __threadfence();                                   // this thread's y stores are visible device-wide
-                    named_bar_sync(1, 128);
-                    if (t == 0) *flag = atomicAdd(p.tn_counters + rchunk * 8 + split, 1u);
-                    named_bar_sync(1, 128);
-                    if (*flag == gridDim.x - 1) {
-                        if (t == 0) p.tn_counters[rchunk * 8 + split] = 0u;      // re-arm for the next launch
-                        __threadfence();
-                        float w[8];
-                        unpack8(__ldg(reinterpret_cast<const uint4*>(p.tn_w) + t), w);
-                        const int quad = warp & 3;
-                        constexpr int TNR = WSRC ? 4 : 8;                // rows per pass (the AWQ kernel has half the registers)
-                        for (int j0 = 0; j0 < per; j0 += TNR) {
-                            uint4 xr[TNR], rr[TNR];
-#pragma unroll
-                            for (int jj = 0; jj < TNR; ++jj) {
-                                const int r = r0 + (j0 + jj) * p.n_split + split;
-                                if (j0 + jj < per && r < p.rows) {
-                                    xr[jj] = __ldcg(reinterpret_cast<const uint4*>(p.y + (size_t)r * p.N) + t);
-                                    rr[jj] = __ldcg(reinterpret_cast<const uint4*>(p.tn_resid + (size_t)r * p.N) + t);
-                                } else {
-                                    xr[jj] = make_uint4(0, 0, 0, 0); rr[jj] = xr[jj];
-                                }
-                            }
-                            float xv[TNR][8];
-#pragma unroll
-                            for (int jj = 0; jj < TNR; ++jj) {
-                                const int r = r0 + (j0 + jj) * p.n_split + split;
-                                float rv[8];
-                                unpack8(xr[jj], xv[jj]);
-                                unpack8(rr[jj], rv);
-                                float ss = 0.f;
-#pragma unroll
-                                for (int e = 0; e < 8; ++e) { xv[jj][e] += rv[e]; ss += xv[jj][e] * xv[jj][e]; }
-                                if (j0 + jj < per && r < p.rows) *(reinterpret_cast<uint4*>(p.tn_resid + (size_t)r * p.N) + t) = pack8(xv[jj]);
-                                ss = warp_sum(ss);
-                                if (lane == 0) s_aux[jj * 4 + quad] = ss;
-                            }
-                            named_bar_sync(1, 128);
-#pragma unroll
-                            for (int jj = 0; jj < TNR; ++jj) {
-                                const int r = r0 + (j0 + jj) * p.n_split + split;
-                                const float tot = (s_aux[jj * 4] + s_aux[jj * 4 + 1]) + (s_aux[jj * 4 + 2] + s_aux[jj * 4 + 3]);
-                                const float rstd = rsqrtf(tot / (float)p.N + p.eps);
-                                float o[8];
-#pragma unroll
-                                for (int e = 0; e < 8; ++e) o[e] = bf16_round(xv[jj][e] * rstd) * w[e];
-                                if (j0 + jj < per && r < p.rows) *(reinterpret_cast<uint4*>(p.tn_out + (size_t)r * p.N) + t) = pack8(o);
-                            }
-                            named_bar_sync(1, 128);
-                        }
-                    }
-                }
             } else if (p.epi == EPI_STORE) {     // N not a multiple of 8 (the 8194-wide speech head): rows are not 16-byte aligned
                 const int n = tile * UM_M + t;
 #pragma unroll 4
@@ -591,35 +369,6 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     float acc = 0.f;
                     for (int c = 0; c < p.n_split; ++c) acc += red[(c * per + j) * UM_M + t];      // fixed order -> deterministic
                     if (n < p.N) p.y[(size_t)r * p.N + n] = __float2bfloat16_rn(acc);
-                }
-            } else if (FZ && p.epi == EPI_RESID) {
-                // residual add of llama.py:316-333 in the GEMM epilogue: the fp32 stream z keeps the unrounded sum the
-                // reference's fused_add_rms_norm normalises; the next residual add reads it back as bf16(z)
-                for (int it0 = 0; it0 < per * 16; it0 += 128) {
-                    const int it = it0 + t, j = it >> 4, g = it & 15, r = r0 + j * p.n_split + split;
-                    const bool live = it < per * 16 && r < p.rows;            // uniform over each half warp
-                    float sq = 0.f;
-                    if (live) {
-                        float acc[8];
-                        red_sum8(red, p.n_split, per, j, g * 8, acc);
-                        float* zp = p.z_out + (size_t)r * p.N + tile * UM_M + g * 8;
-                        float4 ra = zra, rb = zrb;
-                        if (it0 > 0) {
-                            const float4* rp = reinterpret_cast<const float4*>(p.z_res + (size_t)r * p.N + tile * UM_M + g * 8);
-                            ra = __ldcg(rp); rb = __ldcg(rp + 1);
-                        }
-                        float4 za, zb;
-                        za.x = bf16_round(acc[0]) + bf16_round(ra.x); za.y = bf16_round(acc[1]) + bf16_round(ra.y);
-                        za.z = bf16_round(acc[2]) + bf16_round(ra.z); za.w = bf16_round(acc[3]) + bf16_round(ra.w);
-                        zb.x = bf16_round(acc[4]) + bf16_round(rb.x); zb.y = bf16_round(acc[5]) + bf16_round(rb.y);
-                        zb.z = bf16_round(acc[6]) + bf16_round(rb.z); zb.w = bf16_round(acc[7]) + bf16_round(rb.w);
-                        reinterpret_cast<float4*>(zp)[0] = za;
-                        reinterpret_cast<float4*>(zp)[1] = zb;
-                        sq = ((za.x * za.x + za.y * za.y) + (za.z * za.z + za.w * za.w)) + ((zb.x * zb.x + zb.y * zb.y) + (zb.z * zb.z + zb.w * zb.w));
-                    }
-#pragma unroll
-                    for (int o = 8; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);     // the 16 lanes of a row
-                    if (live && g == 0) p.ss_out[(size_t)tile * p.rows + r] = sq;
                 }
             } else {
                 const int ffn = p.N / 2;
@@ -639,13 +388,8 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 }
             }
         }
-        if (threadIdx.x == 128) TRACE(8);
-        if (warp >= 4 && warp < 8 && lane == 0) TRACE(10 + (warp & 3));
     }
-    if (threadIdx.x == 0) TRACE(14);
-    if (threadIdx.x == 32) TRACE(15);
     __syncthreads();
-    if (threadIdx.x == 128) TRACE(9);
     if (warp == 2) tmem_dealloc(tmem_base, p.tmem_cols);
 }
 
@@ -726,34 +470,10 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t o
 
 int t3b_umma_available() { return get_encode_fn() != nullptr; }
 
-// bf16 [outer, inner] row-major activations, box {64, box_outer}, SWIZZLE_128B (used by decode_fused.cu)
-int t3b_make_tmap_act(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, uint64_t row_stride_elems, uint32_t box_outer) {
-    auto enc = get_encode_fn();
-    if (!enc) return -1;
-    cuuint64_t gdim[2] = {inner, outer};
-    cuuint64_t gstride[1] = {row_stride_elems * 2};
-    cuuint32_t box[2] = {UM_K, box_outer};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : (int)r;
-}
-
 // Split-K factor.  Cluster mode (DSMEM reduce): a power of two <= 8 that divides the k-blocks, chosen to
 // put ~one CTA on every SM.  Depends on (N, K, row chunks) only, never on the row count inside a chunk,
 // so a request's arithmetic does not change with the batch it runs in.
 int t3b_umma_pick_split(int rows, int N, int K) {
-    {   // experiment hook: T3B_UMMA_SPLITS="qkv,o,gate_up,down" (0 = automatic) for the four T3 decode shapes
-        static int ov[4] = {-1, 0, 0, 0};
-        if (ov[0] < 0) {
-            ov[0] = 0;
-            const char* e = getenv("T3B_UMMA_SPLITS");
-            if (e) sscanf(e, "%d,%d,%d,%d", &ov[0], &ov[1], &ov[2], &ov[3]);
-        }
-        const int which = (N == 3072 && K == 1024) ? 0 : (N == 1024 && K == 1024) ? 1 : (N == 8192 && K == 1024) ? 2 : (N == 1024 && K == 4096) ? 3 : -1;
-        if (which >= 0 && ov[which] > 0 && rows <= 128) return ov[which];
-    }
     const int tiles = (N + UM_M - 1) / UM_M * ((rows + 127) / 128);
     const int kb = K / UM_K;
     const int sms = t3b_num_sms();
@@ -762,29 +482,14 @@ int t3b_umma_pick_split(int rows, int N, int K) {
     return s;
 }
 
-// Legacy split (global fp32 partials): fill the SMs, keep >= 1 k-block per CTA, bound the partial traffic.
-static int pick_split_partials(int rows, int N, int K) {
-    const int tiles = (N + UM_M - 1) / UM_M * ((rows + 255) / 256);
-    const int kb = K / UM_K;
-    const int sms = t3b_num_sms();
-    int s = (sms + tiles / 2) / tiles;
-    if (s < 1) s = 1;
-    if (s > kb) s = kb;
-    const long budget = 8l << 20;
-    while (s > 1 && (long)s * rows * N * 4 > budget) --s;
-    return s;
-}
-int t3b_umma_pick_split_partials(int rows, int N, int K) { return pick_split_partials(rows, N, K); }
-
 template <int WSRC>
 static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const UmmaParams& p, int tiles, int chunks, bool cluster,
                            cudaStream_t stream) {
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0);
     const size_t ring = (size_t)p.stages * stage_bytes;
     const size_t red = !cluster ? 0 : (p.n_split > 1 ? (size_t)p.Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
-    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 2) * 8 + 256 * 4;
-    const bool fz = p.zx != nullptr || p.epi == EPI_RESID || p.tn_out != nullptr || p.pf_pool != nullptr;
-    auto kern = fz ? linear_umma_kernel<WSRC, true> : linear_umma_kernel<WSRC, false>;
+    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 2) * 8;
+    auto kern = linear_umma_kernel<WSRC>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles, p.n_split, chunks);
@@ -807,23 +512,19 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
 
 // y != NULL: bf16 output (cluster split-K when n_split > 1); partials != NULL: legacy fp32 partials.
 // epi: EPI_STORE / EPI_SILU (bf16 output only).  awq == NULL: bf16 weights `w` [N, K].
+// stages_cap: ring depth cap (0 = 5); row_chunk_req: rows per thread block (0 = 128 with cluster split-K, 256 without).
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, cudaStream_t stream, const t3b_linear_fuse_t* fz) {
+                               int n_split, int epi, int stages_cap, int row_chunk_req, cudaStream_t stream) {
     T3B_CHECK_SHAPE(K % UM_K == 0 && K >= UM_K, "umma: K %d must be a multiple of 64", K);
     T3B_CHECK_SHAPE(rows >= 1, "umma: rows %d", rows);
     const int kb_total = K / UM_K;
     const bool legacy = partials != nullptr && n_split > 1;
     T3B_CHECK_ARG(n_split >= 1 && n_split <= kb_total, "umma: n_split %d not in [1, %d]", n_split, kb_total);
-    T3B_CHECK_ARG(legacy || y != nullptr || epi == EPI_RESID, "umma: y is null");
-    const bool zx = fz != nullptr && fz->x_z != nullptr;
-    T3B_CHECK_ARG(zx || x != nullptr, "umma: x is null");
-    if (zx) T3B_CHECK_ARG(fz->x_ss && fz->norm_w && fz->x_ss_tiles >= 1 && !legacy, "umma: fused norm needs x_ss, norm_w, x_ss_tiles >= 1");
-    if (epi == EPI_RESID) {
-        T3B_CHECK_ARG(fz && fz->res_z && fz->out_z && fz->out_ss && !legacy, "umma: the residual epilogue needs res_z, out_z, out_ss");
-        T3B_CHECK_SHAPE(N % UM_M == 0, "umma: residual epilogue needs N %d to be a multiple of 128", N);
-    }
+    T3B_CHECK_ARG(legacy || y != nullptr, "umma: y is null");
+    T3B_CHECK_ARG(x != nullptr, "umma: x is null");
     T3B_CHECK_ARG(legacy || n_split == 1 || n_split == 2 || n_split == 4 || n_split == 8, "umma: cluster split-K %d must be 1, 2, 4 or 8", n_split);
     T3B_CHECK_ARG(!(legacy && epi != EPI_STORE), "umma: fused epilogues need the bf16 output mode");
+    T3B_CHECK_ARG(epi == EPI_STORE || epi == EPI_SILU, "umma: unknown epilogue %d", epi);
     if (epi == EPI_SILU) T3B_CHECK_SHAPE(N % 128 == 0, "umma: gate_up N %d must be a multiple of 128", N);
     if (awq) {
         T3B_CHECK_SHAPE(N % 128 == 0 && K % 128 == 0, "umma: AWQ needs N %d and K %d to be multiples of 128", N, K);
@@ -832,12 +533,16 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
                       "umma: AWQ gate_up weights repacked with gate_up_interleave must run the SiLU epilogue (and only they may)");
     }
     // cluster split-K keeps a [Rp][128] fp32 buffer per CTA: 128-row chunks there, 256 otherwise
-    const int max_chunk = (!legacy && n_split > 1) ? 128 : 256;
+    int max_chunk = (!legacy && n_split > 1) ? 128 : 256;
+    if (row_chunk_req > 0) {
+        T3B_CHECK_ARG(row_chunk_req % 16 == 0 && row_chunk_req <= max_chunk, "umma: row_chunk %d must be a multiple of 16 <= %d", row_chunk_req, max_chunk);
+        max_chunk = row_chunk_req;
+    }
     const int row_chunk = rows > max_chunk ? max_chunk : rows;
     const int chunks = (rows + row_chunk - 1) / row_chunk;
     const int Rp = (row_chunk + 15) & ~15;
+    if (!legacy && n_split > 1) T3B_CHECK_SHAPE(Rp % n_split == 0, "umma: %d rows per block not divisible by split-K %d", Rp, n_split);
     UmmaParams p = {};
-    p.trace = g_umma_trace;
     p.y = legacy ? nullptr : (bf16*)y;
     p.partials = legacy ? partials : nullptr;
     p.rows = rows; p.N = N; p.kb_total = kb_total; p.n_split = n_split; p.Rp = Rp; p.row_chunk = row_chunk; p.epi = epi;
@@ -850,41 +555,21 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     const int nkb_max = (kb_total + n_split - 1) / n_split;
     if (stages > nkb_max) stages = nkb_max;
     if (stages > UM_MAX_STAGES) stages = UM_MAX_STAGES;
-    {   // Ring depth cap (T3B_UMMA_STAGES, default 5): an 8-deep ring fills the SM's shared memory, so no block of the NEXT kernel
-        // (attention, norm - a few KB) can become resident beside a GEMM block and run its pre-wait part early.  Measured at 64
-        // rows: 8 stages 1.460 ms/step, 4-6 stages 1.397-1.402 (profiles/r01t_notes.md).
-        static const int cap = []() { const char* e = getenv("T3B_UMMA_STAGES"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 5; }();
-        if (stages > cap) stages = cap;
-    }
-    {   // prefill shapes (256-row chunks, no split-K): a 48 KB stage x 4 leaves one block per SM, so the long epilogue (256 TMEM
-        // columns through the exchange buffer) never overlaps another block's main loop; 2 stages -> two blocks per SM
-        static const int big = []() { const char* e = getenv("T3B_UMMA_STAGES_BIG"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 2; }();
-        if (Rp > 128 && stages > big) stages = big;
-    }
+    // Ring depth cap (default 5): an 8-deep ring fills the SM's shared memory, so no block of the NEXT kernel (attention, norm) can
+    // become resident beside a GEMM block and run its pre-wait part early.  Measured at 64 rows: 8 stages 1.460 ms/step, 4-6 stages
+    // 1.397-1.402 (profiles/r01t_notes.md).
+    const int cap = stages_cap > 0 ? stages_cap : 5;
+    if (stages > cap) stages = cap;
+    // prefill shapes (256-row chunks, no split-K): a 48 KB stage x 4 leaves one block per SM, so the long epilogue (256 TMEM
+    // columns through the exchange buffer) never overlaps another block's main loop; 2 stages -> two blocks per SM
+    if (Rp > 128 && stages > 2 && stages_cap <= 0) stages = 2;
     if (stages < 2) stages = 2;
     p.stages = stages;
-    if (g_pf_next.pf_pool) {
-        p.pf_pool = g_pf_next.pf_pool; p.pf_ctx = g_pf_next.pf_ctx; p.pf_bt = g_pf_next.pf_bt;
-        p.pf_rows = g_pf_next.pf_rows; p.pf_heads = g_pf_next.pf_heads; p.pf_max_blocks = g_pf_next.pf_max_blocks;
-        g_pf_next.pf_pool = nullptr;
-    }
     CUtensorMap tw, tx;
     memset(&tw, 0, sizeof(tw));
     int e1 = awq ? 0 : make_tmap(&tw, w, (uint64_t)K, (uint64_t)N, 64, true);
     memset(&tx, 0, sizeof(tx));
-    int e2 = zx ? 0 : make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
-    if (fz && fz->tail_out) {
-        T3B_CHECK_ARG(fz->tail_resid && fz->tail_norm_w && fz->tail_counters, "umma: tail norm needs tail_resid, tail_norm_w, tail_counters");
-        T3B_CHECK_ARG(epi == EPI_STORE && !legacy && n_split > 1 && N == 1024 && chunks <= 8,
-                      "umma: tail norm needs the plain epilogue, cluster split-K and n == 1024 (epi %d, split %d, n %d)", epi, n_split, N);
-        p.tn_resid = (bf16*)fz->tail_resid; p.tn_w = (const bf16*)fz->tail_norm_w; p.tn_out = (bf16*)fz->tail_out;
-        p.tn_counters = fz->tail_counters; p.eps = fz->eps;
-    }
-    if (fz) {
-        p.zx = fz->x_z; p.zx_ss = fz->x_ss; p.norm_w = (const bf16*)fz->norm_w; p.zx_tiles = fz->x_ss_tiles;
-        if (fz->x_z) p.eps = fz->eps;
-        p.z_res = fz->res_z; p.z_out = fz->out_z; p.ss_out = fz->out_ss;
-    }
+    int e2 = make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
     if (e1 || e2) T3B_FAIL(T3B_ERR_CUDA, "umma: cuTensorMapEncodeTiled failed (%d, %d)", e1, e2);
     const int tiles = epi == EPI_SILU ? N / 128 : (N + UM_M - 1) / UM_M;
     if (awq) {

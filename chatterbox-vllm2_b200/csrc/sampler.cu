@@ -98,7 +98,9 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
     __shared__ unsigned long long s_below;
     __shared__ unsigned int s_digit, s_tie_rank_base;
 
-    pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
+    // No early griddepcontrol.launch_dependents here: this kernel advances the decode state (ctx_lens, positions, history), and the
+    // kernels of the next step read that state BEFORE their own dependency wait (attention prefetches K/V by it), so they must not
+    // start until this grid has completed (the implicit trigger at exit).
     pdl_wait();
     const int b = blockIdx.x, tid = threadIdx.x, V = a.V;
     const bool active = a.has_state ? (a.st.active == nullptr || a.st.active[b] != 0) : true;
@@ -151,6 +153,34 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
     __syncthreads();
     if (!active) { if (tid == 0 && a.out_tokens) a.out_tokens[b] = -1; return; }
 
+    // ---- token heuristics of alignment_stream_analyzer.py:143-195, run in the loop: the call that shapes the logits of token i
+    // (i = tokens generated so far) is the analyzer's (i+1)-th step, after it has seen tokens 0..i-1:
+    //   curr_frame_pos = i + 1; text_position = min(frame // 2, n_text - 1); complete from the first frame with
+    //   text_position >= n_text - 3 (a pure function of n_text: frame max(1, 2 (n_text - 3)));
+    //   3 equal tokens in a row or >= 10 frames after completion => every logit -2^15 except EOS = +2^15 (the EOS is then the
+    //   only possible outcome of greedy and of sampling); else EOS = -2^15 while text_position < n_text - 3 and n_text > 5.
+    const int stop_tok = (a.has_state && a.st.stop_tokens) ? a.st.stop_tokens[b] : -1;
+    bool force_eos = false;
+    if (a.sp.analyzer_text_tokens != nullptr && a.has_state && a.st.hist_len != nullptr && stop_tok >= 0 && stop_tok < V) {
+        const int n_text = a.sp.analyzer_text_tokens[b];
+        if (n_text > 0) {
+            const int i = a.st.hist_len[b], frame = i + 1;
+            bool rep = false;
+            if (i >= 3 && i <= a.st.hist_stride) {
+                const int32_t* hh = a.st.history + (size_t)b * a.st.hist_stride;
+                rep = hh[i - 1] == hh[i - 2] && hh[i - 2] == hh[i - 3];
+            }
+            const int f_star = max(1, 2 * (n_text - 3));
+            const bool long_tail = frame - f_star >= 10;
+            const int text_pos = min(frame / 2, n_text - 1);
+            force_eos = rep || long_tail;
+            if (!force_eos && text_pos < n_text - 3 && n_text > 5) {
+                if (tid == 0) lg[stop_tok] = -32768.f;
+                __syncthreads();
+            }
+        }
+    }
+
     // ---- S2: repetition penalty over the generated tokens (utils.py:51-89) -----------------------
     const float rho = a.sp.repetition_penalty ? a.sp.repetition_penalty[b] : 1.0f;
     if (a.has_state && a.st.history != nullptr && rho != 1.0f) {
@@ -168,7 +198,9 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
 
     const float temp = a.sp.temperature ? a.sp.temperature[b] : 0.f;
     int token;
-    if (temp < SMP_EPS) {
+    if (force_eos) {
+        token = stop_tok;
+    } else if (temp < SMP_EPS) {
         // ---- S3 greedy: argmax, first index on ties --------------------------------------------
         float bv = -INFINITY; int bi = 0x7fffffff;
         for (int i = tid; i < V; i += SMP_THREADS) { const float l = lg[i]; if (l > bv) { bv = l; bi = i; } }
@@ -199,9 +231,11 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
         if (top_p < 1.f) {
             // ascending cumulative mass <= (1 - top_p) is dropped (topk_topp_sampler.py:356-363).
             // budget in fixed point; find the key T with mass{key < T} <= budget < mass{key <= T}.
-            const unsigned long long budget = (unsigned long long)((double)(1.0f - top_p) * (double)Z);
+            // top_p is validated on the host to (0, 1]; the clamp keeps the crossing bin defined for any input
+            unsigned long long budget = (unsigned long long)((double)fmaxf(1.0f - top_p, 0.f) * (double)Z);
+            if (budget >= Z) budget = Z > 0 ? Z - 1 : 0;
             uint32_t prefix = 0;
-            if (tid == 0) s_below = 0;
+            if (tid == 0) { s_below = 0; s_digit = 0; }
             for (int pass = 0; pass < 4; ++pass) {
                 const int shift = 24 - 8 * pass;
                 hist[tid] = 0; hcnt[tid] = 0;          // SMP_THREADS == 256 bins
@@ -305,7 +339,7 @@ __global__ void __launch_bounds__(SMP_THREADS) cfg_sample_kernel(const SamplerAr
             st.speech_pos[b] += 1;
             for (int r = 2 * b; r < 2 * b + 2; ++r)
                 if (st.ctx_lens[r] + 1 < st.max_ctx) { st.ctx_lens[r] += 1; st.rope_pos[r] += 1; }
-            if (token == st.stop_token && st.active) st.active[b] = 0;
+            if (stop_tok >= 0 && token == stop_tok && st.active) st.active[b] = 0;
         }
     }
 }

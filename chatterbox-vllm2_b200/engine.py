@@ -2,24 +2,27 @@
 tts.py:445-465 ``self.t3.generate(prompts, sampling_params)``, tts.py:474-492 result shape), for one
 B200.
 
-Continuous batching over fixed request slots; paged KV (block 16) with all blocks of a request
-reserved at admission; prefill of new requests as ONE multi-token pass (t3.py:542-561 layout);
+Continuous batching over fixed request slots; paged KV (block 16) whose block tables GROW with the request
+(a few blocks ahead of the decode position, so a 100-token and a 1000-token request cost what they use);
+the 32 leading positions of a request's cond and uncond rows - bit-identical conditioning prefix,
+t3.py:554-556 - live in ONE pair of physical blocks, shared across requests of the same voice (tts.py:256-288);
+prefill of new requests as ONE multi-token pass (t3.py:542-561 layout, assembled on the device);
 the decode step (embedding gather -> 30 layers -> head -> CFG -> sampler -> state advance) captured
-in a CUDA graph per slot-count bucket and replayed with no host writes between steps.  The host
-only reads back ``hist_len`` / ``active`` every few steps to retire finished requests.
+in a CUDA graph per slot-count bucket and replayed with no host writes between steps.  The host only
+extends block tables and reads back ``hist_len`` / ``active`` every few steps to retire finished requests.
 
-Multi-GPU: replicas only - one engine per GPU, requests sharded by the caller
-(``shard_requests``); no collective on the decode path.
+Multi-GPU: replicas only (SURVEY.md 8(e)) - one engine per GPU, requests assigned by ``dispatch.assign_requests``;
+no collective on the decode path.
 """
-import os
 from dataclasses import dataclass, field
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
 
-from . import _lib
 from .constants import CONDITIONING_SIZE, KV_BLOCK, SPEECH_TOKEN_OFFSET, T3Dims
 from .model import (START_SPEECH_TOKEN, STOP_SPEECH_TOKEN, DecodeState, KVPool, SamplingTensors, T3B200Model)
+
+SHARED_PREFIX_BLOCKS = (CONDITIONING_SIZE // KV_BLOCK)          # 2 blocks = positions 0..31 of the 34-row conditioning prefix
 
 
 @dataclass
@@ -34,6 +37,29 @@ class SamplingParams:
     seed: Optional[int] = None
     cfg_scale: Optional[float] = None      # per-request CFG (the reference has one global, t3.py:296)
     ignore_eos: bool = False               # fixed-work benchmarks: never stop early
+    analyzer_text_tokens: int = 0          # > 0: run the token heuristics of alignment_stream_analyzer.py:143-195 in the loop with
+                                           # text_tokens_count = this (tts.py:496 passes len(prompt.split()) * 2); 0 = off
+
+    def validate(self) -> None:
+        """vLLM rejects the same values (sampling_params.py _verify_args)."""
+        if not (0.0 < self.top_p <= 1.0):
+            raise ValueError(f"top_p must be in (0, 1], got {self.top_p}")
+        if not (0.0 <= self.min_p <= 1.0):
+            raise ValueError(f"min_p must be in [0, 1], got {self.min_p}")
+        if self.temperature < 0.0:
+            raise ValueError(f"temperature must be non-negative, got {self.temperature}")
+        if self.repetition_penalty <= 0.0:
+            raise ValueError(f"repetition_penalty must be positive, got {self.repetition_penalty}")
+        if self.max_tokens < 1:
+            raise ValueError(f"max_tokens must be at least 1, got {self.max_tokens}")
+        if len(self.stop_token_ids) > 1:
+            raise ValueError("one stop token per request is supported (tts.py:457 passes exactly one)")
+
+    def stop_token(self) -> int:
+        """Un-offset stop id, -1 = never stops."""
+        if self.ignore_eos or len(self.stop_token_ids) == 0:
+            return -1
+        return int(self.stop_token_ids[0]) - SPEECH_TOKEN_OFFSET
 
 
 @dataclass
@@ -51,13 +77,15 @@ class RequestOutput:
 @dataclass
 class _Req:
     rid: int
-    cond: torch.Tensor                     # [P, D] bf16 prefill embeddings, cond row
-    uncond: torch.Tensor
+    cond_emb: Optional[torch.Tensor]       # [34, D] conditioning prefix (None when ready-made embeddings were given)
+    text_ids: Optional[List[int]]
+    embeds: Optional[Tuple[torch.Tensor, torch.Tensor]]   # ready (cond, uncond) prefill rows
     sp: SamplingParams
+    n_prompt: int
     slot: int = -1
-    blocks: List[int] = field(default_factory=list)
-    n_prompt: int = 0
-    n_gen: int = 0
+    blocks: List[List[int]] = field(default_factory=lambda: [[], []])     # physical blocks of the cond / uncond row, in order
+    n_gen: int = 0                         # tokens generated so far (host's view)
+    voice: Optional[int] = None            # key of the shared conditioning prefix
 
 
 def shard_requests(n_requests: int, world_size: int, rank: int) -> List[int]:
@@ -68,7 +96,7 @@ def shard_requests(n_requests: int, world_size: int, rank: int) -> List[int]:
 class T3B200Engine:
     def __init__(self, model: T3B200Model, max_num_seqs: int = 32, max_model_len: int = 1200,
                  kv_blocks: Optional[int] = None, check_every: int = 8, prefill_chunk_tokens: int = 8192,
-                 use_graphs: bool = True, decode_lanes: Optional[int] = None):
+                 use_graphs: bool = True, kv_dtype: str = "bf16", share_prefix: bool = True, grow_steps: int = 32):
         self.m = model
         self.dims: T3Dims = model.dims
         self.dev = model.device
@@ -77,68 +105,36 @@ class T3B200Engine:
         self.max_blocks = (max_model_len + KV_BLOCK - 1) // KV_BLOCK
         if kv_blocks is None:
             kv_blocks = 2 * max_num_seqs * self.max_blocks + 1
-        self.kv = KVPool(self.dims, kv_blocks, self.dev)
+        self.kv = KVPool(self.dims, kv_blocks, self.dev, kv_dtype)
         self.state = DecodeState(max_num_seqs, self.max_blocks, max_model_len, max_model_len, self.dev)
         self.sampling = SamplingTensors(max_num_seqs, self.dev, model.combine)
         self.hidden = torch.empty(2 * max_num_seqs, self.dims.hidden, dtype=torch.bfloat16, device=self.dev)
         self.out_tokens = torch.empty(max_num_seqs, dtype=torch.int32, device=self.dev)
         self.check_every = max(1, check_every)
-        self.prefill_chunk = prefill_chunk_tokens
+        self.grow_steps = max(1, grow_steps)
+        self.prefill_chunk = max(prefill_chunk_tokens, 2 * max_model_len)
         self.use_graphs = use_graphs
-        # Decode lanes: the step of a slot bucket is cut into `lanes` independent slices of requests, each a
-        # chain of ~214 small dependent kernels on its own stream (forked / joined inside the CUDA graph).
-        # One chain is latency-bound (a few us per kernel, far below HBM speed); several chains in flight
-        # fill the machine.  Rows never interact, so every request's arithmetic is unchanged.
-        self.decode_lanes = decode_lanes if decode_lanes is not None else (int(os.environ.get("T3B_DECODE_LANES", "0")) or None)
-        self._lane_streams: List[torch.cuda.Stream] = []
+        self.share_prefix = share_prefix
         self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self.slots: List[Optional[_Req]] = [None] * max_num_seqs
         self.steps_run = 0
+        self.preemptions = 0
+        self._voices: Dict[int, List] = {}           # voice key -> [blocks (2), live requests]
         model.bind(self.kv, self.state)
-        model.workspace(max(2 * max_num_seqs, prefill_chunk_tokens))     # sized once: graphs hold its address
-        if model.mega is not None:
-            r = min(2 * max_num_seqs, _lib.lib().t3b_mega_max_rows())
-            model.mega_workspace(r)
-            model.mega_logits(r)
-        if model.fused is not None:
-            r = min(2 * max_num_seqs, _lib.lib().t3b_fused_max_rows())
-            model.fused_workspace(r)
-            model.mega_logits(r)
+        # One workspace for the engine's lifetime, sized for its largest launch: captured graphs hold its address, so it must
+        # never move (the model's own growable scratch is not used here).
+        self.ws = torch.empty(model.workspace_bytes(max(2 * max_num_seqs, self.prefill_chunk)), dtype=torch.uint8, device=self.dev)
 
     # ------------------------------------------------------------------ one decode step
-    def lane_plan(self, n_slots: int) -> List[tuple]:
-        """[(first slot, slots)] per lane.  Default one lane: measured on B200 (cfg2, 32 requests) 1/2/4/8 lanes give
-        19.0k / 20.0k / 19.5k / 13.3k tokens/s - the lanes contend for SMs more than they hide latency."""
-        lanes = self.decode_lanes if self.decode_lanes else 1
-        lanes = max(1, min(lanes, n_slots))
-        base, extra = divmod(n_slots, lanes)
-        plan, s0 = [], 0
-        for g in range(lanes):
-            n = base + (1 if g < extra else 0)
-            plan.append((s0, n))
-            s0 += n
-        return plan
-
     def _step_eager(self, n_slots: int) -> None:
-        plan = self.lane_plan(n_slots)
-        if len(plan) == 1:
-            self.m.decode_lane(self.kv, self.state, self.sampling, 0, n_slots, 0, self.hidden, self.out_tokens)
-            return
-        while len(self._lane_streams) < len(plan):
-            self._lane_streams.append(torch.cuda.Stream(device=self.dev))
-        cur = torch.cuda.current_stream(self.dev)
-        for g, (s0, n) in enumerate(plan):
-            st = self._lane_streams[g]
-            st.wait_stream(cur)                                   # fork
-            with torch.cuda.stream(st):
-                self.m.decode_lane(self.kv, self.state, self.sampling, s0, n, g, self.hidden, self.out_tokens)
-        for g in range(len(plan)):
-            cur.wait_stream(self._lane_streams[g])                # join
+        self.m.decode_and_sample(self.kv, self.state, self.sampling, n_slots, self.hidden, self.out_tokens, self.ws)
 
     def launches_per_step(self, n_slots: int) -> int:
         """Kernels one decode step launches: embed + per layer [norm, qkv, attention(+RoPE+KV write), o, norm,
-        gate_up(+SiLU*mul), down] + final norm + head + sampler."""
-        return len(self.lane_plan(self._bucket(n_slots))) * (1 + self.dims.n_layers * 7 + 3)
+        gate_up(+SiLU*mul), down] + final norm + head + sampler (the two norms ride inside the GEMVs at <= 2 rows)."""
+        rows = 2 * self._bucket(n_slots)
+        gemv = rows <= 2 and self.m.quantization is None and self.m.options is None
+        return 1 + self.dims.n_layers * (5 if gemv else 7) + 3
 
     def _bucket(self, n_slots: int) -> int:
         b = 1
@@ -178,60 +174,121 @@ class T3B200Engine:
         self._graphs[nb] = g
         return g
 
+    # ------------------------------------------------------------------ KV blocks
+    @staticmethod
+    def _nblk(tokens: int) -> int:
+        return (tokens + KV_BLOCK - 1) // KV_BLOCK
+
+    def _voice_key(self, r: _Req) -> Optional[int]:
+        if not self.share_prefix or r.cond_emb is None or r.n_prompt < SHARED_PREFIX_BLOCKS * KV_BLOCK:
+            return None
+        c = r.cond_emb[:SHARED_PREFIX_BLOCKS * KV_BLOCK].detach().to("cpu").contiguous()
+        return hash((str(c.dtype), c.view(torch.uint8).numpy().tobytes()))
+
+    def _alloc_prompt(self, r: _Req) -> bool:
+        """Blocks for the prompt plus the growth look-ahead; False (nothing allocated) if the pool cannot hold them."""
+        nb = self._nblk(min(self.max_len, r.n_prompt + self.grow_steps))
+        key = self._voice_key(r)
+        if key is None:
+            if 2 * nb > len(self.kv.free):
+                return False
+            r.blocks = [self.kv.alloc(nb), self.kv.alloc(nb)]
+            return True
+        v = self._voices.get(key)
+        own = 2 * (nb - SHARED_PREFIX_BLOCKS)
+        if own + (0 if v else SHARED_PREFIX_BLOCKS) > len(self.kv.free):
+            return False
+        if v is None:
+            shared = self.kv.alloc(SHARED_PREFIX_BLOCKS)
+            self.kv.share(shared)                              # the cond and the uncond row both name them
+            v = self._voices[key] = [shared, 0]
+        else:
+            shared = v[0]
+            self.kv.share(shared); self.kv.share(shared)
+        v[1] += 1
+        r.voice = key
+        r.blocks = [list(shared) + self.kv.alloc(nb - SHARED_PREFIX_BLOCKS), list(shared) + self.kv.alloc(nb - SHARED_PREFIX_BLOCKS)]
+        return True
+
+    def _release(self, r: _Req) -> None:
+        self.kv.release(r.blocks[0]); self.kv.release(r.blocks[1])
+        r.blocks = [[], []]
+        if r.voice is not None:
+            v = self._voices[r.voice]
+            v[1] -= 1
+            if v[1] == 0:
+                del self._voices[r.voice]
+            r.voice = None
+
+    def _grow(self, live: List[_Req], steps: int) -> bool:
+        """Every live row gets the blocks its next ``steps`` tokens need; one small host->device copy.  False if the pool is short."""
+        want = []
+        total = 0
+        for r in live:
+            nb = self._nblk(min(self.max_len, r.n_prompt + r.n_gen + steps))
+            add = nb - len(r.blocks[0])
+            if add > 0:
+                want.append((r, add))
+                total += 2 * add
+        if total > len(self.kv.free):
+            return False
+        if not want:
+            return True
+        idx, val = [], []
+        for r, add in want:
+            for half in (0, 1):
+                new = self.kv.alloc(add)
+                base = (2 * r.slot + half) * self.max_blocks + len(r.blocks[half])
+                idx += list(range(base, base + add))
+                val += new
+                r.blocks[half] += new
+        upd = torch.tensor([idx, val], dtype=torch.int64).pin_memory().to(self.dev, non_blocking=True)
+        self.state.block_tables.view(-1)[upd[0]] = upd[1].to(torch.int32)
+        return True
+
+    def kv_tokens_outstanding(self) -> int:
+        """Token-rows of KV currently reserved (the dispatcher's load measure)."""
+        return (self.kv.num_blocks - 1 - len(self.kv.free)) * KV_BLOCK
+
     # ------------------------------------------------------------------ admission + prefill
     def _make_req(self, rid: int, prompt: dict, sp: SamplingParams) -> _Req:
+        sp.validate()
         if "prefill_embeds" in prompt:
             cond, uncond = prompt["prefill_embeds"]
             cond = cond.to(device=self.dev, dtype=torch.bfloat16)
             uncond = uncond.to(device=self.dev, dtype=torch.bfloat16)
+            r = _Req(rid, None, None, (cond, uncond), sp, cond.shape[0])
         else:
             conds = prompt["multi_modal_data"]["conditionals"]
             cond_emb = conds[0] if isinstance(conds, (list, tuple)) else conds
             ids = prompt.get("prompt_token_ids")
             if ids is None:
                 raise ValueError("prompt needs 'prompt_token_ids' (text tokenisation is outside the T3 decode path)")
-            cond, uncond = self.m.prefill_embeds(cond_emb[:CONDITIONING_SIZE], ids)
-        r = _Req(rid, cond, uncond, sp)
-        r.n_prompt = cond.shape[0]
+            ids = list(ids)
+            if ids and ids[0] == 695 and ids[-1] == 697 and len(ids) > CONDITIONING_SIZE:     # packed like t3.py:189-200
+                from .packing import unpack_prompt
+                ids = unpack_prompt(ids)
+            if cond_emb.shape[0] < CONDITIONING_SIZE:
+                raise ValueError(f"conditionals must have {CONDITIONING_SIZE} rows (t3.py:210), got {cond_emb.shape[0]}")
+            r = _Req(rid, cond_emb[:CONDITIONING_SIZE], ids, None, sp, CONDITIONING_SIZE + len(ids) + 1)
         if r.n_prompt + 1 > self.max_len:
             raise ValueError(f"prompt of {r.n_prompt} tokens does not fit max_model_len {self.max_len}")
         return r
 
-    def _embed_prompts(self, prompts: List[dict]) -> List[dict]:
-        """Prompts that come as (conditionals, prompt_token_ids) get their prefill embeddings in ONE batched pass
-        (T3B200Model.prefill_embeds_batch) instead of a dozen small device operations each."""
-        todo = [i for i, p in enumerate(prompts) if "prefill_embeds" not in p and p.get("prompt_token_ids") is not None
-                and "multi_modal_data" in p]
-        if len(todo) < 2:
-            return prompts
-        conds = []
-        for i in todo:
-            c = prompts[i]["multi_modal_data"]["conditionals"]
-            conds.append(c[0] if isinstance(c, (list, tuple)) else c)
-        if any(c.shape[0] < CONDITIONING_SIZE for c in conds) or len({c.device for c in conds}) != 1:
-            return prompts
-        pairs = self.m.prefill_embeds_batch(conds, [prompts[i]["prompt_token_ids"] for i in todo])
-        out = list(prompts)
-        for i, pr in zip(todo, pairs):
-            out[i] = {"prefill_embeds": pr}
-        return out
+    def _limit(self, r: _Req) -> int:
+        return min(r.sp.max_tokens, self.max_len - r.n_prompt)
 
     def _admit(self, reqs: List[_Req]) -> None:
-        """Reserve KV, run the prompts of ``reqs`` through the backbone in one multi-token pass per chunk,
-        sample each request's first speech token and install its slot state."""
-        st, dev = self.state, self.dev
-        # block tables of all admitted requests: built on the host, ONE copy + ONE indexed store on the device
+        """Run the prompts of ``reqs`` (blocks already allocated, slots assigned) through the backbone in one multi-token pass
+        per chunk, sample each request's first speech token and install its slot state."""
+        st, dev, m = self.state, self.dev, self.m
         bt = torch.zeros(2 * len(reqs), self.max_blocks, dtype=torch.int32)
         bt_rows = []
         for i, r in enumerate(reqs):
-            total = min(self.max_len, r.n_prompt + r.sp.max_tokens)
-            nblk = (total + KV_BLOCK - 1) // KV_BLOCK
-            r.blocks = self.kv.alloc(2 * nblk)
-            bt[2 * i, :nblk] = torch.tensor(r.blocks[:nblk], dtype=torch.int32)
-            bt[2 * i + 1, :nblk] = torch.tensor(r.blocks[nblk:], dtype=torch.int32)
+            for half in (0, 1):
+                bt[2 * i + half, :len(r.blocks[half])] = torch.tensor(r.blocks[half], dtype=torch.int32)
             bt_rows += [2 * r.slot, 2 * r.slot + 1]
         st.block_tables[torch.tensor(bt_rows, device=dev)] = bt.to(dev)
-        # token arrays for the multi-token pass: rows in slot order, tokens of a row contiguous
         chunks: List[List[_Req]] = [[]]
         ntok = 0
         for r in reqs:
@@ -239,34 +296,38 @@ class T3B200Engine:
                 chunks.append([]); ntok = 0
             chunks[-1].append(r); ntok += 2 * r.n_prompt
         for ch in chunks:
-            xs, rows, idx, last = [], [], [], []
-            n = 0
-            for r in ch:
-                for half, x in enumerate((r.cond, r.uncond)):
-                    xs.append(x)
-                    rows.append(torch.full((r.n_prompt,), 2 * r.slot + half, dtype=torch.int32))
-                    idx.append(torch.arange(r.n_prompt, dtype=torch.int32))
-                    n += r.n_prompt
-                    last.append(n - 1)
-            x = torch.cat(xs, 0).contiguous()
-            if x.shape[0] > self.prefill_chunk:
-                self.m.workspace(x.shape[0]); self._graphs.clear()
-            tok_row, tok_idx = torch.cat(rows).to(dev), torch.cat(idx).to(dev)
-            h = self.m.forward_tokens(self.kv, x, tok_row, tok_idx, tok_idx, st.block_tables)
-            h_last = h[torch.tensor(last, device=dev)].contiguous()          # hidden of each row's BOS token
+            if all(r.embeds is None for r in ch):
+                x, tok_row, tok_idx, starts = m.prefill_assemble([r.cond_emb for r in ch], [r.text_ids for r in ch], [r.slot for r in ch])
+                seq_start, seq_row = m.last_seq
+            else:                                            # ready-made embeddings: rows built on the host side
+                xs, rows, idx, starts, srow = [], [], [], [0], []
+                for r in ch:
+                    pair = r.embeds if r.embeds is not None else m.prefill_embeds(r.cond_emb, r.text_ids)
+                    for half, xx in enumerate(pair):
+                        xs.append(xx)
+                        rows.append(torch.full((r.n_prompt,), 2 * r.slot + half, dtype=torch.int32))
+                        idx.append(torch.arange(r.n_prompt, dtype=torch.int32))
+                        starts.append(starts[-1] + r.n_prompt)
+                        srow.append(2 * r.slot + half)
+                x = torch.cat(xs, 0).contiguous()
+                tok_row, tok_idx = torch.cat(rows).to(dev), torch.cat(idx).to(dev)
+                seq_start = torch.tensor(starts, dtype=torch.int32, device=dev)
+                seq_row = torch.tensor(srow, dtype=torch.int32, device=dev)
+            max_seq = max(r.n_prompt for r in ch)
+            h = m.forward_tokens(self.kv, x, tok_row, tok_idx, tok_idx, st.block_tables, seq_start, seq_row, max_seq, ws=self.ws)
+            h_last = h[torch.tensor([s - 1 for s in starts[1:]], device=dev)].contiguous()      # hidden of each row's BOS token
             nreq = len(ch)
             tmp_state = DecodeState(nreq, self.max_blocks, self.max_len, self.max_len, dev)
-            tmp_sp = SamplingTensors(nreq, dev, self.m.combine)
+            tmp_sp = SamplingTensors(nreq, dev, m.combine)
             for j, r in enumerate(ch):
                 sp = r.sp
-                tmp_sp.set(j, cfg_scale=self.m.cfg_scale if sp.cfg_scale is None else sp.cfg_scale,
+                tmp_sp.set(j, cfg_scale=m.cfg_scale if sp.cfg_scale is None else sp.cfg_scale,
                            repetition_penalty=sp.repetition_penalty, temperature=sp.temperature, min_p=sp.min_p,
-                           top_p=sp.top_p, seed=(r.rid if sp.seed is None else sp.seed))
-            tmp_state.ctx_lens.fill_(0)
+                           top_p=sp.top_p, seed=(r.rid if sp.seed is None else sp.seed), analyzer_text_tokens=sp.analyzer_text_tokens)
+            tmp_state.stop_tokens.copy_(torch.tensor([r.sp.stop_token() for r in ch], dtype=torch.int32))
             tmp_state.active.fill_(1)
-            tmp_state.c.stop_token = st.c.stop_token
             toks = torch.empty(nreq, dtype=torch.int32, device=dev)
-            self.m.head_cfg_sample(h_last, 2 * nreq, tmp_sp, tmp_state, toks, advance=True)
+            m.head_cfg_sample(h_last, 2 * nreq, tmp_sp, tmp_state, toks, advance=True, ws=self.ws)
             slots = torch.tensor([r.slot for r in ch], device=dev)
             rows2 = torch.stack([2 * slots, 2 * slots + 1], 1).reshape(-1)
             npr = torch.tensor([r.n_prompt for r in ch], dtype=torch.int32, device=dev).repeat_interleave(2)
@@ -276,28 +337,75 @@ class T3B200Engine:
             st.hist_len[slots] = tmp_state.hist_len
             st.step[slots] = tmp_state.step
             st.active[slots] = tmp_state.active
+            st.stop_tokens[slots] = tmp_state.stop_tokens
             st.ctx_lens[rows2] = npr
             st.rope_pos[rows2] = npr
-            for name in ("cfg_scale", "repetition_penalty", "temperature", "min_p", "top_p", "seed"):
+            for name in SamplingTensors.FIELDS:
                 getattr(self.sampling, name)[slots] = getattr(tmp_sp, name)
             for r in ch:
                 r.n_gen = 1
 
+    def install(self, prompts: Sequence[dict], sampling_params, reserve_steps: int = 0) -> List[_Req]:
+        """Admit ``prompts`` into free slots (prefill + first token) WITHOUT running decode steps, with blocks for ``reserve_steps``
+        more tokens per row: the entry point of benchmarks and teacher-forced tests that drive ``step()`` themselves."""
+        sps = list(sampling_params) if isinstance(sampling_params, (list, tuple)) else [sampling_params] * len(prompts)
+        reqs = [self._make_req(i, p, sp) for i, (p, sp) in enumerate(zip(prompts, sps))]
+        free = [i for i, s in enumerate(self.slots) if s is None]
+        if len(free) < len(reqs):
+            raise ValueError(f"{len(reqs)} requests but {len(free)} free slots")
+        for r, slot in zip(reqs, free):
+            r.slot = slot
+            if not self._alloc_prompt(r):
+                raise MemoryError("KV pool exhausted")
+            self.slots[slot] = r
+        self._admit(reqs)
+        if reserve_steps > 0 and not self._grow(reqs, reserve_steps):
+            raise MemoryError("KV pool exhausted")
+        return reqs
+
+    def uninstall(self, reqs: Sequence[_Req]) -> None:
+        for r in reqs:
+            self._release(r)
+            self.slots[r.slot] = None
+        self._park([r.slot for r in reqs])
+
     # ------------------------------------------------------------------ the caller's entry point
+    def _retire(self, done: List[_Req], results: Dict[int, RequestOutput], hist_host: torch.Tensor) -> None:
+        for r in done:
+            toks = hist_host[r.slot, :r.n_gen].tolist()
+            stop = r.sp.stop_token()
+            stopped = stop >= 0 and stop in toks
+            if stopped:
+                toks = toks[:toks.index(stop) + 1]
+            results[r.rid] = RequestOutput(r.rid, [CompletionOutput([t + SPEECH_TOKEN_OFFSET for t in toks],
+                                                                    "stop" if stopped else "length")])
+            self._release(r)
+            self.slots[r.slot] = None
+        self._park([r.slot for r in done])
+
+    def _park(self, slots: List[int]) -> None:
+        """Freed slots become idle rows (they write into scratch block 0): four indexed stores in all."""
+        if not slots:
+            return
+        st = self.state
+        sl = torch.tensor(slots, device=self.dev)
+        rw = torch.stack([2 * sl, 2 * sl + 1], 1).reshape(-1)
+        st.active[sl] = 0
+        st.ctx_lens[rw] = 0
+        st.rope_pos[rw] = 0
+        st.block_tables[rw] = 0
+
     def generate(self, prompts: Sequence[dict], sampling_params=None) -> List[RequestOutput]:
-        """tts.py:445-465.  ``prompts``: dicts with ``prompt_token_ids`` + ``multi_modal_data.conditionals``
-        ([34, 1024] tensor, tts.py:452) or ready ``prefill_embeds`` (cond, uncond).  ``sampling_params``:
-        one SamplingParams or one per prompt.  Returns results in prompt order; ``outputs[0].token_ids``
-        are offset by SPEECH_TOKEN_OFFSET like the reference's (tts.py:474-492)."""
+        """tts.py:445-465.  ``prompts``: dicts with ``prompt_token_ids`` (plain text ids, or packed like t3.py:189-200) +
+        ``multi_modal_data.conditionals`` ([34, 1024] tensor, tts.py:452) or ready ``prefill_embeds`` (cond, uncond).
+        ``sampling_params``: one SamplingParams or one per prompt (stop token, ignore_eos and every knob are per request).
+        Returns results in prompt order; ``outputs[0].token_ids`` are offset by SPEECH_TOKEN_OFFSET like the reference's
+        (tts.py:474-492)."""
         if sampling_params is None:
             sampling_params = SamplingParams()
         sps = list(sampling_params) if isinstance(sampling_params, (list, tuple)) else [sampling_params] * len(prompts)
-        ignore_eos = any(sp.ignore_eos for sp in sps)
-        stop = -1 if ignore_eos else int(sps[0].stop_token_ids[0]) - SPEECH_TOKEN_OFFSET     # tts.py:457
-        if stop != self.state.c.stop_token:
-            self.state.c.stop_token = stop
-            self._graphs.clear()                       # the stop token is baked into captured kernel arguments
-        prompts = self._embed_prompts(list(prompts))
+        if len(sps) != len(prompts):
+            raise ValueError(f"{len(prompts)} prompts but {len(sps)} sampling params")
         waiting = [self._make_req(i, p, sp) for i, (p, sp) in enumerate(zip(prompts, sps))]
         waiting.reverse()
         results: Dict[int, RequestOutput] = {}
@@ -308,44 +416,53 @@ class T3B200Engine:
                 if not waiting:
                     break
                 if self.slots[slot] is None:
-                    r = waiting.pop()
+                    r = waiting[-1]
                     r.slot = slot
+                    if not self._alloc_prompt(r):
+                        r.slot = -1
+                        break                                   # pool is full: wait for a running request to finish
+                    waiting.pop()
                     self.slots[slot] = r
                     new.append(r)
             if new:
                 self._admit(new)
             live = [r for r in self.slots if r is not None]
+            if not live:
+                raise MemoryError(f"KV pool ({self.kv.num_blocks} blocks) cannot hold a single prompt of {waiting[-1].n_prompt} tokens")
             n_slots = max(r.slot for r in live) + 1
-            # steps until the host has to look again: the shortest remaining length, and - only when a stop token can end a
-            # request early - at most check_every
-            budget = min(min(r.sp.max_tokens, self.max_len - r.n_prompt) - r.n_gen for r in live)
-            if stop >= 0:
+            may_stop = any(r.sp.stop_token() >= 0 or r.sp.analyzer_text_tokens > 0 for r in live)
+            # steps until the host has to look again: the shortest remaining length, the block look-ahead, and - only when a
+            # stop token can end a request early - at most check_every
+            budget = min(min(self._limit(r) - r.n_gen for r in live), self.grow_steps)
+            if may_stop:
                 budget = min(budget, self.check_every)
-            for _ in range(max(0, budget)):
+            budget = max(0, budget)
+            while not self._grow(live, budget):
+                # pool exhausted: preempt the youngest request (its tokens are regenerated later - sampling is keyed by
+                # (seed, index, step), so the stream is the same)
+                if len(live) == 1:
+                    raise MemoryError(f"KV pool ({self.kv.num_blocks} blocks) cannot hold one request of {live[0].n_prompt + live[0].n_gen} tokens")
+                victim = max(live, key=lambda r: r.rid)
+                live.remove(victim)
+                self._release(victim)
+                self.slots[victim.slot] = None
+                self._park([victim.slot])
+                victim.slot, victim.n_gen = -1, 0
+                waiting.append(victim)
+                self.preemptions += 1
+                n_slots = max(r.slot for r in live) + 1
+            for _ in range(budget):
                 self.step(n_slots)
-            poll = torch.stack([st.hist_len[:n_slots], st.active[:n_slots].to(st.hist_len.dtype)]).cpu()    # one D2H per poll
-            hist_len, active = poll[0], poll[1]
-            done = []
-            for r in live:
-                r.n_gen = int(hist_len[r.slot])
-                limit = min(r.sp.max_tokens, self.max_len - r.n_prompt)
-                if not bool(active[r.slot]) or r.n_gen >= limit:
-                    done.append(r)
-            hist_host = st.history[:n_slots].cpu() if done else None          # one D2H for every request that finished
-            for r in done:
-                toks = hist_host[r.slot, :r.n_gen].tolist()
-                stopped = stop >= 0 and stop in toks
-                if stopped:
-                    toks = toks[:toks.index(stop) + 1]
-                results[r.rid] = RequestOutput(r.rid, [CompletionOutput([t + SPEECH_TOKEN_OFFSET for t in toks],
-                                                                        "stop" if stopped else "length")])
-                self.kv.release(r.blocks)
-                self.slots[r.slot] = None
-            if done:                                                           # park the freed slots: four indexed stores in all
-                sl = torch.tensor([r.slot for r in done], device=self.dev)
-                rw = torch.stack([2 * sl, 2 * sl + 1], 1).reshape(-1)
-                st.active[sl] = 0
-                st.ctx_lens[rw] = 0
-                st.rope_pos[rw] = 0
-                st.block_tables[rw] = 0
+            if may_stop:
+                poll = torch.stack([st.hist_len[:n_slots], st.active[:n_slots].to(st.hist_len.dtype)]).cpu()    # one D2H per poll
+                hist_len, active = poll[0], poll[1]
+                for r in live:
+                    r.n_gen = int(hist_len[r.slot])
+                done = [r for r in live if not bool(active[r.slot]) or r.n_gen >= self._limit(r)]
+            else:
+                for r in live:                                  # nothing can end early: the host knows every length
+                    r.n_gen += budget
+                done = [r for r in live if r.n_gen >= self._limit(r)]
+            if done:
+                self._retire(done, results, st.history[:n_slots].cpu())       # one D2H for every request that finished
         return [results[i] for i in range(len(prompts))]

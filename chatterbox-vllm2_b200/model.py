@@ -43,30 +43,59 @@ def llama3_rope_table(d: T3Dims) -> torch.Tensor:
 
 
 class KVPool:
-    """Paged KV pool: K and V bf16 [n_layers, num_blocks, n_heads, 16, 64] (include/t3b200.h t3b_kv_t).
-    Block 0 is the scratch block idle rows write to; the allocator hands out 1..num_blocks-1."""
+    """Paged KV pool (include/t3b200.h t3b_kv_t): K and V as bytes [n_layers, num_blocks, n_heads, slice] where a
+    (block, head) slice holds 16 tokens - 2048 B of bf16, or for ``dtype="fp8"`` 1024 B of e4m3 + 16 fp32 scales.
+    Block 0 is the scratch block idle rows write to; the allocator hands out 1..num_blocks-1.  Blocks are reference
+    counted so that rows can share the blocks of a common prefix (t3.py:554-556: the cond and uncond rows of a request
+    start with the same 34 conditioning embeddings)."""
 
-    def __init__(self, dims: T3Dims, num_blocks: int, device):
-        shape = (dims.n_layers, num_blocks, dims.n_heads, KV_BLOCK, dims.head_dim)
-        self.k = torch.zeros(shape, dtype=torch.bfloat16, device=device)
-        self.v = torch.zeros(shape, dtype=torch.bfloat16, device=device)
+    def __init__(self, dims: T3Dims, num_blocks: int, device, dtype: str = "bf16"):
+        if dtype not in ("bf16", "fp8"):
+            raise ValueError(f"KV dtype {dtype!r} not supported (bf16 or fp8)")
+        self.dtype = dtype
+        self.kv_dtype = _lib.T3B_KV_FP8 if dtype == "fp8" else _lib.T3B_KV_BF16
+        self.slice_bytes = 1088 if dtype == "fp8" else 2048
+        shape = (dims.n_layers, num_blocks, dims.n_heads, self.slice_bytes)
+        self.k = torch.zeros(shape, dtype=torch.uint8, device=device)
+        self.v = torch.zeros(shape, dtype=torch.uint8, device=device)
         self.num_blocks = num_blocks
-        self.c = _lib.KV(self.k.data_ptr(), self.v.data_ptr(), num_blocks * dims.n_heads * KV_BLOCK * dims.head_dim, num_blocks)
+        self.c = _lib.KV(self.k.data_ptr(), self.v.data_ptr(), num_blocks * dims.n_heads * self.slice_bytes, num_blocks, self.kv_dtype)
         self.free: List[int] = list(range(num_blocks - 1, 0, -1))
+        self.refs: Dict[int, int] = {}
 
     @staticmethod
-    def bytes_per_block(dims: T3Dims) -> int:
-        return 2 * dims.n_layers * dims.n_heads * KV_BLOCK * dims.head_dim * 2
+    def bytes_per_block(dims: T3Dims, dtype: str = "bf16") -> int:
+        return 2 * dims.n_layers * dims.n_heads * (1088 if dtype == "fp8" else 2048)
 
     def alloc(self, n: int) -> List[int]:
         if n > len(self.free):
             raise MemoryError(f"KV pool exhausted: need {n} blocks, {len(self.free)} free")
-        out = self.free[-n:]
-        del self.free[-n:]
+        out = self.free[-n:] if n else []
+        if n:
+            del self.free[-n:]
+        for b in out:
+            self.refs[b] = 1
         return out
 
+    def share(self, blocks: Sequence[int]) -> None:
+        """One more row names these blocks in its table."""
+        for b in blocks:
+            self.refs[b] += 1
+
     def release(self, blocks: Sequence[int]) -> None:
-        self.free.extend(blocks)
+        for b in blocks:
+            r = self.refs.get(b, 1) - 1
+            if r <= 0:
+                self.refs.pop(b, None)
+                self.free.append(b)
+            else:
+                self.refs[b] = r
+
+    def as_bf16(self, which: str = "k") -> torch.Tensor:
+        """bf16 view [n_layers, num_blocks, n_heads, 16, 64] of a bf16 pool (tests fill / compare it)."""
+        assert self.dtype == "bf16"
+        t = self.k if which == "k" else self.v
+        return t.view(torch.bfloat16).view(t.shape[0], t.shape[1], t.shape[2], KV_BLOCK, 64)
 
 
 class DecodeState:
@@ -76,42 +105,48 @@ class DecodeState:
                  stop_token: int = STOP_SPEECH_TOKEN):
         z = lambda *s: torch.zeros(*s, dtype=torch.int32, device=device)
         self.max_req, self.max_blocks, self.hist_stride, self.max_ctx = max_req, max_blocks, hist_stride, max_ctx
-        self.tokens, self.speech_pos = z(max_req), z(max_req)
-        self.rope_pos, self.ctx_lens = z(2 * max_req), z(2 * max_req)
+        # the per-step counters live in ONE buffer (views below), so a snapshot / restore of a decode position is one copy
+        self.small = z(9 * max_req)
+        v = lambda a, n: self.small[a * max_req:(a + n) * max_req]
+        self.tokens, self.speech_pos, self.hist_len, self.step, self.active = v(0, 1), v(1, 1), v(2, 1), v(3, 1), v(4, 1)
+        self.rope_pos, self.ctx_lens = v(5, 2), v(7, 2)
         self.block_tables = z(2 * max_req, max_blocks)
-        self.history, self.hist_len = z(max_req, hist_stride), z(max_req)
-        self.step, self.active = z(max_req), z(max_req)
-        self.c = self.view(0, stop_token)
+        self.history = z(max_req, hist_stride)
+        self.stop_tokens = torch.full((max_req,), stop_token, dtype=torch.int32, device=device)   # per request; < 0 = never stops
+        self.c = self.view(0)
 
-    def view(self, slot0: int, stop_token: Optional[int] = None) -> _lib.State:
-        """t3b_state_t whose request 0 is slot ``slot0`` (a lane of the decode step works on a slice of slots)."""
+    def view(self, slot0: int) -> _lib.State:
+        """t3b_state_t whose request 0 is slot ``slot0``."""
         p = lambda t, n: t.data_ptr() + 4 * n
-        stop = self.c.stop_token if stop_token is None else stop_token
         return _lib.State(p(self.tokens, slot0), p(self.speech_pos, slot0), p(self.rope_pos, 2 * slot0), p(self.ctx_lens, 2 * slot0),
                           p(self.block_tables, 2 * slot0 * self.max_blocks), self.max_blocks, p(self.history, slot0 * self.hist_stride),
-                          p(self.hist_len, slot0), self.hist_stride, p(self.step, slot0), p(self.active, slot0), stop, self.max_ctx)
+                          p(self.hist_len, slot0), self.hist_stride, p(self.step, slot0), p(self.active, slot0),
+                          p(self.stop_tokens, slot0), self.max_ctx)
 
 
 class SamplingTensors:
     """Per-request sampling knobs on the device (t3b_sampling_t; tts.py:455-464 SamplingParams)."""
+    FIELDS = ("cfg_scale", "repetition_penalty", "temperature", "min_p", "top_p", "seed", "analyzer_text_tokens")
 
     def __init__(self, max_req: int, device, combine: str = "bf16"):
         f = lambda v: torch.full((max_req,), v, dtype=torch.float32, device=device)
         self.cfg_scale, self.repetition_penalty, self.temperature = f(0.5), f(1.0), f(0.0)
         self.min_p, self.top_p = f(0.0), f(1.0)
         self.seed = torch.zeros(max_req, dtype=torch.int64, device=device)
+        self.analyzer_text_tokens = torch.zeros(max_req, dtype=torch.int32, device=device)     # 0 = heuristics off
         self.combine = _lib.T3B_COMBINE_BF16 if combine == "bf16" else _lib.T3B_COMBINE_FP32
         self.c = self.view(0)
 
     def view(self, slot0: int) -> _lib.Sampling:
         p = lambda t: t.data_ptr() + t.element_size() * slot0
         return _lib.Sampling(p(self.cfg_scale), p(self.repetition_penalty), p(self.temperature), p(self.min_p), p(self.top_p),
-                             p(self.seed), self.combine)
+                             p(self.seed), p(self.analyzer_text_tokens), self.combine)
 
-    def set(self, slot: int, *, cfg_scale, repetition_penalty, temperature, min_p, top_p, seed) -> None:
+    def set(self, slot: int, *, cfg_scale, repetition_penalty, temperature, min_p, top_p, seed, analyzer_text_tokens=0) -> None:
         self.cfg_scale[slot], self.repetition_penalty[slot], self.temperature[slot] = cfg_scale, repetition_penalty, temperature
         self.min_p[slot], self.top_p[slot] = min_p, top_p
         self.seed[slot] = seed & 0x7FFFFFFFFFFFFFFF
+        self.analyzer_text_tokens[slot] = analyzer_text_tokens
 
     def fill(self, n: int, *, cfg_scale, repetition_penalty, temperature, min_p, top_p, seeds: Sequence[int]) -> None:
         self.cfg_scale[:n], self.repetition_penalty[:n], self.temperature[:n] = cfg_scale, repetition_penalty, temperature
@@ -123,8 +158,13 @@ class T3B200Model:
     """Drop-in for ``T3VllmModel`` (t3.py:255-716) on one B200."""
 
     def __init__(self, *, vllm_config=None, prefix: str = "", dims: T3Dims = T3Dims(), t3_config: Optional[T3Config] = None,
-                 device="cuda:0", cfg_scale: Optional[float] = None, combine: str = "bf16", quantization: Optional[str] = None):
-        # vllm_config / prefix are accepted for signature compatibility with t3.py:258 and ignored.
+                 device="cuda:0", cfg_scale: Optional[float] = None, combine: str = "bf16", quantization: Optional[str] = None,
+                 options: Optional[_lib.Options] = None):
+        # t3.py:258-263: the reference reads the Llama shapes from vllm_config.model_config.hf_config and forces hidden 1024
+        # (the config file says 2048, the cond|uncond packing hack).  The same fields are honoured here when a config is given.
+        self.prefix = prefix
+        if vllm_config is not None:
+            dims, quantization = self._dims_from_vllm_config(vllm_config, dims, quantization)
         self.dims = dims
         self.cfg = t3_config or T3Config.multilingual()
         self.device = torch.device(device)
@@ -134,17 +174,36 @@ class T3B200Model:
         if quantization not in (None, "awq"):
             raise ValueError(f"quantization {quantization!r} not supported (None or 'awq')")
         self.quantization = quantization
+        self.options = options                      # t3b_options_t (None = library defaults)
         self.w: Dict[str, torch.Tensor] = {}        # device tensors the C structs point into
         self.aux_weights: Dict[str, torch.Tensor] = {}   # cond_enc.* etc: not on the decode path, kept on CPU
         self._layers = None
         self.c: Optional[_lib.Model] = None
         self._ws: Optional[torch.Tensor] = None
-        self._lane_ws: Dict[int, torch.Tensor] = {}
-        self.mega: Optional[_lib.Mega] = None       # repacked weights of the persistent whole-step kernel (bf16 only)
-        self._mega_ws: Optional[torch.Tensor] = None
-        self.fused: Optional[torch.Tensor] = None   # weight blob of the fused step kernel (csrc/decode_fused.cu, bf16 only)
-        self._fused_ws: Optional[torch.Tensor] = None
         self._bound: Optional[Tuple[KVPool, DecodeState]] = None
+
+    @staticmethod
+    def _dims_from_vllm_config(vllm_config, dims: T3Dims, quantization: Optional[str]):
+        """Shapes from a vLLM config object (``vllm_config.model_config.hf_config``, t3.py:259-266) or a plain dict
+        with the keys of t3-model*/config.json."""
+        hf = getattr(getattr(vllm_config, "model_config", None), "hf_config", None)
+        if hf is None:
+            hf = vllm_config.get("hf_config", vllm_config) if isinstance(vllm_config, dict) else None
+        if hf is None:
+            return dims, quantization
+        get = (lambda k, d: hf.get(k, d)) if isinstance(hf, dict) else (lambda k, d: getattr(hf, k, d))
+        rs = get("rope_scaling", None) or {}
+        rs_get = (lambda k, d: rs.get(k, d)) if isinstance(rs, dict) else (lambda k, d: getattr(rs, k, d))
+        heads = int(get("num_attention_heads", dims.n_heads))
+        new = dims.small(n_layers=int(get("num_hidden_layers", dims.n_layers)), n_heads=heads, hidden=heads * dims.head_dim,
+                         ffn=int(get("intermediate_size", dims.ffn)), rms_eps=float(get("rms_norm_eps", dims.rms_eps)),
+                         rope_theta=float(get("rope_theta", dims.rope_theta)), rope_factor=float(rs_get("factor", dims.rope_factor)),
+                         rope_low=float(rs_get("low_freq_factor", dims.rope_low)), rope_high=float(rs_get("high_freq_factor", dims.rope_high)),
+                         rope_orig_max=int(rs_get("original_max_position_embeddings", dims.rope_orig_max)))
+        qc = getattr(vllm_config, "quant_config", None)
+        if quantization is None and qc is not None and "awq" in type(qc).__name__.lower():
+            quantization = "awq"
+        return new, quantization
 
     # ------------------------------------------------------------------ weights
     def load_weights(self, weights: Iterable[Tuple[str, torch.Tensor]]) -> Set[str]:
@@ -195,48 +254,7 @@ class T3B200Model:
         self.c = _lib.Model(d.n_layers, d.hidden, d.n_heads, d.head_dim, d.ffn, d.speech_vocab, self.w["speech_pos_emb"].shape[0],
                             d.max_pos, d.rms_eps, layers, self.w["norm"].data_ptr(), head, self.w["speech_emb"].data_ptr(),
                             self.w["speech_pos_emb"].data_ptr(), self.w["rope"].data_ptr())
-        self.mega = None
-        self.fused = None
-        if self.quantization is None and dev.type == "cuda":
-            if os.environ.get("T3B_MEGA", "0") == "1":
-                self._build_mega()
-            # opt-in (T3B_FUSED=1): the fused persistent kernel hit a cluster-barrier timeout in the 300-step bench at
-            # growing context (profiles/r01d_notes.md), so the PDL-chained kernels are the default decode path
-            if os.environ.get("T3B_FUSED", "0") == "1":
-                self._build_fused()
         return loaded
-
-    def _build_fused(self) -> None:
-        """Per-CTA weight streams of csrc/decode_fused.cu (t3b_fused_repack); None if the shape is not the T3 one."""
-        L = _lib.lib()
-        n = L.t3b_fused_weight_bytes(C.byref(self.c))
-        if n == 0:
-            return
-        blob = torch.empty(n, dtype=torch.uint8, device=self.device)
-        _lib.check(L.t3b_fused_repack(C.byref(self.c), blob.data_ptr(), _lib.stream_ptr()), "t3b_fused_repack")
-        torch.cuda.synchronize(self.device)
-        self.fused = blob
-
-    def _build_mega(self) -> None:
-        """Unit layout of csrc/decode_mega.cu: every projection as 16 KB blocks of 128 x 64 weights (t3b_repack_weights_bf16)."""
-        L, d = _lib.lib(), self.dims
-        s = _lib.stream_ptr()
-
-        def rp(key: str, w: torch.Tensor, gate_up: bool = False) -> int:
-            n, k = w.shape
-            out = torch.empty(L.t3b_repacked_bytes(n, k), dtype=torch.uint8, device=self.device)
-            _lib.check(L.t3b_repack_weights_bf16(w.data_ptr(), n, k, 1 if gate_up else 0, out.data_ptr(), s), "t3b_repack_weights_bf16")
-            self.w["mega." + key] = out
-            return out.data_ptr()
-
-        table = torch.empty(d.n_layers, 6, dtype=torch.int64)
-        for i in range(d.n_layers):
-            table[i] = torch.tensor([rp(f"{i}.qkv", self.w[f"{i}.qkv"]), rp(f"{i}.o", self.w[f"{i}.o"]),
-                                     rp(f"{i}.gate_up", self.w[f"{i}.gate_up"], True), rp(f"{i}.down", self.w[f"{i}.down"]),
-                                     self.w[f"{i}.ln1"].data_ptr(), self.w[f"{i}.ln2"].data_ptr()], dtype=torch.int64)
-        self.w["mega.table"] = table.to(self.device)
-        self.mega = _lib.Mega(self.w["mega.table"].data_ptr(), rp("head", self.w["head"]))
-        torch.cuda.synchronize(self.device)
 
     def _linear_struct(self, key: str, w: torch.Tensor, gate_up: bool = False) -> _lib.Linear:
         """bf16 [N, K] -> t3b_linear_t.  quantization="awq": the weight is quantised here (no pre-quantised T3
@@ -265,7 +283,7 @@ class T3B200Model:
 
     def weight_bytes(self) -> int:
         """Bytes streamed from HBM per decode step (layers + final norm + head)."""
-        keep = lambda k: k[0].isdigit() or k in ("norm", "head")     # "mega.*" / fused copies are the same weights in another layout
+        keep = lambda k: k[0].isdigit() or k in ("norm", "head")
         return sum(t.numel() * t.element_size() for k, t in self.w.items() if keep(k))
 
     # ------------------------------------------------------------------ plumbing
@@ -277,11 +295,19 @@ class T3B200Model:
         return _lib.lib()
 
     def workspace(self, rows: int) -> torch.Tensor:
+        """The model's own scratch for direct calls (grows on demand).  An engine never uses it: captured CUDA graphs hold
+        the workspace address, so ``T3B200Engine`` owns one buffer sized once for its largest launch."""
         L = self._require()
         need = L.t3b_workspace_bytes(C.byref(self.c), rows)
         if self._ws is None or self._ws.numel() < need:
             self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
         return self._ws
+
+    def workspace_bytes(self, rows: int) -> int:
+        return int(self._require().t3b_workspace_bytes(C.byref(self.c), rows))
+
+    def _opt(self):
+        return C.byref(self.options) if self.options is not None else None
 
     def bind(self, kv: KVPool, state: DecodeState) -> None:
         """Attach the KV pool / decode state that ``forward`` uses (vLLM passes these through its
@@ -299,77 +325,32 @@ class T3B200Model:
                                       emb.shape[0], pe.shape[0], dup, out.data_ptr(), _lib.stream_ptr()), "t3b_embed_gather")
         return out
 
-    def forward_tokens(self, kv: KVPool, x: torch.Tensor, tok_row: Optional[torch.Tensor], tok_idx: torch.Tensor,
-                       rope_pos: torch.Tensor, block_tables: torch.Tensor) -> torch.Tensor:
-        """F2 over arbitrary (row, index) tokens: prefill of new rows or a decode step."""
+    def forward_tokens(self, kv: KVPool, x: torch.Tensor, tok_row: torch.Tensor, tok_idx: torch.Tensor,
+                       rope_pos: torch.Tensor, block_tables: torch.Tensor, seq_start: Optional[torch.Tensor] = None,
+                       seq_row: Optional[torch.Tensor] = None, max_seq_len: int = 0, ws: Optional[torch.Tensor] = None,
+                       out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """F2 over (row, index) tokens: the prefill of new rows.  ``seq_start`` / ``seq_row`` (whole prompts starting at index 0)
+        switch the attention to the read-the-prompt-once kernel (t3b_prefill_attn)."""
         L = self._require()
         n = x.shape[0]
-        ws = self.workspace(n)
-        out = torch.empty(n, self.dims.hidden, dtype=torch.bfloat16, device=self.device)
-        _lib.check(L.t3b_forward_tokens(C.byref(self.c), C.byref(kv.c), x.data_ptr(), n, _lib.ptr(tok_row), tok_idx.data_ptr(),
-                                        rope_pos.data_ptr(), block_tables.data_ptr(), block_tables.shape[1], out.data_ptr(),
-                                        ws.data_ptr(), ws.numel(), _lib.stream_ptr()), "t3b_forward_tokens")
+        ws = self.workspace(n) if ws is None else ws
+        if out is None:
+            out = torch.empty(n, self.dims.hidden, dtype=torch.bfloat16, device=self.device)
+        n_seq = 0 if seq_start is None else seq_start.numel() - 1
+        _lib.check(L.t3b_forward_tokens(C.byref(self.c), C.byref(kv.c), x.data_ptr(), n, tok_row.data_ptr(), tok_idx.data_ptr(),
+                                        rope_pos.data_ptr(), block_tables.data_ptr(), block_tables.shape[1], n_seq,
+                                        _lib.ptr(seq_start), _lib.ptr(seq_row), max_seq_len, out.data_ptr(),
+                                        ws.data_ptr(), ws.numel(), self._opt(), _lib.stream_ptr()), "t3b_forward_tokens")
         return out
 
     def decode_step(self, kv: KVPool, state: DecodeState, rows: int, hidden_out: torch.Tensor,
-                    x_in: Optional[torch.Tensor] = None) -> torch.Tensor:
+                    x_in: Optional[torch.Tensor] = None, ws: Optional[torch.Tensor] = None) -> torch.Tensor:
         """F1+F2 for one token per CFG row; embeddings gathered from ``state`` unless ``x_in`` is given."""
         L = self._require()
-        ws = self.workspace(rows)
+        ws = self.workspace(rows) if ws is None else ws
         _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(state.c), _lib.ptr(x_in), rows, hidden_out.data_ptr(),
-                                     ws.data_ptr(), ws.numel(), _lib.stream_ptr()), "t3b_decode_step")
+                                     ws.data_ptr(), ws.numel(), self._opt(), _lib.stream_ptr()), "t3b_decode_step")
         return hidden_out
-
-    def mega_logits(self, rows: int) -> torch.Tensor:
-        """Persistent bf16 [rows, speech_vocab] head-logit buffer (CUDA graphs hold its address)."""
-        if getattr(self, "_mega_lg", None) is None or self._mega_lg.shape[0] < rows:
-            self._mega_lg = torch.empty(max(rows, 2), self.dims.speech_vocab, dtype=torch.bfloat16, device=self.device)
-        return self._mega_lg
-
-    def mega_ok(self, rows: int) -> bool:
-        return self.mega is not None and 0 < rows <= _lib.lib().t3b_mega_max_rows()
-
-    def mega_workspace(self, rows: int) -> torch.Tensor:
-        L = self._require()
-        need = L.t3b_mega_workspace_bytes(C.byref(self.c), rows)
-        if self._mega_ws is None or self._mega_ws.numel() < need:
-            self._mega_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
-        return self._mega_ws
-
-    def decode_step_mega(self, kv: KVPool, state_c, rows: int, hidden_out: Optional[torch.Tensor], logits_out: torch.Tensor,
-                         x_in: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """F1+F2+head in ONE persistent launch (csrc/decode_mega.cu): logits_out bf16 [rows, speech_vocab]."""
-        L = self._require()
-        if not self.mega_ok(rows):
-            raise T3BLibraryError(f"decode_step_mega: rows {rows} not supported (bf16 weights, rows <= {L.t3b_mega_max_rows()})")
-        ws = self.mega_workspace(rows)
-        _lib.check(L.t3b_decode_step_mega(C.byref(self.c), C.byref(self.mega), C.byref(kv.c), C.byref(state_c), _lib.ptr(x_in), rows,
-                                          _lib.ptr(hidden_out), logits_out.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
-                   "t3b_decode_step_mega")
-        return logits_out
-
-    def fused_ok(self, rows: int) -> bool:
-        return self.fused is not None and 0 < rows <= _lib.lib().t3b_fused_max_rows()
-
-    def fused_workspace(self, rows: int) -> torch.Tensor:
-        L = self._require()
-        need = L.t3b_fused_workspace_bytes(C.byref(self.c), rows)
-        if self._fused_ws is None or self._fused_ws.numel() < need:
-            self._fused_ws = torch.empty(need, dtype=torch.uint8, device=self.device)
-        return self._fused_ws
-
-    def decode_step_fused(self, kv: KVPool, state_c, rows: int, hidden_out: Optional[torch.Tensor], logits_out: torch.Tensor,
-                          x_in: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """F1+F2+head in ONE persistent launch with two global exchanges per layer (csrc/decode_fused.cu):
-        logits_out bf16 [rows, speech_vocab]."""
-        L = self._require()
-        if not self.fused_ok(rows):
-            raise T3BLibraryError(f"decode_step_fused: rows {rows} not supported (bf16 T3 shape, rows <= {L.t3b_fused_max_rows()})")
-        ws = self.fused_workspace(rows)
-        _lib.check(L.t3b_decode_step_fused(C.byref(self.c), self.fused.data_ptr(), C.byref(kv.c), C.byref(state_c), _lib.ptr(x_in), rows,
-                                           _lib.ptr(hidden_out), logits_out.data_ptr(), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
-                   "t3b_decode_step_fused")
-        return logits_out
 
     def cfg_sample_head_logits(self, head_logits: torch.Tensor, rows: int, sampling_c, state_c, out_tokens_ptr: int, advance: bool = True,
                                logits_out: Optional[torch.Tensor] = None) -> None:
@@ -378,100 +359,87 @@ class T3B200Model:
                                                 1 if advance else 0, out_tokens_ptr, _lib.ptr(logits_out), _lib.stream_ptr()),
                    "t3b_cfg_sample_head_logits")
 
-    def lane_workspace(self, lane: int, rows: int) -> torch.Tensor:
-        """Scratch of decode lane ``lane`` (lanes run concurrently on their own streams, so each owns one)."""
-        L = self._require()
-        need = L.t3b_workspace_bytes(C.byref(self.c), rows)
-        ws = self._lane_ws.get(lane)
-        if ws is None or ws.numel() < need:
-            ws = self._lane_ws[lane] = torch.empty(need, dtype=torch.uint8, device=self.device)
-        return ws
-
-    def decode_lane(self, kv: KVPool, state: DecodeState, sampling: "SamplingTensors", slot0: int, n_slots: int, lane: int,
-                    hidden: torch.Tensor, out_tokens: torch.Tensor) -> None:
-        """One whole decode step (F1+F2, C1, S1..S4, state advance) for slots [slot0, slot0+n_slots) on the current stream."""
+    def decode_and_sample(self, kv: KVPool, state: DecodeState, sampling: "SamplingTensors", n_slots: int, hidden: torch.Tensor,
+                          out_tokens: torch.Tensor, ws: torch.Tensor) -> None:
+        """One whole decode step (F1+F2, C1, S1..S4, state advance) for slots [0, n_slots) on the current stream."""
         L = self._require()
         rows = 2 * n_slots
-        ws = self.lane_workspace(lane, rows)
-        st, sp = state.view(slot0), sampling.view(slot0)
-        # The persistent kernel is opt-in: measured on B200 it is slower than the PDL-chained kernels below
-        # (profiles/r01c_bench_mega_default.json vs r01c_bench_multikernel.json; DESIGN.md "Persistent step").
-        if lane == 0 and slot0 == 0 and self.fused_ok(rows) and os.environ.get("T3B_FUSED", "0") == "1":
-            lg = self.mega_logits(rows)
-            self.decode_step_fused(kv, st, rows, None, lg)
-            self.cfg_sample_head_logits(lg, rows, sp, st, out_tokens.data_ptr())
-            return
-        if lane == 0 and slot0 == 0 and self.mega_ok(rows) and os.environ.get("T3B_MEGA", "0") == "1":
-            lg = self.mega_logits(rows)
-            self.decode_step_mega(kv, st, rows, None, lg)
-            self.cfg_sample_head_logits(lg, rows, sp, st, out_tokens.data_ptr())
-            return
-        h = hidden.data_ptr() + 2 * slot0 * self.dims.hidden * 2
         s = _lib.stream_ptr()
-        _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(st), None, rows, h, ws.data_ptr(), ws.numel(), s),
-                   "t3b_decode_step")
-        _lib.check(L.t3b_head_cfg_sample(C.byref(self.c), h, rows, C.byref(sp), C.byref(st), 1, out_tokens.data_ptr() + 4 * slot0, None,
-                                         ws.data_ptr(), ws.numel(), s), "t3b_head_cfg_sample")
+        _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(state.c), None, rows, hidden.data_ptr(), ws.data_ptr(),
+                                     ws.numel(), self._opt(), s), "t3b_decode_step")
+        _lib.check(L.t3b_head_cfg_sample(C.byref(self.c), hidden.data_ptr(), rows, C.byref(sampling.c), C.byref(state.c), 1,
+                                         out_tokens.data_ptr(), None, ws.data_ptr(), ws.numel(), self._opt(), s), "t3b_head_cfg_sample")
 
     def head_cfg_sample(self, hidden: torch.Tensor, rows: int, sampling: SamplingTensors, state: Optional[DecodeState],
                         out_tokens: Optional[torch.Tensor], advance: bool = False,
-                        logits_out: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+                        logits_out: Optional[torch.Tensor] = None, ws: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
         """C1 + S1..S4 fused: speech head on both rows, CFG combine, penalties, sampling."""
         L = self._require()
-        ws = self.workspace(rows)
+        ws = self.workspace(rows) if ws is None else ws
         _lib.check(L.t3b_head_cfg_sample(C.byref(self.c), hidden.data_ptr(), rows, C.byref(sampling.c),
                                          C.byref(state.c) if state is not None else None, 1 if advance else 0,
-                                         _lib.ptr(out_tokens), _lib.ptr(logits_out), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
-                   "t3b_head_cfg_sample")
+                                         _lib.ptr(out_tokens), _lib.ptr(logits_out), ws.data_ptr(), ws.numel(), self._opt(),
+                                         _lib.stream_ptr()), "t3b_head_cfg_sample")
         return out_tokens
 
     def prefill_embeds(self, cond_emb: torch.Tensor, text_ids: Sequence[int]) -> Tuple[torch.Tensor, torch.Tensor]:
         """t3.py:542-561: cond = [cond_emb(34) | text_emb+text_pos | BOS], uncond = [cond_emb | zeros | BOS]."""
-        dev = self.device
-        ids = torch.tensor(list(text_ids), dtype=torch.int32, device=dev)
-        pos = torch.arange(len(text_ids), dtype=torch.int32, device=dev)
-        text = self.embed("text_emb", "text_pos_emb", ids, pos)
-        bos = self.embed("speech_emb", "speech_pos_emb", torch.tensor([START_SPEECH_TOKEN], dtype=torch.int32, device=dev),
-                         torch.zeros(1, dtype=torch.int32, device=dev))
-        ce = cond_emb.to(device=dev, dtype=torch.bfloat16)
-        assert ce.shape == (CONDITIONING_SIZE, self.dims.hidden)
-        return torch.cat([ce, text, bos], 0), torch.cat([ce, torch.zeros_like(text), bos], 0)
+        x, _, _, starts = self.prefill_assemble([cond_emb], [text_ids], [0])
+        return x[starts[0]:starts[1]], x[starts[1]:starts[2]]
 
-    def prefill_embeds_batch(self, conds: Sequence[torch.Tensor], text_ids: Sequence[Sequence[int]]) -> List[Tuple[torch.Tensor, torch.Tensor]]:
-        """``prefill_embeds`` for many requests with a constant number of device operations: one host->device copy of all text
-        ids / positions, one of all conditionals, one embedding gather, three indexed stores.  Row layout per request
-        (t3.py:542-561): cond = [cond_emb(34) | text_emb + text_pos | BOS], uncond = [cond_emb | zeros | BOS]."""
+    def prefill_assemble(self, conds: Sequence[torch.Tensor], text_ids: Sequence[Sequence[int]], slots: Sequence[int]):
+        """Prefill rows of n requests in ONE kernel launch (t3b_prefill_embed; layout t3.py:542-561): two host->device copies
+        (conditionals; ids + offsets + slots in one int32 buffer), no per-request device work.
+        Returns (x bf16 [n_tok, D], tok_row int32 [n_tok], tok_idx int32 [n_tok], starts: host list of 2n+1 sequence offsets);
+        sequence 2r / 2r+1 = the cond / uncond row of request r, KV row 2 * slots[r] (+1).  ``self.last_seq`` holds the device
+        copies (seq_start int32 [2n+1], seq_row int32 [2n]) that ``forward_tokens`` takes."""
+        L = self._require()
+        if "text_emb" not in self.w:
+            raise RuntimeError("prefill needs text_emb.weight / text_pos_emb.emb.weight in the checkpoint")
         dev, D, C34 = self.device, self.dims.hidden, CONDITIONING_SIZE
         n = len(conds)
         lens = [len(t) for t in text_ids]
-        P = [C34 + l + 1 for l in lens]
-        big = torch.zeros(2 * sum(P), D, dtype=torch.bfloat16, device=dev)
-        ids_all = torch.tensor([t for ids in text_ids for t in ids], dtype=torch.int32)
-        pos_all = torch.cat([torch.arange(l, dtype=torch.int32) for l in lens]) if n else torch.zeros(0, dtype=torch.int32)
-        ce_all = torch.stack([c[:C34].to(torch.bfloat16) for c in conds]).reshape(n * C34, D)
-        if ce_all.device.type == "cpu":
-            ce_all = ce_all.pin_memory()
-        idx_ce, idx_text, idx_bos, spans = [], [], [], []
-        off = 0
-        for i in range(n):
-            c0, u0 = off, off + P[i]
-            idx_ce.append((torch.arange(C34), c0, u0))
-            idx_text.append(torch.arange(lens[i]) + c0 + C34)
-            idx_bos += [c0 + P[i] - 1, u0 + P[i] - 1]
-            spans.append((c0, u0, u0 + P[i]))
-            off += 2 * P[i]
-        ce_dev = ce_all.to(dev, non_blocking=True)
-        i_ce_c = torch.cat([a + c0 for a, c0, _ in idx_ce]).to(dev, non_blocking=True)
-        i_ce_u = torch.cat([a + u0 for a, _, u0 in idx_ce]).to(dev, non_blocking=True)
-        big.index_copy_(0, i_ce_c, ce_dev)
-        big.index_copy_(0, i_ce_u, ce_dev)
-        if ids_all.numel():
-            text = self.embed("text_emb", "text_pos_emb", ids_all.to(dev), pos_all.to(dev))
-            big.index_copy_(0, torch.cat(idx_text).to(dev), text)
-        bos = self.embed("speech_emb", "speech_pos_emb", torch.tensor([START_SPEECH_TOKEN], dtype=torch.int32, device=dev),
-                         torch.zeros(1, dtype=torch.int32, device=dev))
-        big[torch.tensor(idx_bos, device=dev)] = bos
-        return [(big[a:b], big[b:c]) for a, b, c in spans]
+        starts, tstart = [0], [0]
+        for l in lens:
+            starts += [starts[-1] + C34 + l + 1, starts[-1] + 2 * (C34 + l + 1)]
+            tstart.append(tstart[-1] + l)
+        n_tok = starts[-1]
+        flat = [t for ids in text_ids for t in ids] or [0]
+        seq_rows = [2 * sl + half for sl in slots for half in (0, 1)]
+        meta = torch.tensor(flat + tstart + starts + list(slots) + seq_rows, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+        o_t, o_s, o_o = len(flat), len(flat) + n + 1, len(flat) + n + 1 + 2 * n + 1
+        self.last_seq = (meta[o_s:o_o], meta[o_o + n:o_o + 3 * n])
+        for c in conds:
+            if c.shape[0] < C34 or c.shape[1] != D:
+                raise ValueError(f"conditionals must be [>= {C34}, {D}], got {tuple(c.shape)}")
+        ce = torch.stack([c[:C34].to(torch.bfloat16) for c in conds])
+        if ce.device.type == "cpu":
+            ce = ce.pin_memory()
+        ce = ce.to(dev, non_blocking=True).contiguous()
+        x = torch.empty(n_tok, D, dtype=torch.bfloat16, device=dev)
+        tok_row = torch.empty(n_tok, dtype=torch.int32, device=dev)
+        tok_idx = torch.empty(n_tok, dtype=torch.int32, device=dev)
+        p = meta.data_ptr()
+        _lib.check(L.t3b_prefill_embed(ce.data_ptr(), p, p + 4 * o_t, p + 4 * o_s, p + 4 * o_o, n, self.w["text_emb"].data_ptr(),
+                                       self.w["text_pos_emb"].data_ptr(), self.w["text_emb"].shape[0], self.w["text_pos_emb"].shape[0],
+                                       self.w["speech_emb"].data_ptr(), self.w["speech_pos_emb"].data_ptr(), START_SPEECH_TOKEN, D, C34,
+                                       x.data_ptr(), tok_row.data_ptr(), tok_idx.data_ptr(), _lib.stream_ptr()), "t3b_prefill_embed")
+        return x, tok_row, tok_idx, starts
+
+    def prefill_embeds_batch(self, conds: Sequence[torch.Tensor], text_ids: Sequence[Sequence[int]]) -> List[Tuple[torch.Tensor, torch.Tensor]]:
+        """Per-request (cond, uncond) views of ``prefill_assemble``."""
+        x, _, _, st = self.prefill_assemble(conds, text_ids, list(range(len(conds))))
+        return [(x[st[2 * i]:st[2 * i + 1]], x[st[2 * i + 1]:st[2 * i + 2]]) for i in range(len(conds))]
+
+    def filter_speech_tokens(self, token_ids: torch.Tensor) -> torch.Tensor:
+        """S3Gen hand-off (tts.py:492-514): offset ids -> un-offset ids in [0, 6561), order kept."""
+        L = self._require()
+        ids = token_ids.to(device=self.device, dtype=torch.int32).contiguous()
+        out = torch.empty_like(ids)
+        n_out = torch.zeros(1, dtype=torch.int32, device=self.device)
+        _lib.check(L.t3b_filter_speech_tokens(ids.data_ptr(), ids.numel(), SPEECH_TOKEN_OFFSET, self.cfg.start_speech_token, out.data_ptr(),
+                                              n_out.data_ptr(), _lib.stream_ptr()), "t3b_filter_speech_tokens")
+        return out[:int(n_out.item())]
 
     # ------------------------------------------------------------------ the reference's operator surface
     def get_language_model(self):                                 # t3.py:715
@@ -483,17 +451,46 @@ class T3B200Model:
 
     def get_input_embeddings(self, input_ids: torch.Tensor, multimodal_embeddings=None, *,
                              speech_pos: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """Decode branch of t3.py:429-486: ids are offset speech ids (>= 2500).  Returns bf16 [N, 2048]
-        (cond‖uncond carry the same decode embedding, t3.py:480).  ``speech_pos`` is the explicit
-        positional index the reference fails to track; None = the reference's
-        literal fallback, index 0 for every token."""
-        if multimodal_embeddings is not None and len(multimodal_embeddings) > 0:
-            raise NotImplementedError("prefill batches go through T3B200Engine (prefill_embeds + forward_tokens)")
-        ids = (input_ids.to(self.device) - SPEECH_TOKEN_OFFSET).to(torch.int32)
-        if bool((ids < 0).any()):
-            raise ValueError("get_input_embeddings: decode ids must be speech ids (>= SPEECH_TOKEN_OFFSET)")
-        pos = torch.zeros_like(ids) if speech_pos is None else speech_pos.to(device=self.device, dtype=torch.int32)
-        return self.embed("speech_emb", "speech_pos_emb", ids, pos, dup=2).view(ids.numel(), 2 * self.dims.hidden)
+        """t3.py:424-647.  Decode ids are offset speech ids (>= 2500): bf16 [N, 2048] with the same embedding in both
+        halves (t3.py:480).  ``speech_pos`` is the explicit positional index the reference fails to track (SURVEY.md
+        0.3-2); None = the reference's literal fallback, index 0 for every token.
+        With ``multimodal_embeddings`` (the stretched conditionals of ``packing.pack_prompt`` / t3.py:212-221) the batch
+        may hold prefill blocks: it is cut like ``split_prefill_decode`` (t3.py:340-421) and every block gets the cond | uncond
+        rows of t3.py:542-639, including the three partial-chunk cases."""
+        from . import packing
+        ids_all = input_ids.to("cpu").to(torch.int64).tolist() if input_ids.device.type != "cpu" else input_ids.to(torch.int64).tolist()
+        if multimodal_embeddings is None or len(multimodal_embeddings) == 0:
+            if any(t < SPEECH_TOKEN_OFFSET for t in ids_all):
+                raise ValueError("get_input_embeddings: decode ids must be speech ids (>= SPEECH_TOKEN_OFFSET)")
+            ids = torch.tensor([t - SPEECH_TOKEN_OFFSET for t in ids_all], dtype=torch.int32, device=self.device)
+            pos = torch.zeros_like(ids) if speech_pos is None else speech_pos.to(device=self.device, dtype=torch.int32)
+            return self.embed("speech_emb", "speech_pos_emb", ids, pos, dup=2).view(ids.numel(), 2 * self.dims.hidden)
+        D, dev = self.dims.hidden, self.device
+        out: List[torch.Tensor] = []
+        done = 0
+        for blk, rows in packing.split_prefill_decode(ids_all, multimodal_embeddings):
+            n = len(blk)
+            if rows is None:                                   # a decode run inside a mixed batch (t3.py:497-527)
+                ids = torch.tensor([t - SPEECH_TOKEN_OFFSET for t in blk], dtype=torch.int32, device=dev)
+                pos = torch.zeros_like(ids) if speech_pos is None else speech_pos[done:done + n].to(device=dev, dtype=torch.int32)
+                out.append(self.embed("speech_emb", "speech_pos_emb", ids, pos, dup=2).view(n, 2 * D))
+            else:
+                n_cond, text, tpos, has_bos = packing.prefill_block_plan(blk, rows)
+                parts_c, parts_u = [], []
+                if n_cond:
+                    ce = rows[:n_cond].to(device=dev, dtype=torch.bfloat16)
+                    parts_c.append(ce); parts_u.append(ce)
+                if text:
+                    te = self.embed("text_emb", "text_pos_emb", torch.tensor(text, dtype=torch.int32, device=dev),
+                                    torch.tensor(tpos, dtype=torch.int32, device=dev))
+                    parts_c.append(te); parts_u.append(torch.zeros_like(te))          # t3.py:556
+                if has_bos:
+                    bos = self.embed("speech_emb", "speech_pos_emb", torch.tensor([START_SPEECH_TOKEN], dtype=torch.int32, device=dev),
+                                     torch.zeros(1, dtype=torch.int32, device=dev))
+                    parts_c.append(bos); parts_u.append(bos)
+                out.append(torch.cat([torch.cat(parts_c, 0), torch.cat(parts_u, 0)], dim=1))    # t3.py:560 side by side
+            done += n
+        return torch.cat(out, dim=0)
 
     def forward(self, input_ids, positions: torch.Tensor, intermediate_tensors=None,
                 inputs_embeds: Optional[torch.Tensor] = None) -> torch.Tensor:

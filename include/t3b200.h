@@ -53,7 +53,11 @@ extern "C" {
 /* fused epilogues of t3b_linear_* */
 #define T3B_EPI_NONE     0       /* y[rows, n] = bf16(x W^T)                                             */
 #define T3B_EPI_SILU_MUL 1       /* w = gate_up [2*ffn, k]: y[rows, ffn] = silu(gate) * up (llama.py:117-121) */
-#define T3B_EPI_RESIDUAL 2       /* t3b_linear_fused only: out_z = bf16(x W^T) + bf16(res_z) (llama.py:316-333)   */
+
+/* paged-KV element formats (t3b_kv_t.dtype) */
+#define T3B_KV_BF16 0            /* (block, head) slice = 16 tok x 64 bf16 = 2048 B                        */
+#define T3B_KV_FP8  1            /* slice = 16 tok x 64 e4m3 (1024 B) | 16 fp32 scales, one per (token, head): value = e4m3 * scale,
+                                    scale = max|x| / 448 over the head's 64 dims (1 if the vector is zero) = 1088 B         */
 
 /* t3b_linear_t.flags */
 #define T3B_LIN_GATE_UP_INTERLEAVED 1   /* AWQ tiles repacked as 64 gate rows + 64 up rows (SILU_MUL epilogue only) */
@@ -70,27 +74,6 @@ typedef struct t3b_linear {
     const void* zeros;           /* AWQ: uint8 [k/128, n]         (else NULL) */
     int32_t flags;               /* T3B_LIN_* */
 } t3b_linear_t;
-
-/* F2.1 folded into the projections around it (t3b_linear_fused).  The residual stream of a decode step is
- * kept as z = fp32 [rows, hidden] (the unrounded sum fused_add_rms_norm normalises, layernorm.py:40-59)
- * together with ss = fp32 [hidden/128][rows], the sum of squares of every 128-feature slice of a row. */
-typedef struct t3b_linear_fuse {
-    const float* x_z;            /* != NULL: the projection's input is rmsnorm(x_z) * norm_w, built inside the kernel */
-    const float* x_ss;           /*          [x_ss_tiles][rows] partial sums of squares of x_z's rows                */
-    int32_t      x_ss_tiles;
-    const void*  norm_w;         /*          bf16 [k]                                                                */
-    float        eps;
-    const float* res_z;          /* T3B_EPI_RESIDUAL: residual in, fp32 [rows, n]                                     */
-    float*       out_z;          /*                   residual out, fp32 [rows, n] (may alias res_z)                  */
-    float*       out_ss;         /*                   [n/128][rows] sums of squares of out_z                          */
-    /* tail norm (T3B_EPI_NONE, n == 1024, cluster split-K): the fused_add_rms_norm that FOLLOWS the projection runs in
-     * its tail - the last thread block to finish a group of rows does  resid += y;  out = rmsnorm(resid) * norm  with the
-     * arithmetic of t3b_add_rmsnorm (bit-identical), saving the separate launch.  y is still written.              */
-    void*        tail_resid;     /* bf16 [rows, n], updated in place                                                  */
-    const void*  tail_norm_w;    /* bf16 [n]   (eps = the eps field above)                                            */
-    void*        tail_out;       /* bf16 [rows, n]; NULL = no tail norm                                               */
-    uint32_t*    tail_counters;  /* 64 x uint32, zero before the first use; the kernel leaves them zero              */
-} t3b_linear_fuse_t;
 
 typedef struct t3b_layer {       /* one LlamaDecoderLayer (vllm:model_executor/models/llama.py:316-333) */
     t3b_linear_t qkv;            /* [3*hidden, hidden]  q|k|v rows stacked (llama.py:437-443) */
@@ -114,13 +97,15 @@ typedef struct t3b_model {
     const void* rope_cos_sin;    /* bf16 [max_pos, head_dim]  cos(32) | sin(32) */
 } t3b_model_t;
 
-/* Paged KV pool.  Layout per layer: [num_blocks][n_heads][T3B_KV_BLOCK][head_dim] bf16, K and V
- * separate.  (vLLM's flash layout is [block][token][head][dim]; heads are hoisted here so one
- * (block, head) slice is 2 KB contiguous.)  Block 0 is reserved as a scratch block for idle rows. */
+/* Paged KV pool.  Layout per layer: [num_blocks][n_heads] slices of T3B_KV_BLOCK tokens x head_dim (T3B_KV_BF16:
+ * [16][64] bf16; T3B_KV_FP8: see above), K and V separate.  (vLLM's flash layout is [block][token][head][dim]; heads are
+ * hoisted here so one (block, head) slice is one contiguous bulk copy.)  Block 0 is reserved as a scratch block for idle
+ * rows.  Several rows may name the same block in their tables (shared conditioning prefix, t3.py:554-556). */
 typedef struct t3b_kv {
-    void* k; void* v;            /* bf16 [n_layers][num_blocks][n_heads][16][64] */
-    int64_t layer_stride;        /* elements between layers = num_blocks*n_heads*16*64 */
+    void* k; void* v;            /* [n_layers][num_blocks][n_heads][slice] */
+    int64_t layer_stride;        /* BYTES between layers = num_blocks * n_heads * slice bytes */
     int32_t num_blocks;
+    int32_t dtype;               /* T3B_KV_* */
 } t3b_kv_t;
 
 /* Per-step device-resident request state; the sampler advances it so a captured graph can be
@@ -137,7 +122,8 @@ typedef struct t3b_state {
     int32_t  hist_stride;
     int32_t* step;               /* [B]  sampler step counter (Philox counter word 1)             */
     int32_t* active;             /* [B]  1 = decoding, 0 = idle slot / finished                   */
-    int32_t  stop_token;         /* 6562 (t3_config.py:9); sampling it clears active[b]           */
+    const int32_t* stop_tokens;  /* [B]  per request (tts.py:457 stop_token_ids[0] - 2500 = 6562, t3_config.py:9); sampling it
+                                         clears active[b]; < 0 or NULL = never stops (ignore_eos)  */
     int32_t  max_ctx;            /* capacity guard: a row never advances past this many tokens     */
 } t3b_state_t;
 
@@ -148,15 +134,30 @@ typedef struct t3b_sampling {    /* per-request device arrays [B]; tts.py:455-46
     const float* min_p;
     const float* top_p;
     const uint64_t* seed;
+    const int32_t* analyzer_text_tokens;  /* [B] or NULL: > 0 runs the token heuristics of alignment_stream_analyzer.py:143-195
+                                             in the loop with text_tokens_count = this value (early-EOS suppression, 3x repeat
+                                             => EOS, long tail => EOS); <= 0 = off                    */
     int32_t combine;             /* T3B_COMBINE_* */
 } t3b_sampling_t;
+
+/* Launch-shape knobs of the decode path (NULL / 0 fields = the library's measured defaults).  Everything that used to be an
+ * environment variable inside the library is an explicit argument here. */
+typedef struct t3b_options {
+    int32_t gemv_max_rows;       /* bf16 projections use the SIMT GEMV up to this many rows (0 = default 2, max 4; -1 = never) */
+    int32_t gemv_no_norm;        /* 1 = keep add+RMSNorm as separate launches at GEMV row counts (default: folded in)     */
+    int32_t umma_stages;         /* tcgen05 GEMM: shared-memory ring depth cap (0 = default 5)                             */
+    int32_t umma_row_chunk;      /* tcgen05 GEMM: CFG rows per thread block, multiple of 16 (0 = default)                  */
+    int32_t umma_split[4];       /* cluster split-K of the qkv / o / gate_up / down projections (0 = automatic)            */
+} t3b_options_t;
 
 const char* t3b_last_error(void);
 int32_t     t3b_version(void);
 /* 0 if the current device is sm_100 and the driver entry points resolve, else T3B_ERR_UNSUPPORTED */
 int32_t     t3b_check_device(void);
-/* scratch needed by t3b_decode_step / t3b_head_cfg_sample for up to max_rows CFG rows */
+/* scratch needed by t3b_decode_step / t3b_forward_tokens / t3b_head_cfg_sample for up to max_rows rows (tokens) */
 size_t      t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows);
+/* bytes of one (block, head) K or V slice for a T3B_KV_* format (0 = unknown format) */
+int32_t     t3b_kv_slice_bytes(int32_t kv_dtype);
 
 /* E1  t3.py:440,475-480 (+ learned_pos_emb.py:21-32): out[dup*b + j] = emb[tokens[b]] +
  *     pos_emb[speech_pos[b] % pos_rows], j < dup.  out bf16 [n_req*dup, hidden]. */
@@ -175,35 +176,24 @@ int32_t t3b_add_rmsnorm(const void* x, const float* partials, int32_t n_split, v
 /* F2.2 / F2.5 / F2.6 / C1  the projections (llama.py:164-180,228-232,117-121; t3.py:659-660):
  *     y[r, n] = sum_k x[r,k] * w[n,k], fp32 accumulate, bf16 output [rows, n] (T3B_EPI_NONE) or the fused
  *     SiLU*mul of the gate_up projection [rows, n/2] (T3B_EPI_SILU_MUL, activation.py:138-141).
+ *     impl: T3B_IMPL_AUTO picks the SIMT GEMV for rows <= opt->gemv_max_rows (default 2) and the tcgen05 kernel above.
  *     Split-K: n_split <= 0 lets the library pick (returned through *n_split_out, may be NULL); the
  *     partial tiles are reduced on-chip through the thread-block cluster's distributed shared memory in a
  *     fixed order (deterministic) and y is written.  Only when partials != NULL AND n_split > 1 is given
  *     explicitly are the fp32 partials written to global memory instead ([n_split, rows, n], y untouched)
- *     for a consumer that sums them (t3b_add_rmsnorm / t3b_rope_kv_write / t3b_silu_mul accept them). */
+ *     for a consumer that sums them (t3b_add_rmsnorm / t3b_rope_kv_write / t3b_silu_mul accept them).
+ *     opt may be NULL. */
 int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials,
-                        int32_t n_split, int32_t* n_split_out, int32_t impl, int32_t epilogue, void* stream);
-
-/* F2.1 + F2.2/F2.5/F2.6 in one launch (tcgen05 path, any row count; bf16 or AWQ weights):
- *     input  = x (bf16 [rows,k]) or, when f->x_z is set, bf16(bf16(x_z * rstd) * norm_w) with
- *              rstd_r = rsqrt(sum_t x_ss[t][r] / k + eps)   (vllm:ir/ops/layernorm.py:40-59);
- *     output = y per `epilogue`, or for T3B_EPI_RESIDUAL the updated residual stream out_z / out_ss
- *              (the residual add of llama.py:316-333; y may be NULL).
- *     n_split <= 0 lets the library pick the cluster split-K.  Sums run in fixed orders that depend on the
- *     shapes only. */
-int32_t t3b_linear_fused(const void* x, const t3b_linear_t* w, int32_t rows, void* y, const t3b_linear_fuse_t* f,
-                         int32_t n_split, int32_t epilogue, void* stream);
-/* start / end of a step's fp32 residual stream: z = x (bf16 [rows,hidden]) with its ss; and
- * y = bf16(bf16(z * rstd) * weight) (the final norm, llama.py:430-431). */
-int32_t t3b_z_init(const void* x, int32_t rows, int32_t hidden, float* z, float* ss, void* stream);
-int32_t t3b_z_rmsnorm(const float* z, const float* ss, const void* weight, int32_t rows, int32_t hidden, float eps,
-                      void* y, void* stream);
+                        int32_t n_split, int32_t* n_split_out, int32_t impl, int32_t epilogue,
+                        const t3b_options_t* opt, void* stream);
 
 /* Q   vllm:model_executor/layers/quantization/awq.py:214-283: same contract as t3b_linear_bf16 with
  *     W[k,n] = bf16((nib - zero) * scale), group 128, dequantised on the fly into the tcgen05 operand tile
  *     (every row count runs T3B_IMPL_UMMA; activations are bf16, scales are converted fp16 -> bf16 by
  *     t3b_repack_weights_awq). */
 int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials,
-                       int32_t n_split, int32_t* n_split_out, int32_t impl, int32_t epilogue, void* stream);
+                       int32_t n_split, int32_t* n_split_out, int32_t impl, int32_t epilogue,
+                       const t3b_options_t* opt, void* stream);
 
 /* one-off layout transform of AutoAWQ tensors (qweight int32 [k, n/8], qzeros int32 [k/128, n/8],
  * scales fp16 [k/128, n]; nibble order 0,2,4,6,1,3,5,7 - awq_triton.py:56-62) into the kernel
@@ -218,26 +208,51 @@ int32_t t3b_repack_weights_awq(const int32_t* qweight, const int32_t* qzeros, co
 /* F2.3 + KV write  (rotary_embedding/common.py:144-174, llama3 table; reshape_and_cache of
  *     llama.py:231): qkv as bf16 [n_tok, 3*hidden] or split-K partials.  Token j belongs to KV row
  *     tok_row[j] (NULL = j), sits at index tok_idx[j] of that row's sequence and is rotated by
- *     rope_pos[j].  Writes q (rotated) bf16 [n_tok, hidden] and k (rotated), v into the pool. */
+ *     rope_pos[j].  Writes q (rotated) bf16 [n_tok, hidden] and k (rotated), v into the pool (kv_dtype = T3B_KV_*). */
 int32_t t3b_rope_kv_write(const void* qkv, const float* partials, int32_t n_split, int32_t n_tok,
                           const int32_t* tok_row, const int32_t* tok_idx, const int32_t* rope_pos,
                           const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables,
-                          int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads, void* q_out,
-                          void* stream);
+                          int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads, int32_t kv_dtype,
+                          void* q_out, void* stream);
 
 /* F2.4 paged decode attention (llama.py:211-221,231): o[j] = softmax(q[j] K^T / 8) V over the
  *     first tok_idx[j]+1 tokens of row tok_row[j], per head.  out bf16 [n_tok, hidden]. */
 int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
                               const int32_t* block_tables, int32_t max_blocks, const void* k_pool,
-                              const void* v_pool, int32_t n_heads, void* out, void* stream);
+                              const void* v_pool, int32_t n_heads, int32_t kv_dtype, void* out, void* stream);
 
 /* F2.3 + KV write + F2.4 in one launch for a decode step (token j <-> KV row j): reads q/k/v of every head
  *     from qkv bf16 [n_tok, 3*hidden], rotates q and k by rope_pos[j], stores k (rotated) and v at index
- *     tok_idx[j] of row j and attends over tokens 0..tok_idx[j].  out bf16 [n_tok, hidden]. */
+ *     tok_idx[j] of row j and attends over tokens 0..tok_idx[j].  out bf16 [n_tok, hidden].
+ *     Persistent kernel: K/V slices staged through shared memory by bulk copies (csrc/attention.cu). */
 int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const int32_t* tok_idx, const int32_t* rope_pos,
                               const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables,
-                              int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads, void* out,
-                              void* stream);
+                              int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads, int32_t kv_dtype,
+                              void* out, void* stream);
+
+/* Prefill attention (the causal pass of llama.py:231 over whole prompts, t3.py:542-561): sequence s is the tokens
+ *     [seq_start[s], seq_start[s+1]) of q (bf16 [n_tok, hidden], already rotated), belongs to KV row seq_row[s] and starts
+ *     at index 0 of that row; its K/V must already be in the pool (t3b_rope_kv_write).  Every (sequence, head) reads the
+ *     prompt's K/V from the pool ONCE into shared memory and serves all of its queries from there:
+ *     out[j] = softmax(q[j] K[0..j]^T / 8) V[0..j].  out bf16 [n_tok, hidden].  Prompts up to 432 tokens (bf16 KV) /
+ *     800 tokens (fp8 KV); longer prompts run t3b_paged_attn_decode per token. */
+int32_t t3b_prefill_attn(const void* q, int32_t n_seq, const int32_t* seq_start, const int32_t* seq_row,
+                         const int32_t* block_tables, int32_t max_blocks, const void* k_pool, const void* v_pool,
+                         int32_t n_heads, int32_t kv_dtype, int32_t max_seq_len, void* out, void* stream);
+int32_t t3b_prefill_attn_max_len(int32_t kv_dtype);
+
+/* Prefill embedding assembly (t3.py:542-561) for n_req requests in one launch:
+ *     cond row   = [cond_emb(34) | text_emb[id] + text_pos_emb[i] | speech_emb[6561] + speech_pos_emb[0]]
+ *     uncond row = [cond_emb(34) | zeros                          | the same BOS embedding]
+ *     conds bf16 [n_req, 34, hidden]; text ids of request r are text_ids[text_start[r] .. text_start[r+1]).
+ *     Request r's cond sequence starts at token out_start[2r], its uncond sequence at out_start[2r+1]
+ *     (out_start int32 [2 n_req + 1], the caller's prefix sums of P_r = 34 + n_text_r + 1 taken twice).
+ *     Writes x bf16 [n_tok, hidden] and the per-token index arrays tok_row[j] = 2 * slot[r] + half, tok_idx[j] = position. */
+int32_t t3b_prefill_embed(const void* conds, const int32_t* text_ids, const int32_t* text_start, const int32_t* out_start,
+                          const int32_t* slots, int32_t n_req, const void* text_emb, const void* text_pos_emb,
+                          int32_t text_rows, int32_t text_pos_rows, const void* speech_emb, const void* speech_pos_emb,
+                          int32_t bos_token, int32_t hidden, int32_t cond_len, void* x_out, int32_t* tok_row,
+                          int32_t* tok_idx, void* stream);
 
 /* F2.6 activation (vllm:model_executor/layers/activation.py:138-141): act = silu(g) * u with the
  *     bf16 roundings of the reference; gate_up as bf16 [rows, 2*ffn] or split-K partials. */
@@ -245,92 +260,53 @@ int32_t t3b_silu_mul(const void* gate_up, const float* partials, int32_t n_split
                      void* act, void* stream);
 
 /* F2   LlamaModel.forward (llama.py:395-432) over n_tok tokens given as embeddings x_in (bf16
- *     [n_tok, hidden]): token j belongs to KV row tok_row[j] (NULL = j), is the tok_idx[j]-th token of
+ *     [n_tok, hidden]): token j belongs to KV row tok_row[j], is the tok_idx[j]-th token of
  *     that row (its K/V are written there and it attends causally to tokens 0..tok_idx[j]) and is
  *     rotated by rope_pos[j].  One call with every prompt token of the new rows is the prefill of
- *     t3.py:542-561; one token per row is a decode step.  hidden_out bf16 [n_tok, hidden]. */
+ *     t3.py:542-561.  seq_start / seq_row (n_seq sequences, see t3b_prefill_attn; NULL / 0 = none) let the
+ *     attention read each prompt's K/V once; without them every token runs the paged decode kernel.
+ *     hidden_out bf16 [n_tok, hidden].  Launch shapes are fixed (no split-K), so a prompt's result does not
+ *     depend on the prompts it is batched with. */
 int32_t t3b_forward_tokens(const t3b_model_t* m, const t3b_kv_t* kv, const void* x_in, int32_t n_tok,
                            const int32_t* tok_row, const int32_t* tok_idx, const int32_t* rope_pos,
-                           const int32_t* block_tables, int32_t max_blocks, void* hidden_out,
-                           void* workspace, size_t workspace_bytes, void* stream);
+                           const int32_t* block_tables, int32_t max_blocks, int32_t n_seq, const int32_t* seq_start,
+                           const int32_t* seq_row, int32_t max_seq_len, void* hidden_out, void* workspace,
+                           size_t workspace_bytes, const t3b_options_t* opt, void* stream);
 
 /* F1 + F2  T3VllmModel.forward (t3.py:676-713) over LlamaModel.forward (llama.py:395-432) for one
  *     decode token per CFG row.  x_in (bf16 [rows, hidden]) != NULL feeds given embeddings (prefill-
  *     by-decode, t3.py:542-561 rows); x_in == NULL gathers E1 from st->tokens/speech_pos.  Uses
- *     st->rope_pos / ctx_lens / block_tables.  hidden_out bf16 [rows, hidden] = final-norm output. */
+ *     st->rope_pos / ctx_lens / block_tables.  hidden_out bf16 [rows, hidden] = final-norm output.
+ *     opt (may be NULL) = launch-shape knobs. */
 int32_t t3b_decode_step(const t3b_model_t* m, const t3b_kv_t* kv, const t3b_state_t* st, const void* x_in,
-                        int32_t rows, void* hidden_out, void* workspace, size_t workspace_bytes, void* stream);
+                        int32_t rows, void* hidden_out, void* workspace, size_t workspace_bytes,
+                        const t3b_options_t* opt, void* stream);
 
 /* C1 + S1..S4  compute_logits (t3.py:650-673) fused with the sampler the engine runs next
  *     (vllm:v1/sample/sampler.py:67-307, ops/topk_topp_sampler.py:328-416, layers/utils.py:51-89):
- *     head on both rows, l = c + w (c - u), repetition penalty over st->history, greedy or
+ *     head on both rows, l = c + w (c - u), the analyzer's token heuristics when sp->analyzer_text_tokens
+ *     is set (alignment_stream_analyzer.py:143-195), repetition penalty over st->history, greedy or
  *     temperature/min-p/top-p + exponential race (Philox4x32-10 keyed by seed, counter (index, step)).
  *     Writes out_tokens[b] (un-offset id; caller adds SPEECH_TOKEN_OFFSET = 2500, t3.py:666-672),
  *     optionally the combined fp32 logits [B, speech_vocab], and - if advance != 0 - appends to
  *     history and advances tokens/speech_pos/rope_pos/ctx_lens/step, clearing active[b] on stop. */
 int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden, int32_t rows, const t3b_sampling_t* sp,
                             const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out,
-                            void* workspace, size_t workspace_bytes, void* stream);
+                            void* workspace, size_t workspace_bytes, const t3b_options_t* opt, void* stream);
 
 /* S1..S4 alone on caller-provided combined fp32 logits [n_req, vocab] (parity tests of the sampler). */
 int32_t t3b_sample_logits(const float* logits, int32_t n_req, int32_t vocab, const t3b_sampling_t* sp,
                           const t3b_state_t* st, int32_t* out_tokens, void* stream);
 
-/* ---- the persistent whole-step kernel -------------------------------------------------------------
- * Same arithmetic as t3b_decode_step + the speech head of t3b_head_cfg_sample (t3.py:676-713,
- * llama.py:395-432, t3.py:650-660), executed by ONE cooperative launch (one CTA per SM) that streams
- * weights and past KV pages through a shared-memory ring; see csrc/decode_mega.cu. */
-
-/* device pointers to the weights of one LlamaDecoderLayer in the unit layout of
- * t3b_repack_weights_bf16 (gate_up with gate_up_interleave = 1) + the two norm weights (bf16 [hidden]) */
-typedef struct t3b_mega_layer {
-    const void* qkv; const void* o; const void* gate_up; const void* down;
-    const void* ln1; const void* ln2;
-} t3b_mega_layer_t;
-
-typedef struct t3b_mega {
-    const t3b_mega_layer_t* layers;   /* DEVICE array [n_layers] */
-    const void* head;                 /* speech_head repacked (rows past speech_vocab zero-filled) */
-} t3b_mega_t;
-
-/* bytes of the repacked form of a bf16 [n, k] weight: ceil(n/128) * 128 * k * 2 */
-size_t  t3b_repacked_bytes(int32_t n, int32_t k);
-/* one-off layout transform: bf16 [n, k] -> [tile][k/64] blocks
- * of 128 x 64, 128B-swizzled K-major, 16 KB each; gate_up_interleave pairs 64 gate rows with 64 up rows */
-int32_t t3b_repack_weights_bf16(const void* w, int32_t n, int32_t k, int32_t gate_up_interleave, void* out, void* stream);
-int32_t t3b_mega_max_rows(void);      /* largest `rows` t3b_decode_step_mega accepts (128) */
-size_t  t3b_mega_workspace_bytes(const t3b_model_t* m, int32_t max_rows);
-/* F1 + F2 + C1(head): one decode token per CFG row, rows even and <= t3b_mega_max_rows().  Inputs as
- * t3b_decode_step.  hidden_out (optional) bf16 [rows, hidden] = final-norm output; logits_out bf16
- * [rows, speech_vocab] = speech_head on every row (NULL = kept in the workspace). */
-int32_t t3b_decode_step_mega(const t3b_model_t* m, const t3b_mega_t* mw, const t3b_kv_t* kv, const t3b_state_t* st,
-                             const void* x_in, int32_t rows, void* hidden_out, void* logits_out, void* workspace,
-                             size_t workspace_bytes, void* stream);
 /* C1(combine) + S1..S4 on head logits bf16 [rows, speech_vocab] (row 2b = cond, 2b+1 = uncond), the
  * second half of t3b_head_cfg_sample.  Same outputs and state advance. */
 int32_t t3b_cfg_sample_head_logits(const void* head_logits, int32_t rows, int32_t vocab, const t3b_sampling_t* sp,
                                    const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out, void* stream);
 
-/* ---- the fused persistent step kernel (two global exchanges per layer) --------------------------------
- * Same arithmetic and interface as t3b_decode_step_mega; see csrc/decode_fused.cu.  16 clusters x 8 CTAs:
- * cluster = attention head = FFN slice, q|k|v -> attention -> o-partial and gate_up -> SiLU*mul ->
- * down-partial stay inside a cluster (distributed shared memory); the only global exchanges are the two
- * split-K reductions + RMSNorm per layer.  Built for hidden 1024, 16 heads x 64, ffn 4096, bf16 weights. */
-
-/* bytes of the repacked weight blob (0 if the model shape is not supported) */
-size_t  t3b_fused_weight_bytes(const t3b_model_t* m);
-/* one-off layout transform of every bf16 projection, the speech head and the norm weights of `m` into the
- * per-CTA streams the kernel's producer warp walks (`out`: t3b_fused_weight_bytes(m) bytes, 16-byte aligned) */
-int32_t t3b_fused_repack(const t3b_model_t* m, void* out, void* stream);
-int32_t t3b_fused_max_rows(void);     /* largest `rows` t3b_decode_step_fused accepts (128) */
-size_t  t3b_fused_workspace_bytes(const t3b_model_t* m, int32_t max_rows);
-/* F1 + F2 + C1(head) (t3.py:676-713, llama.py:395-432, t3.py:650-660): one decode token per CFG row, rows
- * even and <= t3b_fused_max_rows().  Inputs as t3b_decode_step.  hidden_out (optional) bf16 [rows, hidden] =
- * final-norm output; logits_out bf16 [rows, speech_vocab] = speech_head on every row (NULL = kept in the
- * workspace).  Follow with t3b_cfg_sample_head_logits. */
-int32_t t3b_decode_step_fused(const t3b_model_t* m, const void* fused_weights, const t3b_kv_t* kv, const t3b_state_t* st,
-                              const void* x_in, int32_t rows, void* hidden_out, void* logits_out, void* workspace,
-                              size_t workspace_bytes, void* stream);
+/* S3Gen hand-off (tts.py:492-514): out[i] = ids[i] - 2500 for the ids with 0 <= ids[i] - 2500 < 6561, in order;
+ * *n_out (device int32) receives the count.  ids / out int32 [n] device arrays (out may alias ids). */
+int32_t t3b_filter_speech_tokens(const int32_t* ids, int32_t n, int32_t offset, int32_t n_valid, int32_t* out,
+                                 int32_t* n_out, void* stream);
 
 #ifdef __cplusplus
 }

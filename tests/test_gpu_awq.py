@@ -53,7 +53,7 @@ def _awq_linear(L, x, w, rows, gate_up=False, split=0):
     xd = x.to(DEV)
     y = torch.full((rows, N // 2 if gate_up else N), float("nan"), dtype=torch.bfloat16, device=DEV)
     _lib.check(L.t3b_linear_awq(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, split, None, _lib.T3B_IMPL_AUTO,
-                                _lib.T3B_EPI_SILU_MUL if gate_up else _lib.T3B_EPI_NONE, sp()), "t3b_linear_awq")
+                                _lib.T3B_EPI_SILU_MUL if gate_up else _lib.T3B_EPI_NONE, None, sp()), "t3b_linear_awq")
     torch.cuda.synchronize()
     return y.float().cpu()
 

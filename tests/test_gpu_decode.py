@@ -41,19 +41,13 @@ def teacher_forced_cuda(m: T3B200Model, prompts, forced: np.ndarray, rho=2.0):
     greedy token the CUDA sampler picks at every step."""
     B, T = forced.shape
     eng = T3B200Engine(m, max_num_seqs=B, max_model_len=256, use_graphs=False)
-    reqs = [eng._make_req(i, {"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}},
-                          SamplingParams(temperature=0.0, repetition_penalty=rho, max_tokens=T + 1, ignore_eos=True))
-            for i, (cond, ids) in enumerate(prompts)]
-    for i, r in enumerate(reqs):
-        r.slot = i
-        eng.slots[i] = r
-    eng.state.c.stop_token = -1
     st = eng.state
     V = m.dims.speech_vocab
     logits = torch.empty(T, B, V, dtype=torch.float32, device=DEV)
     toks = torch.empty(T, B, dtype=torch.int32, device=DEV)
-    # step 0: prefill, first token from the BOS hidden state.  _admit samples it; recompute logits for the record.
-    eng._admit(reqs)
+    # step 0: prefill, first token from the BOS hidden state (install() samples it)
+    eng.install([{"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}} for cond, ids in prompts],
+                SamplingParams(temperature=0.0, repetition_penalty=rho, max_tokens=T + 1, ignore_eos=True), reserve_steps=T + 1)
     toks[0] = st.tokens[:B]
     logits[0] = float("nan")
     for t in range(1, T):

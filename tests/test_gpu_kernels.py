@@ -133,7 +133,7 @@ def test_linear_gemv(L, rows, N, K):
     xd, wd = bf(x), bf(w)
     y = torch.empty(rows, N, dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_GEMV, 0, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_GEMV, 0, None, sp()))
     _check_linear(y, _linear_ref(x, w), K)
 
 
@@ -146,7 +146,7 @@ def test_linear_umma_single(L, rows, N, K):
     xd, wd = bf(x), bf(w)
     y = torch.empty(rows, N, dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, 0, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, 0, None, sp()))
     _check_linear(y, _linear_ref(x, w), K)
 
 
@@ -159,7 +159,7 @@ def test_linear_umma_split_k_partials(L, rows, N, K, split):
     parts = torch.full((split, rows, N), float("nan"), dtype=torch.float32, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
     ns = C.c_int32(0)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, None, parts.data_ptr(), split, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, None, parts.data_ptr(), split, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, None, sp()))
     assert ns.value == split
     y = parts.sum(0).bfloat16()
     assert torch.isfinite(parts).all()
@@ -183,11 +183,11 @@ def test_linear_umma_cluster_split_k(L, rows, N, K, split):
     y = torch.full((rows, N), float("nan"), dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), None, None)
     ns = C.c_int32(0)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, split, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, split, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, None, sp()))
     assert ns.value == split and torch.isfinite(y.float()).all()
     _check_linear(y, _linear_ref(x, w), K)
     y2 = torch.empty_like(y)                                        # fixed reduction order -> bit-reproducible
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y2.data_ptr(), None, split, None, _lib.T3B_IMPL_UMMA, 0, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y2.data_ptr(), None, split, None, _lib.T3B_IMPL_UMMA, 0, None, sp()))
     assert torch.equal(y, y2)
 
 
@@ -201,7 +201,7 @@ def test_linear_gate_up_silu_epilogue(L, rows, impl, split):
     xd, wd = bf(x), bf(w)
     act = torch.full((rows, F), float("nan"), dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, 2 * F, K, wd.data_ptr(), None, None)
-    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, act.data_ptr(), None, split, None, impl, _lib.T3B_EPI_SILU_MUL, sp()))
+    _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, act.data_ptr(), None, split, None, impl, _lib.T3B_EPI_SILU_MUL, None, sp()))
     gu = (x.float() @ w.float().t()).bfloat16()
     ref = (torch.nn.functional.silu(gu[:, :F]) * gu[:, F:]).float()
     d = ulp_diff(act, ref)
@@ -221,7 +221,7 @@ def test_linear_auto_picks_and_is_deterministic(L):
     for _ in range(2):
         y = torch.zeros(64, 8192, dtype=torch.bfloat16, device=DEV)
         ns = C.c_int32(0)
-        _lib.check(L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 64, y.data_ptr(), None, 0, C.byref(ns), 0, 0, sp()))
+        _lib.check(L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 64, y.data_ptr(), None, 0, C.byref(ns), 0, 0, None, sp()))
         outs.append((ns.value, y.clone()))
     assert outs[0][0] == outs[1][0] >= 1 and torch.equal(outs[0][1], outs[1][1])
     # the split never depends on the row count inside a 128-row chunk (batch invariance of a request's arithmetic)
@@ -230,7 +230,7 @@ def test_linear_auto_picks_and_is_deterministic(L):
     for rows in (6, 64, 100, 128):
         ns = C.c_int32(0)
         y = torch.zeros(rows, 8192, dtype=torch.bfloat16, device=DEV)
-        _lib.check(L.t3b_linear_bf16(x256.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 0, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, sp()))
+        _lib.check(L.t3b_linear_bf16(x256.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 0, C.byref(ns), _lib.T3B_IMPL_UMMA, 0, None, sp()))
         splits.add(ns.value)
     assert len(splits) == 1
 
@@ -262,7 +262,7 @@ def test_rope_kv_write_bit_exact(L, orc):
     cs = bf(rope_cos_sin_table(SMALL))
     q_out = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     _lib.check(L.t3b_rope_kv_write(dptr(bf(qkv)), None, 1, n, dptr(i32(rows)), dptr(i32(idx)), dptr(i32(pos)),
-                                   cs.data_ptr(), SMALL.max_pos, dptr(bt.to(DEV)), 13, kp.data_ptr(), vp.data_ptr(), 16,
+                                   cs.data_ptr(), SMALL.max_pos, dptr(bt.to(DEV)), 13, kp.data_ptr(), vp.data_ptr(), 16, 0,
                                    q_out.data_ptr(), sp()))
     q_ref = orc.rope(qkv[:, :1024].float().reshape(n, 16, 64), pos)
     k_ref = orc.rope(qkv[:, 1024:2048].float().reshape(n, 16, 64), pos)
@@ -279,7 +279,9 @@ def test_rope_kv_write_bit_exact(L, orc):
 
 @pytest.mark.parametrize("ctxs", [[1], [16, 17, 33], [1, 15, 16, 33, 99, 100, 399, 1200], list(range(1, 65))])
 def test_attention_fused_rope_kvwrite_equals_separate_kernels(L, ctxs):
-    """t3b_attn_decode_fused == t3b_rope_kv_write + t3b_paged_attn_decode, bit for bit (outputs and KV pool)."""
+    """t3b_attn_decode_fused == t3b_rope_kv_write + t3b_paged_attn_decode: the KV pool bit for bit; the outputs to 1 bf16 ulp (the
+    fused kernel attends to the new token from registers first, the separate one reads it back in page order: another fp32
+    summation order of the same softmax)."""
     n = len(ctxs)
     mb = (max(ctxs) + 15) // 16
     bt, kp, vp = _kv_setup(n, mb, 3)
@@ -295,13 +297,18 @@ def test_attention_fused_rope_kvwrite_equals_separate_kernels(L, ctxs):
     out_a = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     out_b = torch.empty_like(out_a)
     _lib.check(L.t3b_rope_kv_write(qkv.data_ptr(), None, 1, n, None, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos,
-                                   btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, q.data_ptr(), sp()))
-    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, None, idx.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16,
+                                   btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, 0, q.data_ptr(), sp()))
+    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, None, idx.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, 0,
                                        out_a.data_ptr(), sp()))
     _lib.check(L.t3b_attn_decode_fused(qkv.data_ptr(), n, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb,
-                                       kp2.data_ptr(), vp2.data_ptr(), 16, out_b.data_ptr(), sp()))
+                                       kp2.data_ptr(), vp2.data_ptr(), 16, 0, out_b.data_ptr(), sp()))
     assert torch.equal(kp, kp2) and torch.equal(vp, vp2)
-    assert torch.equal(out_a, out_b)
+    a, b = out_a.float().cpu(), out_b.float().cpu()
+    assert ((ulp_diff(a, b) <= 1.0) | ((a - b).abs() < 2e-3)).all(), float((a - b).abs().max())
+    out_c = torch.empty_like(out_b)                       # run-to-run: bit-reproducible
+    _lib.check(L.t3b_attn_decode_fused(qkv.data_ptr(), n, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb,
+                                       kp2.data_ptr(), vp2.data_ptr(), 16, 0, out_c.data_ptr(), sp()))
+    assert torch.equal(out_b, out_c)
 
 
 @pytest.mark.parametrize("ctxs", [[1], [16, 17], [1, 15, 16, 33, 99, 100, 399, 1200], list(range(1, 65))])
@@ -323,7 +330,7 @@ def test_paged_attention(L, ctxs):
     out = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     idx = i32([c - 1 for c in ctxs])
     _lib.check(L.t3b_paged_attn_decode(dptr(bf(q)), n, None, idx.data_ptr(), dptr(bt.to(DEV)), mb, kp.data_ptr(),
-                                       vp.data_ptr(), 16, out.data_ptr(), sp()))
+                                       vp.data_ptr(), 16, 0, out.data_ptr(), sp()))
     for r, c in enumerate(ctxs):
         s = torch.einsum("hd,lhd->hl", q[r].float(), Ks[r].float()) * 0.125
         ref = torch.einsum("hl,lhd->hd", torch.softmax(s, -1), Vs[r].float()).bfloat16().float().reshape(-1)
@@ -341,7 +348,7 @@ def test_paged_attention_tail_ignores_stale_tokens(L):
     vp[bt[0, 0], :, :5, :] = 1.0
     out = torch.empty(1, 1024, dtype=torch.bfloat16, device=DEV)
     _lib.check(L.t3b_paged_attn_decode(dptr(bf(q)), 1, None, dptr(i32([4])), dptr(bt.to(DEV)), 2, kp.data_ptr(),
-                                       vp.data_ptr(), 16, out.data_ptr(), sp()))
+                                       vp.data_ptr(), 16, 0, out.data_ptr(), sp()))
     assert torch.equal(out.float().cpu(), torch.ones(1, 1024))
 
 
@@ -451,11 +458,11 @@ def test_error_paths(L):
     x = torch.zeros(4, 1024, dtype=torch.bfloat16, device=DEV)
     lin = _lib.Linear(_lib.T3B_W_BF16, 1024, 1000, x.data_ptr(), None, None)        # K not a multiple of 64
     y = torch.zeros(4, 1024, dtype=torch.bfloat16, device=DEV)
-    rc = L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 4, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, 0, sp())
+    rc = L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), 4, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, 0, None, sp())
     assert rc == -2 and b"multiple of 64" in L.t3b_last_error()
-    rc = L.t3b_linear_bf16(None, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, 0, sp())
+    rc = L.t3b_linear_bf16(None, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, 0, None, sp())
     assert rc == -1
-    rc = L.t3b_linear_bf16(x.data_ptr() + 2, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, 0, sp())
+    rc = L.t3b_linear_bf16(x.data_ptr() + 2, C.byref(lin), 4, y.data_ptr(), None, 1, None, 0, 0, None, sp())
     assert rc == -3
     with pytest.raises(_lib.T3BLibraryError):
         _lib.check(rc, "linear")

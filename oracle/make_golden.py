@@ -10,6 +10,9 @@ Files (small; committed):
   t3_small_sampled.npz  same model, T=0.8 min_p=0.05 top_p=0.8 rho=2, seeds 42+i (Philox contract)
   sampler_cases.npz     sampler-only cases on seeded logits (greedy+penalty, min-p/top-p/race)
   rope_table.npz        llama3 cos/sin rows 0,1,99,100,1199 of the full-size table (pinned to vLLM's)
+  analyzer_cases.json   decisions of the REFERENCE's own AlignmentStreamAnalyzer.step on seeded token streams (needs /root/reference)
+  t3_full_greedy300.npz / t3_full_sampled300.npz  (python -m oracle.make_golden --full; ~10 min of CPU) the real 30-layer shape,
+                        2 requests x 300 steps: tokens, decision margins and, for the greedy stream, the top-8 logits of every step
 """
 import hashlib
 import os
@@ -74,7 +77,57 @@ def main():
     full = rope_cos_sin_table(T3Dims())
     np.savez_compressed(os.path.join(GOLD, "rope_table.npz"), rows=np.array([0, 1, 99, 100, 1199]),
                         table=full[[0, 1, 99, 100, 1199]].numpy())
+    mint_analyzer()
+    if "--full" in sys.argv:
+        mint_full_streams()
+        mint_full_streams(n_req=1, n_steps=1000, sampled=False)      # BASELINE.json configs[3]: context to ~1100
     print("golden fixtures written to", GOLD)
+
+
+REF_ANALYZER = "/root/reference/src/chatterbox_vllm/models/t3/inference/alignment_stream_analyzer.py"
+
+
+def mint_analyzer():
+    """Token streams through the reference's own class (importable on CPU): the fixture pins oracle/analyzer_ref.py and the CUDA
+    sampler's in-loop heuristics to the reference itself."""
+    import json
+    import random
+    if not os.path.exists(REF_ANALYZER):
+        print("reference not present: analyzer_cases.json left as committed")
+        return
+    from oracle import analyzer_ref
+    rng = random.Random(3)
+    cases = []
+    for n_text in [1, 2, 3, 4, 5, 6, 7, 10, 20, 40, 128]:
+        for trial in range(3):
+            T = min(2 * n_text + 30, 120)
+            toks = [rng.randrange(0, 6561) for _ in range(T)]
+            if trial == 1:
+                k = rng.randrange(3, T - 3)
+                toks[k] = toks[k + 1] = toks[k + 2] = 77
+            if trial == 2:
+                k = rng.randrange(0, T - 2)
+                toks[k] = toks[k + 1] = 5
+            cases.append({"n_text": n_text, "tokens": toks, "decisions": analyzer_ref.run_reference_class(REF_ANALYZER, n_text, toks, 6562)})
+    with open(os.path.join(GOLD, "analyzer_cases.json"), "w") as f:
+        json.dump({"eos": 6562, "source": "AlignmentStreamAnalyzer.step of the reference (alignment_stream_analyzer.py:114-195) run on CPU "
+                                          "by oracle/make_golden.py", "cases": cases}, f)
+
+
+def mint_full_streams(n_req=2, n_steps=300, sampled=True):
+    full = T3Dims()
+    sd = synthetic_checkpoint(full)
+    prompts = [synthetic_request(i, full, n_text=64) for i in range(n_req)]
+    orc = T3Oracle(sd, full, mode="bf16")
+    g = oracle_generate(orc, prompts, n_steps, rho=2.0)
+    ti, tv = top8(g["logits"])
+    np.savez_compressed(os.path.join(GOLD, f"t3_full_greedy{n_steps}.npz"), tokens=g["tokens"], margins=g["margins"], top_idx=ti, top_val=tv)
+    if not sampled:
+        return
+    orc = T3Oracle(sd, full, mode="bf16")
+    s = oracle_generate(orc, prompts, n_steps, rho=2.0, temperature=0.8, min_p=0.05, top_p=0.8, seeds=[42 + i for i in range(n_req)])
+    np.savez_compressed(os.path.join(GOLD, f"t3_full_sampled{n_steps}.npz"), tokens=s["tokens"], race_margins=s["margins"],
+                        minp_margins=s["minp_margins"], topp_margins=s["topp_margins"])
 
 
 if __name__ == "__main__":

@@ -17,8 +17,11 @@ no collective on the decode path.
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import ctypes as C
+
 import torch
 
+from . import _lib
 from .constants import CONDITIONING_SIZE, KV_BLOCK, SPEECH_TOKEN_OFFSET, T3Dims
 from .model import (START_SPEECH_TOKEN, STOP_SPEECH_TOKEN, DecodeState, KVPool, SamplingTensors, T3B200Model)
 
@@ -120,6 +123,13 @@ class T3B200Engine:
         self.steps_run = 0
         self.preemptions = 0
         self._voices: Dict[int, List] = {}           # voice key -> [blocks (2), live requests]
+        # Launch shapes that change the fp32 summation order are fixed per ENGINE, not per step: a batch engine runs the tcgen05
+        # projections at every live-row count (also when only one request is left), a single-request engine the GEMV - so a
+        # request's tokens do not depend on how many other requests are running beside it.
+        if model.options is not None:
+            self.opt = model.options
+        else:
+            self.opt = _lib.Options(0 if max_num_seqs == 1 else -1, 0, 0, 0, (C.c_int32 * 4)(0, 0, 0, 0))
         model.bind(self.kv, self.state)
         # One workspace for the engine's lifetime, sized for its largest launch: captured graphs hold its address, so it must
         # never move (the model's own growable scratch is not used here).
@@ -127,13 +137,14 @@ class T3B200Engine:
 
     # ------------------------------------------------------------------ one decode step
     def _step_eager(self, n_slots: int) -> None:
-        self.m.decode_and_sample(self.kv, self.state, self.sampling, n_slots, self.hidden, self.out_tokens, self.ws)
+        self.m.decode_and_sample(self.kv, self.state, self.sampling, n_slots, self.hidden, self.out_tokens, self.ws, opt=self.opt)
 
     def launches_per_step(self, n_slots: int) -> int:
         """Kernels one decode step launches: embed + per layer [norm, qkv, attention(+RoPE+KV write), o, norm,
         gate_up(+SiLU*mul), down] + final norm + head + sampler (the two norms ride inside the GEMVs at <= 2 rows)."""
         rows = 2 * self._bucket(n_slots)
-        gemv = rows <= 2 and self.m.quantization is None and self.m.options is None
+        gmax = 2 if self.opt.gemv_max_rows == 0 else max(0, min(4, self.opt.gemv_max_rows))
+        gemv = rows <= gmax and self.m.quantization is None and not self.opt.gemv_no_norm
         return 1 + self.dims.n_layers * (5 if gemv else 7) + 3
 
     def _bucket(self, n_slots: int) -> int:
@@ -314,7 +325,7 @@ class T3B200Engine:
                 seq_start = torch.tensor(starts, dtype=torch.int32, device=dev)
                 seq_row = torch.tensor(srow, dtype=torch.int32, device=dev)
             max_seq = max(r.n_prompt for r in ch)
-            h = m.forward_tokens(self.kv, x, tok_row, tok_idx, tok_idx, st.block_tables, seq_start, seq_row, max_seq, ws=self.ws)
+            h = m.forward_tokens(self.kv, x, tok_row, tok_idx, tok_idx, st.block_tables, seq_start, seq_row, max_seq, ws=self.ws, opt=self.opt)
             h_last = h[torch.tensor([s - 1 for s in starts[1:]], device=dev)].contiguous()      # hidden of each row's BOS token
             nreq = len(ch)
             tmp_state = DecodeState(nreq, self.max_blocks, self.max_len, self.max_len, dev)
@@ -327,7 +338,7 @@ class T3B200Engine:
             tmp_state.stop_tokens.copy_(torch.tensor([r.sp.stop_token() for r in ch], dtype=torch.int32))
             tmp_state.active.fill_(1)
             toks = torch.empty(nreq, dtype=torch.int32, device=dev)
-            m.head_cfg_sample(h_last, 2 * nreq, tmp_sp, tmp_state, toks, advance=True, ws=self.ws)
+            m.head_cfg_sample(h_last, 2 * nreq, tmp_sp, tmp_state, toks, advance=True, ws=self.ws, opt=self.opt)
             slots = torch.tensor([r.slot for r in ch], device=dev)
             rows2 = torch.stack([2 * slots, 2 * slots + 1], 1).reshape(-1)
             npr = torch.tensor([r.n_prompt for r in ch], dtype=torch.int32, device=dev).repeat_interleave(2)

@@ -306,8 +306,10 @@ class T3B200Model:
     def workspace_bytes(self, rows: int) -> int:
         return int(self._require().t3b_workspace_bytes(C.byref(self.c), rows))
 
-    def _opt(self):
-        return C.byref(self.options) if self.options is not None else None
+    def _opt(self, opt=None):
+        """t3b_options_t* of a call: the caller's (an engine fixes its launch shapes once), else the model's, else NULL."""
+        o = opt if opt is not None else self.options
+        return C.byref(o) if o is not None else None
 
     def bind(self, kv: KVPool, state: DecodeState) -> None:
         """Attach the KV pool / decode state that ``forward`` uses (vLLM passes these through its
@@ -328,7 +330,7 @@ class T3B200Model:
     def forward_tokens(self, kv: KVPool, x: torch.Tensor, tok_row: torch.Tensor, tok_idx: torch.Tensor,
                        rope_pos: torch.Tensor, block_tables: torch.Tensor, seq_start: Optional[torch.Tensor] = None,
                        seq_row: Optional[torch.Tensor] = None, max_seq_len: int = 0, ws: Optional[torch.Tensor] = None,
-                       out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                       out: Optional[torch.Tensor] = None, opt=None) -> torch.Tensor:
         """F2 over (row, index) tokens: the prefill of new rows.  ``seq_start`` / ``seq_row`` (whole prompts starting at index 0)
         switch the attention to the read-the-prompt-once kernel (t3b_prefill_attn)."""
         L = self._require()
@@ -340,7 +342,7 @@ class T3B200Model:
         _lib.check(L.t3b_forward_tokens(C.byref(self.c), C.byref(kv.c), x.data_ptr(), n, tok_row.data_ptr(), tok_idx.data_ptr(),
                                         rope_pos.data_ptr(), block_tables.data_ptr(), block_tables.shape[1], n_seq,
                                         _lib.ptr(seq_start), _lib.ptr(seq_row), max_seq_len, out.data_ptr(),
-                                        ws.data_ptr(), ws.numel(), self._opt(), _lib.stream_ptr()), "t3b_forward_tokens")
+                                        ws.data_ptr(), ws.numel(), self._opt(opt), _lib.stream_ptr()), "t3b_forward_tokens")
         return out
 
     def decode_step(self, kv: KVPool, state: DecodeState, rows: int, hidden_out: torch.Tensor,
@@ -360,25 +362,25 @@ class T3B200Model:
                    "t3b_cfg_sample_head_logits")
 
     def decode_and_sample(self, kv: KVPool, state: DecodeState, sampling: "SamplingTensors", n_slots: int, hidden: torch.Tensor,
-                          out_tokens: torch.Tensor, ws: torch.Tensor) -> None:
+                          out_tokens: torch.Tensor, ws: torch.Tensor, opt=None) -> None:
         """One whole decode step (F1+F2, C1, S1..S4, state advance) for slots [0, n_slots) on the current stream."""
         L = self._require()
         rows = 2 * n_slots
         s = _lib.stream_ptr()
         _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(state.c), None, rows, hidden.data_ptr(), ws.data_ptr(),
-                                     ws.numel(), self._opt(), s), "t3b_decode_step")
+                                     ws.numel(), self._opt(opt), s), "t3b_decode_step")
         _lib.check(L.t3b_head_cfg_sample(C.byref(self.c), hidden.data_ptr(), rows, C.byref(sampling.c), C.byref(state.c), 1,
-                                         out_tokens.data_ptr(), None, ws.data_ptr(), ws.numel(), self._opt(), s), "t3b_head_cfg_sample")
+                                         out_tokens.data_ptr(), None, ws.data_ptr(), ws.numel(), self._opt(opt), s), "t3b_head_cfg_sample")
 
     def head_cfg_sample(self, hidden: torch.Tensor, rows: int, sampling: SamplingTensors, state: Optional[DecodeState],
                         out_tokens: Optional[torch.Tensor], advance: bool = False,
-                        logits_out: Optional[torch.Tensor] = None, ws: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+                        logits_out: Optional[torch.Tensor] = None, ws: Optional[torch.Tensor] = None, opt=None) -> Optional[torch.Tensor]:
         """C1 + S1..S4 fused: speech head on both rows, CFG combine, penalties, sampling."""
         L = self._require()
         ws = self.workspace(rows) if ws is None else ws
         _lib.check(L.t3b_head_cfg_sample(C.byref(self.c), hidden.data_ptr(), rows, C.byref(sampling.c),
                                          C.byref(state.c) if state is not None else None, 1 if advance else 0,
-                                         _lib.ptr(out_tokens), _lib.ptr(logits_out), ws.data_ptr(), ws.numel(), self._opt(),
+                                         _lib.ptr(out_tokens), _lib.ptr(logits_out), ws.data_ptr(), ws.numel(), self._opt(opt),
                                          _lib.stream_ptr()), "t3b_head_cfg_sample")
         return out_tokens
 

@@ -84,7 +84,10 @@ def test_fp8_kv_write_bit_exact_and_attention_matches_dequantised_oracle(L):
     pos = torch.tensor(idx) % SMALL.max_pos
     q_out = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     btd = bt.to(DEV)
-    _lib.check(L.t3b_rope_kv_write(qkv.to(DEV).data_ptr(), None, 1, n, i32(rows).data_ptr(), i32(idx).data_ptr(), i32(pos).data_ptr(),
+    # every device tensor is held in a variable until the launch has run: a temporary's block goes back to the caching
+    # allocator as soon as data_ptr() returns and the next temporary would reuse it
+    qkv_d, rows_d, idx_d, pos_d = qkv.to(DEV), i32(rows), i32(idx), i32(pos)
+    _lib.check(L.t3b_rope_kv_write(qkv_d.data_ptr(), None, 1, n, rows_d.data_ptr(), idx_d.data_ptr(), pos_d.data_ptr(),
                                    cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, _lib.T3B_KV_FP8,
                                    q_out.data_ptr(), sp()))
     torch.cuda.synchronize()
@@ -102,8 +105,10 @@ def test_fp8_kv_write_bit_exact_and_attention_matches_dequantised_oracle(L):
     last = [sum(ctxs[:r + 1]) - 1 for r in range(n_rows)]
     q = q_out[torch.tensor(last, device=DEV)].contiguous()
     out = torch.empty(n_rows, 1024, dtype=torch.bfloat16, device=DEV)
-    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n_rows, None, i32([c - 1 for c in ctxs]).data_ptr(), btd.data_ptr(), mb, kp.data_ptr(),
+    last_d = i32([c - 1 for c in ctxs])
+    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n_rows, None, last_d.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(),
                                        vp.data_ptr(), 16, _lib.T3B_KV_FP8, out.data_ptr(), sp()))
+    torch.cuda.synchronize()
     kd, vd = kv_fp8_ref.dequantize(kq, ks), kv_fp8_ref.dequantize(vq, vs)
     o0 = 0
     for r, c in enumerate(ctxs):
@@ -167,16 +172,18 @@ def test_prefill_attention_matches_causal_softmax(L, kv_dtype):
     cs = rope_cos_sin_table(SMALL).to(device=DEV, dtype=torch.bfloat16)
     q = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     btd = bt.to(DEV)
-    _lib.check(L.t3b_rope_kv_write(qkv.to(DEV).data_ptr(), None, 1, n, i32(rows).data_ptr(), i32(idx).data_ptr(), i32(idx).data_ptr(),
+    qkv_d, rows_d, idx_d, starts_d, seqrow_d = qkv.to(DEV), i32(rows), i32(idx), i32(starts), i32(list(range(n_seq)))   # held, not temporaries
+    _lib.check(L.t3b_rope_kv_write(qkv_d.data_ptr(), None, 1, n, rows_d.data_ptr(), idx_d.data_ptr(), idx_d.data_ptr(),
                                    cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, kv_dtype, q.data_ptr(), sp()))
     out = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     assert max(lens) <= L.t3b_prefill_attn_max_len(kv_dtype)
-    _lib.check(L.t3b_prefill_attn(q.data_ptr(), n_seq, i32(starts).data_ptr(), i32(list(range(n_seq))).data_ptr(), btd.data_ptr(), mb,
+    _lib.check(L.t3b_prefill_attn(q.data_ptr(), n_seq, starts_d.data_ptr(), seqrow_d.data_ptr(), btd.data_ptr(), mb,
                                   kp.data_ptr(), vp.data_ptr(), 16, kv_dtype, max(lens), out.data_ptr(), sp()))
     # the same queries through the per-token paged kernel: another summation order of the same softmax
     out2 = torch.empty_like(out)
-    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, i32(rows).data_ptr(), i32(idx).data_ptr(), btd.data_ptr(), mb, kp.data_ptr(),
+    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, rows_d.data_ptr(), idx_d.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(),
                                        vp.data_ptr(), 16, kv_dtype, out2.data_ptr(), sp()))
+    torch.cuda.synchronize()
     orc = T3Oracle(synthetic_checkpoint(SMALL), SMALL, mode="bf16")
     k_ref = orc.rope(qkv[:, 1024:2048].float().reshape(n, 16, 64), torch.tensor(idx))
     v_ref = qkv[:, 2048:].float().reshape(n, 16, 64)
@@ -277,7 +284,8 @@ def test_sampler_analyzer_heuristics_match_the_reference_class(L):
             s.analyzer_text_tokens.fill_(n_text)
             s.seed.copy_(torch.arange(B, dtype=torch.int64) + 5)
             out = torch.empty(B, dtype=torch.int32, device=DEV)
-            _lib.check(L.t3b_sample_logits(lg.to(DEV).data_ptr(), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
+            lg_d = lg.to(DEV)
+            _lib.check(L.t3b_sample_logits(lg_d.data_ptr(), B, V, C.byref(s.c), C.byref(st.c), out.data_ptr(), sp()))
             got = out.cpu().tolist()
             for i in range(B):
                 if dec[i] == analyzer_ref.FORCE:

@@ -368,7 +368,7 @@ def kernel_breakdown(m, eng, B, ctx):
         off = li * kv.c.layer_stride
         _lib.check(L.t3b_attn_decode_fused(y_qkv.data_ptr(), R, idx.data_ptr(), idx.data_ptr(), m.w["rope"].data_ptr(), d.max_pos,
                                            bt.data_ptr(), eng.max_blocks, kv.k.data_ptr() + off, kv.v.data_ptr() + off, d.n_heads,
-                                           kv.kv_dtype, attn.data_ptr(), cur["s"]), "attn")
+                                           kv.kv_dtype, attn.data_ptr(), C.byref(eng.opt), cur["s"]), "attn")
 
     def norm_f(li):
         _lib.check(L.t3b_add_rmsnorm(y_d.data_ptr(), None, 1, res.data_ptr(), m.w[f"{li}.ln1"].data_ptr(), x.data_ptr(), R, d.hidden,

@@ -67,10 +67,14 @@ class Sampling(C.Structure):        # t3b_sampling_t
 
 class Options(C.Structure):         # t3b_options_t
     _fields_ = [("gemv_max_rows", i32), ("gemv_no_norm", i32), ("umma_stages", i32), ("umma_row_chunk", i32),
-                ("umma_split", i32 * 4)]
+                ("umma_split", i32 * 4), ("attn_team_warps", i32)]
 
 
 p_opt = C.POINTER(Options)
+
+
+def make_options(gemv_max_rows=0, gemv_no_norm=0, umma_stages=0, umma_row_chunk=0, umma_split=(0, 0, 0, 0), attn_team_warps=0) -> Options:
+    return Options(gemv_max_rows, gemv_no_norm, umma_stages, umma_row_chunk, (i32 * 4)(*umma_split), attn_team_warps)
 
 _PROTOS = {
     "t3b_last_error": (C.c_char_p, []),
@@ -83,9 +87,9 @@ _PROTOS = {
     "t3b_linear_bf16": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, p_opt, vp]),
     "t3b_linear_awq": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, p_opt, vp]),
     "t3b_repack_weights_awq": (i32, [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp]),
-    "t3b_attn_decode_fused": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, vp]),
+    "t3b_attn_decode_fused": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, p_opt, vp]),
     "t3b_rope_kv_write": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, vp]),
-    "t3b_paged_attn_decode": (i32, [vp, i32, vp, vp, vp, i32, vp, vp, i32, i32, vp, vp]),
+    "t3b_paged_attn_decode": (i32, [vp, i32, vp, vp, vp, i32, vp, vp, i32, i32, vp, p_opt, vp]),
     "t3b_prefill_attn": (i32, [vp, i32, vp, vp, vp, i32, vp, vp, i32, i32, i32, vp, vp]),
     "t3b_prefill_attn_max_len": (i32, [i32]),
     "t3b_prefill_embed": (i32, [vp, vp, vp, vp, vp, i32, vp, vp, i32, i32, vp, vp, i32, i32, i32, vp, vp, vp, vp]),

@@ -18,9 +18,10 @@ int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_s
                            cudaStream_t stream);
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
                               const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, int kv_dtype, void* out,
-                              cudaStream_t s);
+                              int team_warps, cudaStream_t s);
 int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
-                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, cudaStream_t s);
+                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, int team_warps,
+                              cudaStream_t s);
 
 #define GEMV_MAX_ROWS_DEFAULT 2       // measured: 4 rows run 0.87 ms/step on the tcgen05 path, 0.96 on the GEMV (profiles/r02_notes.md)
 static thread_local char g_err[512] = "";
@@ -91,16 +92,17 @@ extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
 }
 
 struct Opt {
-    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4];
+    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team;
 };
 static Opt resolve(const t3b_options_t* o) {
-    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}};
+    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0};
     if (o) {
         if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > 4 ? 4 : o->gemv_max_rows);
         r.gemv_norm = o->gemv_no_norm ? 0 : 1;
         r.stages = o->umma_stages > 0 ? o->umma_stages : 0;
         r.row_chunk = o->umma_row_chunk > 0 ? o->umma_row_chunk : 0;
         for (int i = 0; i < 4; ++i) r.split[i] = o->umma_split[i] > 0 ? o->umma_split[i] : 0;
+        r.attn_team = o->attn_team_warps;
     }
     return r;
 }
@@ -214,7 +216,7 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
             if (rc) return rc;
             { char* t = rcur; rcur = roth; roth = t; }
             rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
-                                       vpool(li), H, kv->dtype, ws.attn, s);
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, s);
             if (rc) return rc;
             rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE);
             if (rc) return rc;
@@ -243,10 +245,10 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
                 rc = t3b_prefill_attn(ws.q, ps->n_seq, ps->seq_start, ps->seq_row, block_tables, max_blocks, kpool(li), vpool(li), H,
                                       kv->dtype, ps->max_seq_len, ws.attn, stream);
             else
-                rc = t3b_paged_attn_launch(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kpool(li), vpool(li), H, kv->dtype, ws.attn, s);
+                rc = t3b_paged_attn_launch(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kpool(li), vpool(li), H, kv->dtype, ws.attn, 1, s);   // one warp per (token, head): fixed, so a prompt's result does not depend on its batch
         } else {
             rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
-                                       vpool(li), H, kv->dtype, ws.attn, s);
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, s);
         }
         if (rc) return rc;
         rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE);

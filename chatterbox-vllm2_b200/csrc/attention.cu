@@ -4,17 +4,24 @@
 // HBM-bound byte work: per (query, head) item the kernel streams the row's cached K and V exactly once.  The pool layout
 // [block][head][16 tok][64] makes one (block, head) slice ONE contiguous bulk copy (2 KB bf16 / 1088 B fp8).
 //
-// Persistent kernel, one CTA per SM, AT_NW warps.  Items (token, head) are dealt round-robin to CTAs; the pages of an item are
-// dealt round-robin to the CTA's warps two at a time ("pair" = pages 2p, 2p+1).  Every warp owns a private ring of S pair slots
-// in shared memory that lane 0 fills with cp.async.bulk (K0 | K1 | V0 | V1 -> one mbarrier per slot) S pairs AHEAD of the pair
-// the warp is computing - across item boundaries, so the head of an item (q/k/v load, RoPE, KV write) and its tail (merge of
-// the warps' online-softmax states through shared memory, fixed warp order -> deterministic) never leave HBM idle.  The first
-// ring fill is issued before griddepcontrol.wait: cached K/V, context lengths and block tables were written by earlier steps
-// (the sampler that advances them does not trigger its dependents early), so only q/k/v of the new token wait for the QKV GEMM.
+// Persistent kernel, one CTA of AT_NW warps per SM.  A TEAM of W warps (W = 1, 2, 4 or 8; AT_NW / W teams per CTA) owns a whole
+// (token, head) item: the item's head - q/k/v load, RoPE, KV write - and its fold run once per item, and with W = 1 (every batch
+// of >= 37 requests) a warp never meets another warp: no barrier, no exchange, the result goes from registers to global memory.
+// Items are dealt round-robin to the teams of the grid; inside a team the item's pages are dealt round-robin two at a time
+// ("pair" = pages 2p, 2p+1).  Every warp owns a private ring of S pair slots in shared memory that lane 0 fills with
+// cp.async.bulk (K0 | K1 | V0 | V1 -> one mbarrier per slot) S pairs AHEAD of the pair the warp is computing - across item
+// boundaries, so the head and the tail of an item never leave HBM idle.  The first ring fill is issued before
+// griddepcontrol.wait: cached K/V, context lengths, RoPE positions and block tables were written by earlier steps (the sampler
+// that advances them does not trigger its dependents early), so only q/k/v of the new token wait for the QKV GEMM.
+// W > 1 (small batches, where one warp per item would leave most of the machine idle): the team's warps merge their
+// online-softmax states through shared memory at a named barrier of their own, in warp order (deterministic).
+// (The first version of this kernel split every item over all 8 warps of a CTA: 962 warp instructions per (item, warp) for a
+// pair that needs ~250, and a CTA barrier per item - issue-latency bound at 0.36 of HBM, profiles/r2_notes.md.)
 //
-// The new token of a decode step never round-trips through the pool: warp 0 seeds its state with (q.k_new, v_new) from
-// registers and stores k (rotated) and v for the following steps.  A request's arithmetic depends on its own context only
-// (pair p -> warp p % AT_NW, merge in warp order), never on the batch it runs in.
+// The new token of a decode step never round-trips through the pool: warp 0 of the team seeds its state with (q.k_new, v_new)
+// from registers and stores k (rotated) and v for the following steps.  A request's arithmetic depends on its own context and on
+// W only (pair p -> warp p % W, merge in warp order); W is chosen from the item count, or fixed by the caller
+// (t3b_options_t.attn_team_warps - an engine fixes it so that a request's tokens do not depend on the live batch).
 //
 // KVT = 1: FP8-e4m3 K/V with one fp32 scale per (token, head), slice = 16 x 64 B values | 16 x 4 B scales; the scale of a key is
 // applied to its score and the scale of a value to its probability, so the inner products run on the raw fp8 values.
@@ -23,7 +30,7 @@
 #include "t3b_common.cuh"
 
 #define AT_NW 8
-#define AT_MAXK 128                 // items per CTA whose metadata is staged in shared memory
+#define AT_CAP 128                  // items per CTA (all its teams) whose metadata is staged in shared memory
 
 struct AttnArgs {
     const bf16* q;                  // FUSED: qkv bf16 [n_tok, 3 * hidden]; else q bf16 [n_tok, hidden] (already rotated)
@@ -150,28 +157,36 @@ __device__ __forceinline__ void attn_pair(const unsigned char* k0, const unsigne
     }
 }
 
-template <bool FUSED, int S, int KVT>
+template <bool FUSED, int W, int S, int KVT>
 __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs a) {
     constexpr int SLICE = KvFmt<KVT>::SLICE;
     constexpr int PAIR = 4 * SLICE;                       // K0 | K1 | V0 | V1
+    constexpr int T = AT_NW / W;                          // teams per CTA
+    constexpr int CAP = AT_CAP / T;                       // items per team whose metadata is staged
     extern __shared__ __align__(128) unsigned char at_smem[];
     unsigned char* ring = at_smem;                        // [AT_NW][S][PAIR]
     uint64_t* full = reinterpret_cast<uint64_t*>(at_smem + (size_t)AT_NW * S * PAIR);      // [AT_NW * S]
     float* part_acc = reinterpret_cast<float*>(full + AT_NW * S);                          // [2][AT_NW][64]
     float* part_ml = part_acc + 2 * AT_NW * 64;                                            // [2][AT_NW][2]
-    int* s_nc = reinterpret_cast<int*>(part_ml + 2 * AT_NW * 2);                           // [AT_MAXK] cached tokens to stream
-    int* s_row = s_nc + AT_MAXK;                                                           // [AT_MAXK] KV row
+    int* s_nc = reinterpret_cast<int*>(part_ml + 2 * AT_NW * 2);                           // [AT_CAP] cached tokens to stream
+    int* s_row = s_nc + AT_CAP;                                                            // [AT_CAP] KV row
+    int* s_pos = s_row + AT_CAP;                                                           // [AT_CAP] RoPE position (FUSED)
 
     pdl_launch_dependents();       // the next kernel's launch overlaps this one (it waits before reading)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int team = warp / W, wt = warp - team * W;      // team = the warps that share one item
     const int t4 = lane >> 3, c = lane & 7;
     const int G = gridDim.x, H = a.n_heads;
-    const int n_my = (a.n_items - (int)blockIdx.x + G - 1) / G;
-    for (int k = threadIdx.x; k < n_my; k += AT_NW * 32) {
-        const int t = ((int)blockIdx.x + k * G) / H;
+    const int NT = G * T;                                 // teams in the grid; team-major so that every SM gets teams before any gets two
+    const int gt = team * G + (int)blockIdx.x;
+    const int n_my = gt < a.n_items ? (a.n_items - gt + NT - 1) / NT : 0;
+    const int mb = team * CAP;                            // this team's slice of the metadata arrays
+    for (int k = wt * 32 + lane; k < n_my; k += W * 32) {
+        const int t = (gt + k * NT) / H;
         const int idx = ld_act(a.tok_idx + t);
-        s_nc[k] = FUSED ? idx : idx + 1;
-        s_row[k] = a.tok_row ? ld_act(a.tok_row + t) : t;
+        s_nc[mb + k] = FUSED ? idx : idx + 1;
+        s_row[mb + k] = a.tok_row ? ld_act(a.tok_row + t) : t;
+        if (FUSED) s_pos[mb + k] = min(max(ld_act(a.rope_pos + t), 0), a.max_pos - 1);
     }
     if (threadIdx.x < AT_NW * S) mbar_init(&full[threadIdx.x], 1);
     mbar_fence_init();
@@ -180,37 +195,26 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
     unsigned char* my_ring = ring + (size_t)warp * S * PAIR;
     uint64_t* my_full = full + warp * S;
 
-    // ---- producer cursor: (pk, pp) = next pair of this warp to fetch; lane i holds the block ids of this warp's i-th pair of
-    // the cursor's item (cur) and of the item after it (nxt), so a block-table read is never in front of a copy
-    int pk = 0, pp = warp, pn = 0;
-    int b0c = 0, b1c = 0, b0n = 0, b1n = 0;
-    auto load_bt = [&](int k, int& b0, int& b1) {
-        b0 = 0; b1 = 0;
-        if (k < n_my) {
-            const int npg = (s_nc[k] + 15) >> 4;
-            const int pg = (warp + lane * AT_NW) * 2;
-            const int32_t* bt = a.block_tables + (size_t)s_row[k] * a.max_blocks;
-            if (pg < npg) b0 = ld_act(bt + pg);
-            if (pg + 1 < npg) b1 = ld_act(bt + pg + 1);
+    // ---- producer cursor: (pk, pp) = next pair of this warp to fetch, (nb0, nb1) its two block ids - loaded when the cursor
+    // moves, so that a block-table read is never right in front of the copy it feeds
+    int pk = 0, pp = wt, pn = 0, nb0 = 0, nb1 = 0;
+    auto settle = [&]() {
+        while (pk < n_my && pp >= ((s_nc[mb + pk] + 31) >> 5)) { ++pk; pp = wt; }
+        nb0 = 0; nb1 = 0;
+        if (pk < n_my) {
+            const int32_t* bt = a.block_tables + (size_t)s_row[mb + pk] * a.max_blocks + 2 * pp;
+            nb0 = ld_act(bt);
+            if (2 * pp + 1 < ((s_nc[mb + pk] + 15) >> 4)) nb1 = ld_act(bt + 1);
         }
     };
-    load_bt(0, b0c, b1c);
-    load_bt(1, b0n, b1n);
     auto produce = [&]() {
-        while (pk < n_my && pp >= ((s_nc[pk] + 31) >> 5)) {
-            ++pk; pp = warp;
-            b0c = b0n; b1c = b1n;
-            load_bt(pk + 1, b0n, b1n);
-        }
         if (pk >= n_my) return;                                            // warp-uniform
-        const int j = (pp - warp) / AT_NW;
-        const int blk0 = __shfl_sync(0xffffffffu, b0c, j), blk1 = __shfl_sync(0xffffffffu, b1c, j);
         if (lane == 0) {
-            const int h = ((int)blockIdx.x + pk * G) % H;
-            const bool two = pp * 2 + 1 < ((s_nc[pk] + 15) >> 4);
+            const int h = (gt + pk * NT) % H;
+            const bool two = pp * 2 + 1 < ((s_nc[mb + pk] + 15) >> 4);
             const int slot = pn % S;
             unsigned char* dst = my_ring + (size_t)slot * PAIR;
-            const size_t o0 = ((size_t)blk0 * H + h) * SLICE, o1 = ((size_t)blk1 * H + h) * SLICE;
+            const size_t o0 = ((size_t)nb0 * H + h) * SLICE, o1 = ((size_t)nb1 * H + h) * SLICE;
             mbar_expect_tx(&my_full[slot], (two ? 4u : 2u) * SLICE);
             bulk_load_1d(dst, a.k_pool + o0, SLICE, &my_full[slot]);
             bulk_load_1d(dst + 2 * SLICE, a.v_pool + o0, SLICE, &my_full[slot]);
@@ -219,11 +223,13 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
                 bulk_load_1d(dst + 3 * SLICE, a.v_pool + o1, SLICE, &my_full[slot]);
             }
         }
-        ++pn; pp += AT_NW;
+        ++pn; pp += W;
+        settle();
     };
     // FUSED (decode): everything the ring reads was written by earlier steps -> the first fill goes out before the dependency
     // wait.  Otherwise (prefill) the K/V of this very pass were written by the kernel right in front of this one.
     if (!FUSED) pdl_wait();
+    settle();
 #pragma unroll 1
     for (int i = 0; i < S; ++i) produce();
     if (FUSED) pdl_wait();
@@ -235,17 +241,16 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
     auto load_head = [&](int k) {
         hq = hk = hv = hcs = hsn = make_uint4(0, 0, 0, 0);
         if (k >= n_my) return;
-        const int item = (int)blockIdx.x + k * G, t = item / H, h = item - t * H;
+        const int item = gt + k * NT, t = item / H, h = item - t * H;
         if (FUSED) {
             const bf16* src = a.q + (size_t)t * 3 * hidden + h * 64 + c * 8;
             hq = ld_act(reinterpret_cast<const uint4*>(src));
             hk = ld_act(reinterpret_cast<const uint4*>(src + hidden));
             hv = ld_act(reinterpret_cast<const uint4*>(src + 2 * hidden));
-            int pos = ld_act(a.rope_pos + t);
-            pos = min(max(pos, 0), a.max_pos - 1);
+            const int pos = s_pos[mb + k];
             hcs = __ldg(reinterpret_cast<const uint4*>(a.cos_sin + (size_t)pos * 64 + (c & 3) * 8));
             hsn = __ldg(reinterpret_cast<const uint4*>(a.cos_sin + (size_t)pos * 64 + 32 + (c & 3) * 8));
-            if (warp == 0) hblk = ld_act(a.block_tables + (size_t)s_row[k] * a.max_blocks + (s_nc[k] >> 4));
+            if (wt == 0) hblk = ld_act(a.block_tables + (size_t)s_row[mb + k] * a.max_blocks + (s_nc[mb + k] >> 4));
         } else {
             hq = ld_act(reinterpret_cast<const uint4*>(a.q + ((size_t)t * H + h) * 64 + c * 8));
         }
@@ -255,8 +260,8 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
     int cn = 0;
 #pragma unroll 1
     for (int k = 0; k < n_my; ++k) {
-        const int item = (int)blockIdx.x + k * G, t = item / H, h = item - t * H;
-        const int nc = s_nc[k], np = (nc + 31) >> 5, n_pages = (nc + 15) >> 4;
+        const int item = gt + k * NT, t = item / H, h = item - t * H;
+        const int nc = s_nc[mb + k], np = (nc + 31) >> 5, n_pages = (nc + 15) >> 4;
         float qf[8], m = -INFINITY, l = 0.f, acc[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[e] = 0.f;
@@ -267,13 +272,17 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
             const bool hi = c >= 4;                           // lanes c < 4 hold x1 (dims 0..31), c >= 4 hold x2
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
-                const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4), kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
+                const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4);
                 // o1 = x1*cos - x2*sin ; o2 = x2*cos + x1*sin, every product and the sum rounded to bf16
                 qf[e] = hi ? bf16_round(bf16_round(qf[e] * cs[e]) + bf16_round(qp * sn[e])) : bf16_round(bf16_round(qf[e] * cs[e]) - bf16_round(qp * sn[e]));
-                kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
             }
-            if (warp == 0) {
-                // the new token: stored for the following steps, and attended to straight from registers
+            if (wt == 0) {
+                // the new token: rotated, stored for the following steps, and attended to straight from registers
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const float kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
+                    kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
+                }
                 const size_t sl = ((size_t)hblk * H + h) * SLICE;
                 if (KVT == 1) {
                     float ka = 0.f, va = 0.f;
@@ -316,7 +325,7 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
         load_head(k + 1);                                  // in flight while this item's pairs are processed
 
 #pragma unroll 1
-        for (int pr = warp; pr < np; pr += AT_NW) {
+        for (int pr = wt; pr < np; pr += W) {
             const int slot = cn % S;
             mbar_wait(&my_full[slot], (uint32_t)((cn / S) & 1));
             const unsigned char* sl = my_ring + (size_t)slot * PAIR;
@@ -326,34 +335,47 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
             __syncwarp();                                   // every lane is done reading the slot
             produce();                                      // refill it with the pair S ahead
         }
-        // fold the four token groups (t4) of the warp, then the row sum; park the warp's state
+        // fold the four token groups (t4) of the warp, then the row sum
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
             acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
             acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
         }
         l = warp_sum(l);
-        float* pa = part_acc + ((k & 1) * AT_NW + warp) * 64;
-        if (lane < 8) {
-            *reinterpret_cast<float4*>(pa + lane * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
-            *reinterpret_cast<float4*>(pa + lane * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
-        }
-        if (lane == 0) { part_ml[((k & 1) * AT_NW + warp) * 2] = m; part_ml[((k & 1) * AT_NW + warp) * 2 + 1] = l; }
-        __syncthreads();
-        if (threadIdx.x < 64) {
-            const float* pm = part_ml + (k & 1) * AT_NW * 2;
-            const float* pb = part_acc + (k & 1) * AT_NW * 64;
-            float mm = -INFINITY;
+        if (W == 1) {
+            // the warp owns the whole item: no exchange, lanes 0..7 store 8 dims each
+            if (lane < 8) {
+                const float inv = 1.f / l;
+                float o[8];
 #pragma unroll
-            for (int w = 0; w < AT_NW; ++w) mm = fmaxf(mm, pm[w * 2]);
-            float ll = 0.f, o = 0.f;
-#pragma unroll
-            for (int w = 0; w < AT_NW; ++w) {
-                const float f = pm[w * 2] == -INFINITY ? 0.f : exp2f(pm[w * 2] - mm);
-                ll += pm[w * 2 + 1] * f;
-                o += pb[w * 64 + threadIdx.x] * f;
+                for (int e = 0; e < 8; ++e) o[e] = acc[e] * inv;
+                *reinterpret_cast<uint4*>(a.out + ((size_t)t * H + h) * 64 + lane * 8) = pack8(o);
             }
-            a.out[((size_t)t * H + h) * 64 + threadIdx.x] = __float2bfloat16_rn(o / ll);
+        } else {
+            // park the warp's state; the team meets at its own named barrier and merges in warp order (deterministic)
+            float* pa = part_acc + ((k & 1) * AT_NW + warp) * 64;
+            if (lane < 8) {
+                *reinterpret_cast<float4*>(pa + lane * 8) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                *reinterpret_cast<float4*>(pa + lane * 8 + 4) = make_float4(acc[4], acc[5], acc[6], acc[7]);
+            }
+            if (lane == 0) { part_ml[((k & 1) * AT_NW + warp) * 2] = m; part_ml[((k & 1) * AT_NW + warp) * 2 + 1] = l; }
+            asm volatile("bar.sync %0, %1;" :: "r"(1 + team), "r"(W * 32) : "memory");
+            const int tt = wt * 32 + lane;
+            if (tt < 64) {
+                const float* pm = part_ml + ((k & 1) * AT_NW + team * W) * 2;
+                const float* pb = part_acc + ((k & 1) * AT_NW + team * W) * 64;
+                float mm = -INFINITY;
+#pragma unroll
+                for (int w = 0; w < W; ++w) mm = fmaxf(mm, pm[w * 2]);
+                float ll = 0.f, o = 0.f;
+#pragma unroll
+                for (int w = 0; w < W; ++w) {
+                    const float f = pm[w * 2] == -INFINITY ? 0.f : exp2f(pm[w * 2] - mm);
+                    ll += pm[w * 2 + 1] * f;
+                    o += pb[w * 64 + tt] * f;
+                }
+                a.out[((size_t)t * H + h) * 64 + tt] = __float2bfloat16_rn(o / ll);
+            }
         }
     }
 }
@@ -458,72 +480,95 @@ extern "C" int32_t t3b_prefill_attn(const void* q, int32_t n_seq, const int32_t*
 }
 
 // ------------------------------------------------------------------ host
-static int at_ring_depth(int kvt) { return kvt == 1 ? 5 : 3; }
+// Warps per item.  0 = by item count: the largest power of two <= 8 that still gives every item its own team in one wave
+// (items x W <= SMs x 8).  An engine passes a fixed value (t3b_options_t.attn_team_warps) so that a request's summation order
+// does not change with the number of live requests.
+static int at_team_warps(int n_items, int requested) {
+    if (requested == 1 || requested == 2 || requested == 4 || requested == 8) return requested;
+    const int slots = t3b_num_sms() * AT_NW;
+    int w = AT_NW;
+    while (w > 1 && (long)n_items * w > slots) w >>= 1;
+    return w;
+}
 
-template <bool FUSED, int S, int KVT>
+template <bool FUSED, int W, int S, int KVT>
 static cudaError_t launch_ring(const AttnArgs& a, cudaStream_t s) {
     constexpr int PAIR = 4 * KvFmt<KVT>::SLICE;
-    const size_t smem = (size_t)AT_NW * S * PAIR + AT_NW * S * 8 + 2 * AT_NW * 66 * 4 + 2 * AT_MAXK * 4;
-    auto kern = attn_ring_kernel<FUSED, S, KVT>;
+    constexpr int T = AT_NW / W;
+    const size_t smem = (size_t)AT_NW * S * PAIR + AT_NW * S * 8 + 2 * AT_NW * 66 * 4 + 3 * AT_CAP * 4;
+    auto kern = attn_ring_kernel<FUSED, W, S, KVT>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const int sms = t3b_num_sms();
-    int grid = a.n_items < sms ? a.n_items : sms;
-    const int need = (a.n_items + AT_MAXK - 1) / AT_MAXK;
+    const int teams = a.n_items;                          // one team per item until the grid is full
+    int grid = (teams + T - 1) / T;
+    if (grid > sms) grid = sms;
+    if (teams < sms) grid = teams;                        // few items: one team per SM rather than T teams on a few SMs
+    const int need = (a.n_items + AT_CAP - 1) / AT_CAP;
     if (grid < need) grid = need;
     return t3b_launch(kern, dim3((unsigned)grid), dim3(AT_NW * 32), smem, s, a);
 }
 
-static int32_t attn_launch(bool fused, const AttnArgs& a, int kv_dtype, cudaStream_t s) {
-    T3B_CHECK_SHAPE(a.max_blocks <= 2 * AT_NW * 32, "attention: max_blocks %d > %d (context > %d tokens)", a.max_blocks, 2 * AT_NW * 32,
-                    2 * AT_NW * 32 * T3B_KV_BLOCK);
+template <bool FUSED, int S, int KVT>
+static cudaError_t launch_ring_w(const AttnArgs& a, int w, cudaStream_t s) {
+    switch (w) {
+        case 1: return launch_ring<FUSED, 1, S, KVT>(a, s);
+        case 2: return launch_ring<FUSED, 2, S, KVT>(a, s);
+        case 4: return launch_ring<FUSED, 4, S, KVT>(a, s);
+        default: return launch_ring<FUSED, 8, S, KVT>(a, s);
+    }
+}
+
+static int32_t attn_launch(bool fused, const AttnArgs& a, int kv_dtype, int team_warps, cudaStream_t s) {
     T3B_CHECK_ARG(kv_dtype == T3B_KV_BF16 || kv_dtype == T3B_KV_FP8, "attention: unknown KV dtype %d", kv_dtype);
+    const int w = at_team_warps(a.n_items, team_warps);
     cudaError_t e;
-    if (kv_dtype == T3B_KV_FP8) e = fused ? launch_ring<true, 5, 1>(a, s) : launch_ring<false, 5, 1>(a, s);
-    else e = fused ? launch_ring<true, 3, 0>(a, s) : launch_ring<false, 3, 0>(a, s);
-    (void)at_ring_depth;
+    if (kv_dtype == T3B_KV_FP8) e = fused ? launch_ring_w<true, 5, 1>(a, w, s) : launch_ring_w<false, 5, 1>(a, w, s);
+    else e = fused ? launch_ring_w<true, 3, 0>(a, w, s) : launch_ring_w<false, 3, 0>(a, w, s);
     T3B_CUDA(e);
     return T3B_OK;
 }
 
 int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
-                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, cudaStream_t s) {
+                              int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, int team_warps,
+                              cudaStream_t s) {
     AttnArgs a = {};
     a.q = (const bf16*)q; a.tok_row = tok_row; a.tok_idx = tok_idx; a.block_tables = block_tables; a.max_blocks = max_blocks;
     a.k_pool = (unsigned char*)const_cast<void*>(k_pool); a.v_pool = (unsigned char*)const_cast<void*>(v_pool);
     a.n_heads = n_heads; a.out = (bf16*)out; a.n_items = n_tok * n_heads;
-    return attn_launch(false, a, kv_dtype, s);
+    return attn_launch(false, a, kv_dtype, team_warps, s);
 }
 
 // decode step: one token per KV row (token j <-> row j)
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
                               const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, int kv_dtype, void* out,
-                              cudaStream_t s) {
+                              int team_warps, cudaStream_t s) {
     AttnArgs a = {};
     a.q = (const bf16*)qkv; a.tok_idx = tok_idx; a.rope_pos = rope_pos; a.cos_sin = (const bf16*)rope_cos_sin; a.max_pos = max_pos;
     a.block_tables = block_tables; a.max_blocks = max_blocks; a.k_pool = (unsigned char*)k_pool; a.v_pool = (unsigned char*)v_pool;
     a.n_heads = n_heads; a.out = (bf16*)out; a.n_items = n_tok * n_heads;
-    return attn_launch(true, a, kv_dtype, s);
+    return attn_launch(true, a, kv_dtype, team_warps, s);
 }
 
 extern "C" int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const int32_t* tok_idx, const int32_t* rope_pos,
                                          const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables, int32_t max_blocks,
-                                         void* k_pool, void* v_pool, int32_t n_heads, int32_t kv_dtype, void* out, void* stream) {
+                                         void* k_pool, void* v_pool, int32_t n_heads, int32_t kv_dtype, void* out,
+                                         const t3b_options_t* opt, void* stream) {
     T3B_CHECK_ARG(qkv && tok_idx && rope_pos && rope_cos_sin && block_tables && k_pool && v_pool && out, "t3b_attn_decode_fused: null pointer");
     T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && max_pos > 0 && n_heads >= 1, "t3b_attn_decode_fused: bad sizes");
     T3B_CHECK_ALIGN(qkv); T3B_CHECK_ALIGN(rope_cos_sin); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
     if (n_tok == 0) return T3B_OK;
     return t3b_attn_fused_launch(qkv, n_tok, tok_idx, rope_pos, rope_cos_sin, max_pos, block_tables, max_blocks, k_pool, v_pool, n_heads,
-                                 kv_dtype, out, t3b_stream(stream));
+                                 kv_dtype, out, opt ? opt->attn_team_warps : 0, t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
                                          const int32_t* block_tables, int32_t max_blocks, const void* k_pool, const void* v_pool,
-                                         int32_t n_heads, int32_t kv_dtype, void* out, void* stream) {
+                                         int32_t n_heads, int32_t kv_dtype, void* out, const t3b_options_t* opt, void* stream) {
     T3B_CHECK_ARG(q && tok_idx && block_tables && k_pool && v_pool && out, "t3b_paged_attn_decode: null pointer");
     T3B_CHECK_ARG(n_tok >= 0 && max_blocks > 0 && n_heads >= 1, "t3b_paged_attn_decode: bad sizes");
     T3B_CHECK_ALIGN(q); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
     if (n_tok == 0) return T3B_OK;
     return t3b_paged_attn_launch(q, n_tok, tok_row, tok_idx, block_tables, max_blocks, k_pool, v_pool, n_heads, kv_dtype, out,
-                                 t3b_stream(stream));
+                                 opt ? opt->attn_team_warps : 0, t3b_stream(stream));
 }

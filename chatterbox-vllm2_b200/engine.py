@@ -129,7 +129,11 @@ class T3B200Engine:
         if model.options is not None:
             self.opt = model.options
         else:
-            self.opt = _lib.Options(0 if max_num_seqs == 1 else -1, 0, 0, 0, (C.c_int32 * 4)(0, 0, 0, 0))
+            items = 2 * max_num_seqs * self.dims.n_heads        # (row, head) items of a full step
+            team = 8
+            while team > 1 and items * team > 148 * 8:
+                team //= 2
+            self.opt = _lib.make_options(gemv_max_rows=0 if max_num_seqs == 1 else -1, attn_team_warps=team)
         model.bind(self.kv, self.state)
         # One workspace for the engine's lifetime, sized for its largest launch: captured graphs hold its address, so it must
         # never move (the model's own growable scratch is not used here).

@@ -148,6 +148,7 @@ typedef struct t3b_options {
     int32_t umma_stages;         /* tcgen05 GEMM: shared-memory ring depth cap (0 = default 5)                             */
     int32_t umma_row_chunk;      /* tcgen05 GEMM: CFG rows per thread block, multiple of 16 (0 = default)                  */
     int32_t umma_split[4];       /* cluster split-K of the qkv / o / gate_up / down projections (0 = automatic)            */
+    int32_t attn_team_warps;     /* decode attention: warps that share one (row, head) item: 1, 2, 4 or 8 (0 = by item count) */
 } t3b_options_t;
 
 const char* t3b_last_error(void);
@@ -216,10 +217,11 @@ int32_t t3b_rope_kv_write(const void* qkv, const float* partials, int32_t n_spli
                           void* q_out, void* stream);
 
 /* F2.4 paged decode attention (llama.py:211-221,231): o[j] = softmax(q[j] K^T / 8) V over the
- *     first tok_idx[j]+1 tokens of row tok_row[j], per head.  out bf16 [n_tok, hidden]. */
+ *     first tok_idx[j]+1 tokens of row tok_row[j], per head.  out bf16 [n_tok, hidden].  opt (may be NULL): attn_team_warps. */
 int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,
                               const int32_t* block_tables, int32_t max_blocks, const void* k_pool,
-                              const void* v_pool, int32_t n_heads, int32_t kv_dtype, void* out, void* stream);
+                              const void* v_pool, int32_t n_heads, int32_t kv_dtype, void* out, const t3b_options_t* opt,
+                              void* stream);
 
 /* F2.3 + KV write + F2.4 in one launch for a decode step (token j <-> KV row j): reads q/k/v of every head
  *     from qkv bf16 [n_tok, 3*hidden], rotates q and k by rope_pos[j], stores k (rotated) and v at index
@@ -228,7 +230,7 @@ int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_r
 int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const int32_t* tok_idx, const int32_t* rope_pos,
                               const void* rope_cos_sin, int32_t max_pos, const int32_t* block_tables,
                               int32_t max_blocks, void* k_pool, void* v_pool, int32_t n_heads, int32_t kv_dtype,
-                              void* out, void* stream);
+                              void* out, const t3b_options_t* opt, void* stream);
 
 /* Prefill attention (the causal pass of llama.py:231 over whole prompts, t3.py:542-561): sequence s is the tokens
  *     [seq_start[s], seq_start[s+1]) of q (bf16 [n_tok, hidden], already rotated), belongs to KV row seq_row[s] and starts

@@ -299,15 +299,15 @@ def test_attention_fused_rope_kvwrite_equals_separate_kernels(L, ctxs):
     _lib.check(L.t3b_rope_kv_write(qkv.data_ptr(), None, 1, n, None, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos,
                                    btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, 0, q.data_ptr(), sp()))
     _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, None, idx.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, 0,
-                                       out_a.data_ptr(), sp()))
+                                       out_a.data_ptr(), None, sp()))
     _lib.check(L.t3b_attn_decode_fused(qkv.data_ptr(), n, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb,
-                                       kp2.data_ptr(), vp2.data_ptr(), 16, 0, out_b.data_ptr(), sp()))
+                                       kp2.data_ptr(), vp2.data_ptr(), 16, 0, out_b.data_ptr(), None, sp()))
     assert torch.equal(kp, kp2) and torch.equal(vp, vp2)
     a, b = out_a.float().cpu(), out_b.float().cpu()
     assert ((ulp_diff(a, b) <= 1.0) | ((a - b).abs() < 2e-3)).all(), float((a - b).abs().max())
     out_c = torch.empty_like(out_b)                       # run-to-run: bit-reproducible
     _lib.check(L.t3b_attn_decode_fused(qkv.data_ptr(), n, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb,
-                                       kp2.data_ptr(), vp2.data_ptr(), 16, 0, out_c.data_ptr(), sp()))
+                                       kp2.data_ptr(), vp2.data_ptr(), 16, 0, out_c.data_ptr(), None, sp()))
     assert torch.equal(out_b, out_c)
 
 
@@ -330,7 +330,7 @@ def test_paged_attention(L, ctxs):
     out = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
     idx = i32([c - 1 for c in ctxs])
     _lib.check(L.t3b_paged_attn_decode(dptr(bf(q)), n, None, idx.data_ptr(), dptr(bt.to(DEV)), mb, kp.data_ptr(),
-                                       vp.data_ptr(), 16, 0, out.data_ptr(), sp()))
+                                       vp.data_ptr(), 16, 0, out.data_ptr(), None, sp()))
     for r, c in enumerate(ctxs):
         s = torch.einsum("hd,lhd->hl", q[r].float(), Ks[r].float()) * 0.125
         ref = torch.einsum("hl,lhd->hd", torch.softmax(s, -1), Vs[r].float()).bfloat16().float().reshape(-1)
@@ -348,7 +348,7 @@ def test_paged_attention_tail_ignores_stale_tokens(L):
     vp[bt[0, 0], :, :5, :] = 1.0
     out = torch.empty(1, 1024, dtype=torch.bfloat16, device=DEV)
     _lib.check(L.t3b_paged_attn_decode(dptr(bf(q)), 1, None, dptr(i32([4])), dptr(bt.to(DEV)), 2, kp.data_ptr(),
-                                       vp.data_ptr(), 16, 0, out.data_ptr(), sp()))
+                                       vp.data_ptr(), 16, 0, out.data_ptr(), None, sp()))
     assert torch.equal(out.float().cpu(), torch.ones(1, 1024))
 
 

@@ -107,7 +107,7 @@ def test_fp8_kv_write_bit_exact_and_attention_matches_dequantised_oracle(L):
     out = torch.empty(n_rows, 1024, dtype=torch.bfloat16, device=DEV)
     last_d = i32([c - 1 for c in ctxs])
     _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n_rows, None, last_d.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(),
-                                       vp.data_ptr(), 16, _lib.T3B_KV_FP8, out.data_ptr(), sp()))
+                                       vp.data_ptr(), 16, _lib.T3B_KV_FP8, out.data_ptr(), None, sp()))
     torch.cuda.synchronize()
     kd, vd = kv_fp8_ref.dequantize(kq, ks), kv_fp8_ref.dequantize(vq, vs)
     o0 = 0
@@ -146,12 +146,53 @@ def test_fused_decode_attention_equals_write_then_attend(L, kv_dtype):
     _lib.check(L.t3b_rope_kv_write(qkv.data_ptr(), None, 1, n, None, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos,
                                    btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, kv_dtype, q.data_ptr(), sp()))
     _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, None, idx.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, kv_dtype,
-                                       out_a.data_ptr(), sp()))
+                                       out_a.data_ptr(), None, sp()))
     _lib.check(L.t3b_attn_decode_fused(qkv.data_ptr(), n, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb,
-                                       kp2.data_ptr(), vp2.data_ptr(), 16, kv_dtype, out_b.data_ptr(), sp()))
+                                       kp2.data_ptr(), vp2.data_ptr(), 16, kv_dtype, out_b.data_ptr(), None, sp()))
     assert torch.equal(kp, kp2) and torch.equal(vp, vp2)
     a, b = out_a.float().cpu(), out_b.float().cpu()
     assert ((ulp_diff(a, b) <= 1.0) | ((a - b).abs() < 2e-3)).all(), float((a - b).abs().max())
+
+
+@pytest.mark.parametrize("team", [1, 2, 4, 8])
+def test_attention_team_sizes_match_fp32_softmax_and_each_other(L, team):
+    """t3b_options_t.attn_team_warps: 1, 2, 4 or 8 warps per (row, head) item - every split of the online softmax equals the fp32
+    softmax over the pool (1 bf16 ulp), for ragged contexts from 1 token to the 1200-token limit, many items per warp (more items
+    than the grid has teams) and the fused decode variant (new token from registers)."""
+    g = torch.Generator().manual_seed(40 + team)
+    ctxs = [1, 15, 16, 17, 31, 32, 33, 64, 100, 250, 700, 1200] * 8            # 96 rows x 16 heads = 1536 items
+    n, mb = len(ctxs), (max(ctxs) + 15) // 16
+    bt, kp, vp = _pool(n, mb, _lib.T3B_KV_BF16, 6)
+    kp.view(torch.bfloat16).copy_(torch.randn(kp.numel() // 2, generator=g).bfloat16().reshape(kp.view(torch.bfloat16).shape))
+    vp.view(torch.bfloat16).copy_(torch.randn(vp.numel() // 2, generator=g).bfloat16().reshape(vp.view(torch.bfloat16).shape))
+    kp2, vp2 = kp.clone(), vp.clone()
+    qkv = torch.randn(n, 3072, generator=g).bfloat16().to(DEV)
+    idx, pos = i32([c - 1 for c in ctxs]), i32([(c * 7) % SMALL.max_pos for c in ctxs])
+    cs = rope_cos_sin_table(SMALL).to(device=DEV, dtype=torch.bfloat16)
+    btd = bt.to(DEV)
+    opt = _lib.make_options(attn_team_warps=team)
+    q = torch.empty(n, 1024, dtype=torch.bfloat16, device=DEV)
+    out_a, out_b = torch.empty_like(q), torch.empty_like(q)
+    _lib.check(L.t3b_rope_kv_write(qkv.data_ptr(), None, 1, n, None, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos,
+                                   btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, 0, q.data_ptr(), sp()))
+    _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, None, idx.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(), vp.data_ptr(), 16, 0,
+                                       out_a.data_ptr(), C.byref(opt), sp()))
+    _lib.check(L.t3b_attn_decode_fused(qkv.data_ptr(), n, idx.data_ptr(), pos.data_ptr(), cs.data_ptr(), SMALL.max_pos, btd.data_ptr(), mb,
+                                       kp2.data_ptr(), vp2.data_ptr(), 16, 0, out_b.data_ptr(), C.byref(opt), sp()))
+    torch.cuda.synchronize()
+    assert torch.equal(kp, kp2) and torch.equal(vp, vp2)
+    kh = kp.view(torch.bfloat16).view(-1, 16, 16, 64).float().cpu()            # [block, head, tok, d]
+    vh = vp.view(torch.bfloat16).view(-1, 16, 16, 64).float().cpu()
+    qh = q.float().cpu().reshape(n, 16, 64)
+    a, b = out_a.float().cpu(), out_b.float().cpu()
+    for r in range(0, n, 5):
+        c = ctxs[r]
+        blocks = bt[r, :(c + 15) // 16].long()
+        K = kh[blocks].permute(0, 2, 1, 3).reshape(-1, 16, 64)[:c]
+        V = vh[blocks].permute(0, 2, 1, 3).reshape(-1, 16, 64)[:c]
+        ref = _softmax_ref(qh[r], K, V)
+        for name, o in (("paged", a[r]), ("fused", b[r])):
+            assert ((ulp_diff(o, ref) <= 1.0) | ((o - ref).abs() < 2e-3)).all(), (name, team, r, c, float((o - ref).abs().max()))
 
 
 # ---------------------------------------------------------------------------------------------- prefill
@@ -182,7 +223,7 @@ def test_prefill_attention_matches_causal_softmax(L, kv_dtype):
     # the same queries through the per-token paged kernel: another summation order of the same softmax
     out2 = torch.empty_like(out)
     _lib.check(L.t3b_paged_attn_decode(q.data_ptr(), n, rows_d.data_ptr(), idx_d.data_ptr(), btd.data_ptr(), mb, kp.data_ptr(),
-                                       vp.data_ptr(), 16, kv_dtype, out2.data_ptr(), sp()))
+                                       vp.data_ptr(), 16, kv_dtype, out2.data_ptr(), None, sp()))
     torch.cuda.synchronize()
     orc = T3Oracle(synthetic_checkpoint(SMALL), SMALL, mode="bf16")
     k_ref = orc.rope(qkv[:, 1024:2048].float().reshape(n, 16, 64), torch.tensor(idx))
@@ -307,7 +348,7 @@ def test_gemv_norm_fold_equals_separate_norm_launches(L, small_model, rows):
     outs = []
     for no_norm in (0, 1):
         kv, st = random_state(SMALL, rows, lens, seed=3)
-        opt = _lib.Options(4, no_norm, 0, 0, (C.c_int32 * 4)(0, 0, 0, 0))
+        opt = _lib.make_options(gemv_max_rows=4, gemv_no_norm=no_norm)
         ws = m.workspace(rows)
         hid = torch.empty(rows, 1024, dtype=torch.bfloat16, device=DEV)
         _lib.check(L.t3b_decode_step(C.byref(m.c), C.byref(kv.c), C.byref(st.c), None, rows, hid.data_ptr(), ws.data_ptr(), ws.numel(),
@@ -325,7 +366,7 @@ def test_umma_row_chunk_and_stage_options_do_not_change_results(L, rows, chunk, 
         w = (torch.randn(N, K, generator=g) * K ** -0.5).bfloat16().to(DEV)
         lin = _lib.Linear(_lib.T3B_W_BF16, N, K, w.data_ptr(), None, None)
         ys = []
-        for opt in (None, _lib.Options(0, 0, stages, chunk, (C.c_int32 * 4)(0, 0, 0, 0))):
+        for opt in (None, _lib.make_options(umma_stages=stages, umma_row_chunk=chunk)):
             y = torch.zeros(rows, N // (2 if epi else 1), dtype=torch.bfloat16, device=DEV)
             split = 2 if chunk % 8 else 0
             _lib.check(L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, split, None, _lib.T3B_IMPL_UMMA, epi,

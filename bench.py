@@ -59,6 +59,8 @@ def parse():
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg5"], help="cfg2 = BASELINE.json configs[1] (default); cfg5 = "
                     "configs[4]: 4096 mixed-length requests through the dispatcher + generate()")
     ap.add_argument("--requests", type=int, default=4096, help="cfg5: total requests over all GPUs")
+    ap.add_argument("--opt", default="", help="A/B of launch-shape options: comma-separated t3b_options_t fields, e.g. "
+                                              "no_weight_prefetch=1,attn_team_warps=2 (applied to every engine this run builds)")
     return ap.parse_args()
 
 
@@ -237,6 +239,9 @@ def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN, quant=None, k
     if kv_tokens_per_row is not None:
         kv_blocks = 2 * batch * ((kv_tokens_per_row + 15) // 16 + 1) + 8
     eng = T3B200Engine(m, max_num_seqs=batch, max_model_len=max_model_len, kv_blocks=kv_blocks, kv_dtype=kv_dtype)
+    for kv in [t for t in OPT_OVERRIDES.split(",") if t]:
+        k, v = kv.split("=")
+        setattr(eng.opt, k, int(v))
     return m, eng, sd
 
 
@@ -506,7 +511,7 @@ def run_b200(args):
 
     sb = step_bytes(m, eng, B, r["mean_ctx"])
     cfg = bench_config(B, world, K)
-    notes = {"decode_positions": r["positions"], "measured_mean_context": r["mean_ctx"],
+    notes = {"options": args.opt or "defaults", "decode_positions": r["positions"], "measured_mean_context": r["mean_ctx"],
              "timed_region": "K CUDA-graph replays of the step + one 9*B int32 device copy per step that selects the decode position"}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3), "ms_per_step": ms / K,
@@ -636,8 +641,13 @@ def run_cfg5(args, rank, world, local, dev, pk, barrier, max_over_ranks):
         print(json.dumps(line), flush=True)
 
 
+OPT_OVERRIDES = ""
+
+
 def main():
+    global OPT_OVERRIDES
     args = parse()
+    OPT_OVERRIDES = args.opt
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -8,9 +8,9 @@
 
 // implemented in the kernel translation units
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
-                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res);
+                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf);
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, int stages_cap, int row_chunk, cudaStream_t s);
+                               int n_split, int epi, int stages_cap, int row_chunk, PfArgs pf, cudaStream_t s);
 int t3b_umma_pick_split(int rows, int N, int K);
 int t3b_umma_available();
 int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_split, const float* logits_in, int V, int n_req,
@@ -18,7 +18,7 @@ int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_s
                            cudaStream_t stream);
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
                               const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, int kv_dtype, void* out,
-                              int team_warps, cudaStream_t s);
+                              int team_warps, PfArgs pf, cudaStream_t s);
 int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
                               int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, int team_warps,
                               cudaStream_t s);
@@ -92,10 +92,10 @@ extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
 }
 
 struct Opt {
-    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team;
+    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch;
 };
 static Opt resolve(const t3b_options_t* o) {
-    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0};
+    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0};
     if (o) {
         if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > 4 ? 4 : o->gemv_max_rows);
         r.gemv_norm = o->gemv_no_norm ? 0 : 1;
@@ -103,6 +103,7 @@ static Opt resolve(const t3b_options_t* o) {
         r.row_chunk = o->umma_row_chunk > 0 ? o->umma_row_chunk : 0;
         for (int i = 0; i < 4; ++i) r.split[i] = o->umma_split[i] > 0 ? o->umma_split[i] : 0;
         r.attn_team = o->attn_team_warps;
+        r.prefetch = o->weight_prefetch ? 1 : 0;
     }
     return r;
 }
@@ -110,7 +111,7 @@ static Opt resolve(const t3b_options_t* o) {
 // ------------------------------------------------------------------ linear dispatch
 // epi: 0 = y[rows, n]; 1 = gate_up with the SiLU*mul epilogue -> y[rows, n/2].
 static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* y, float* partials, int n_split, int* n_split_out, int impl,
-                          int epi, const Opt& o, cudaStream_t s) {
+                          int epi, const Opt& o, PfArgs pf, cudaStream_t s) {
     T3B_CHECK_ARG(x && w && w->w, "linear: null pointer");
     T3B_CHECK_ARG(rows >= 0 && w->n > 0 && w->k > 0, "linear: bad sizes rows=%d n=%d k=%d", rows, w->n, w->k);
     T3B_CHECK_ALIGN(x); T3B_CHECK_ALIGN(w->w);
@@ -125,7 +126,7 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
         T3B_CHECK_ARG(n_split <= 1, "linear: the GEMV path has no split-K (n_split %d)", n_split);
         T3B_CHECK_ARG(y != nullptr, "linear: y is null");
         if (n_split_out) *n_split_out = 1;
-        return t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, epi, s, nullptr, nullptr, nullptr, 0.f, 0);
+        return t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, epi, s, nullptr, nullptr, nullptr, 0.f, 0, pf);
     }
     T3B_CHECK_ARG(impl == T3B_IMPL_UMMA, "linear: unknown impl %d", impl);
     const bool legacy = partials != nullptr && n_split > 1;      // explicit request for global fp32 partials
@@ -137,14 +138,14 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     if (!legacy && y == nullptr) T3B_FAIL(T3B_ERR_ARG, "linear: y is null (partials are only written for an explicit n_split > 1)");
     if (n_split_out) *n_split_out = n_split;
     return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, legacy ? partials : nullptr, n_split, epi, o.stages,
-                                  o.row_chunk, s);
+                                  o.row_chunk, pf, s);
 }
 
 extern "C" int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
                                    int32_t* n_split_out, int32_t impl, int32_t epilogue, const t3b_options_t* opt, void* stream) {
     T3B_CHECK_ARG(w && w->kind == T3B_W_BF16, "t3b_linear_bf16: weight kind must be T3B_W_BF16");
     T3B_CHECK_ARG(epilogue == T3B_EPI_NONE || epilogue == T3B_EPI_SILU_MUL, "t3b_linear_bf16: unknown epilogue %d", epilogue);
-    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, epilogue, resolve(opt), t3b_stream(stream));
+    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, epilogue, resolve(opt), pf_none(), t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
@@ -152,7 +153,7 @@ extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t 
     T3B_CHECK_ARG(w && w->kind == T3B_W_AWQ, "t3b_linear_awq: weight kind must be T3B_W_AWQ");
     T3B_CHECK_ARG(w->scales && w->zeros, "t3b_linear_awq: scales / zeros are null");
     T3B_CHECK_ARG(epilogue == T3B_EPI_NONE || epilogue == T3B_EPI_SILU_MUL, "t3b_linear_awq: unknown epilogue %d", epilogue);
-    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, epilogue, resolve(opt), t3b_stream(stream));
+    return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, epilogue, resolve(opt), pf_none(), t3b_stream(stream));
 }
 
 // ------------------------------------------------------------------ whole step
@@ -195,9 +196,15 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     // request's prefill is bit-identical no matter which other requests are admitted with it.  Decode steps pick shapes by row
     // count (identical within a slot bucket).
     const bool prefill = tok_row != nullptr;
-    auto lin = [&](const void* x, const t3b_linear_t* w, void* y, int epi) -> int32_t {
-        return linear_any(x, w, n_tok, y, nullptr, prefill ? 1 : 0, nullptr, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, epi, o, s);
+    auto lin = [&](const void* x, const t3b_linear_t* w, void* y, int epi, PfArgs pf) -> int32_t {
+        return linear_any(x, w, n_tok, y, nullptr, prefill ? 1 : 0, nullptr, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, epi, o, pf, s);
     };
+    // Decode steps are HBM-bound and every kernel of the chain is short: each launch pulls the weights of the projection two
+    // launches ahead into L2 (qkv -> o, attention -> gate_up, o -> down, gate_up -> the next layer's qkv / the speech head), so
+    // the weight stream never waits for the dependent chain.  Prefill passes are compute-bound: no prefetch.
+    const bool pfo = !prefill && o.prefetch;
+    auto pfw = [&](const t3b_linear_t* w) { return pfo ? pf_linear(w) : pf_none(); };
+    auto pf_after = [&](int li) { return li + 1 < m->n_layers ? pfw(&m->layers[li + 1].qkv) : pfw(&m->head); };
     auto kpool = [&](int li) { return static_cast<char*>(kv->k) + (size_t)li * kv->layer_stride; };
     auto vpool = [&](int li) { return static_cast<char*>(kv->v) + (size_t)li * kv->layer_stride; };
     // Small batch (rows <= gemv_max_rows, bf16): F2.1 runs in front of the qkv / gate_up GEMVs (each block normalises the <= 4 rows
@@ -212,18 +219,19 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
         for (int li = 0; li < m->n_layers; ++li) {
             const t3b_layer_t* L = &m->layers[li];
             T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
-            rc = t3b_linear_gemv_launch(xin, L->qkv.w, n_tok, L->qkv.n, L->qkv.k, ws.qkv, 0, s, rcur, roth, L->ln1, m->rms_eps, li > 0);
+            rc = t3b_linear_gemv_launch(xin, L->qkv.w, n_tok, L->qkv.n, L->qkv.k, ws.qkv, 0, s, rcur, roth, L->ln1, m->rms_eps, li > 0, pfw(&L->o));
             if (rc) return rc;
             { char* t = rcur; rcur = roth; roth = t; }
             rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
-                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, s);
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), s);
             if (rc) return rc;
-            rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE);
+            rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE, pfw(&L->down));
             if (rc) return rc;
-            rc = t3b_linear_gemv_launch(ws.lin, L->gate_up.w, n_tok, L->gate_up.n, L->gate_up.k, ws.act, 1, s, rcur, roth, L->ln2, m->rms_eps, 1);
+            rc = t3b_linear_gemv_launch(ws.lin, L->gate_up.w, n_tok, L->gate_up.n, L->gate_up.k, ws.act, 1, s, rcur, roth, L->ln2, m->rms_eps, 1,
+                                        pf_after(li));
             if (rc) return rc;
             { char* t = rcur; rcur = roth; roth = t; }
-            rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE);
+            rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE, pf_none());
             if (rc) return rc;
             xin = ws.lin;
         }
@@ -235,7 +243,7 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
         T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
         rc = t3b_add_rmsnorm(prev, nullptr, 1, ws.resid, L->ln1, ws.normed, n_tok, D, m->rms_eps, li > 0, stream);
         if (rc) return rc;
-        rc = lin(ws.normed, &L->qkv, ws.qkv, T3B_EPI_NONE);
+        rc = lin(ws.normed, &L->qkv, ws.qkv, T3B_EPI_NONE, pfw(&L->o));
         if (rc) return rc;
         if (prefill) {
             rc = t3b_rope_kv_write(ws.qkv, nullptr, 1, n_tok, tok_row, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables,
@@ -248,16 +256,16 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
                 rc = t3b_paged_attn_launch(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kpool(li), vpool(li), H, kv->dtype, ws.attn, 1, s);   // one warp per (token, head): fixed, so a prompt's result does not depend on its batch
         } else {
             rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
-                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, s);
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), s);
         }
         if (rc) return rc;
-        rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE);
+        rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE, pfw(&L->down));
         if (rc) return rc;
         rc = t3b_add_rmsnorm(ws.lin, nullptr, 1, ws.resid, L->ln2, ws.normed, n_tok, D, m->rms_eps, 1, stream);
         if (rc) return rc;
-        rc = lin(ws.normed, &L->gate_up, ws.act, T3B_EPI_SILU_MUL);
+        rc = lin(ws.normed, &L->gate_up, ws.act, T3B_EPI_SILU_MUL, pf_after(li));
         if (rc) return rc;
-        rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE);
+        rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE, pf_none());
         if (rc) return rc;
         prev = ws.lin;
     }
@@ -322,7 +330,7 @@ extern "C" int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden,
     if (rows == 0) return T3B_OK;
     T3B_CHECK_ARG(workspace_bytes >= t3b_workspace_bytes(m, rows), "t3b_head_cfg_sample: workspace too small");
     const Workspace ws = carve(m, rows, workspace);
-    rc = linear_any(hidden, &m->head, rows, ws.head, nullptr, 0, nullptr, T3B_IMPL_AUTO, T3B_EPI_NONE, resolve(opt), t3b_stream(stream));
+    rc = linear_any(hidden, &m->head, rows, ws.head, nullptr, 0, nullptr, T3B_IMPL_AUTO, T3B_EPI_NONE, resolve(opt), pf_none(), t3b_stream(stream));
     if (rc) return rc;
     return t3b_sampler_launch(ws.head, nullptr, 1, nullptr, m->speech_vocab, rows / 2, sp, st, advance, out_tokens, logits_out,
                               t3b_stream(stream));

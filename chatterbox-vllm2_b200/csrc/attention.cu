@@ -4,7 +4,9 @@
 // HBM-bound byte work: per (query, head) item the kernel streams the row's cached K and V exactly once.  The pool layout
 // [block][head][16 tok][64] makes one (block, head) slice ONE contiguous bulk copy (2 KB bf16 / 1088 B fp8).
 //
-// Persistent kernel, one CTA of AT_NW warps per SM.  A TEAM of W warps (W = 1, 2, 4 or 8; AT_NW / W teams per CTA) owns a whole
+// Persistent kernel, one CTA of AT_NW = 8 warps per SM.  (Two 4-warp CTAs with a 2-deep ring - small enough to sit beside a running
+// QKV GEMM block - measured the same at 64 rows and 2-6 % slower at 256 / 512 rows: profiles/r2_notes.md r2h.)
+// A TEAM of W warps (W = 1, 2, 4 or 8; AT_NW / W teams per CTA) owns a whole
 // (token, head) item: the item's head - q/k/v load, RoPE, KV write - and its fold run once per item, and with W = 1 (every batch
 // of >= 37 requests) a warp never meets another warp: no barrier, no exchange, the result goes from registers to global memory.
 // Items are dealt round-robin to the teams of the grid; inside a team the item's pages are dealt round-robin two at a time
@@ -29,7 +31,9 @@
 
 #include "t3b_common.cuh"
 
-#define AT_NW 8
+#define AT_NW 8                     // warps per CTA of the decode kernel
+#define AT_CTAS 1                   // resident CTAs per SM the decode kernel is sized for
+#define PF_NW 8                     // warps per CTA of the prefill kernel
 #define AT_CAP 128                  // items per CTA (all its teams) whose metadata is staged in shared memory
 
 struct AttnArgs {
@@ -46,6 +50,7 @@ struct AttnArgs {
     int n_heads;
     bf16* out;
     int n_items;                    // n_tok * n_heads
+    PfArgs pf;                      // weights of a later launch to pull into L2 (hint)
 };
 
 template <int KVT> struct KvFmt;
@@ -158,7 +163,7 @@ __device__ __forceinline__ void attn_pair(const unsigned char* k0, const unsigne
 }
 
 template <bool FUSED, int W, int S, int KVT>
-__global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs a) {
+__global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const AttnArgs a) {
     constexpr int SLICE = KvFmt<KVT>::SLICE;
     constexpr int PAIR = 4 * SLICE;                       // K0 | K1 | V0 | V1
     constexpr int T = AT_NW / W;                          // teams per CTA
@@ -198,6 +203,7 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
     // ---- producer cursor: (pk, pp) = next pair of this warp to fetch, (nb0, nb1) its two block ids - loaded when the cursor
     // moves, so that a block-table read is never right in front of the copy it feeds
     int pk = 0, pp = wt, pn = 0, nb0 = 0, nb1 = 0;
+    const uint64_t kv_policy = l2_policy_evict_first();     // K/V is read once per step: it must not displace prefetched weights
     auto settle = [&]() {
         while (pk < n_my && pp >= ((s_nc[mb + pk] + 31) >> 5)) { ++pk; pp = wt; }
         nb0 = 0; nb1 = 0;
@@ -209,18 +215,18 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
     };
     auto produce = [&]() {
         if (pk >= n_my) return;                                            // warp-uniform
-        if (lane == 0) {
+        {
+            // One cp.async.bulk costs the issuing THREAD ~600 cycles; four lanes issue the four copies of a pair with one warp
+            // instruction instead (scripts/probe/bulk_bw.cu: 2,470 -> 725 cycles per pair, 5.4 -> 6.6 TB/s at 8 warps per SM).
             const int h = (gt + pk * NT) % H;
             const bool two = pp * 2 + 1 < ((s_nc[mb + pk] + 15) >> 4);
             const int slot = pn % S;
             unsigned char* dst = my_ring + (size_t)slot * PAIR;
-            const size_t o0 = ((size_t)nb0 * H + h) * SLICE, o1 = ((size_t)nb1 * H + h) * SLICE;
-            mbar_expect_tx(&my_full[slot], (two ? 4u : 2u) * SLICE);
-            bulk_load_1d(dst, a.k_pool + o0, SLICE, &my_full[slot]);
-            bulk_load_1d(dst + 2 * SLICE, a.v_pool + o0, SLICE, &my_full[slot]);
-            if (two) {
-                bulk_load_1d(dst + SLICE, a.k_pool + o1, SLICE, &my_full[slot]);
-                bulk_load_1d(dst + 3 * SLICE, a.v_pool + o1, SLICE, &my_full[slot]);
+            if (lane == 0) mbar_expect_tx(&my_full[slot], (two ? 4u : 2u) * SLICE);
+            if (lane < 4 && (two || (lane & 1) == 0)) {
+                const size_t off = ((size_t)((lane & 1) ? nb1 : nb0) * H + h) * SLICE;
+                const unsigned char* src = ((lane & 2) ? a.v_pool : a.k_pool) + off;
+                bulk_load_1d_hint(dst + lane * SLICE, src, SLICE, &my_full[slot], kv_policy);      // slot = K0 | K1 | V0 | V1
             }
         }
         ++pn; pp += W;
@@ -232,6 +238,7 @@ __global__ void __launch_bounds__(AT_NW * 32, 1) attn_ring_kernel(const AttnArgs
     settle();
 #pragma unroll 1
     for (int i = 0; i < S; ++i) produce();
+    if (warp == AT_NW - 1 && lane == 1) pf_slice(a.pf, (int)blockIdx.x, G);      // behind the first ring fill
     if (FUSED) pdl_wait();
     const float kScale = 0.125f * 1.4426950408889634f;   // head_dim^-0.5 * log2(e)
     const int hidden = H * 64;
@@ -398,7 +405,7 @@ struct PrefillArgs {
 };
 
 template <int KVT>
-__global__ void __launch_bounds__(AT_NW * 32) prefill_attn_kernel(const PrefillArgs a) {
+__global__ void __launch_bounds__(PF_NW * 32) prefill_attn_kernel(const PrefillArgs a) {
     constexpr int SLICE = KvFmt<KVT>::SLICE;
     extern __shared__ __align__(128) unsigned char at_smem[];
     __shared__ uint64_t bar;
@@ -425,7 +432,7 @@ __global__ void __launch_bounds__(AT_NW * 32) prefill_attn_kernel(const PrefillA
     mbar_wait(&bar, 0);
     const float kScale = 0.125f * 1.4426950408889634f;
     // longest queries first: warp w takes queries P-1-w, P-1-w-NW, ...
-    for (int j = P - 1 - warp; j >= 0; j -= AT_NW) {
+    for (int j = P - 1 - warp; j >= 0; j -= PF_NW) {
         float qf[8], m = -INFINITY, l = 0.f, acc[8];
         unpack8(ld_act(reinterpret_cast<const uint4*>(a.q + ((size_t)(t0 + j) * H + h) * 64 + c * 8)), qf);
 #pragma unroll
@@ -475,7 +482,7 @@ extern "C" int32_t t3b_prefill_attn(const void* q, int32_t n_seq, const int32_t*
     const size_t smem = (size_t)a.max_pages * 2 * slice;
     auto kern = kv_dtype == T3B_KV_FP8 ? prefill_attn_kernel<1> : prefill_attn_kernel<0>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    T3B_CUDA(t3b_launch(kern, dim3((unsigned)(n_seq * n_heads)), dim3(AT_NW * 32), smem, t3b_stream(stream), a));
+    T3B_CUDA(t3b_launch(kern, dim3((unsigned)(n_seq * n_heads)), dim3(PF_NW * 32), smem, t3b_stream(stream), a));
     return T3B_OK;
 }
 
@@ -485,7 +492,7 @@ extern "C" int32_t t3b_prefill_attn(const void* q, int32_t n_seq, const int32_t*
 // does not change with the number of live requests.
 static int at_team_warps(int n_items, int requested) {
     if (requested == 1 || requested == 2 || requested == 4 || requested == 8) return requested;
-    const int slots = t3b_num_sms() * AT_NW;
+    const int slots = t3b_num_sms() * AT_NW * AT_CTAS;
     int w = AT_NW;
     while (w > 1 && (long)n_items * w > slots) w >>= 1;
     return w;
@@ -499,11 +506,11 @@ static cudaError_t launch_ring(const AttnArgs& a, cudaStream_t s) {
     auto kern = attn_ring_kernel<FUSED, W, S, KVT>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    const int sms = t3b_num_sms();
+    const int slots = t3b_num_sms() * AT_CTAS;            // resident CTAs
     const int teams = a.n_items;                          // one team per item until the grid is full
     int grid = (teams + T - 1) / T;
-    if (grid > sms) grid = sms;
-    if (teams < sms) grid = teams;                        // few items: one team per SM rather than T teams on a few SMs
+    if (grid > slots) grid = slots;
+    if (teams < slots) grid = teams;                      // few items: one team per CTA slot rather than T teams on a few SMs
     const int need = (a.n_items + AT_CAP - 1) / AT_CAP;
     if (grid < need) grid = need;
     return t3b_launch(kern, dim3((unsigned)grid), dim3(AT_NW * 32), smem, s, a);
@@ -542,8 +549,9 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
 // decode step: one token per KV row (token j <-> row j)
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
                               const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, int kv_dtype, void* out,
-                              int team_warps, cudaStream_t s) {
+                              int team_warps, PfArgs pf, cudaStream_t s) {
     AttnArgs a = {};
+    a.pf = pf;
     a.q = (const bf16*)qkv; a.tok_idx = tok_idx; a.rope_pos = rope_pos; a.cos_sin = (const bf16*)rope_cos_sin; a.max_pos = max_pos;
     a.block_tables = block_tables; a.max_blocks = max_blocks; a.k_pool = (unsigned char*)k_pool; a.v_pool = (unsigned char*)v_pool;
     a.n_heads = n_heads; a.out = (bf16*)out; a.n_items = n_tok * n_heads;
@@ -559,7 +567,7 @@ extern "C" int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const i
     T3B_CHECK_ALIGN(qkv); T3B_CHECK_ALIGN(rope_cos_sin); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
     if (n_tok == 0) return T3B_OK;
     return t3b_attn_fused_launch(qkv, n_tok, tok_idx, rope_pos, rope_cos_sin, max_pos, block_tables, max_blocks, k_pool, v_pool, n_heads,
-                                 kv_dtype, out, opt ? opt->attn_team_warps : 0, t3b_stream(stream));
+                                 kv_dtype, out, opt ? opt->attn_team_warps : 0, pf_none(), t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,

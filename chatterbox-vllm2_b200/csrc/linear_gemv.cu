@@ -22,9 +22,11 @@ struct GemvNorm {
     int has_res;
 };
 
-template <int R, int FPW, int KSTEP, int MODE>
-__global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, int rows, int N, int K,
-                                                          bf16* __restrict__ y, const GemvNorm nz) {
+// ONE: K == KSTEP * 256, the warp's whole weight slice is the batch requested before the wait - no second register buffer (the
+// double-buffered loop costs 170 registers for gate_up: one block per SM, two waves; single-shot 2 blocks per SM, one wave)
+template <int R, int FPW, int KSTEP, int MODE, bool ONE>
+__global__ void __launch_bounds__(256, 2) linear_gemv_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w, int rows, int N, int K,
+                                                          bf16* __restrict__ y, const GemvNorm nz, const PfArgs pf) {
     __shared__ float s_red[4][4];
     extern __shared__ __align__(16) unsigned char smem_raw[];
     pdl_launch_dependents();       // early trigger: the next kernel's launch overlaps this one (it waits before reading)
@@ -50,6 +52,7 @@ __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict
 #pragma unroll
             for (int c = 0; c < KSTEP; ++c) wv[f][c] = ldg_stream(wrow[f] + c * 32 + lane);
     }
+    if (threadIdx.x == 0) pf_slice(pf, blockIdx.x, gridDim.x);      // behind this block's own weight loads
     uint4 nwraw = make_uint4(0, 0, 0, 0);
     if (nz.norm_w != nullptr) nwraw = __ldg(reinterpret_cast<const uint4*>(nz.norm_w) + (threadIdx.x & 127));     // before the wait: constant
     pdl_wait();
@@ -112,31 +115,49 @@ __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict
 #pragma unroll
         for (int r = 0; r < R; ++r) acc[f][r] = 0.f;
 
-    for (int k0 = 0; k0 < K8; k0 += KSTEP * 32) {
-        uint4 cur[NW][KSTEP];
-#pragma unroll
-        for (int f = 0; f < NW; ++f)
-#pragma unroll
-            for (int c = 0; c < KSTEP; ++c) cur[f][c] = wv[f][c];
-        if (k0 + KSTEP * 32 < K8) {
-#pragma unroll
-            for (int f = 0; f < NW; ++f)
-#pragma unroll
-                for (int c = 0; c < KSTEP; ++c) wv[f][c] = ldg_stream(wrow[f] + k0 + KSTEP * 32 + c * 32 + lane);
-        }
+    if (ONE) {
 #pragma unroll
         for (int c = 0; c < KSTEP; ++c) {
             float xf[R][8];
 #pragma unroll
-            for (int r = 0; r < R; ++r) unpack8(xs[r * K8 + k0 + c * 32 + lane], xf[r]);
+            for (int r = 0; r < R; ++r) unpack8(xs[r * K8 + c * 32 + lane], xf[r]);
 #pragma unroll
             for (int f = 0; f < NW; ++f) {
                 float wf[8];
-                unpack8(cur[f][c], wf);
+                unpack8(wv[f][c], wf);
 #pragma unroll
                 for (int r = 0; r < R; ++r)
 #pragma unroll
                     for (int e = 0; e < 8; ++e) acc[f][r] = fmaf(wf[e], xf[r][e], acc[f][r]);
+            }
+        }
+    } else {
+        for (int k0 = 0; k0 < K8; k0 += KSTEP * 32) {
+            uint4 cur[NW][KSTEP];
+    #pragma unroll
+            for (int f = 0; f < NW; ++f)
+    #pragma unroll
+                for (int c = 0; c < KSTEP; ++c) cur[f][c] = wv[f][c];
+            if (k0 + KSTEP * 32 < K8) {
+    #pragma unroll
+                for (int f = 0; f < NW; ++f)
+    #pragma unroll
+                    for (int c = 0; c < KSTEP; ++c) wv[f][c] = ldg_stream(wrow[f] + k0 + KSTEP * 32 + c * 32 + lane);
+            }
+    #pragma unroll
+            for (int c = 0; c < KSTEP; ++c) {
+                float xf[R][8];
+    #pragma unroll
+                for (int r = 0; r < R; ++r) unpack8(xs[r * K8 + k0 + c * 32 + lane], xf[r]);
+    #pragma unroll
+                for (int f = 0; f < NW; ++f) {
+                    float wf[8];
+                    unpack8(cur[f][c], wf);
+    #pragma unroll
+                    for (int r = 0; r < R; ++r)
+    #pragma unroll
+                        for (int e = 0; e < 8; ++e) acc[f][r] = fmaf(wf[e], xf[r][e], acc[f][r]);
+                }
             }
         }
     }
@@ -164,34 +185,43 @@ __global__ void __launch_bounds__(256) linear_gemv_kernel(const bf16* __restrict
     }
 }
 
-template <int R, int FPW, int KSTEP, int MODE>
-static cudaError_t launch_gemv(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s, const GemvNorm& nz) {
+template <int R, int FPW, int KSTEP, int MODE, bool ONE>
+static cudaError_t launch_gemv1(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s, const GemvNorm& nz,
+                               const PfArgs& pf) {
     const int n_out = MODE == 1 ? N / 2 : N;
     const int warps = (n_out + FPW - 1) / FPW;
     const size_t smem = (size_t)R * K * 2;
-    auto kern = linear_gemv_kernel<R, FPW, KSTEP, MODE>;
+    auto kern = linear_gemv_kernel<R, FPW, KSTEP, MODE, ONE>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    return t3b_launch(kern, dim3((warps + 7) / 8), dim3(256), smem, s, (const bf16*)x, (const bf16*)w, rows, N, K, (bf16*)y, nz);
+    return t3b_launch(kern, dim3((warps + 7) / 8), dim3(256), smem, s, (const bf16*)x, (const bf16*)w, rows, N, K, (bf16*)y, nz, pf);
+}
+
+template <int R, int FPW, int KSTEP, int MODE>
+static cudaError_t launch_gemv(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s, const GemvNorm& nz,
+                               const PfArgs& pf) {
+    if (K == KSTEP * 256) return launch_gemv1<R, FPW, KSTEP, MODE, true>(x, w, rows, N, K, y, s, nz, pf);
+    return launch_gemv1<R, FPW, KSTEP, MODE, false>(x, w, rows, N, K, y, s, nz, pf);
 }
 
 template <int R, int MODE>
-static cudaError_t dispatch_gemv_r(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s, const GemvNorm& nz) {
+static cudaError_t dispatch_gemv_r(const void* x, const void* w, int rows, int N, int K, void* y, cudaStream_t s, const GemvNorm& nz,
+                                   const PfArgs& pf) {
     const int n_out = MODE == 1 ? N / 2 : N;
     const int sms = t3b_num_sms();
-    if (MODE == 1) return launch_gemv<R, 2, 4, 1>(x, w, rows, N, K, y, s, nz);
+    if (MODE == 1) return launch_gemv<R, 2, 4, 1>(x, w, rows, N, K, y, s, nz, pf);
     // few, long rows (o / down with K = 4096): one feature per warp, 16 chunks in flight
-    if (K % 4096 == 0 && n_out / 4 < sms * 8) return launch_gemv<R, 1, 16, 0>(x, w, rows, N, K, y, s, nz);
-    if (n_out % 4 == 0 && n_out / 4 >= sms * 8) return launch_gemv<R, 4, 4, 0>(x, w, rows, N, K, y, s, nz);
-    if (n_out % 2 == 0 && n_out / 2 >= sms * 8) return launch_gemv<R, 2, 4, 0>(x, w, rows, N, K, y, s, nz);
-    return launch_gemv<R, 1, 4, 0>(x, w, rows, N, K, y, s, nz);
+    if (K % 4096 == 0 && n_out / 4 < sms * 8) return launch_gemv<R, 1, 16, 0>(x, w, rows, N, K, y, s, nz, pf);
+    if (n_out % 4 == 0 && n_out / 4 >= sms * 8) return launch_gemv<R, 4, 4, 0>(x, w, rows, N, K, y, s, nz, pf);
+    if (n_out % 2 == 0 && n_out / 2 >= sms * 8) return launch_gemv<R, 2, 4, 0>(x, w, rows, N, K, y, s, nz, pf);
+    return launch_gemv<R, 1, 4, 0>(x, w, rows, N, K, y, s, nz, pf);
 }
 
 // mode: 0 = y[rows, N]; 1 = gate_up with fused SiLU*mul -> y[rows, N/2]
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
-                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res) {
+                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf) {
     GemvNorm nz = {(const bf16*)res_in, (bf16*)res_out, (const bf16*)norm_w, eps, has_res};
     if (norm_w != nullptr) {
         T3B_CHECK_SHAPE(K == 1024, "gemv: the fused norm needs K == 1024 (got %d)", K);
@@ -201,9 +231,9 @@ int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, in
     T3B_CHECK_SHAPE(K % 1024 == 0 && K <= 8192, "gemv: K %d must be a multiple of 1024 (<= 8192)", K);
     T3B_CHECK_SHAPE(mode == 0 || N % 4 == 0, "gemv: gate_up N %d", N);
     cudaError_t e;
-    if (rows == 1) e = mode ? dispatch_gemv_r<1, 1>(x, w, rows, N, K, y, s, nz) : dispatch_gemv_r<1, 0>(x, w, rows, N, K, y, s, nz);
-    else if (rows == 2) e = mode ? dispatch_gemv_r<2, 1>(x, w, rows, N, K, y, s, nz) : dispatch_gemv_r<2, 0>(x, w, rows, N, K, y, s, nz);
-    else e = mode ? dispatch_gemv_r<4, 1>(x, w, rows, N, K, y, s, nz) : dispatch_gemv_r<4, 0>(x, w, rows, N, K, y, s, nz);
+    if (rows == 1) e = mode ? dispatch_gemv_r<1, 1>(x, w, rows, N, K, y, s, nz, pf) : dispatch_gemv_r<1, 0>(x, w, rows, N, K, y, s, nz, pf);
+    else if (rows == 2) e = mode ? dispatch_gemv_r<2, 1>(x, w, rows, N, K, y, s, nz, pf) : dispatch_gemv_r<2, 0>(x, w, rows, N, K, y, s, nz, pf);
+    else e = mode ? dispatch_gemv_r<4, 1>(x, w, rows, N, K, y, s, nz, pf) : dispatch_gemv_r<4, 0>(x, w, rows, N, K, y, s, nz, pf);
     T3B_CUDA(e);
     return T3B_OK;
 }

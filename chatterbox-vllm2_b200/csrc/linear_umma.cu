@@ -59,6 +59,7 @@ struct UmmaParams {
     const unsigned char* qw; // repacked nibbles [N/128][K/64][2][128][16 B]
     const bf16* scales;      // bf16 [K/128, N]
     const unsigned char* zeros;   // u8 [K/128, N]
+    PfArgs pf;               // weights of a later launch to pull into L2 (hint)
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
@@ -169,22 +170,25 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     };
     const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + x_bytes;
     const int pre = nkb < stages ? nkb : stages;
-    // The first ring of weight tiles goes out before anything else: weights never depend on the previous kernel.
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < pre; ++i) {
-            mbar_expect_tx(&full_bar[i], tx);
-            load_w(i, i);
-        }
+    // The first ring of weight tiles goes out before anything else: weights never depend on the previous kernel.  A TMA / bulk
+    // copy instruction costs the issuing THREAD several hundred cycles (scripts/probe/bulk_bw.cu), so lane i of warp 0 issues the
+    // loads of stage i: one warp instruction for the whole ring instead of a serial loop.
+    if (warp == 0 && lane < pre) {
+        mbar_expect_tx(&full_bar[lane], tx);
+        load_w(lane, lane);
     }
+    // an otherwise idle warp pulls this block's slice of a later launch's weights into L2
+    if (warp == 3 && lane == 0)
+        pf_slice(p.pf, (int)(blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z)), (int)(gridDim.x * gridDim.y * gridDim.z));
     // Every CTA of the cluster must be running before a peer stores into its shared memory (hidden under the
     // first-byte latency of the loads above).
     if (p.partials == nullptr && p.n_split > 1) cluster_sync_all();
 
     if (warp == 0) {
+        pdl_wait();
+        if (lane < pre)
+            tma_load_2d(smem + (size_t)lane * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[lane], (kb_begin + lane) * UM_K, rchunk * p.row_chunk);
         if (lane == 0) {
-            pdl_wait();
-            for (int i = 0; i < pre; ++i)
-                tma_load_2d(smem + (size_t)i * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[i], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
             for (int i = pre; i < nkb; ++i) {
                 const int s = i % stages, round = i / stages;
                 mbar_wait(&empty_bar[s], (round & 1) ^ 1);
@@ -514,7 +518,7 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
 // epi: EPI_STORE / EPI_SILU (bf16 output only).  awq == NULL: bf16 weights `w` [N, K].
 // stages_cap: ring depth cap (0 = 5); row_chunk_req: rows per thread block (0 = 128 with cluster split-K, 256 without).
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, int stages_cap, int row_chunk_req, cudaStream_t stream) {
+                               int n_split, int epi, int stages_cap, int row_chunk_req, PfArgs pf, cudaStream_t stream) {
     T3B_CHECK_SHAPE(K % UM_K == 0 && K >= UM_K, "umma: K %d must be a multiple of 64", K);
     T3B_CHECK_SHAPE(rows >= 1, "umma: rows %d", rows);
     const int kb_total = K / UM_K;
@@ -546,6 +550,7 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     p.y = legacy ? nullptr : (bf16*)y;
     p.partials = legacy ? partials : nullptr;
     p.rows = rows; p.N = N; p.kb_total = kb_total; p.n_split = n_split; p.Rp = Rp; p.row_chunk = row_chunk; p.epi = epi;
+    p.pf = pf;
     p.tmem_cols = 32;
     while ((int)p.tmem_cols < Rp) p.tmem_cols <<= 1;
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u + (awq ? UM_RAW_BYTES : 0);

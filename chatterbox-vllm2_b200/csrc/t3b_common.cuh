@@ -20,6 +20,23 @@ void t3b_set_error(const char* fmt, ...);
 #define T3B_LAUNCH_CHECK() T3B_CUDA(cudaPeekAtLastError())
 
 static inline cudaStream_t t3b_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// A region of weights the NEXT kernels of the decode chain will stream (t3b_decode_step hands every launch the weights of the
+// projection two launches ahead): the kernel's blocks pull their slices into L2 with bulk prefetches before they wait for their
+// own inputs, so HBM keeps streaming while the dependent chain (wait -> load x -> MMA -> exchange -> store) runs from L2.
+// bytes == 0: nothing.  A hint only - never affects results.
+struct PfArgs {
+    const unsigned char* p;
+    unsigned long long bytes;      // multiple of 16
+};
+static inline PfArgs pf_none() { PfArgs a; a.p = nullptr; a.bytes = 0; return a; }
+static inline PfArgs pf_linear(const t3b_linear_t* w) {
+    PfArgs a;
+    a.p = static_cast<const unsigned char*>(w->w);
+    a.bytes = w->kind == T3B_W_AWQ ? (unsigned long long)w->n * w->k / 2 : (unsigned long long)w->n * w->k * 2;
+    a.bytes &= ~15ull;
+    return a;
+}
 int t3b_num_sms();
 
 // launch with the programmatic-dependent-launch attribute: the kernel may start while its
@@ -128,6 +145,29 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
 __device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  :: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// L2 prefetch of [p, p + bytes) (16-byte aligned, multiple of 16): fire and forget, nothing to wait for
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(p), "r"(bytes) : "memory");
+}
+// block `cta` of `ncta` prefetches its 4 KB-aligned slice of the region in 16 KB pieces; call from ONE thread
+__device__ __forceinline__ void pf_slice(const PfArgs pf, int cta, int ncta) {
+    if (pf.bytes == 0) return;
+    const unsigned long long per = ((pf.bytes + ncta - 1) / ncta + 4095ull) & ~4095ull;
+    unsigned long long a = per * (unsigned long long)cta;
+    const unsigned long long e = a + per < pf.bytes ? a + per : pf.bytes;
+    for (; a < e; a += 16384ull) l2_prefetch_bulk(pf.p + a, (uint32_t)(e - a < 16384ull ? e - a : 16384ull));
+}
+// 1-D bulk copy with an L2 evict-first hint: data read once per step (K/V) must not push the prefetched weights out of L2
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_load_1d_hint(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 :: "r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(policy) : "memory");
 }
 
 // ---- tcgen05 / TMEM -------------------------------------------------------

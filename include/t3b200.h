@@ -149,6 +149,8 @@ typedef struct t3b_options {
     int32_t umma_row_chunk;      /* tcgen05 GEMM: CFG rows per thread block, multiple of 16 (0 = default)                  */
     int32_t umma_split[4];       /* cluster split-K of the qkv / o / gate_up / down projections (0 = automatic)            */
     int32_t attn_team_warps;     /* decode attention: warps that share one (row, head) item: 1, 2, 4 or 8 (0 = by item count) */
+    int32_t weight_prefetch;     /* 1 = every launch of t3b_decode_step pulls the weights of the projection two launches ahead into
+                                    L2 (measured: no gain, the chain is latency-bound - profiles/r2_notes.md; default off)       */
 } t3b_options_t;
 
 const char* t3b_last_error(void);

@@ -78,6 +78,10 @@ def main():
     np.savez_compressed(os.path.join(GOLD, "rope_table.npz"), rows=np.array([0, 1, 99, 100, 1199]),
                         table=full[[0, 1, 99, 100, 1199]].numpy())
     mint_analyzer()
+    if "--batch" in sys.argv:
+        mint_batch_fixture()
+        mint_awq_fixture()
+        return
     if "--full" in sys.argv:
         mint_full_streams()
         mint_full_streams(n_req=1, n_steps=1000, sampled=False)      # BASELINE.json configs[3]: context to ~1100
@@ -128,6 +132,46 @@ def mint_full_streams(n_req=2, n_steps=300, sampled=True):
     s = oracle_generate(orc, prompts, n_steps, rho=2.0, temperature=0.8, min_p=0.05, top_p=0.8, seeds=[42 + i for i in range(n_req)])
     np.savez_compressed(os.path.join(GOLD, f"t3_full_sampled{n_steps}.npz"), tokens=s["tokens"], race_margins=s["margins"],
                         minp_margins=s["minp_margins"], topp_margins=s["topp_margins"])
+
+
+SAMPLE_IDX = np.arange(0, 8194, 64, dtype=np.int64)          # a fixed 129-column sample of every logit row (cosine / max-abs)
+
+
+def mint_batch_fixture(n_req=32, n_steps=8):
+    """BASELINE.json configs[1] at its own shape: 30 layers, 32 requests = 64 CFG rows, P = 99, greedy, rho = 2; the first
+    ``n_steps`` tokens of every request with the top-8 logits and a fixed column sample of every step."""
+    full = T3Dims()
+    sd = synthetic_checkpoint(full)
+    prompts = [synthetic_request(i, full, n_text=64) for i in range(n_req)]
+    g = oracle_generate(T3Oracle(sd, full, mode="bf16"), prompts, n_steps, rho=2.0)
+    ti, tv = top8(g["logits"])
+    np.savez_compressed(os.path.join(GOLD, f"t3_full_batch{n_req}.npz"), tokens=g["tokens"], margins=g["margins"], top_idx=ti, top_val=tv,
+                        sample_idx=SAMPLE_IDX, sample_val=g["logits"][..., SAMPLE_IDX].astype(np.float32))
+
+
+def mint_awq_fixture(n_req=64, n_steps=4):
+    """BASELINE.json configs[2] at full depth: AWQ W4A16 projections (oracle on the dequantised weights), 64 requests = 128 CFG
+    rows, temperature 0.8 / top-p 0.8 / min-p 0.05 / rho 2, seeds 42 + i.  Also the same steps (teacher-forced with the same
+    tokens) under the reference engine's fp16 dequant definition (awq_ref.dequantize_fp16, vllm awq.py:71-72): its top-8 /
+    sampled logits, so the GPU test can report the distance of the bf16-dequant build to the fp16 definition."""
+    from oracle import awq_ref
+    full = T3Dims()
+    sd = synthetic_checkpoint(full)
+    sd_deq, packed = awq_ref.quantize_state_dict(sd)
+    prompts = [synthetic_request(i, full, n_text=64) for i in range(n_req)]
+    seeds = [42 + i for i in range(n_req)]
+    s = oracle_generate(T3Oracle(sd_deq, full, mode="bf16"), prompts, n_steps, rho=2.0, temperature=0.8, min_p=0.05, top_p=0.8, seeds=seeds)
+    ti, tv = top8(s["logits"])
+    sd16 = dict(sd)
+    for k, (qw, qz, sc) in packed.items():
+        sd16[k] = awq_ref.dequantize_fp16(qw, qz, sc).float().t().contiguous()
+    f = oracle_generate(T3Oracle(sd16, full, mode="bf16"), prompts, n_steps, rho=2.0, temperature=0.8, min_p=0.05, top_p=0.8, seeds=seeds,
+                        forced=s["tokens"])
+    np.savez_compressed(os.path.join(GOLD, f"t3_full_awq{n_req}_sampled.npz"), tokens=s["tokens"], race_margins=s["margins"],
+                        minp_margins=s["minp_margins"], topp_margins=s["topp_margins"], top_idx=ti, top_val=tv, sample_idx=SAMPLE_IDX,
+                        sample_val=s["logits"][..., SAMPLE_IDX].astype(np.float32),
+                        fp16_sample_val=f["logits"][..., SAMPLE_IDX].astype(np.float32),
+                        fp16_top_val=np.take_along_axis(f["logits"], ti.astype(np.int64), -1).astype(np.float32))
 
 
 if __name__ == "__main__":

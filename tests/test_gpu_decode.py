@@ -72,7 +72,7 @@ def check_logits(name, got, ref, max_abs, min_cos):
 @pytest.mark.parametrize("dims,n_req,n_text,T,max_abs,min_cos", [
     (SMALL, 3, 12, 16, 0.0625, 0.9999),                 # golden-fixture case (rows 6 -> tcgen05 path)
     (SMALL, 1, 12, 12, 0.0625, 0.9999),                 # rows 2 -> GEMV path
-    (SMALL, 2, 5, 8, 0.0625, 0.9999),                   # rows 4 -> GEMV path, 4-row kernels
+    (SMALL, 2, 5, 8, 0.0625, 0.9999),                   # rows 4 -> tcgen05 path at a small row count
     (T3Dims(), 2, 64, 6, 0.25, 0.999),                   # the real 30-layer / P=99 shape
 ])
 def test_decode_teacher_forced_logits_and_greedy(dims, n_req, n_text, T, max_abs, min_cos):

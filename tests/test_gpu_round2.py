@@ -373,3 +373,4 @@ def test_umma_row_chunk_and_stage_options_do_not_change_results(L, rows, chunk, 
                                          C.byref(opt) if opt is not None else None, sp()))
             ys.append(y)
         assert torch.equal(ys[0], ys[1]), (N, K)
+

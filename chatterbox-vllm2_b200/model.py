@@ -346,12 +346,12 @@ class T3B200Model:
         return out
 
     def decode_step(self, kv: KVPool, state: DecodeState, rows: int, hidden_out: torch.Tensor,
-                    x_in: Optional[torch.Tensor] = None, ws: Optional[torch.Tensor] = None) -> torch.Tensor:
+                    x_in: Optional[torch.Tensor] = None, ws: Optional[torch.Tensor] = None, opt=None) -> torch.Tensor:
         """F1+F2 for one token per CFG row; embeddings gathered from ``state`` unless ``x_in`` is given."""
         L = self._require()
         ws = self.workspace(rows) if ws is None else ws
         _lib.check(L.t3b_decode_step(C.byref(self.c), C.byref(kv.c), C.byref(state.c), _lib.ptr(x_in), rows, hidden_out.data_ptr(),
-                                     ws.data_ptr(), ws.numel(), self._opt(), _lib.stream_ptr()), "t3b_decode_step")
+                                     ws.data_ptr(), ws.numel(), self._opt(opt), _lib.stream_ptr()), "t3b_decode_step")
         return hidden_out
 
     def cfg_sample_head_logits(self, head_logits: torch.Tensor, rows: int, sampling_c, state_c, out_tokens_ptr: int, advance: bool = True,

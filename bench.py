@@ -268,6 +268,7 @@ def device_resident(eng, prompts, steps, warmup, sampler, sampled=False, gen_len
     sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=gen_len, ignore_eos=True)
     if sampled:      # configs[2]: min-p / top-p sampling with repetition penalty (tts.py:455-464 defaults)
         sp = SamplingParams(temperature=0.8, top_p=0.8, min_p=0.05, repetition_penalty=2.0, max_tokens=gen_len, ignore_eos=True, seed=1234)
+    eng.uninstall(eng.install(prompts, sp, reserve_steps=1))        # warm the prefill path (tensor maps, kernel attributes, allocator)
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     t0.record()

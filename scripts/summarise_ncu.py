@@ -47,7 +47,9 @@ def full(src, dst):
     out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     h, units = rows[0], rows[1]
-    cols = [("Kernel Name", h.index("Kernel Name"))] + [(m, h.index(m)) for m in FULL if m in h]
+    # every tensor-pipe metric the report holds (names differ between ncu releases), whatever the kernel
+    tensor = [m for m in h if "tensor" in m and m not in FULL and ("pipe" in m or "inst_executed" in m) and "dmma" not in m and "imma" not in m]
+    cols = [("Kernel Name", h.index("Kernel Name"))] + [(m, h.index(m)) for m in FULL + tensor if m in h]
     with open(dst, "w", newline="") as f:
         w = csv.writer(f)
         w.writerow([c if c == "Kernel Name" else f"{c} [{units[i]}]" for c, i in cols])

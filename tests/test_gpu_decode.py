@@ -5,7 +5,7 @@ Tolerances (north star: "logits within stated bf16 tolerance, max-abs and cosine
 token ids bit-exact"): the oracle's bf16 mode rounds where the kernels round, so the only difference
 is fp32 summation order, which flips individual bf16 roundings by 1 ulp and compounds over layers.
   logits (|l| <= ~6, bf16 ulp 2^-6..2^-5):  2 layers: max-abs <= 0.0625, cosine >= 0.9999
-                                            30 layers: max-abs <= 0.25,  cosine >= 0.999
+                                            30 layers: max-abs <= 0.1875, cosine >= 0.999
   greedy tokens: identical wherever the oracle's own top-2 margin exceeds the logit tolerance; a
   mismatch on a smaller margin is a tie broken by rounding, and is reported, not hidden.
 Measured values are appended to gpurun_out/parity.jsonl.
@@ -73,7 +73,8 @@ def check_logits(name, got, ref, max_abs, min_cos):
     (SMALL, 3, 12, 16, 0.0625, 0.9999),                 # golden-fixture case (rows 6 -> tcgen05 path)
     (SMALL, 1, 12, 12, 0.0625, 0.9999),                 # rows 2 -> GEMV path
     (SMALL, 2, 5, 8, 0.0625, 0.9999),                   # rows 4 -> tcgen05 path at a small row count
-    (T3Dims(), 2, 64, 6, 0.25, 0.999),                   # the real 30-layer / P=99 shape
+    (T3Dims(), 2, 64, 6, 0.1875, 0.999),                 # the real 30-layer / P=99 shape (measured 0.125-0.14 + 50 %; long streams and
+                                                         # the benchmarked shapes: tests/test_gpu_parity_full.py)
 ])
 def test_decode_teacher_forced_logits_and_greedy(dims, n_req, n_text, T, max_abs, min_cos):
     torch.set_num_threads(os.cpu_count() or 1)
@@ -145,20 +146,66 @@ def test_engine_graph_replay_equals_eager_and_is_batch_invariant():
 
 
 def test_engine_sampled_stream_vs_golden():
+    """Fixed-seed sampling through generate() (CUDA graphs, continuous batching) against the committed sampled fixture: the stream
+    follows the fixture until the first step where a min-p / top-p / race decision of the ORACLE lands within rounding of its
+    threshold; at that step, and at every step of a teacher-forced replay, the CUDA sampler must pick exactly what the oracle's
+    sampler picks on the CUDA logits of that step - so a sampler or RNG-state bug cannot hide behind a 'near-threshold' excuse."""
+    from oracle import sampler_ref
     m, sd = make_model(SMALL)
     gold = np.load(os.path.join(GOLD, "t3_small_sampled.npz"))
     prompts = [synthetic_request(i, SMALL, n_text=12) for i in range(3)]
+    seeds = [42 + i for i in range(3)]
     eng = T3B200Engine(m, max_num_seqs=4, max_model_len=256)
-    sps = [SamplingParams(temperature=0.8, top_p=0.8, min_p=0.05, repetition_penalty=2.0, max_tokens=16, ignore_eos=True, seed=42 + i)
-           for i in range(3)]
-    outs = eng.generate([{"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}} for cond, ids in prompts], sps)
-    ks = []
-    for b, o in enumerate(outs):
-        ids = [t - SPEECH_TOKEN_OFFSET for t in o.outputs[0].token_ids]
-        ks.append(first_divergence(ids, gold["tokens"][b]))
-    record("engine_sampled_stream", {"first_divergence": ks, "steps": 16})
-    # fixed-seed sampling follows the oracle until a filter/race decision lands within rounding of its threshold
-    assert min(ks) >= 4 and sum(k == 16 for k in ks) >= 1, ks
+    sps = [SamplingParams(temperature=0.8, top_p=0.8, min_p=0.05, repetition_penalty=2.0, max_tokens=16, ignore_eos=True, seed=s) for s in seeds]
+    pd = [{"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}} for cond, ids in prompts]
+    outs = eng.generate(pd, sps)
+    streams = [[t - SPEECH_TOKEN_OFFSET for t in o.outputs[0].token_ids] for o in outs]
+    ks = [first_divergence(ids, gold["tokens"][b]) for b, ids in enumerate(streams)]
+    del eng
+    # teacher-forced replay of the ENGINE's own streams (eager launches): logits of every step + the sampler's choice
+    forced = np.array(streams, dtype=np.int32)
+    T = forced.shape[1]
+    eng = T3B200Engine(m, max_num_seqs=4, max_model_len=256, use_graphs=False)
+    st = eng.state
+    eng.install(pd, sps, reserve_steps=T + 1)
+    logits = torch.empty(T, 3, SMALL.speech_vocab, dtype=torch.float32, device=DEV)
+    toks = torch.empty(T, 3, dtype=torch.int32, device=DEV)
+    toks[0] = st.tokens[:3]
+    for t in range(1, T):
+        st.tokens[:3] = torch.as_tensor(forced[:, t - 1]).to(DEV)
+        st.history[:3, t - 1] = st.tokens[:3]
+        m.decode_step(eng.kv, st, 6, eng.hidden, ws=eng.ws, opt=eng.opt)
+        m.head_cfg_sample(eng.hidden, 6, eng.sampling, st, eng.out_tokens, advance=True, logits_out=logits[t], ws=eng.ws, opt=eng.opt)
+        toks[t] = eng.out_tokens[:3]
+    torch.cuda.synchronize()
+    lg, tk = logits.cpu().numpy(), toks.cpu().numpy().T
+    assert (tk == forced).all(), "graph replay inside generate() and the eager teacher-forced replay must sample the same tokens"
+    mism = []
+    for t in range(1, T):
+        info = []
+        ref = sampler_ref.sample_ref(lg[t], [forced[b, :t].tolist() for b in range(3)], repetition_penalty=[2.0] * 3, temperature=[0.8] * 3,
+                                     min_p=[0.05] * 3, top_p=[0.8] * 3, seeds=seeds, steps=[t] * 3, info=info)
+        for b in range(3):
+            if ref[b] != tk[b, t]:
+                mism.append((b, t, min(info[b].get("race_margin", 1.0), info[b].get("minp_margin", 1.0), info[b].get("topp_margin", 1.0))))
+    record("engine_sampled_stream", {"first_divergence_from_fixture": ks, "steps": 16, "sampler_mismatches_on_cuda_logits": mism})
+    assert all(mg <= 1e-3 for _, _, mg in mism) and len(mism) <= 1, mism
+
+
+def test_small_bucket_graph_survives_larger_batches():
+    """a CUDA graph captured for the 1-slot bucket must still be valid after a larger batch ran on the same engine
+    (the engine owns one workspace sized for its largest launch; captured graphs hold its address): generate(1 prompt),
+    generate(8), generate(1) - the last equals the first and a fresh engine's result."""
+    m, _ = make_model(SMALL)
+    prompts = [{"prompt_token_ids": ids, "multi_modal_data": {"conditionals": [cond]}}
+               for cond, ids in (synthetic_request(i, SMALL, n_text=7 + i) for i in range(8))]
+    sp = SamplingParams(temperature=0.8, top_p=0.9, min_p=0.02, repetition_penalty=2.0, max_tokens=20, ignore_eos=True, seed=7)
+    eng = T3B200Engine(m, max_num_seqs=8, max_model_len=128)
+    a = eng.generate(prompts[:1], sp)[0].outputs[0].token_ids
+    big = [o.outputs[0].token_ids for o in eng.generate(prompts, sp)]
+    b = eng.generate(prompts[:1], sp)[0].outputs[0].token_ids
+    fresh = T3B200Engine(m, max_num_seqs=8, max_model_len=128).generate(prompts[:1], sp)[0].outputs[0].token_ids
+    assert a == b == fresh == big[0]
 
 
 def test_stop_token_ends_request_and_frees_blocks():

@@ -132,10 +132,31 @@ def test_replicas_world_size_2_gloo(tmp_path):
 
 
 def test_golden_greedy_stream_reproduces_from_oracle():
-    from helpers import GOLD
-    path = os.path.join(GOLD, "t3_small_greedy.npz")
-    g = np.load(path, allow_pickle=False)
-    assert "tokens" in g.files and g["tokens"].ndim == 2 and g["tokens"].min() >= 0 and g["tokens"].max() < 8194
+    """Re-run the oracle (2-layer model, 3 requests, 16 greedy steps) and require the committed fixture: teacher-forced with the
+    fixture's tokens, its top-8 logits to 2 bf16 ulps (this host's BLAS may order fp32 sums differently from the build container's) and
+    its tokens wherever its own top-2 margin exceeds the bf16 noise floor; the sampled fixture the same way."""
+    import torch
+    from helpers import GOLD, oracle_generate
+    from chatterbox_vllm2_b200 import T3Dims
+    from chatterbox_vllm2_b200.synthetic import synthetic_checkpoint, synthetic_request
+    from oracle.t3_ref import T3Oracle
+    g = np.load(os.path.join(GOLD, "t3_small_greedy.npz"), allow_pickle=False)
+    small = T3Dims().small(n_layers=2, max_pos=512)
+    sd = synthetic_checkpoint(small)
+    prompts = [synthetic_request(i, small, n_text=12) for i in range(3)]
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    ref = oracle_generate(T3Oracle(sd, small, mode="bf16"), prompts, 16, rho=2.0, forced=g["tokens"])
+    at = np.take_along_axis(ref["logits"], g["top_idx"].astype(np.int64), -1)
+    # the oracle rounds to bf16 where the kernels round, so another host's fp32 summation order shows up as whole bf16 ulps
+    # (0.03125 at |l| in [4, 8)): at most 2 ulps, and most values identical
+    assert np.abs(at - g["top_val"]).max() <= 0.0625 and (at == g["top_val"]).mean() > 0.5
+    bad = [(b, t) for b in range(3) for t in range(16) if ref["tokens"][b, t] != g["tokens"][b, t] and g["margins"][t, b] > 0.125]
+    assert not bad, bad
+    assert (ref["tokens"] == g["tokens"]).mean() > 0.9
+    s = np.load(os.path.join(GOLD, "t3_small_sampled.npz"), allow_pickle=False)
+    rs = oracle_generate(T3Oracle(sd, small, mode="bf16"), prompts, 16, rho=2.0, temperature=0.8, min_p=0.05, top_p=0.8,
+                         seeds=[42, 43, 44], forced=s["tokens"])
+    assert (rs["tokens"] == s["tokens"]).mean() > 0.9
 
 
 def test_bench_reference_arm_contract():

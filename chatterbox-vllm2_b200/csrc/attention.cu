@@ -53,6 +53,19 @@ struct AttnArgs {
     PfArgs pf;                      // weights of a later launch to pull into L2 (hint)
 };
 
+// Profiling build only (-DT3B_ATTN_TRACE, scripts/probe/attn_trace.py): lane 0 of warp 0 of every CTA stamps %globaltimer at the
+// phases of the kernel into g_attn_trace[block][8].  Not compiled into the product library.
+#ifdef T3B_ATTN_TRACE
+__device__ unsigned long long* g_attn_trace = nullptr;
+extern "C" int32_t t3b_debug_set_attn_trace(unsigned long long* buf) {
+    return cudaMemcpyToSymbol(g_attn_trace, &buf, sizeof(buf)) == cudaSuccess ? 0 : -4;
+}
+#define AT_STAMP(i) do { if (g_attn_trace && threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
+                         g_attn_trace[(size_t)blockIdx.x * 8 + (i)] = t_; } } while (0)
+#else
+#define AT_STAMP(i) do { } while (0)
+#endif
+
 template <int KVT> struct KvFmt;
 template <> struct KvFmt<0> { static constexpr int SLICE = 2048; };                 // 16 x 64 bf16
 template <> struct KvFmt<1> { static constexpr int SLICE = 1024 + 64; };            // 16 x 64 e4m3 | 16 fp32 scales
@@ -178,6 +191,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
     int* s_pos = s_row + AT_CAP;                                                           // [AT_CAP] RoPE position (FUSED)
 
     pdl_launch_dependents();       // the next kernel's launch overlaps this one (it waits before reading)
+    AT_STAMP(0);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int team = warp / W, wt = warp - team * W;      // team = the warps that share one item
     const int t4 = lane >> 3, c = lane & 7;
@@ -235,11 +249,34 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
     // FUSED (decode): everything the ring reads was written by earlier steps -> the first fill goes out before the dependency
     // wait.  Otherwise (prefill) the K/V of this very pass were written by the kernel right in front of this one.
     if (!FUSED) pdl_wait();
+    AT_STAMP(1);
+    // First ring fill in ONE round trip: lane 4 j + c takes copy c (K0 | K1 | V0 | V1) of the warp's j-th pair of its first item,
+    // loads that page's block id itself and issues its copy - one block-table latency and one bulk-copy issue for the whole ring
+    // instead of S times (load ids -> issue -> load ids ...): 2.0 -> 0.7 us before the first byte is requested (r2l trace).
+    while (pk < n_my && pp >= ((s_nc[mb + pk] + 31) >> 5)) { ++pk; pp = wt; }
+    if (pk < n_my) {
+        const int nc0 = s_nc[mb + pk], npg0 = (nc0 + 15) >> 4, np0 = (nc0 + 31) >> 5;
+        const int cnt = min(S, (np0 - pp + W - 1) / W);
+        const int j = lane >> 2, which = lane & 3;
+        const int pr = pp + j * W, page = 2 * pr + (which & 1);
+        const bool act = j < cnt && page < npg0;
+        int blk = 0;
+        if (act) blk = ld_act(a.block_tables + (size_t)s_row[mb + pk] * a.max_blocks + page);
+        if (j < cnt && which == 0) mbar_expect_tx(&my_full[j], (2 * pr + 1 < npg0 ? 4u : 2u) * SLICE);
+        if (act) {
+            const int h = (gt + pk * NT) % H;
+            bulk_load_1d_hint(my_ring + (size_t)j * PAIR + which * SLICE, ((which & 2) ? a.v_pool : a.k_pool) + ((size_t)blk * H + h) * SLICE, SLICE,
+                              &my_full[j], kv_policy);
+        }
+        pn = cnt; pp += cnt * W;
+    }
     settle();
 #pragma unroll 1
-    for (int i = 0; i < S; ++i) produce();
+    for (int i = pn; i < S; ++i) produce();
+    AT_STAMP(2);
     if (warp == AT_NW - 1 && lane == 1) pf_slice(a.pf, (int)blockIdx.x, G);      // behind the first ring fill
     if (FUSED) pdl_wait();
+    AT_STAMP(3);
     const float kScale = 0.125f * 1.4426950408889634f;   // head_dim^-0.5 * log2(e)
     const int hidden = H * 64;
     // head of an item: q (and k, v of the new token) with the RoPE table rows, fetched one item ahead
@@ -335,6 +372,8 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
         for (int pr = wt; pr < np; pr += W) {
             const int slot = cn % S;
             mbar_wait(&my_full[slot], (uint32_t)((cn / S) & 1));
+            if (cn == 0) AT_STAMP(4);
+            if (cn == S) AT_STAMP(5);
             const unsigned char* sl = my_ring + (size_t)slot * PAIR;
             const bool two = pr * 2 + 1 < n_pages;         // warp-uniform
             attn_pair<KVT>(sl, sl + SLICE, sl + 2 * SLICE, sl + 3 * SLICE, two, pr * 32, nc, qf, lane, m, l, acc);
@@ -342,6 +381,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
             __syncwarp();                                   // every lane is done reading the slot
             produce();                                      // refill it with the pair S ahead
         }
+        if (k == 0) AT_STAMP(6);
         // fold the four token groups (t4) of the warp, then the row sum
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
@@ -385,6 +425,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
             }
         }
     }
+    AT_STAMP(7);
 }
 
 // ------------------------------------------------------------------ prefill (causal) attention
@@ -507,10 +548,9 @@ static cudaError_t launch_ring(const AttnArgs& a, cudaStream_t s) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const int slots = t3b_num_sms() * AT_CTAS;            // resident CTAs
-    const int teams = a.n_items;                          // one team per item until the grid is full
-    int grid = (teams + T - 1) / T;
-    if (grid > slots) grid = slots;
-    if (teams < slots) grid = teams;                      // few items: one team per CTA slot rather than T teams on a few SMs
+    // teams are dealt CTA-first (team j of every CTA before team j + 1 of any), so every SM pulls its share of the bytes:
+    // one CTA per SM as soon as there are that many items (1024 items -> 148 CTAs with 6-7 busy warps, not 128 full ones)
+    int grid = a.n_items < slots ? a.n_items : slots;
     const int need = (a.n_items + AT_CAP - 1) / AT_CAP;
     if (grid < need) grid = need;
     return t3b_launch(kern, dim3((unsigned)grid), dim3(AT_NW * 32), smem, s, a);

@@ -431,10 +431,12 @@ def step_bytes(m, eng, B, mean_ctx):
 def sweep_point(tok, dev, sd, rank, K, W, pk, local):
     """One extra measurement of the metric's other batch points / BASELINE.json configs:
     "N" = N bf16 requests, greedy (300-token job); "awqN" = configs[2] (AWQ W4A16, N requests, min-p / top-p sampling, rep. penalty);
-    "cfg4" = configs[3] (bf16, 128 requests, 1000-token job: contexts 100..1098); "fp8N" = N bf16-weight requests on an FP8 KV pool."""
+    "cfg4" = configs[3] (bf16, 128 requests, 1000-token job: contexts 100..1098); "fp8N" = N bf16-weight requests on an FP8 KV pool;
+    "awqfp8N" = configs[2] on an FP8 KV pool (the KV-traffic reducer of SURVEY.md 8(f) rank 2 where K/V is 98 % of the bytes)."""
     import torch
-    awq, fp8, cfg4 = tok.startswith("awq"), tok.startswith("fp8"), tok == "cfg4"
-    b = 128 if cfg4 else int(tok[3:] if (awq or fp8) else tok)
+    import re
+    awq, fp8, cfg4 = "awq" in tok, "fp8" in tok, tok == "cfg4"
+    b = 128 if cfg4 else int(re.sub(r"[a-z]", "", tok.replace("fp8", "")))
     gen_len = 1000 if cfg4 else GEN_LEN
     m2, eng, _ = build_engine(b, dev, sd, quant="awq" if awq else None, kv_dtype="fp8" if fp8 else "bf16",
                               kv_tokens_per_row=P_PROMPT + gen_len + 40)

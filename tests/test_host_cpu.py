@@ -169,3 +169,40 @@ def test_bench_reference_arm_contract():
     for k in ("impl", "metric", "value", "unit", "n_gpus", "steps", "ms_per_step", "cpu_baseline", "e2e", "config"):
         assert k in line
     assert line["impl"] == "reference" and line["cpu_baseline"]["kind"] == "port" and line["value"] > 0
+
+
+def test_dispatcher_least_outstanding_kv_tokens():
+    """whole requests go to the replica with the least outstanding KV tokens; static and online forms."""
+    from chatterbox_vllm2_b200.dispatch import ReplicaDispatcher, assign_requests, kv_token_cost, kv_traffic_cost
+    import random
+    rng = random.Random(7)
+    lens = [rng.randint(100, 1000) for _ in range(4096)]            # BASELINE.json configs[4]
+    costs = [kv_traffic_cost(99, n) for n in lens]
+    for world in (1, 2, 4, 8):
+        shares = assign_requests(costs, world)
+        assert sorted(i for s in shares for i in s) == list(range(4096))             # a partition, nothing lost or duplicated
+        loads = [sum(costs[i] for i in s) for s in shares]
+        assert max(loads) - min(loads) <= max(costs)                                 # greedy bound: within one request of each other
+        assert all(s == sorted(s) for s in shares)                                   # arrival order kept inside a replica
+    assert kv_token_cost(99, 300) == 2 * 399 and kv_traffic_cost(99, 2) == 2 * (2 * 99 + 3)
+    d = ReplicaDispatcher(3)
+    where = [d.submit(i, 99, n) for i, n in enumerate([1000, 100, 100, 100, 100])]
+    assert where[:3] == [0, 1, 2] and where[3] in (1, 2) and where[4] in (1, 2) and where[3] != where[4]
+    d.complete(0)
+    assert d.outstanding()[0] == 0 and d.submit(9, 99, 10) == 0                      # the drained replica takes the next request
+    probed = ReplicaDispatcher(2, probe=lambda r: [500, 10][r])                      # true loads reported by the engines win
+    assert probed.submit(0, 99, 100) == 1
+
+
+def test_vllm_plugin_registers_architecture_and_s3gen_filter():
+    """models/t3/__init__.py:5 registers "ChatterboxT3"; the shim registers the same architecture name with the installed vLLM (lazy
+    form: no CUDA needed) and answers to the 0.10 and the 0.22 hook names.  tts.py:492-514: the S3Gen hand-off filter."""
+    from chatterbox_vllm2_b200 import SPEECH_TOKEN_OFFSET, vllm_plugin
+    from vllm import ModelRegistry
+    vllm_plugin.register()
+    assert "ChatterboxT3" in ModelRegistry.get_supported_archs()
+    for hook in ("load_weights", "get_multimodal_embeddings", "embed_multimodal", "get_input_embeddings", "embed_input_ids", "forward",
+                 "compute_logits", "get_language_model"):
+        assert callable(getattr(vllm_plugin.T3B200ForVllm, hook))
+    ids = [SPEECH_TOKEN_OFFSET + t for t in (0, 5, 6560, 6561, 6562, 8193)] + [17, 2499]
+    assert vllm_plugin.speech_tokens_for_s3gen(ids) == [0, 5, 6560]

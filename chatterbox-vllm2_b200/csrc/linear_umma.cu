@@ -536,8 +536,11 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
         T3B_CHECK_ARG(((awq->flags & T3B_LIN_GATE_UP_INTERLEAVED) != 0) == (epi == EPI_SILU),
                       "umma: AWQ gate_up weights repacked with gate_up_interleave must run the SiLU epilogue (and only they may)");
     }
-    // cluster split-K keeps a [Rp][128] fp32 buffer per CTA: 128-row chunks there, 256 otherwise
-    int max_chunk = (!legacy && n_split > 1) ? 128 : 256;
+    // cluster split-K keeps a [Rp][128] fp32 buffer per CTA: 128-row chunks there, 256 otherwise.  Decode batches of 129..512 rows
+    // without split-K (gate_up: 64 tiles) also run 128-row chunks: twice the blocks (128 of 148 SMs instead of 64) and a 5-deep ring
+    // instead of 2 x 48 KB stages - 256 rows: 3.59 -> 3.20 ms/step (profiles/r2_notes.md r2p).  Prefill passes (thousands of rows)
+    // keep 256-row chunks: they have blocks to spare and would only re-read the weights more often.
+    int max_chunk = (!legacy && n_split > 1) ? 128 : (rows <= 512 ? 128 : 256);
     if (row_chunk_req > 0) {
         T3B_CHECK_ARG(row_chunk_req % 16 == 0 && row_chunk_req <= max_chunk, "umma: row_chunk %d must be a multiple of 16 <= %d", row_chunk_req, max_chunk);
         max_chunk = row_chunk_req;

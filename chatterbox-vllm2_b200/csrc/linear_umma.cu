@@ -474,16 +474,22 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t o
 
 int t3b_umma_available() { return get_encode_fn() != nullptr; }
 
-// Split-K factor.  Cluster mode (DSMEM reduce): a power of two <= 8 that divides the k-blocks, chosen to
-// put ~one CTA on every SM.  Depends on (N, K, row chunks) only, never on the row count inside a chunk,
-// so a request's arithmetic does not change with the batch it runs in.
+// Split-K factor (cluster mode, DSMEM reduce): the largest power of two <= 8 that divides the k-blocks and whose grid still
+// co-schedules in one wave.  The limits are measured (scripts/probe/split_sweep.py, profiles/r2t_split_sweep.log): clusters of 8
+// need 8 free SMs inside one GPC, so ~13 of them run at once (o / down at 256 rows: 128 blocks as 16 clusters of 8 took 11.2 /
+// 15.4 us, 64 blocks as 16 clusters of 4 take 5.6 / 9.9); the exchange of a 128-row partial tile also costs more per peer than
+// the k-blocks it saves.  Depends on (N, K, 128-row chunks) only, never on the row count inside a chunk, so a request's
+// arithmetic does not change with the batch it runs in.
 int t3b_umma_pick_split(int rows, int N, int K) {
     const int tiles = (N + UM_M - 1) / UM_M * ((rows + 127) / 128);
     const int kb = K / UM_K;
-    const int sms = t3b_num_sms();
-    int s = 1;
-    while (s < 8 && tiles * s * 2 <= sms + sms / 4 && kb % (s * 2) == 0 && kb / (s * 2) >= 2) s *= 2;
-    return s;
+    static const int cand[3] = {8, 4, 2};
+    static const int limit[3] = {104, 128, 160};        // blocks of the whole grid at that cluster size
+    for (int i = 0; i < 3; ++i) {
+        const int s = cand[i];
+        if (kb % s == 0 && kb / s >= 2 && tiles * s <= limit[i]) return s;
+    }
+    return 1;
 }
 
 template <int WSRC>
@@ -536,11 +542,15 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
         T3B_CHECK_ARG(((awq->flags & T3B_LIN_GATE_UP_INTERLEAVED) != 0) == (epi == EPI_SILU),
                       "umma: AWQ gate_up weights repacked with gate_up_interleave must run the SiLU epilogue (and only they may)");
     }
-    // cluster split-K keeps a [Rp][128] fp32 buffer per CTA: 128-row chunks there, 256 otherwise.  Decode batches of 129..512 rows
-    // without split-K (gate_up: 64 tiles) also run 128-row chunks: twice the blocks (128 of 148 SMs instead of 64) and a 5-deep ring
-    // instead of 2 x 48 KB stages - 256 rows: 3.59 -> 3.20 ms/step (profiles/r2_notes.md r2p).  Prefill passes (thousands of rows)
-    // keep 256-row chunks: they have blocks to spare and would only re-read the weights more often.
-    int max_chunk = (!legacy && n_split > 1) ? 128 : (rows <= 512 ? 128 : 256);
+    // Rows per block.  Cluster split-K keeps a [Rp][128] fp32 buffer per CTA: 128-row chunks.  Without split-K (measured table,
+    // scripts/probe/split_sweep.py, profiles/r2u_split_sweep.log): decode batches of 129..1024 rows run 128-row chunks - twice the
+    // blocks and a deeper ring than 256-row chunks (gate_up at 256 rows: 25 -> 14 us; qkv at 1024 rows: 15.9 -> 10.6) - except the
+    // widest projection above 512 rows (gate_up at 1024 rows: 26 us with 256-row chunks, 31 with 128); prefill passes (thousands of
+    // rows) keep 256-row chunks: they have blocks to spare and would only re-read the weights more often.
+    const int n_tiles = (N + UM_M - 1) / UM_M;
+    // (bf16 only: every extra row chunk of an AWQ tile repeats its dequantisation - 512 rows: 5.02 ms/step with 128-row chunks, 4.91 with 256)
+    const bool mid = !legacy && !awq && n_split == 1 && rows > 128 && rows <= 1024 && !(n_tiles >= 64 && rows > 512);
+    int max_chunk = (!legacy && n_split > 1) ? 128 : (mid ? 128 : 256);
     if (row_chunk_req > 0) {
         T3B_CHECK_ARG(row_chunk_req % 16 == 0 && row_chunk_req <= max_chunk, "umma: row_chunk %d must be a multiple of 16 <= %d", row_chunk_req, max_chunk);
         max_chunk = row_chunk_req;
@@ -571,6 +581,9 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     // prefill shapes (256-row chunks, no split-K): a 48 KB stage x 4 leaves one block per SM, so the long epilogue (256 TMEM
     // columns through the exchange buffer) never overlaps another block's main loop; 2 stages -> two blocks per SM
     if (Rp > 128 && stages > 2 && stages_cap <= 0) stages = 2;
+    // 128-row chunks without split-K and more blocks than SMs: a 3-deep ring (96 KB) lets two blocks share an SM, so one block's
+    // epilogue runs under the other's main loop and the grid is one wave (gate_up at 512 rows: 27.8 -> 15.6 us)
+    if (mid && stages_cap <= 0 && n_tiles * chunks > t3b_num_sms() && stages > 3) stages = 3;
     if (stages < 2) stages = 2;
     p.stages = stages;
     CUtensorMap tw, tx;

@@ -99,7 +99,8 @@ def shard_requests(n_requests: int, world_size: int, rank: int) -> List[int]:
 class T3B200Engine:
     def __init__(self, model: T3B200Model, max_num_seqs: int = 32, max_model_len: int = 1200,
                  kv_blocks: Optional[int] = None, check_every: int = 8, prefill_chunk_tokens: int = 8192,
-                 use_graphs: bool = True, kv_dtype: str = "bf16", share_prefix: bool = True, grow_steps: int = 32):
+                 use_graphs: bool = True, kv_dtype: str = "bf16", share_prefix: bool = True, grow_steps: int = 32,
+                 admit_batch: Optional[int] = None, admit_wait_steps: int = 16):
         self.m = model
         self.dims: T3Dims = model.dims
         self.dev = model.device
@@ -115,6 +116,11 @@ class T3B200Engine:
         self.out_tokens = torch.empty(max_num_seqs, dtype=torch.int32, device=self.dev)
         self.check_every = max(1, check_every)
         self.grow_steps = max(1, grow_steps)
+        # Admission batching: a prefill pass costs milliseconds whether it carries 1 prompt or 16, so with a queue of waiting
+        # requests freed slots are refilled in groups - when ``admit_batch`` slots are free (default max_num_seqs / 32) or
+        # ``admit_wait_steps`` steps have passed since a slot freed up - instead of one prefill per finished request.
+        self.admit_batch = max(1, max_num_seqs // 32) if admit_batch is None else max(1, admit_batch)
+        self.admit_wait_steps = max(0, admit_wait_steps)
         self.prefill_chunk = max(prefill_chunk_tokens, 2 * max_model_len)
         self.use_graphs = use_graphs
         self.share_prefix = share_prefix
@@ -386,8 +392,8 @@ class T3B200Engine:
 
     # ------------------------------------------------------------------ the caller's entry point
     def _retire(self, done: List[_Req], results: Dict[int, RequestOutput], hist_host: torch.Tensor) -> None:
-        for r in done:
-            toks = hist_host[r.slot, :r.n_gen].tolist()
+        for i, r in enumerate(done):
+            toks = hist_host[i, :r.n_gen].tolist()
             stop = r.sp.stop_token()
             stopped = stop >= 0 and stop in toks
             if stopped:
@@ -425,10 +431,13 @@ class T3B200Engine:
         waiting.reverse()
         results: Dict[int, RequestOutput] = {}
         st = self.state
+        waited = 0                                              # steps run since a slot became free with requests still waiting
         while waiting or any(s is not None for s in self.slots):
             new: List[_Req] = []
+            n_free = sum(s is None for s in self.slots)
+            admit_now = n_free == self.max_req or n_free >= min(self.admit_batch, len(waiting)) or waited >= self.admit_wait_steps
             for slot in range(self.max_req):
-                if not waiting:
+                if not waiting or not admit_now:
                     break
                 if self.slots[slot] is None:
                     r = waiting[-1]
@@ -441,6 +450,7 @@ class T3B200Engine:
                     new.append(r)
             if new:
                 self._admit(new)
+                waited = 0
             live = [r for r in self.slots if r is not None]
             if not live:
                 raise MemoryError(f"KV pool ({self.kv.num_blocks} blocks) cannot hold a single prompt of {waiting[-1].n_prompt} tokens")
@@ -451,6 +461,8 @@ class T3B200Engine:
             budget = min(min(self._limit(r) - r.n_gen for r in live), self.grow_steps)
             if may_stop:
                 budget = min(budget, self.check_every)
+            if waiting and len(live) < self.max_req:
+                budget = min(budget, max(1, self.admit_wait_steps - waited))     # come back in time to refill the free slots
             budget = max(0, budget)
             while not self._grow(live, budget):
                 # pool exhausted: preempt the youngest request (its tokens are regenerated later - sampling is keyed by
@@ -468,6 +480,8 @@ class T3B200Engine:
                 n_slots = max(r.slot for r in live) + 1
             for _ in range(budget):
                 self.step(n_slots)
+            if waiting and len(live) < self.max_req:
+                waited += budget
             if may_stop:
                 poll = torch.stack([st.hist_len[:n_slots], st.active[:n_slots].to(st.hist_len.dtype)]).cpu()    # one D2H per poll
                 hist_len, active = poll[0], poll[1]
@@ -479,5 +493,6 @@ class T3B200Engine:
                     r.n_gen += budget
                 done = [r for r in live if r.n_gen >= self._limit(r)]
             if done:
-                self._retire(done, results, st.history[:n_slots].cpu())       # one D2H for every request that finished
+                rows = torch.tensor([r.slot for r in done], device=self.dev)
+                self._retire(done, results, st.history[rows].cpu())           # one D2H, the finished requests' rows only
         return [results[i] for i in range(len(prompts))]

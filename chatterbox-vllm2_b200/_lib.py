@@ -57,7 +57,7 @@ class KV(C.Structure):              # t3b_kv_t
 class State(C.Structure):           # t3b_state_t
     _fields_ = [("tokens", vp), ("speech_pos", vp), ("rope_pos", vp), ("ctx_lens", vp), ("block_tables", vp),
                 ("max_blocks", i32), ("history", vp), ("hist_len", vp), ("hist_stride", i32), ("step", vp),
-                ("active", vp), ("stop_tokens", vp), ("max_ctx", i32)]
+                ("active", vp), ("stop_tokens", vp), ("max_ctx", i32), ("row_order", vp)]
 
 
 class Sampling(C.Structure):        # t3b_sampling_t

@@ -10,7 +10,8 @@
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
                                const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf);
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, int stages_cap, int row_chunk, PfArgs pf, cudaStream_t s);
+                               int n_split, int epi, int stages_cap, int row_chunk, PfArgs pf, int w_wait, cudaStream_t s);
+int32_t t3b_awq_dequant_launch(const t3b_linear_t* const* lins, int n_lin, void* scratch, cudaStream_t stream);
 int t3b_umma_pick_split(int rows, int N, int K);
 int t3b_umma_available();
 int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_split, const float* logits_in, int V, int n_req,
@@ -18,11 +19,12 @@ int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_s
                            cudaStream_t stream);
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
                               const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, int kv_dtype, void* out,
-                              int team_warps, PfArgs pf, cudaStream_t s);
+                              int team_warps, PfArgs pf, const int32_t* row_order, cudaStream_t s);
 int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, const int32_t* tok_idx, const int32_t* block_tables,
                               int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, int team_warps,
                               cudaStream_t s);
 
+#define AWQ_DEQUANT_MIN_ROWS 256      // from here on AWQ layers are dequantised once per layer into a bf16 scratch (vllm awq.py:276-281 does the same)
 #define GEMV_MAX_ROWS_DEFAULT 2       // measured: 4 rows run 0.87 ms/step on the tcgen05 path, 0.96 on the GEMV (profiles/r02_notes.md)
 static thread_local char g_err[512] = "";
 
@@ -61,7 +63,7 @@ namespace {
 inline size_t al(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct Workspace {
-    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *resid2;
+    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *resid2, *deq;
     size_t total;
 };
 
@@ -80,6 +82,9 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
     w.lin = take(R * D * 2);
     w.head = take(R * V * 2 + 64);
     w.resid2 = take((R < 4 ? R : 4) * D * 2);    // ping-pong residual of the small-batch path (rows <= 4)
+    // bf16 copy of ONE layer's projections for AWQ models at large row counts
+    const bool awq_big = m->layers && m->layers[0].qkv.kind == T3B_W_AWQ && rows >= AWQ_DEQUANT_MIN_ROWS;
+    w.deq = take(awq_big ? (3 * D * D + D * D + 2 * F * D + D * F) * 2 : 0);
     w.total = static_cast<size_t>(p - static_cast<char*>(base));
     return w;
 }
@@ -92,10 +97,10 @@ extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
 }
 
 struct Opt {
-    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch;
+    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch, w_wait;
 };
 static Opt resolve(const t3b_options_t* o) {
-    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0};
+    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0};
     if (o) {
         if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > 4 ? 4 : o->gemv_max_rows);
         r.gemv_norm = o->gemv_no_norm ? 0 : 1;
@@ -138,7 +143,7 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     if (!legacy && y == nullptr) T3B_FAIL(T3B_ERR_ARG, "linear: y is null (partials are only written for an explicit n_split > 1)");
     if (n_split_out) *n_split_out = n_split;
     return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, legacy ? partials : nullptr, n_split, epi, o.stages,
-                                  o.row_chunk, pf, s);
+                                  o.row_chunk, pf, o.w_wait, s);
 }
 
 extern "C" int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
@@ -188,7 +193,8 @@ struct PrefillSeqs {          // sequences of a multi-token pass (t3b_prefill_at
 // gate_up GEMM (SiLU*mul epilogue), down GEMM; at GEMV row counts the two add+norms run inside the qkv / gate_up GEMVs (5 launches).
 static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void* x0, int n_tok, const int32_t* tok_row,
                             const int32_t* tok_idx, const int32_t* rope_pos, const int32_t* block_tables, int max_blocks,
-                            const PrefillSeqs* ps, void* hidden_out, const Workspace& ws, const Opt& o, void* stream) {
+                            const PrefillSeqs* ps, void* hidden_out, const Workspace& ws, const Opt& o, void* stream,
+                            const int32_t* row_order = nullptr) {
     cudaStream_t s = t3b_stream(stream);
     const int D = m->hidden, H = m->n_heads;
     int32_t rc;
@@ -196,8 +202,13 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     // request's prefill is bit-identical no matter which other requests are admitted with it.  Decode steps pick shapes by row
     // count (identical within a slot bucket).
     const bool prefill = tok_row != nullptr;
+    // AWQ models at >= 256 rows: the bf16 kernels read a scratch the dequant launch of the same layer wrote, so they must not
+    // request weights before their dependency wait (every other weight is constant and IS requested before it)
+    const bool deq = n_tok >= AWQ_DEQUANT_MIN_ROWS && m->layers[0].qkv.kind == T3B_W_AWQ;
+    Opt ol = o;
+    ol.w_wait = deq ? 1 : 0;
     auto lin = [&](const void* x, const t3b_linear_t* w, void* y, int epi, PfArgs pf) -> int32_t {
-        return linear_any(x, w, n_tok, y, nullptr, prefill ? 1 : 0, nullptr, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, epi, o, pf, s);
+        return linear_any(x, w, n_tok, y, nullptr, prefill ? 1 : 0, nullptr, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, epi, ol, pf, s);
     };
     // Decode steps are HBM-bound and every kernel of the chain is short: each launch pulls the weights of the projection two
     // launches ahead into L2 (qkv -> o, attention -> gate_up, o -> down, gate_up -> the next layer's qkv / the speech head), so
@@ -223,7 +234,7 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
             if (rc) return rc;
             { char* t = rcur; rcur = roth; roth = t; }
             rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
-                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), s);
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), row_order, s);
             if (rc) return rc;
             rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE, pfw(&L->down));
             if (rc) return rc;
@@ -238,9 +249,24 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
         return t3b_add_rmsnorm(xin, nullptr, 1, rcur, m->final_norm, hidden_out, n_tok, D, m->rms_eps, 1, stream);
     }
     const void* prev = x0;
+    t3b_layer_t tmp = {};
     for (int li = 0; li < m->n_layers; ++li) {
         const t3b_layer_t* L = &m->layers[li];
         T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
+        if (deq) {
+            // one launch dequantises the layer's four projections into the scratch; the bf16 kernels run on the copy
+            const t3b_linear_t* lins[4] = {&L->qkv, &L->o, &L->gate_up, &L->down};
+            rc = t3b_awq_dequant_launch(lins, 4, ws.deq, s);
+            if (rc) return rc;
+            tmp = *L;
+            char* p = ws.deq;
+            t3b_linear_t* dst[4] = {&tmp.qkv, &tmp.o, &tmp.gate_up, &tmp.down};
+            for (int j = 0; j < 4; ++j) {
+                dst[j]->kind = T3B_W_BF16; dst[j]->w = p; dst[j]->scales = nullptr; dst[j]->zeros = nullptr; dst[j]->flags = 0;
+                p += (size_t)dst[j]->n * dst[j]->k * 2;
+            }
+            L = &tmp;
+        }
         rc = t3b_add_rmsnorm(prev, nullptr, 1, ws.resid, L->ln1, ws.normed, n_tok, D, m->rms_eps, li > 0, stream);
         if (rc) return rc;
         rc = lin(ws.normed, &L->qkv, ws.qkv, T3B_EPI_NONE, pfw(&L->o));
@@ -256,7 +282,7 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
                 rc = t3b_paged_attn_launch(ws.q, n_tok, tok_row, tok_idx, block_tables, max_blocks, kpool(li), vpool(li), H, kv->dtype, ws.attn, 1, s);   // one warp per (token, head): fixed, so a prompt's result does not depend on its batch
         } else {
             rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
-                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), s);
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), row_order, s);
         }
         if (rc) return rc;
         rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE, pfw(&L->down));
@@ -316,7 +342,7 @@ extern "C" int32_t t3b_decode_step(const t3b_model_t* m, const t3b_kv_t* kv, con
         x0 = ws.x_emb;
     }
     return forward_impl(m, kv, x0, rows, nullptr, st->ctx_lens, st->rope_pos, st->block_tables, st->max_blocks, nullptr, hidden_out, ws,
-                        resolve(opt), stream);
+                        resolve(opt), stream, st->row_order);
 }
 
 extern "C" int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden, int32_t rows, const t3b_sampling_t* sp,

@@ -38,6 +38,7 @@
 
 struct AttnArgs {
     const bf16* q;                  // FUSED: qkv bf16 [n_tok, 3 * hidden]; else q bf16 [n_tok, hidden] (already rotated)
+    const int32_t* row_order;       // deal order of the tokens (NULL = identity): item i = (token row_order[i / H], head i % H)
     const int32_t* tok_row;         // KV row of token j (NULL = j)
     const int32_t* tok_idx;         // index of token j in its row: FUSED = cached tokens before it; else it attends 0..idx
     const int32_t* rope_pos;
@@ -189,6 +190,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
     int* s_nc = reinterpret_cast<int*>(part_ml + 2 * AT_NW * 2);                           // [AT_CAP] cached tokens to stream
     int* s_row = s_nc + AT_CAP;                                                            // [AT_CAP] KV row
     int* s_pos = s_row + AT_CAP;                                                           // [AT_CAP] RoPE position (FUSED)
+    int* s_tok = s_pos + AT_CAP;                                                           // [AT_CAP] token (= row of the step) of the item
 
     pdl_launch_dependents();       // the next kernel's launch overlaps this one (it waits before reading)
     AT_STAMP(0);
@@ -201,7 +203,9 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
     const int n_my = gt < a.n_items ? (a.n_items - gt + NT - 1) / NT : 0;
     const int mb = team * CAP;                            // this team's slice of the metadata arrays
     for (int k = wt * 32 + lane; k < n_my; k += W * 32) {
-        const int t = (gt + k * NT) / H;
+        const int rank = (gt + k * NT) / H;
+        const int t = a.row_order ? ld_act(a.row_order + rank) : rank;
+        s_tok[mb + k] = t;
         const int idx = ld_act(a.tok_idx + t);
         s_nc[mb + k] = FUSED ? idx : idx + 1;
         s_row[mb + k] = a.tok_row ? ld_act(a.tok_row + t) : t;
@@ -285,7 +289,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
     auto load_head = [&](int k) {
         hq = hk = hv = hcs = hsn = make_uint4(0, 0, 0, 0);
         if (k >= n_my) return;
-        const int item = gt + k * NT, t = item / H, h = item - t * H;
+        const int item = gt + k * NT, h = item % H, t = s_tok[mb + k];
         if (FUSED) {
             const bf16* src = a.q + (size_t)t * 3 * hidden + h * 64 + c * 8;
             hq = ld_act(reinterpret_cast<const uint4*>(src));
@@ -304,7 +308,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
     int cn = 0;
 #pragma unroll 1
     for (int k = 0; k < n_my; ++k) {
-        const int item = gt + k * NT, t = item / H, h = item - t * H;
+        const int item = gt + k * NT, h = item % H, t = s_tok[mb + k];
         const int nc = s_nc[mb + k], np = (nc + 31) >> 5, n_pages = (nc + 15) >> 4;
         float qf[8], m = -INFINITY, l = 0.f, acc[8];
 #pragma unroll
@@ -543,7 +547,7 @@ template <bool FUSED, int W, int S, int KVT>
 static cudaError_t launch_ring(const AttnArgs& a, cudaStream_t s) {
     constexpr int PAIR = 4 * KvFmt<KVT>::SLICE;
     constexpr int T = AT_NW / W;
-    const size_t smem = (size_t)AT_NW * S * PAIR + AT_NW * S * 8 + 2 * AT_NW * 66 * 4 + 3 * AT_CAP * 4;
+    const size_t smem = (size_t)AT_NW * S * PAIR + AT_NW * S * 8 + 2 * AT_NW * 66 * 4 + 4 * AT_CAP * 4;
     auto kern = attn_ring_kernel<FUSED, W, S, KVT>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -589,9 +593,10 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
 // decode step: one token per KV row (token j <-> row j)
 int32_t t3b_attn_fused_launch(const void* qkv, int n_tok, const int32_t* tok_idx, const int32_t* rope_pos, const void* rope_cos_sin, int max_pos,
                               const int32_t* block_tables, int max_blocks, void* k_pool, void* v_pool, int n_heads, int kv_dtype, void* out,
-                              int team_warps, PfArgs pf, cudaStream_t s) {
+                              int team_warps, PfArgs pf, const int32_t* row_order, cudaStream_t s) {
     AttnArgs a = {};
     a.pf = pf;
+    a.row_order = row_order;
     a.q = (const bf16*)qkv; a.tok_idx = tok_idx; a.rope_pos = rope_pos; a.cos_sin = (const bf16*)rope_cos_sin; a.max_pos = max_pos;
     a.block_tables = block_tables; a.max_blocks = max_blocks; a.k_pool = (unsigned char*)k_pool; a.v_pool = (unsigned char*)v_pool;
     a.n_heads = n_heads; a.out = (bf16*)out; a.n_items = n_tok * n_heads;
@@ -607,7 +612,7 @@ extern "C" int32_t t3b_attn_decode_fused(const void* qkv, int32_t n_tok, const i
     T3B_CHECK_ALIGN(qkv); T3B_CHECK_ALIGN(rope_cos_sin); T3B_CHECK_ALIGN(k_pool); T3B_CHECK_ALIGN(v_pool); T3B_CHECK_ALIGN(out);
     if (n_tok == 0) return T3B_OK;
     return t3b_attn_fused_launch(qkv, n_tok, tok_idx, rope_pos, rope_cos_sin, max_pos, block_tables, max_blocks, k_pool, v_pool, n_heads,
-                                 kv_dtype, out, opt ? opt->attn_team_warps : 0, pf_none(), t3b_stream(stream));
+                                 kv_dtype, out, opt ? opt->attn_team_warps : 0, pf_none(), nullptr, t3b_stream(stream));
 }
 
 extern "C" int32_t t3b_paged_attn_decode(const void* q, int32_t n_tok, const int32_t* tok_row, const int32_t* tok_idx,

@@ -60,6 +60,7 @@ struct UmmaParams {
     const bf16* scales;      // bf16 [K/128, N]
     const unsigned char* zeros;   // u8 [K/128, N]
     PfArgs pf;               // weights of a later launch to pull into L2 (hint)
+    int w_wait;              // 1 = the weights were written by an earlier kernel of the chain (AWQ scratch): no loads before the wait
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
@@ -174,6 +175,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     // copy instruction costs the issuing THREAD several hundred cycles (scripts/probe/bulk_bw.cu), so lane i of warp 0 issues the
     // loads of stage i: one warp instruction for the whole ring instead of a serial loop.
     if (warp == 0 && lane < pre) {
+        if (p.w_wait) pdl_wait();
         mbar_expect_tx(&full_bar[lane], tx);
         load_w(lane, lane);
     }
@@ -430,6 +432,80 @@ __global__ void awq_repack_kernel(const int32_t* __restrict__ qweight, const int
     }
 }
 
+// ------------------------------------------------------------------ AWQ -> bf16 for large batches
+// Upstream runs dequantise-then-GEMM at >= 256 tokens (vllm awq.py:276-281).  Same here: from 256 rows on, every extra 128-row
+// chunk of the dequant-fused kernel repeats the dequantisation of its weight tile, so t3b_decode_step / t3b_forward_tokens
+// dequantise a layer's four projections ONCE into a bf16 scratch (nn.Linear layout, L2-resident for the GEMMs that follow) and
+// run the bf16 kernels.  The arithmetic is the fused kernel's: bf16_rn((q - z) * s) through the 0x4300 magic.
+struct AwqDeqJob {
+    const uint32_t* qw;          // repacked nibbles [N/128][K/64][2][128][4 words]
+    const unsigned char* zeros;  // u8 [K/128, N]
+    const bf16* scales;          // bf16 [K/128, N]
+    bf16* out;                   // bf16 [N, K]
+    int N, K, gate_up;
+    unsigned first_word;         // prefix sum of N * K / 8 over the jobs
+};
+struct AwqDeqArgs {
+    AwqDeqJob job[4];
+    unsigned total_words;
+};
+
+__global__ void __launch_bounds__(256) awq_dequant_kernel(const AwqDeqArgs a) {
+    pdl_launch_dependents();
+    pdl_wait();                      // the scratch may still be read by the previous layer's GEMMs
+    for (unsigned gi = blockIdx.x * blockDim.x + threadIdx.x; gi < a.total_words; gi += gridDim.x * blockDim.x) {
+        int j = 0;
+#pragma unroll
+        for (int t = 1; t < 4; ++t) if (gi >= a.job[t].first_word) j = t;
+        const AwqDeqJob& jb = a.job[j];
+        const unsigned i = gi - jb.first_word;
+        const int w = (int)(i & 3), row = (int)((i >> 2) & 127), half = (int)((i >> 9) & 1);
+        const unsigned blk = i >> 10;
+        const int kbs = jb.K / 64;
+        const int kb = (int)(blk % (unsigned)kbs), tile = (int)(blk / (unsigned)kbs);
+        const int n = jb.gate_up ? (row < 64 ? tile * 64 + row : jb.N / 2 + tile * 64 + (row - 64)) : tile * 128 + row;
+        const int k0 = kb * 64 + half * 32 + w * 8;
+        const int g = k0 >> 7;
+        const __nv_bfloat162 s2 = __bfloat162bfloat162(jb.scales[(size_t)g * jb.N + n]);
+        const __nv_bfloat162 zb2 = __float2bfloat162_rn(128.f + (float)jb.zeros[(size_t)g * jb.N + n]);
+        const uint32_t word = __ldg(jb.qw + i);
+        uint32_t o[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t t = ((word >> (4 * q)) & 0x000F000Fu) | 0x43004300u;        // bf16x2 (128 + q[2q], 128 + q[2q+1])
+            __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&t);
+            v = __hmul2(__hsub2(v, zb2), s2);
+            o[q] = *reinterpret_cast<uint32_t*>(&v);
+        }
+        *reinterpret_cast<uint4*>(jb.out + (size_t)n * jb.K + k0) = make_uint4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// dequantise up to 4 AWQ projections (t3b_linear_t, kind T3B_W_AWQ) into consecutive bf16 [N, K] matrices starting at `scratch`
+int32_t t3b_awq_dequant_launch(const t3b_linear_t* const* lins, int n_lin, void* scratch, cudaStream_t stream) {
+    T3B_CHECK_ARG(n_lin >= 1 && n_lin <= 4 && scratch, "awq dequant: bad arguments");
+    AwqDeqArgs a = {};
+    unsigned words = 0;
+    char* out = static_cast<char*>(scratch);
+    for (int i = 0; i < 4; ++i) {
+        const t3b_linear_t* l = lins[i < n_lin ? i : n_lin - 1];
+        AwqDeqJob& j = a.job[i];
+        j.first_word = i < n_lin ? words : 0xffffffffu;
+        if (i >= n_lin) continue;
+        T3B_CHECK_ARG(l->kind == T3B_W_AWQ && l->w && l->scales && l->zeros, "awq dequant: projection %d is not AWQ", i);
+        j.qw = (const uint32_t*)l->w; j.zeros = (const unsigned char*)l->zeros; j.scales = (const bf16*)l->scales;
+        j.out = (bf16*)out; j.N = l->n; j.K = l->k; j.gate_up = (l->flags & T3B_LIN_GATE_UP_INTERLEAVED) ? 1 : 0;
+        words += (unsigned)((size_t)l->n * l->k / 8);
+        out += (size_t)l->n * l->k * 2;
+    }
+    a.total_words = words;
+    int blocks = (int)((words + 255) / 256);
+    const int cap = t3b_num_sms() * 16;
+    if (blocks > cap) blocks = cap;
+    T3B_CUDA(t3b_launch(awq_dequant_kernel, dim3((unsigned)blocks), dim3(256), 0, stream, a));
+    return T3B_OK;
+}
+
 extern "C" int32_t t3b_repack_weights_awq(const int32_t* qweight, const int32_t* qzeros, const void* scales_fp16, int32_t n, int32_t k,
                                           int32_t gate_up_interleave, void* w_out, void* zeros_out, void* scales_out, void* stream) {
     T3B_CHECK_ARG(qweight && qzeros && scales_fp16 && w_out && zeros_out && scales_out, "t3b_repack_weights_awq: null pointer");
@@ -524,7 +600,7 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
 // epi: EPI_STORE / EPI_SILU (bf16 output only).  awq == NULL: bf16 weights `w` [N, K].
 // stages_cap: ring depth cap (0 = 5); row_chunk_req: rows per thread block (0 = 128 with cluster split-K, 256 without).
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, int stages_cap, int row_chunk_req, PfArgs pf, cudaStream_t stream) {
+                               int n_split, int epi, int stages_cap, int row_chunk_req, PfArgs pf, int w_wait, cudaStream_t stream) {
     T3B_CHECK_SHAPE(K % UM_K == 0 && K >= UM_K, "umma: K %d must be a multiple of 64", K);
     T3B_CHECK_SHAPE(rows >= 1, "umma: rows %d", rows);
     const int kb_total = K / UM_K;
@@ -564,6 +640,7 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     p.partials = legacy ? partials : nullptr;
     p.rows = rows; p.N = N; p.kb_total = kb_total; p.n_split = n_split; p.Rp = Rp; p.row_chunk = row_chunk; p.epi = epi;
     p.pf = pf;
+    p.w_wait = w_wait;
     p.tmem_cols = 32;
     while ((int)p.tmem_cols < Rp) p.tmem_cols <<= 1;
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u + (awq ? UM_RAW_BYTES : 0);

@@ -267,6 +267,20 @@ class T3B200Engine:
         self.state.block_tables.view(-1)[upd[0]] = upd[1].to(torch.int32)
         return True
 
+    def _reorder(self) -> None:
+        """Deal order of the attention (t3b_state_t.row_order): rows of the current slot bucket by context, longest first, idle rows
+        last.  Every live row grows by one token per step, so the order only changes when requests come or go - recomputed on the
+        host then, one small asynchronous copy."""
+        live = [r for r in self.slots if r is not None]
+        if not live:
+            return
+        nb = self._bucket(max(r.slot for r in live) + 1)
+        by_ctx = sorted(live, key=lambda r: -(r.n_prompt + r.n_gen))
+        rows = [2 * r.slot + h for r in by_ctx for h in (0, 1)]
+        used = {r.slot for r in live}
+        rows += [2 * sl + h for sl in range(nb) if sl not in used for h in (0, 1)]
+        self.state.row_order[:2 * nb].copy_(torch.tensor(rows, dtype=torch.int32).pin_memory(), non_blocking=True)
+
     def kv_tokens_outstanding(self) -> int:
         """Token-rows of KV currently reserved (the dispatcher's load measure)."""
         return (self.kv.num_blocks - 1 - len(self.kv.free)) * KV_BLOCK
@@ -382,6 +396,7 @@ class T3B200Engine:
         self._admit(reqs)
         if reserve_steps > 0 and not self._grow(reqs, reserve_steps):
             raise MemoryError("KV pool exhausted")
+        self._reorder()
         return reqs
 
     def uninstall(self, reqs: Sequence[_Req]) -> None:
@@ -391,18 +406,28 @@ class T3B200Engine:
         self._park([r.slot for r in reqs])
 
     # ------------------------------------------------------------------ the caller's entry point
-    def _retire(self, done: List[_Req], results: Dict[int, RequestOutput], hist_host: torch.Tensor) -> None:
-        for i, r in enumerate(done):
-            toks = hist_host[i, :r.n_gen].tolist()
-            stop = r.sp.stop_token()
-            stopped = stop >= 0 and stop in toks
-            if stopped:
-                toks = toks[:toks.index(stop) + 1]
-            results[r.rid] = RequestOutput(r.rid, [CompletionOutput([t + SPEECH_TOKEN_OFFSET for t in toks],
-                                                                    "stop" if stopped else "length")])
+    def _retire(self, done: List[_Req], pending: List[Tuple[List[Tuple[int, int, int]], torch.Tensor]]) -> None:
+        """Finished requests leave their slots at once; their history rows start an ASYNCHRONOUS copy into pinned host memory
+        (stream-ordered in front of whatever reuses the slots) and are turned into results by ``_collect`` when generate()
+        returns - the host never waits for the GPU inside the decode loop, so the next steps are queued while this one runs."""
+        rows = torch.tensor([r.slot for r in done], device=self.dev)
+        host = torch.empty((len(done), self.state.hist_stride), dtype=torch.int32, pin_memory=True)
+        host.copy_(self.state.history[rows], non_blocking=True)
+        pending.append(([(r.rid, r.n_gen, r.sp.stop_token()) for r in done], host))
+        for r in done:
             self._release(r)
             self.slots[r.slot] = None
         self._park([r.slot for r in done])
+
+    @staticmethod
+    def _collect(pending, results: Dict[int, RequestOutput]) -> None:
+        for metas, host in pending:
+            for i, (rid, n_gen, stop) in enumerate(metas):
+                toks = host[i, :n_gen].tolist()
+                stopped = stop >= 0 and stop in toks
+                if stopped:
+                    toks = toks[:toks.index(stop) + 1]
+                results[rid] = RequestOutput(rid, [CompletionOutput([t + SPEECH_TOKEN_OFFSET for t in toks], "stop" if stopped else "length")])
 
     def _park(self, slots: List[int]) -> None:
         """Freed slots become idle rows (they write into scratch block 0): four indexed stores in all."""
@@ -430,8 +455,10 @@ class T3B200Engine:
         waiting = [self._make_req(i, p, sp) for i, (p, sp) in enumerate(zip(prompts, sps))]
         waiting.reverse()
         results: Dict[int, RequestOutput] = {}
+        pending: List[Tuple[List[Tuple[int, int, int]], torch.Tensor]] = []
         st = self.state
         waited = 0                                              # steps run since a slot became free with requests still waiting
+        changed = True                                          # the live set changed: the attention's deal order is stale
         while waiting or any(s is not None for s in self.slots):
             new: List[_Req] = []
             n_free = sum(s is None for s in self.slots)
@@ -451,6 +478,7 @@ class T3B200Engine:
             if new:
                 self._admit(new)
                 waited = 0
+                changed = True
             live = [r for r in self.slots if r is not None]
             if not live:
                 raise MemoryError(f"KV pool ({self.kv.num_blocks} blocks) cannot hold a single prompt of {waiting[-1].n_prompt} tokens")
@@ -477,7 +505,11 @@ class T3B200Engine:
                 victim.slot, victim.n_gen = -1, 0
                 waiting.append(victim)
                 self.preemptions += 1
+                changed = True
                 n_slots = max(r.slot for r in live) + 1
+            if changed:
+                self._reorder()
+                changed = False
             for _ in range(budget):
                 self.step(n_slots)
             if waiting and len(live) < self.max_req:
@@ -493,6 +525,8 @@ class T3B200Engine:
                     r.n_gen += budget
                 done = [r for r in live if r.n_gen >= self._limit(r)]
             if done:
-                rows = torch.tensor([r.slot for r in done], device=self.dev)
-                self._retire(done, results, st.history[rows].cpu())           # one D2H, the finished requests' rows only
+                self._retire(done, pending)
+                changed = True
+        torch.cuda.current_stream(self.dev).synchronize()      # the one wait of the call: every queued step and result copy
+        self._collect(pending, results)
         return [results[i] for i in range(len(prompts))]

@@ -113,15 +113,16 @@ class DecodeState:
         self.block_tables = z(2 * max_req, max_blocks)
         self.history = z(max_req, hist_stride)
         self.stop_tokens = torch.full((max_req,), stop_token, dtype=torch.int32, device=device)   # per request; < 0 = never stops
-        self.c = self.view(0)
+        self.row_order = torch.arange(2 * max_req, dtype=torch.int32, device=device)              # attention deal order (a hint)
+        self.c = self.view(0, ordered=True)
 
-    def view(self, slot0: int) -> _lib.State:
-        """t3b_state_t whose request 0 is slot ``slot0``."""
+    def view(self, slot0: int, ordered: bool = False) -> _lib.State:
+        """t3b_state_t whose request 0 is slot ``slot0`` (``ordered``: with the row_order hint, slot0 = 0 only)."""
         p = lambda t, n: t.data_ptr() + 4 * n
         return _lib.State(p(self.tokens, slot0), p(self.speech_pos, slot0), p(self.rope_pos, 2 * slot0), p(self.ctx_lens, 2 * slot0),
                           p(self.block_tables, 2 * slot0 * self.max_blocks), self.max_blocks, p(self.history, slot0 * self.hist_stride),
                           p(self.hist_len, slot0), self.hist_stride, p(self.step, slot0), p(self.active, slot0),
-                          p(self.stop_tokens, slot0), self.max_ctx)
+                          p(self.stop_tokens, slot0), self.max_ctx, self.row_order.data_ptr() if (ordered and slot0 == 0) else None)
 
 
 class SamplingTensors:

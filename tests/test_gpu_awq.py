@@ -115,3 +115,36 @@ def test_awq_decode_matches_oracle_with_dequantised_weights():
         record("awq_engine_greedy_stream", {"req": b, "first_divergence": k, "steps": T,
                                             "margin_at_divergence": float(ref["margins"][k, b]) if k < T else None})
         assert k == T or ref["margins"][k, b] <= 0.125, (b, k, float(ref["margins"][k, b]))
+
+
+def test_awq_large_batch_dequantise_once_equals_fused_kernel():
+    """From 256 rows on t3b_decode_step dequantises a layer's AWQ projections once into a bf16 scratch and runs the bf16 kernels
+    (upstream switches to dequantise-then-GEMM at 256 tokens too, vllm awq.py:276-281).  The same 256 rows as two 128-row steps go
+    through the dequant-fused kernel: same definition bf16_rn((q - z) * s), so the hidden states agree to bf16 rounding (the
+    split-K factor differs between the two row counts) and the KV pool bit for bit where both wrote it."""
+    import ctypes as C
+    from helpers import random_state
+    m = T3B200Model(dims=SMALL, device=DEV, cfg_scale=0.5, quantization="awq")
+    m.load_weights(synthetic_checkpoint(SMALL).items())
+    L = _lib.lib()
+    rows = 256
+    lens = [20 + (7 * r) % 90 for r in range(rows)]
+    kv, st = random_state(SMALL, rows, lens, seed=11)
+    ws = m.workspace(rows)
+    big = torch.empty(rows, 1024, dtype=torch.bfloat16, device=DEV)
+    s = torch.cuda.current_stream().cuda_stream
+    _lib.check(L.t3b_decode_step(C.byref(m.c), C.byref(kv.c), C.byref(st.c), None, rows, big.data_ptr(), ws.data_ptr(), ws.numel(), None, s))
+    k_big, v_big = kv.k.clone(), kv.v.clone()
+    halves = torch.empty_like(big)
+    for h in range(2):
+        view = st.view(64 * h)
+        _lib.check(L.t3b_decode_step(C.byref(m.c), C.byref(kv.c), C.byref(view), None, 128, halves[128 * h:].data_ptr(), ws.data_ptr(),
+                                     ws.numel(), None, s))
+    torch.cuda.synchronize()
+    a, b = big.float().cpu(), halves.float().cpu()
+    assert torch.isfinite(a).all() and (a - b).abs().max() <= 0.0625, float((a - b).abs().max())
+    assert torch.nn.functional.cosine_similarity(a.flatten().double(), b.flatten().double(), dim=0) > 0.9999
+    # layer 0's new K/V come from the same embeddings through the same weights: the pools agree up to the split-K rounding of the projections
+    for now, then in ((kv.k, k_big), (kv.v, v_big)):
+        d = (now.view(torch.bfloat16).float() - then.view(torch.bfloat16).float()).abs().max()
+        assert float(d) <= 0.0625, float(d)

@@ -374,3 +374,28 @@ def test_umma_row_chunk_and_stage_options_do_not_change_results(L, rows, chunk, 
             ys.append(y)
         assert torch.equal(ys[0], ys[1]), (N, K)
 
+
+
+def test_row_order_hint_does_not_change_results(L, small_model):
+    """t3b_state_t.row_order only changes which warp serves which (row, head) item: a decode step with the rows dealt in a random
+    order (and in longest-context-first order, what the engine passes) is bit-identical to the identity order - hidden states and
+    the KV pool."""
+    m, _ = small_model
+    rows = 96
+    g = torch.Generator().manual_seed(3)
+    lens = torch.randint(5, 400, (rows // 2,), generator=g).repeat_interleave(2).tolist()
+    outs = []
+    for mode in ("identity", "random", "longest_first"):
+        kv, st = random_state(SMALL, rows, lens, seed=8)
+        if mode == "random":
+            st.row_order.copy_(torch.randperm(rows, generator=g).to(torch.int32))
+        elif mode == "longest_first":
+            st.row_order.copy_(torch.tensor(sorted(range(rows), key=lambda r: -lens[r]), dtype=torch.int32))
+        view = st.view(0, ordered=(mode != "identity"))
+        ws = m.workspace(rows)
+        hid = torch.empty(rows, 1024, dtype=torch.bfloat16, device=DEV)
+        _lib.check(L.t3b_decode_step(C.byref(m.c), C.byref(kv.c), C.byref(view), None, rows, hid.data_ptr(), ws.data_ptr(), ws.numel(), None, sp()))
+        torch.cuda.synchronize()
+        outs.append((hid.clone(), kv.k.clone(), kv.v.clone()))
+    for o in outs[1:]:
+        assert all(torch.equal(a, b) for a, b in zip(outs[0], o))

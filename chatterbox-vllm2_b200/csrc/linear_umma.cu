@@ -110,6 +110,29 @@ __device__ __forceinline__ void red_sum8(const float* red, int n_split, int per,
     else red_sum8_n<2>(red, per, j, col, acc);
 }
 
+// Split-K push: row rl of the block's partial tile belongs to CTA (rl % NS) of the cluster; thread `f` (one accumulator lane = one
+// output feature) stores its 4-byte partial of it into the owner's buffer red[src split][rl / NS][128] through distributed shared
+// memory.  The owner addresses are mapped once (mapa), the TMEM loads of 32 columns are issued back to back before the stores.
+template <int NS>
+__device__ __forceinline__ void push_partials(uint32_t tmem_base, int quad, int f, int valid, int Rp, int split, uint32_t red_s) {
+    const int per = Rp / NS;                                   // rows each CTA owns
+    uint32_t owner[NS];
+#pragma unroll
+    for (int o = 0; o < NS; ++o) owner[o] = map_to_cta(red_s + (uint32_t)(split * per * UM_M + f) * 4u, (uint32_t)o);
+    for (int c0 = 0; c0 < valid; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
+        if (c0 + 16 < valid) tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(c0 + 16), v + 16);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            if (c0 + j < valid)                                // c0 is a multiple of 32: (c0 + j) % NS == j % NS, a compile-time index
+                asm volatile("st.shared::cluster.u32 [%0], %1;"
+                             :: "r"(owner[j % NS] + (uint32_t)(((c0 + j) / NS) * UM_M) * 4u), "r"(v[j]) : "memory");
+        }
+    }
+}
+
 template <int WSRC>
 __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                           const __grid_constant__ CUtensorMap tmap_x,
@@ -276,24 +299,9 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                 }
             }
         } else if (p.n_split > 1) {
-            // push: row rl belongs to CTA (rl % n_split) of the cluster; store this CTA's partial of it into the
-            // owner's buffer red[src split][rl / n_split][128] through distributed shared memory
-            const uint32_t red_s = smem_u32(red);
-            const int sh = p.n_split == 2 ? 1 : (p.n_split == 4 ? 2 : 3);
-            const int per = Rp >> sh;                                   // rows each CTA owns
-            for (int c0 = 0; c0 < valid; c0 += 16) {
-                uint32_t v[16];
-                tmem_ld16(tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)c0, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    const int rl = c0 + j;
-                    if (rl < valid) {
-                        const uint32_t off = (uint32_t)((split * per + (rl >> sh)) * UM_M + f) * 4u;
-                        asm volatile("st.shared::cluster.u32 [%0], %1;" :: "r"(map_to_cta(red_s + off, (uint32_t)(rl & (p.n_split - 1)))), "r"(v[j]) : "memory");
-                    }
-                }
-            }
+            if (p.n_split == 8) push_partials<8>(tmem_base, quad, f, valid, Rp, split, smem_u32(red));
+            else if (p.n_split == 4) push_partials<4>(tmem_base, quad, f, valid, Rp, split, smem_u32(red));
+            else push_partials<2>(tmem_base, quad, f, valid, Rp, split, smem_u32(red));
         } else {
             // n_split == 1: 16 rows at a time through a small exchange buffer so that the stores of a row are
             // 256 B contiguous and gate / up (lanes f and f + 64) meet
@@ -348,6 +356,8 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     tc_fence_before();
     if (p.partials == nullptr && p.n_split > 1) {
         cluster_sync_all();                      // release / acquire: every peer's pushes into this CTA's buffer have landed
+        // (per-owner mbarriers with remote arrives + an acquire.cluster wait instead of this barrier measured SLOWER: qkv 5.6 -> 6.0 us,
+        //  o 4.0 -> 4.4, down 6.8 -> 7.5 - barrier.cluster is the cheapest cluster-wide rendezvous there is; profiles/r2_notes.md r3b)
         // after the barrier the producer / MMA warps are idle too: the pure store epilogues run on every thread of the block
         const bool wide = p.epi == EPI_SILU || (p.epi == EPI_STORE && (p.N & 7) == 0);
         const int nthr = wide ? (int)blockDim.x : 128;
@@ -574,7 +584,7 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0);
     const size_t ring = (size_t)p.stages * stage_bytes;
     const size_t red = !cluster ? 0 : (p.n_split > 1 ? (size_t)p.Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
-    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 2) * 8;
+    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 3) * 8;
     auto kern = linear_umma_kernel<WSRC>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};

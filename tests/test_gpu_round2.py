@@ -399,3 +399,43 @@ def test_row_order_hint_does_not_change_results(L, small_model):
         outs.append((hid.clone(), kv.k.clone(), kv.v.clone()))
     for o in outs[1:]:
         assert all(torch.equal(a, b) for a, b in zip(outs[0], o))
+
+
+def test_prefill_hidden_states_match_oracle_for_ragged_prompts(small_model):
+    """t3.py:542-561 + the multi-token pass (t3b_prefill_embed -> t3b_forward_tokens with the read-once prefill attention): the
+    final-norm hidden state of EVERY prompt token of ragged cond / uncond rows against oracle.forward_tokens (bf16 mode), and the
+    K/V the pass leaves in the pool against the oracle's cache (what the decode steps will attend to)."""
+    from chatterbox_vllm2_b200.model import KVPool
+    m, sd = small_model
+    n_texts = (1, 9, 40, 64, 17)
+    reqs = [synthetic_request(20 + i, SMALL, n_text=n) for i, n in enumerate(n_texts)]
+    slots = [2, 0, 4, 1, 3]
+    x, tok_row, tok_idx, starts = m.prefill_assemble([c for c, _ in reqs], [ids for _, ids in reqs], slots)
+    seq_start, seq_row = m.last_seq
+    max_blocks = 8
+    kv = KVPool(SMALL, 2 * len(reqs) * max_blocks + 1, DEV)
+    bt = (torch.arange(2 * len(reqs) * max_blocks, dtype=torch.int32) + 1).reshape(2 * len(reqs), max_blocks).to(DEV)
+    h = m.forward_tokens(kv, x, tok_row, tok_idx, tok_idx, bt, seq_start, seq_row, max(34 + n + 1 for n in n_texts))
+    torch.cuda.synchronize()
+    hs = h.float().cpu()
+    orc = T3Oracle(sd, SMALL, mode="bf16")
+    worst, cos_min = 0.0, 1.0
+    kpool = kv.as_bf16("k").float().cpu()                    # [layer, block, head, 16, 64]
+    for r, (cond, ids) in enumerate(reqs):
+        c_ref, u_ref = orc.prefill_embeds(cond.float(), ids)
+        P = c_ref.shape[0]
+        rc, ru = orc.new_rows(2)
+        for half, (emb, row) in enumerate(((c_ref, rc), (u_ref, ru))):
+            ref = orc.forward_tokens(emb, [row] * P, range(P))
+            got = hs[starts[2 * r + half]:starts[2 * r + half + 1]]
+            worst = max(worst, float((got - ref).abs().max()))
+            cos_min = min(cos_min, float(torch.nn.functional.cosine_similarity(got.flatten().double(), ref.flatten().double(), dim=0)))
+            # K of the last layer at every position of this row
+            kv_row = 2 * slots[r] + half
+            blocks = bt[kv_row].cpu().long()
+            k_got = kpool[SMALL.n_layers - 1][blocks].permute(0, 2, 1, 3).reshape(-1, 16, 64)[:P]
+            k_ref = orc.kc[row][SMALL.n_layers - 1][:P]
+            assert (k_got - k_ref).abs().max() <= 0.0625, (r, half, float((k_got - k_ref).abs().max()))
+    from helpers import record
+    record("prefill_hidden_ragged_L2", {"max_abs": worst, "min_cosine": cos_min, "prompts": list(n_texts)})
+    assert worst <= 0.125 and cos_min >= 0.9999, (worst, cos_min)     # measured 0.0625 = one bf16 ulp at |h| in [8, 16)

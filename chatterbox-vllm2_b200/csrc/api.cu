@@ -12,6 +12,7 @@ int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, in
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
                                int n_split, int epi, int stages_cap, int row_chunk, PfArgs pf, int w_wait, cudaStream_t s);
 int32_t t3b_awq_dequant_launch(const t3b_linear_t* const* lins, int n_lin, void* scratch, cudaStream_t stream);
+int32_t t3b_linear_big_launch(const void* x, const void* w, int rows, int N, int K, void* y, int epi, cudaStream_t stream);
 int t3b_umma_pick_split(int rows, int N, int K);
 int t3b_umma_available();
 int32_t t3b_sampler_launch(const void* head, const float* head_partials, int n_split, const float* logits_in, int V, int n_req,
@@ -97,10 +98,10 @@ extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
 }
 
 struct Opt {
-    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch, w_wait;
+    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch, w_wait, big_min_rows;
 };
 static Opt resolve(const t3b_options_t* o) {
-    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0};
+    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0, 1024};
     if (o) {
         if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > 4 ? 4 : o->gemv_max_rows);
         r.gemv_norm = o->gemv_no_norm ? 0 : 1;
@@ -109,6 +110,7 @@ static Opt resolve(const t3b_options_t* o) {
         for (int i = 0; i < 4; ++i) r.split[i] = o->umma_split[i] > 0 ? o->umma_split[i] : 0;
         r.attn_team = o->attn_team_warps;
         r.prefetch = o->weight_prefetch ? 1 : 0;
+        if (o->umma_big_min_rows != 0) r.big_min_rows = o->umma_big_min_rows < 0 ? 0x7fffffff : o->umma_big_min_rows;
     }
     return r;
 }
@@ -142,6 +144,10 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     }
     if (!legacy && y == nullptr) T3B_FAIL(T3B_ERR_ARG, "linear: y is null (partials are only written for an explicit n_split > 1)");
     if (n_split_out) *n_split_out = n_split;
+    // thousands of rows, no split-K, bf16 (AWQ layers arrive as their dequantised copy): the persistent double-buffered kernel.
+    // (it requests weights after its dependency wait, so it is also safe on the AWQ scratch)
+    if (!awq && !legacy && n_split == 1 && rows >= o.big_min_rows)
+        return t3b_linear_big_launch(x, w->w, rows, w->n, w->k, y, epi, s);
     return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, legacy ? partials : nullptr, n_split, epi, o.stages,
                                   o.row_chunk, pf, o.w_wait, s);
 }

@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
 #pragma unroll
                         for (int e = 0; e < 8; ++e) {
                             const float g = bf16_round(gv[e]);
-                            o[e] = bf16_round(g / (1.0f + expf(-g))) * bf16_round(uv[e]);
+                            o[e] = bf16_round(__fdividef(g, 1.0f + __expf(-g))) * bf16_round(uv[e]);       // the split-K epilogue's formula
                         }
                         *reinterpret_cast<uint4*>(p.y + (size_t)(r0 + c0 + j) * ffn + tile * 64 + g8) = pack8(o);
                     }
@@ -556,6 +556,10 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t o
                      weights ? CU_TENSOR_MAP_L2_PROMOTION_L2_256B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
+int t3b_make_tmap_bf16(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, uint32_t box_outer, bool weights) {
+    return make_tmap(m, ptr, inner, outer, box_outer, weights);
 }
 
 int t3b_umma_available() { return get_encode_fn() != nullptr; }

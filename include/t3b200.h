@@ -154,6 +154,8 @@ typedef struct t3b_options {
     int32_t attn_team_warps;     /* decode attention: warps that share one (row, head) item: 1, 2, 4 or 8 (0 = by item count) */
     int32_t weight_prefetch;     /* 1 = every launch of t3b_decode_step pulls the weights of the projection two launches ahead into
                                     L2 (measured: no gain, the chain is latency-bound - profiles/r2_notes.md; default off)       */
+    int32_t umma_big_min_rows;   /* bf16 projections without split-K run the persistent double-buffered tcgen05 kernel (csrc/linear_big.cu)
+                                    from this many rows on (0 = default 1024: prefill passes and decode batches of >= 512 requests; < 0 = never)                       */
 } t3b_options_t;
 
 const char* t3b_last_error(void);

@@ -26,10 +26,8 @@ for name, N, K, epi in SHAPES:
         y = torch.empty(rows, N // 2 if epi else N, dtype=torch.bfloat16, device=dev)
         best = None
         for split in (1, 2, 4, 8):
-            for chunk, stages in (((0, 0),) if split > 1 else ((128, 0), (128, 3), (128, 2), (256, 0))):
-                if (rows <= 128 or rows <= 512) and chunk == 256:
-                    continue
-                opt = _lib.make_options(umma_row_chunk=chunk, umma_stages=stages)
+            for chunk, stages, big in (((0, 0, -1),) if split > 1 else ((0, 0, -1), (0, 0, 1))):
+                opt = _lib.make_options(umma_row_chunk=chunk, umma_stages=stages, umma_big_min_rows=big)
                 side = torch.cuda.Stream()
                 side.wait_stream(torch.cuda.current_stream())
                 try:
@@ -49,10 +47,10 @@ for name, N, K, epi in SHAPES:
                             if rep: t = min(t, e0.elapsed_time(e1) / NL * 1e3)
                         del g
                 except Exception as e:  # noqa: BLE001
-                    print(f"{rows:5d} {name:8s} {split} {chunk:3d} st{stages} failed: {str(e)[:80]}")
+                    print(f"{rows:5d} {name:8s} {split} {chunk:3d} st{stages} big{big} failed: {str(e)[:80]}")
                     continue
                 torch.cuda.current_stream().wait_stream(side)
-                print(f"{rows:5d} {name:8s} {split} {chunk:3d} st{stages} {t:8.2f}")
+                print(f"{rows:5d} {name:8s} {split} {chunk:3d} st{stages} big{big} {t:8.2f}")
                 if best is None or t < best[0]:
                     best = (t, split, chunk)
         print(f"# best rows {rows} {name}: split {best[1]} chunk {best[2]} {best[0]:.2f} us")

@@ -439,3 +439,22 @@ def test_prefill_hidden_states_match_oracle_for_ragged_prompts(small_model):
     from helpers import record
     record("prefill_hidden_ragged_L2", {"max_abs": worst, "min_cosine": cos_min, "prompts": list(n_texts)})
     assert worst <= 0.125 and cos_min >= 0.9999, (worst, cos_min)     # measured 0.0625 = one bf16 ulp at |h| in [8, 16)
+
+
+@pytest.mark.parametrize("rows", [257, 512, 1000, 2500, 6336])
+def test_persistent_big_gemm_equals_tiled_kernel(L, rows):
+    """csrc/linear_big.cu (persistent blocks, 4-deep ring, double-buffered TMEM accumulator; the default for > 1024 rows without
+    split-K): the same tcgen05 accumulation per output element as linear_umma_kernel, so y is bit-identical - ragged last row
+    chunk, more tiles than blocks (several tiles per block, both accumulators reused), SiLU epilogue, the 8194-wide head."""
+    g = torch.Generator().manual_seed(rows)
+    for N, K, epi in ((3072, 1024, 0), (8192, 1024, 1), (1024, 4096, 0), (8194, 1024, 0)):
+        x = torch.randn(rows, K, generator=g).bfloat16().to(DEV)
+        w = (torch.randn(N, K, generator=g) * K ** -0.5).bfloat16().to(DEV)
+        lin = _lib.Linear(_lib.T3B_W_BF16, N, K, w.data_ptr(), None, None)
+        ys = []
+        for opt in (_lib.make_options(umma_big_min_rows=-1), _lib.make_options(umma_big_min_rows=1)):
+            y = torch.full((rows, N // (2 if epi else 1)), float("nan"), dtype=torch.bfloat16, device=DEV)
+            _lib.check(L.t3b_linear_bf16(x.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 1, None, _lib.T3B_IMPL_UMMA, epi, C.byref(opt), sp()))
+            ys.append(y)
+        torch.cuda.synchronize()
+        assert torch.isfinite(ys[1].float()).all() and torch.equal(ys[0], ys[1]), (N, K, epi)

@@ -168,6 +168,70 @@ __global__ void __launch_bounds__(512) rope_kv_write_kernel(const bf16* __restri
     }
 }
 
+// The same operation on bf16 qkv with 128-bit accesses (the prefill pass: thousands of tokens): 8 lanes per head, lane c holds dims
+// [8c, 8c+8) (c < 4: x1, c >= 4: x2 - the rotation partner sits 4 lanes away); 128 threads per token, 4 tokens per block.  Same
+// roundings as the scalar kernel (each product and the sum round to bf16) - bit-identical; 56 -> ~15 us per layer at 6,336 tokens.
+template <int KVT>
+__global__ void __launch_bounds__(512) rope_kv_write_vec_kernel(const bf16* __restrict__ qkv, int n_tok, const int32_t* __restrict__ tok_row,
+                                                                const int32_t* __restrict__ tok_idx, const int32_t* __restrict__ rope_pos,
+                                                                const bf16* __restrict__ cos_sin, int max_pos,
+                                                                const int32_t* __restrict__ block_tables, int max_blocks,
+                                                                unsigned char* __restrict__ k_pool, unsigned char* __restrict__ v_pool,
+                                                                bf16* __restrict__ q_out) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int t = blockIdx.x * 4 + (threadIdx.x >> 7);
+    if (t >= n_tok) return;
+    const int u = threadIdx.x & 127, h = u >> 3, c = u & 7;          // 16 heads x 8 lanes
+    const int hidden = 1024;
+    const int row = tok_row ? ld_act(tok_row + t) : t;
+    const int idx = ld_act(tok_idx + t);
+    int pos = ld_act(rope_pos + t);
+    pos = min(max(pos, 0), max_pos - 1);
+    const int blk = ld_act(block_tables + (size_t)row * max_blocks + (idx >> 4));
+    const bf16* src = qkv + (size_t)t * 3 * hidden + h * 64 + c * 8;
+    float qf[8], kf[8], vf[8], cs[8], sn[8];
+    unpack8(ld_act(reinterpret_cast<const uint4*>(src)), qf);
+    unpack8(ld_act(reinterpret_cast<const uint4*>(src + hidden)), kf);
+    const uint4 vraw = ld_act(reinterpret_cast<const uint4*>(src + 2 * hidden));
+    unpack8(__ldg(reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + (c & 3) * 8)), cs);
+    unpack8(__ldg(reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + 32 + (c & 3) * 8)), sn);
+    const bool hi = c >= 4;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4), kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
+        qf[e] = hi ? bf16_round(bf16_round(qf[e] * cs[e]) + bf16_round(qp * sn[e])) : bf16_round(bf16_round(qf[e] * cs[e]) - bf16_round(qp * sn[e]));
+        kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
+    }
+    *reinterpret_cast<uint4*>(q_out + (size_t)t * hidden + h * 64 + c * 8) = pack8(qf);
+    if (KVT == 1) {
+        unpack8(vraw, vf);
+        float ka = 0.f, va = 0.f;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { ka = fmaxf(ka, fabsf(kf[e])); va = fmaxf(va, fabsf(vf[e])); }
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) { ka = fmaxf(ka, __shfl_xor_sync(0xffffffffu, ka, o)); va = fmaxf(va, __shfl_xor_sync(0xffffffffu, va, o)); }
+        const float ks = ka > 0.f ? ka / 448.f : 1.f, vs = va > 0.f ? va / 448.f : 1.f;
+        uint32_t kw[2] = {0u, 0u}, vw[2] = {0u, 0u};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            kw[i >> 1] |= (uint32_t)__nv_cvt_float2_to_fp8x2(make_float2(kf[2 * i] / ks, kf[2 * i + 1] / ks), __NV_SATFINITE, __NV_E4M3) << (16 * (i & 1));
+            vw[i >> 1] |= (uint32_t)__nv_cvt_float2_to_fp8x2(make_float2(vf[2 * i] / vs, vf[2 * i + 1] / vs), __NV_SATFINITE, __NV_E4M3) << (16 * (i & 1));
+        }
+        const size_t sl = ((size_t)blk * 16 + h) * 1088;
+        *reinterpret_cast<uint2*>(k_pool + sl + (idx & 15) * 64 + c * 8) = make_uint2(kw[0], kw[1]);
+        *reinterpret_cast<uint2*>(v_pool + sl + (idx & 15) * 64 + c * 8) = make_uint2(vw[0], vw[1]);
+        if (c == 0) {
+            *reinterpret_cast<float*>(k_pool + sl + 1024 + (idx & 15) * 4) = ks;
+            *reinterpret_cast<float*>(v_pool + sl + 1024 + (idx & 15) * 4) = vs;
+        }
+    } else {
+        const size_t sl = ((size_t)blk * 16 + h) * 2048 + ((idx & 15) * 64 + c * 8) * 2;
+        *reinterpret_cast<uint4*>(k_pool + sl) = pack8(kf);
+        *reinterpret_cast<uint4*>(v_pool + sl) = vraw;
+    }
+}
+
 // ------------------------------------------------------------------ prefill embedding assembly (t3.py:542-561)
 // One CTA per sequence (2 per request: cond, uncond); 128 threads = one 1024-wide row per pass.
 __global__ void __launch_bounds__(256) prefill_embed_kernel(const uint4* __restrict__ conds, const int32_t* __restrict__ text_ids,
@@ -323,6 +387,13 @@ extern "C" int32_t t3b_rope_kv_write(const void* qkv, const float* partials, int
     T3B_CHECK_SHAPE(n_heads >= 1 && n_heads <= 64, "t3b_rope_kv_write: n_heads %d", n_heads);
     T3B_CHECK_ARG(kv_dtype == T3B_KV_BF16 || kv_dtype == T3B_KV_FP8, "t3b_rope_kv_write: unknown KV dtype %d", kv_dtype);
     if (n_tok == 0) return T3B_OK;
+    if (qkv != nullptr && n_heads == 16 && n_tok >= 64) {              // the prefill pass: 128-bit accesses, 4 tokens per block
+        auto vk = kv_dtype == T3B_KV_FP8 ? rope_kv_write_vec_kernel<1> : rope_kv_write_vec_kernel<0>;
+        T3B_CUDA(t3b_launch(vk, dim3((n_tok + 3) / 4), dim3(512), 0, t3b_stream(stream), (const bf16*)qkv, n_tok, tok_row, tok_idx, rope_pos,
+                            (const bf16*)rope_cos_sin, max_pos, block_tables, max_blocks, (unsigned char*)k_pool, (unsigned char*)v_pool,
+                            (bf16*)q_out));
+        return T3B_OK;
+    }
     const int threads = 32 * (n_heads < 16 ? n_heads : 16);
     auto kern = kv_dtype == T3B_KV_FP8 ? rope_kv_write_kernel<1> : rope_kv_write_kernel<0>;
     T3B_CUDA(t3b_launch(kern, dim3(n_tok), dim3(threads), 0, t3b_stream(stream), (const bf16*)qkv, partials, n_split,

@@ -1,6 +1,6 @@
 #!/bin/bash
 # One full GPU-box visit: every parity test file (own process), smoke, the bench (both arms), the ncu launch list and full-set
-# captures of the dominant kernels at 64 rows (configs[1]) and at 256 rows (tensor-pipe evidence for the large-batch GEMM).
+# captures of the dominant kernels at 64 rows (configs[1]) and of the projections at 256..6336 rows (tensor-pipe evidence).
 # Everything lands in gpurun_out/$TAG_*; nothing printed under ncu is a bench value.
 TAG=${1:-r2}
 O=gpurun_out
@@ -27,9 +27,9 @@ if [ "${SKIP_NCU:-0}" != "1" ]; then
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"attn_ring|linear_umma|add_rmsnorm|cfg_sample" -c 9 --launch-skip 1500 -o $O/${TAG}_full -f \
     python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-breakdown --sweep '' > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full exit $?"
   python scripts/summarise_ncu.py full $O/${TAG}_full.ncu-rep $O/${TAG}_full_summary.csv
-  timeout 900 ncu --set full --clock-control none -k regex:"linear_umma|attn_ring" -c 6 --launch-skip 2000 -o $O/${TAG}_full256 -f \
-    python bench.py --batch 128 --steps 3 --warmup 3 --no-cpu-baseline --no-breakdown --sweep '' > $O/${TAG}_ncu_full256.log 2>&1; echo "ncu full256 exit $?"
-  python scripts/summarise_ncu.py full $O/${TAG}_full256.ncu-rep $O/${TAG}_full256_summary.csv
-  rm -f $O/${TAG}_full256.ncu-rep
+  timeout 600 ncu --set full --clock-control none -k regex:"linear_umma|linear_big" -o $O/${TAG}_gemm -f \
+    python scripts/probe/gemm_ncu.py > $O/${TAG}_ncu_gemm.log 2>&1; echo "ncu gemm exit $?"
+  python scripts/summarise_ncu.py full $O/${TAG}_gemm.ncu-rep $O/${TAG}_gemm_summary.csv
+  rm -f $O/${TAG}_gemm.ncu-rep
 fi
 ls -la $O | tail -14

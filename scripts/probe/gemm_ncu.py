@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """The decode / prefill projections at large row counts, a few launches each, for an ncu --set full capture (tensor-pipe evidence):
-    ncu --set full --clock-control none -k regex:linear_umma -o out python scripts/probe/gemm_ncu.py"""
+    ncu --set full --clock-control none -k regex:"linear_umma|linear_big" -o out python scripts/probe/gemm_ncu.py"""
 import ctypes as C
 import os
 import sys

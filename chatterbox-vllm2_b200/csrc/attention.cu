@@ -503,6 +503,159 @@ __global__ void __launch_bounds__(PF_NW * 32) prefill_attn_kernel(const PrefillA
     }
 }
 
+// ------------------------------------------------------------------ prefill attention on the tensor cores (bf16 K/V)
+// The warp-per-query kernel above spends ~250 instructions per (query, 32 keys): 110 us per layer for 64 prompts of 99 tokens,
+// the largest piece of a prefill pass after the projections.  Here a warp owns a TILE of 16 queries of one (sequence, head) and
+// runs S = Q K^T and O = P V as mma.sync.m16n8k16 (bf16 in, fp32 accumulate) over key chunks of 64 with the usual online softmax:
+//   - K / V of the prompt are copied once into shared memory, rows of 128 B with their 16-byte chunks XOR-swizzled by (token & 7),
+//     so the ldmatrix reads (K as the col-major B operand; V through ldmatrix.trans) are bank-conflict free;
+//   - Q fragments come straight from global memory; the softmax scale is applied to the fp32 scores;
+//   - P is split into bf16 hi + lo parts (two MMAs), so the probabilities enter P V with ~2^-17 relative error, not bf16's 2^-9:
+//     the result stays within the 1-ulp band of the fp32-softmax tests.
+// A prompt's result depends on nothing but the prompt (tile i of a sequence always sees keys 0..16i+15 in the same order).
+__device__ __forceinline__ void ldsm_x4(uint32_t* r, uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t* r, uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+#define PM_NW 4
+__global__ void __launch_bounds__(PM_NW * 32) prefill_attn_mma_kernel(const PrefillArgs a) {
+    extern __shared__ __align__(128) unsigned char at_smem[];
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const int H = a.n_heads, seq = blockIdx.x / H, h = blockIdx.x - seq * H;
+    const int t0 = a.seq_start[seq], P = a.seq_start[seq + 1] - t0;
+    const int P16 = (P + 15) & ~15;
+    unsigned char* ks = at_smem;                                   // [P16][128 B], chunk c of token r at ((c ^ (r & 7)) * 16)
+    unsigned char* vs = at_smem + (size_t)a.max_pages * 2048;
+    pdl_wait();                                                    // the K/V of this pass were written by the kernel in front
+    {
+        const int32_t* bt = a.block_tables + (size_t)a.seq_row[seq] * a.max_blocks;
+        for (int i = threadIdx.x; i < P16 * 8; i += PM_NW * 32) {
+            const int r = i >> 3, c = i & 7;
+            uint4 kq = make_uint4(0, 0, 0, 0), vq = kq;            // rows past the prompt are zero: they meet probability 0, never NaN
+            if (r < P) {
+                const size_t off = ((size_t)bt[r >> 4] * H + h) * 2048 + (size_t)(r & 15) * 128 + c * 16;
+                kq = ld_act(reinterpret_cast<const uint4*>(a.k_pool + off));
+                vq = ld_act(reinterpret_cast<const uint4*>(a.v_pool + off));
+            }
+            const int sw = r * 128 + ((c ^ (r & 7)) << 4);
+            *reinterpret_cast<uint4*>(ks + sw) = kq;
+            *reinterpret_cast<uint4*>(vs + sw) = vq;
+        }
+    }
+    __syncthreads();
+    const uint32_t ks_u = smem_u32(ks), vs_u = smem_u32(vs);
+    const float kScale = 0.125f * 1.4426950408889634f;
+    const int hidden = H * 64, n_tiles = P16 >> 4;
+    // longest tiles first, round-robin over the warps
+    for (int ti = n_tiles - 1 - warp; ti >= 0; ti -= PM_NW) {
+        const int q0 = ti * 16;
+        uint32_t qa[4][4];                                         // A fragments of Q for the 4 k-steps of 16 dims
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const int r0 = min(q0 + g, P - 1), r1 = min(q0 + g + 8, P - 1);        // rows past the prompt repeat the last one (never stored)
+            const bf16* p0 = a.q + (size_t)(t0 + r0) * hidden + h * 64 + kk * 16 + 2 * t;
+            const bf16* p1 = a.q + (size_t)(t0 + r1) * hidden + h * 64 + kk * 16 + 2 * t;
+            qa[kk][0] = ld_act(reinterpret_cast<const unsigned*>(p0));
+            qa[kk][1] = ld_act(reinterpret_cast<const unsigned*>(p1));
+            qa[kk][2] = ld_act(reinterpret_cast<const unsigned*>(p0 + 8));
+            qa[kk][3] = ld_act(reinterpret_cast<const unsigned*>(p1 + 8));
+        }
+        float o[8][4], m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
+        const int k_end = q0 + 16;                                 // keys this tile may see (causal), a multiple of 16
+        for (int kc = 0; kc < k_end; kc += 64) {
+            const int nt = min(8, (k_end - kc) >> 3);              // 8-key tiles in this chunk (even)
+            float sc[8][4];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { sc[j][0] = sc[j][1] = sc[j][2] = sc[j][3] = 0.f; }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j < nt) {
+                    const int key = kc + 8 * j + (lane & 7);
+#pragma unroll
+                    for (int k2 = 0; k2 < 2; ++k2) {               // two k-steps per ldmatrix.x4: chunks 4 k2 .. 4 k2 + 3 of the key rows
+                        uint32_t b[4];
+                        ldsm_x4(b, ks_u + key * 128 + ((((4 * k2 + (lane >> 3)) ^ (key & 7))) << 4));
+                        mma_bf16(sc[j], qa[2 * k2], b[0], b[1]);
+                        mma_bf16(sc[j], qa[2 * k2 + 1], b[2], b[3]);
+                    }
+                }
+            }
+            // scale, causal mask, online softmax (rows q0 + g and q0 + g + 8; a row's 4 lanes differ in t)
+            float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j < nt) {
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int key = kc + 8 * j + 2 * t + e;
+                        sc[j][e] = key <= q0 + g ? sc[j][e] * kScale : -INFINITY;
+                        sc[j][2 + e] = key <= q0 + g + 8 ? sc[j][2 + e] * kScale : -INFINITY;
+                        mx0 = fmaxf(mx0, sc[j][e]); mx1 = fmaxf(mx1, sc[j][2 + e]);
+                    }
+                }
+            }
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+            const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);             // finite: key kc <= every query of the tile
+            const float c0 = exp2f(m0 - mn0), c1 = exp2f(m1 - mn1);
+            m0 = mn0; m1 = mn1; l0 *= c0; l1 *= c1;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { o[j][0] *= c0; o[j][1] *= c0; o[j][2] *= c1; o[j][3] *= c1; }
+            uint32_t ph[8][2], pl[8][2];                            // P as bf16 hi / lo pairs: [j][0] = row g, [j][1] = row g + 8
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (j < nt) {
+                    const float p0 = exp2f(sc[j][0] - m0), p1 = exp2f(sc[j][1] - m0), p2 = exp2f(sc[j][2] - m1), p3 = exp2f(sc[j][3] - m1);
+                    l0 += p0 + p1; l1 += p2 + p3;
+                    const float h0 = bf16_round(p0), h1 = bf16_round(p1), h2 = bf16_round(p2), h3 = bf16_round(p3);
+                    ph[j][0] = pack_bf16(h0, h1); ph[j][1] = pack_bf16(h2, h3);
+                    pl[j][0] = pack_bf16(p0 - h0, p1 - h1); pl[j][1] = pack_bf16(p2 - h2, p3 - h3);
+                } else {
+                    ph[j][0] = ph[j][1] = pl[j][0] = pl[j][1] = 0u;
+                }
+            }
+            // O += P V: k-step kk covers keys kc + 16 kk .. + 15 = score tiles 2 kk, 2 kk + 1
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                if (2 * kk < nt) {
+                    const uint32_t ah[4] = {ph[2 * kk][0], ph[2 * kk][1], ph[2 * kk + 1][0], ph[2 * kk + 1][1]};
+                    const uint32_t al[4] = {pl[2 * kk][0], pl[2 * kk][1], pl[2 * kk + 1][0], pl[2 * kk + 1][1]};
+                    const int key = kc + 16 * kk + ((lane >> 3) & 1) * 8 + (lane & 7);
+#pragma unroll
+                    for (int d2 = 0; d2 < 4; ++d2) {               // two 8-dim tiles per ldmatrix.x4.trans: chunks 2 d2, 2 d2 + 1
+                        uint32_t b[4];
+                        ldsm_x4_t(b, vs_u + key * 128 + ((((2 * d2 + (lane >> 4)) ^ (key & 7))) << 4));
+                        mma_bf16(o[2 * d2], ah, b[0], b[1]);
+                        mma_bf16(o[2 * d2], al, b[0], b[1]);
+                        mma_bf16(o[2 * d2 + 1], ah, b[2], b[3]);
+                        mma_bf16(o[2 * d2 + 1], al, b[2], b[3]);
+                    }
+                }
+            }
+        }
+        l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+        l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+        const float i0 = 1.f / l0, i1 = 1.f / l1;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (q0 + g < P)
+                *reinterpret_cast<uint32_t*>(a.out + (size_t)(t0 + q0 + g) * hidden + h * 64 + 8 * j + 2 * t) = pack_bf16(o[j][0] * i0, o[j][1] * i0);
+            if (q0 + g + 8 < P)
+                *reinterpret_cast<uint32_t*>(a.out + (size_t)(t0 + q0 + g + 8) * hidden + h * 64 + 8 * j + 2 * t) = pack_bf16(o[j][2] * i1, o[j][3] * i1);
+        }
+    }
+}
+
 extern "C" int32_t t3b_prefill_attn_max_len(int32_t kv_dtype) {
     const int slice = kv_dtype == T3B_KV_FP8 ? KvFmt<1>::SLICE : KvFmt<0>::SLICE;
     return (220 * 1024 / (2 * slice)) * T3B_KV_BLOCK;
@@ -523,6 +676,12 @@ extern "C" int32_t t3b_prefill_attn(const void* q, int32_t n_seq, const int32_t*
     a.k_pool = (const unsigned char*)k_pool; a.v_pool = (const unsigned char*)v_pool; a.n_heads = n_heads; a.out = (bf16*)out;
     a.max_pages = (max_seq_len + 15) / 16;
     if (a.max_pages > max_blocks) a.max_pages = max_blocks;
+    if (kv_dtype == T3B_KV_BF16) {                     // tensor-core kernel: a warp per 16-query tile
+        const size_t smem_mma = (size_t)a.max_pages * 2 * 2048;
+        T3B_CUDA(cudaFuncSetAttribute(prefill_attn_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_mma));
+        T3B_CUDA(t3b_launch(prefill_attn_mma_kernel, dim3((unsigned)(n_seq * n_heads)), dim3(PM_NW * 32), smem_mma, t3b_stream(stream), a));
+        return T3B_OK;
+    }
     const int slice = kv_dtype == T3B_KV_FP8 ? KvFmt<1>::SLICE : KvFmt<0>::SLICE;
     const size_t smem = (size_t)a.max_pages * 2 * slice;
     auto kern = kv_dtype == T3B_KV_FP8 ? prefill_attn_kernel<1> : prefill_attn_kernel<0>;

@@ -317,13 +317,12 @@ class T3B200Engine:
         """Run the prompts of ``reqs`` (blocks already allocated, slots assigned) through the backbone in one multi-token pass
         per chunk, sample each request's first speech token and install its slot state."""
         st, dev, m = self.state, self.dev, self.m
-        bt = torch.zeros(2 * len(reqs), self.max_blocks, dtype=torch.int32)
-        bt_rows = []
-        for i, r in enumerate(reqs):
+        bt_rows, bt_host = [], []
+        for r in reqs:
             for half in (0, 1):
-                bt[2 * i + half, :len(r.blocks[half])] = torch.tensor(r.blocks[half], dtype=torch.int32)
+                bt_host.append(r.blocks[half] + [0] * (self.max_blocks - len(r.blocks[half])))
             bt_rows += [2 * r.slot, 2 * r.slot + 1]
-        st.block_tables[torch.tensor(bt_rows, device=dev)] = bt.to(dev)
+        st.block_tables[torch.tensor(bt_rows, device=dev)] = torch.tensor(bt_host, dtype=torch.int32).to(dev)
         chunks: List[List[_Req]] = [[]]
         ntok = 0
         for r in reqs:
@@ -354,11 +353,10 @@ class T3B200Engine:
             nreq = len(ch)
             tmp_state = DecodeState(nreq, self.max_blocks, self.max_len, self.max_len, dev)
             tmp_sp = SamplingTensors(nreq, dev, m.combine)
-            for j, r in enumerate(ch):
-                sp = r.sp
-                tmp_sp.set(j, cfg_scale=m.cfg_scale if sp.cfg_scale is None else sp.cfg_scale,
-                           repetition_penalty=sp.repetition_penalty, temperature=sp.temperature, min_p=sp.min_p,
-                           top_p=sp.top_p, seed=(r.rid if sp.seed is None else sp.seed), analyzer_text_tokens=sp.analyzer_text_tokens)
+            tmp_sp.set_many([dict(cfg_scale=m.cfg_scale if r.sp.cfg_scale is None else r.sp.cfg_scale,
+                                  repetition_penalty=r.sp.repetition_penalty, temperature=r.sp.temperature, min_p=r.sp.min_p,
+                                  top_p=r.sp.top_p, seed=(r.rid if r.sp.seed is None else r.sp.seed),
+                                  analyzer_text_tokens=r.sp.analyzer_text_tokens) for r in ch])
             tmp_state.stop_tokens.copy_(torch.tensor([r.sp.stop_token() for r in ch], dtype=torch.int32))
             tmp_state.active.fill_(1)
             toks = torch.empty(nreq, dtype=torch.int32, device=dev)

@@ -149,6 +149,16 @@ class SamplingTensors:
         self.seed[slot] = seed & 0x7FFFFFFFFFFFFFFF
         self.analyzer_text_tokens[slot] = analyzer_text_tokens
 
+    def set_many(self, rows: Sequence[dict]) -> None:
+        """Slots 0..len(rows)-1 from per-request dicts with the keys of ``set``: one host->device copy per field instead of seven
+        scalar stores per request (32 admitted requests: 224 tiny launches, ~3 ms of host time)."""
+        n = len(rows)
+        dev = self.cfg_scale.device
+        for name in ("cfg_scale", "repetition_penalty", "temperature", "min_p", "top_p"):
+            getattr(self, name)[:n] = torch.tensor([float(r[name]) for r in rows], dtype=torch.float32).to(dev, non_blocking=True)
+        self.seed[:n] = torch.tensor([int(r["seed"]) & 0x7FFFFFFFFFFFFFFF for r in rows], dtype=torch.int64).to(dev, non_blocking=True)
+        self.analyzer_text_tokens[:n] = torch.tensor([int(r.get("analyzer_text_tokens", 0)) for r in rows], dtype=torch.int32).to(dev, non_blocking=True)
+
     def fill(self, n: int, *, cfg_scale, repetition_penalty, temperature, min_p, top_p, seeds: Sequence[int]) -> None:
         self.cfg_scale[:n], self.repetition_penalty[:n], self.temperature[:n] = cfg_scale, repetition_penalty, temperature
         self.min_p[:n], self.top_p[:n] = min_p, top_p

@@ -67,16 +67,16 @@ class Sampling(C.Structure):        # t3b_sampling_t
 
 class Options(C.Structure):         # t3b_options_t
     _fields_ = [("gemv_max_rows", i32), ("gemv_no_norm", i32), ("umma_stages", i32), ("umma_row_chunk", i32),
-                ("umma_split", i32 * 4), ("attn_team_warps", i32), ("weight_prefetch", i32), ("umma_big_min_rows", i32)]
+                ("umma_split", i32 * 4), ("attn_team_warps", i32), ("weight_prefetch", i32), ("umma_big_min_rows", i32), ("norm_fusion", i32)]
 
 
 p_opt = C.POINTER(Options)
 
 
 def make_options(gemv_max_rows=0, gemv_no_norm=0, umma_stages=0, umma_row_chunk=0, umma_split=(0, 0, 0, 0), attn_team_warps=0,
-                 weight_prefetch=0, umma_big_min_rows=0) -> Options:
+                 weight_prefetch=0, umma_big_min_rows=0, norm_fusion=0) -> Options:
     return Options(gemv_max_rows, gemv_no_norm, umma_stages, umma_row_chunk, (i32 * 4)(*umma_split), attn_team_warps, weight_prefetch,
-                   umma_big_min_rows)
+                   umma_big_min_rows, norm_fusion)
 
 _PROTOS = {
     "t3b_last_error": (C.c_char_p, []),

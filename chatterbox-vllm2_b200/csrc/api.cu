@@ -10,7 +10,9 @@
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
                                const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf);
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, int stages_cap, int row_chunk, PfArgs pf, int w_wait, cudaStream_t s);
+                               int n_split, int epi, int stages_cap, int row_chunk, PfArgs pf, int w_wait, cudaStream_t s,
+                               const UmmaFuse* fuse);
+int32_t t3b_rmsnorm_s32_launch(const float* s32, const void* weight, void* y, int rows, int hidden, float eps, cudaStream_t stream);
 int32_t t3b_awq_dequant_launch(const t3b_linear_t* const* lins, int n_lin, void* scratch, cudaStream_t stream);
 int32_t t3b_linear_big_launch(const void* x, const void* w, int rows, int N, int K, void* y, int epi, cudaStream_t stream);
 int t3b_umma_pick_split(int rows, int N, int K);
@@ -25,6 +27,9 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
                               int max_blocks, const void* k_pool, const void* v_pool, int n_heads, int kv_dtype, void* out, int team_warps,
                               cudaStream_t s);
 
+#define NORM_FUSE_MIN_ROWS 9          // below: the two norm launches are cheaper than the operand build (4 rows: 0.877 -> 0.903 ms/step)
+#define NORM_FUSE_MAX_ROWS 32         // decode steps of 3..32 rows run F2.1 inside the projections (measured: 1.157 -> 1.076 ms/step at 32 rows;
+                                      // at 64 rows the operand build costs what the two launches saved: 1.351 -> 1.369, profiles/r2_notes.md r4)
 #define AWQ_DEQUANT_MIN_ROWS 256      // from here on AWQ layers are dequantised once per layer into a bf16 scratch (vllm awq.py:276-281 does the same)
 #define GEMV_MAX_ROWS_DEFAULT 2       // measured: 4 rows run 0.87 ms/step on the tcgen05 path, 0.96 on the GEMV (profiles/r02_notes.md)
 static thread_local char g_err[512] = "";
@@ -64,7 +69,7 @@ namespace {
 inline size_t al(size_t x) { return (x + 255) & ~size_t(255); }
 
 struct Workspace {
-    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *resid2, *deq;
+    char *x_emb, *resid, *normed, *qkv, *q, *attn, *act, *lin, *head, *resid2, *deq, *s32, *ssq;
     size_t total;
 };
 
@@ -86,6 +91,10 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
     // bf16 copy of ONE layer's projections for AWQ models at large row counts
     const bool awq_big = m->layers && m->layers[0].qkv.kind == T3B_W_AWQ && rows >= AWQ_DEQUANT_MIN_ROWS;
     w.deq = take(awq_big ? (3 * D * D + D * D + 2 * F * D + D * F) * 2 : 0);
+    // decode chain at <= 128 rows: fp32 residual sum + per-tile sums of squares handed from o / down to gate_up / qkv
+    const size_t Rf = R < NORM_FUSE_MAX_ROWS ? R : NORM_FUSE_MAX_ROWS;
+    w.s32 = take(Rf * D * 4);
+    w.ssq = take(Rf * (D / 128) * 4);
     w.total = static_cast<size_t>(p - static_cast<char*>(base));
     return w;
 }
@@ -98,10 +107,10 @@ extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
 }
 
 struct Opt {
-    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch, w_wait, big_min_rows;
+    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch, w_wait, big_min_rows, norm_fuse;
 };
 static Opt resolve(const t3b_options_t* o) {
-    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0, 1024};
+    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0, 1024, 1};      // norm_fuse: 0 never, 1 where faster, 2 wherever possible
     if (o) {
         if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > 4 ? 4 : o->gemv_max_rows);
         r.gemv_norm = o->gemv_no_norm ? 0 : 1;
@@ -110,6 +119,7 @@ static Opt resolve(const t3b_options_t* o) {
         for (int i = 0; i < 4; ++i) r.split[i] = o->umma_split[i] > 0 ? o->umma_split[i] : 0;
         r.attn_team = o->attn_team_warps;
         r.prefetch = o->weight_prefetch ? 1 : 0;
+        r.norm_fuse = o->norm_fusion < 0 ? 0 : (o->norm_fusion > 0 ? 2 : 1);
         if (o->umma_big_min_rows != 0) r.big_min_rows = o->umma_big_min_rows < 0 ? 0x7fffffff : o->umma_big_min_rows;
     }
     return r;
@@ -118,7 +128,7 @@ static Opt resolve(const t3b_options_t* o) {
 // ------------------------------------------------------------------ linear dispatch
 // epi: 0 = y[rows, n]; 1 = gate_up with the SiLU*mul epilogue -> y[rows, n/2].
 static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* y, float* partials, int n_split, int* n_split_out, int impl,
-                          int epi, const Opt& o, PfArgs pf, cudaStream_t s) {
+                          int epi, const Opt& o, PfArgs pf, cudaStream_t s, const UmmaFuse* fuse = nullptr) {
     T3B_CHECK_ARG(x && w && w->w, "linear: null pointer");
     T3B_CHECK_ARG(rows >= 0 && w->n > 0 && w->k > 0, "linear: bad sizes rows=%d n=%d k=%d", rows, w->n, w->k);
     T3B_CHECK_ALIGN(x); T3B_CHECK_ALIGN(w->w);
@@ -129,6 +139,7 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     T3B_CHECK_ARG(awq || w->kind == T3B_W_BF16, "linear: unknown weight kind %d", w->kind);
     if (impl == T3B_IMPL_AUTO) impl = (!awq && rows <= o.gemv_max_rows && w->k % 1024 == 0 && w->k <= 8192) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
     if (impl == T3B_IMPL_GEMV) {
+        T3B_CHECK_ARG(fuse == nullptr, "linear: the fused normalisation runs on the tcgen05 kernel only");
         T3B_CHECK_ARG(!awq, "linear: AWQ weights run on the dequant-fused tcgen05 kernel at every row count (no GEMV)");
         T3B_CHECK_ARG(n_split <= 1, "linear: the GEMV path has no split-K (n_split %d)", n_split);
         T3B_CHECK_ARG(y != nullptr, "linear: y is null");
@@ -146,10 +157,10 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     if (n_split_out) *n_split_out = n_split;
     // thousands of rows, no split-K, bf16 (AWQ layers arrive as their dequantised copy): the persistent double-buffered kernel.
     // (it requests weights after its dependency wait, so it is also safe on the AWQ scratch)
-    if (!awq && !legacy && n_split == 1 && rows >= o.big_min_rows)
+    if (!awq && !legacy && n_split == 1 && rows >= o.big_min_rows && !fuse)
         return t3b_linear_big_launch(x, w->w, rows, w->n, w->k, y, epi, s);
     return t3b_linear_umma_launch(x, w->w, awq ? w : nullptr, rows, w->n, w->k, y, legacy ? partials : nullptr, n_split, epi, o.stages,
-                                  o.row_chunk, pf, o.w_wait, s);
+                                  o.row_chunk, pf, o.w_wait, s, fuse);
 }
 
 extern "C" int32_t t3b_linear_bf16(const void* x, const t3b_linear_t* w, int32_t rows, void* y, float* partials, int32_t n_split,
@@ -213,6 +224,9 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     const bool deq = n_tok >= AWQ_DEQUANT_MIN_ROWS && m->layers[0].qkv.kind == T3B_W_AWQ;
     Opt ol = o;
     ol.w_wait = deq ? 1 : 0;
+    // 17..32 rows: a 3-deep ring leaves room for a block of the NEXT projection on the same SM, whose weight loads (issued before
+    // its dependency wait) then overlap this one (32 rows: 1.157 -> 1.115 ms/step without the folded norms, 1.134 -> 1.076 with)
+    if (!prefill && o.stages == 0 && n_tok > 16 && n_tok <= 32) ol.stages = 3;
     auto lin = [&](const void* x, const t3b_linear_t* w, void* y, int epi, PfArgs pf) -> int32_t {
         return linear_any(x, w, n_tok, y, nullptr, prefill ? 1 : 0, nullptr, prefill ? T3B_IMPL_UMMA : T3B_IMPL_AUTO, epi, ol, pf, s);
     };
@@ -253,6 +267,48 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
             xin = ws.lin;
         }
         return t3b_add_rmsnorm(xin, nullptr, 1, rcur, m->final_norm, hidden_out, n_tok, D, m->rms_eps, 1, stream);
+    }
+    // Decode steps at <= 128 rows (every projection runs the cluster split-K kernel): F2.1 is folded into the projections either
+    // side of it.  o / down add the residual in their epilogue and leave the fp32 sum plus per-tile sums of squares; gate_up / the
+    // next layer's qkv normalise their activation operand from those while the weight tiles are in flight.  5 launches per layer
+    // instead of 7; only layer 0's first normalisation and the final one stay kernels.
+    const bool fuse = !prefill && (o.norm_fuse == 2 || (o.norm_fuse == 1 && n_tok >= NORM_FUSE_MIN_ROWS)) && n_tok <= NORM_FUSE_MAX_ROWS &&
+                      n_tok > o.gemv_max_rows && D == 1024 && !deq &&
+                      t3b_umma_pick_split(n_tok, D, D) > 1 && t3b_umma_pick_split(n_tok, D, m->ffn) > 1 && o.split[1] != 1 && o.split[3] != 1;
+    if (fuse) {
+        float* s32 = reinterpret_cast<float*>(ws.s32);
+        float* ssq = reinterpret_cast<float*>(ws.ssq);
+        UmmaFuse f_out = {};
+        f_out.resid = ws.resid; f_out.s32 = s32; f_out.ssq = ssq;
+        auto lin_f = [&](const void* x, const t3b_linear_t* w, void* y, int epi, PfArgs pf, const UmmaFuse* f) -> int32_t {
+            return linear_any(x, w, n_tok, y, nullptr, 0, nullptr, T3B_IMPL_UMMA, epi, ol, pf, s, f);
+        };
+        for (int li = 0; li < m->n_layers; ++li) {
+            const t3b_layer_t* L = &m->layers[li];
+            T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
+            UmmaFuse f_in = {};
+            f_in.xs32 = s32; f_in.xssq = ssq; f_in.eps = m->rms_eps; f_in.ssq_tiles = D / 128;
+            if (li == 0) {
+                rc = t3b_add_rmsnorm(x0, nullptr, 1, ws.resid, L->ln1, ws.normed, n_tok, D, m->rms_eps, 0, stream);
+                if (rc) return rc;
+                rc = lin_f(ws.normed, &L->qkv, ws.qkv, T3B_EPI_NONE, pfw(&L->o), nullptr);
+            } else {
+                f_in.ln_w = L->ln1;
+                rc = lin_f(ws.normed, &L->qkv, ws.qkv, T3B_EPI_NONE, pfw(&L->o), &f_in);
+            }
+            if (rc) return rc;
+            rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), row_order, s);
+            if (rc) return rc;
+            rc = lin_f(ws.attn, &L->o, ws.lin, T3B_EPI_NONE, pfw(&L->down), &f_out);
+            if (rc) return rc;
+            f_in.ln_w = L->ln2;
+            rc = lin_f(ws.normed, &L->gate_up, ws.act, T3B_EPI_SILU_MUL, pf_after(li), &f_in);
+            if (rc) return rc;
+            rc = lin_f(ws.act, &L->down, ws.lin, T3B_EPI_NONE, pf_none(), &f_out);
+            if (rc) return rc;
+        }
+        return t3b_rmsnorm_s32_launch(s32, m->final_norm, hidden_out, n_tok, D, m->rms_eps, s);
     }
     const void* prev = x0;
     t3b_layer_t tmp = {};

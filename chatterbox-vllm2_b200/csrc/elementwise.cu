@@ -93,6 +93,45 @@ __global__ void __launch_bounds__(128) add_rmsnorm_kernel(const uint4* __restric
     }
 }
 
+// F2.1 over a row whose residual sum already exists in fp32 (left by the o / down projection's epilogue, linear_umma.cu EPI_RESID):
+// the last normalisation of the stack when the per-layer ones ride inside the projections.  Same arithmetic and the same
+// reduction order as add_rmsnorm_kernel.
+__global__ void __launch_bounds__(128) rmsnorm_s32_kernel(const float4* __restrict__ s32, const uint4* __restrict__ weight, uint4* __restrict__ y,
+                                                          int hidden8, float eps) {
+    __shared__ float red[4];
+    pdl_launch_dependents();
+    const int i = threadIdx.x;
+    const uint4 wraw = i < hidden8 ? __ldg(weight + i) : make_uint4(0, 0, 0, 0);
+    pdl_wait();
+    const int row = blockIdx.x;
+    float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    float ss = 0.f;
+    if (i < hidden8) {
+        const float4* p = s32 + ((size_t)row * hidden8 + i) * 2;
+        const float4 a = ld_act(p), b = ld_act(p + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss += v[e] * v[e];
+    }
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = ss;
+    __syncthreads();
+    const float tot = (red[0] + red[1]) + (red[2] + red[3]);
+    const float rstd = rsqrtf(tot / (float)(hidden8 * 8) + eps);
+    if (i < hidden8) {
+        float w[8], o[8];
+        unpack8(wraw, w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = bf16_round(v[e] * rstd) * w[e];
+        y[(size_t)row * hidden8 + i] = pack8(o);
+    }
+}
+int32_t t3b_rmsnorm_s32_launch(const float* s32, const void* weight, void* y, int rows, int hidden, float eps, cudaStream_t stream) {
+    T3B_CHECK_SHAPE(hidden % 8 == 0 && hidden <= 1024, "rmsnorm_s32: hidden %d unsupported", hidden);
+    T3B_CUDA(t3b_launch(rmsnorm_s32_kernel, dim3(rows), dim3(128), 0, stream, (const float4*)s32, (const uint4*)weight, (uint4*)y, hidden / 8, eps));
+    return T3B_OK;
+}
+
 // ------------------------------------------------------------------ F2.3 + KV write
 // One CTA per token, one warp per head: lane j rotates the pair (j, j+32) of q and k
 // (rotary_embedding/common.py:144-174 in bf16 tensor arithmetic: each product and the sum round).

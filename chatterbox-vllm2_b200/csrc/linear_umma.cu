@@ -28,6 +28,11 @@
 //            SILU   tile t = gate features [64t, 64t+64) in lanes 0..63 and up features [ffn + 64t, ..) in
 //                   lanes 64..127;  act[r, 64t + p] = bf16(bf16(silu(bf16 g)) * bf16 u)
 //                   (llama.py:117-121, activation.py:138-141).
+//            RESID  (o / down of a small decode step) s = bf16(acc) + resid in fp32; resid := bf16(s), s32 := s,
+//                   ssq[tile][r] := sum of s^2 over the tile's 128 features: F2.1's first half, done where the sum is born.
+// Normalising operand (xsrc, qkv / gate_up of the same steps): tmap_x describes the fp32 sums; the producer stages a
+//   [Rp][64] fp32 slice per k-block next to the operand stage and warps 4-11 (4-7 with AWQ) write
+//   bf16(bf16(s * rstd) * ln_w) into the swizzled X stage - F2.1's second half, so a layer is 5 launches instead of 7.
 // Legacy mode (partials != NULL): each split writes its fp32 tile to global memory [split][rows][N].
 //
 // grid = (ceil(N/128), n_split, ceil(rows/256)), cluster = (1, n_split, 1).
@@ -47,7 +52,7 @@
 #define UM_RAW_BYTES 4096                  // AWQ: 128 x 64 nibbles
 #define UM_MAX_STAGES 8
 
-enum { EPI_STORE = 0, EPI_SILU = 1 };
+enum { EPI_STORE = 0, EPI_SILU = 1, EPI_RESID = 2 };
 
 struct UmmaParams {
     bf16* y;                 // bf16 [rows, N] (STORE) or [rows, N/2] (SILU); NULL in legacy mode
@@ -61,6 +66,18 @@ struct UmmaParams {
     const unsigned char* zeros;   // u8 [K/128, N]
     PfArgs pf;               // weights of a later launch to pull into L2 (hint)
     int w_wait;              // 1 = the weights were written by an earlier kernel of the chain (AWQ scratch): no loads before the wait
+    // ---- F2.1 folded into the projections on either side of it (decode chain, rows <= 128; t3b_decode_step):
+    // producer (o / down, EPI_RESID): s = bf16(acc) + resid; resid := bf16(s); s32 := s (fp32); ssq[tile][row] := sum of s^2 over the tile
+    bf16* resid;             // bf16 [rows, N], updated in place
+    float* s32;              // fp32 [rows, N]
+    float* ssq;              // fp32 [N / 128, rows]
+    // consumer (qkv / gate_up, xsrc = 1): the activation operand is not fetched by TMA but built by the epilogue warps:
+    // x[r, k] = bf16(bf16(s32[r, k] * rstd[r]) * ln_w[k]),  rstd[r] = rsqrt(sum_t ssq[t][r] / K + eps)   (layernorm.py:40-59)
+    int xsrc, ssq_tiles;
+    const float* xs32;       // fp32 [rows, K]
+    const float* xssq;       // fp32 [ssq_tiles, rows]
+    const bf16* ln_w;        // bf16 [K]
+    float eps;
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
@@ -134,7 +151,7 @@ __device__ __forceinline__ void push_partials(uint32_t tmem_base, int quad, int 
 }
 
 template <int WSRC>
-__global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
+__global__ void __launch_bounds__(WSRC ? 512 : 384, 1) linear_umma_kernel(const __grid_constant__ CUtensorMap tmap_w,
                                                                           const __grid_constant__ CUtensorMap tmap_x,
                                                                           const UmmaParams p) {
     extern __shared__ unsigned char smem_dyn[];
@@ -143,7 +160,9 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     unsigned char* smem = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);
     const int stages = p.stages, Rp = p.Rp;
     const uint32_t x_bytes = (uint32_t)Rp * 128u;
-    const uint32_t stage_bytes = UM_A_BYTES + x_bytes + (WSRC ? UM_RAW_BYTES : 0);   // [A | X | raw]
+    const uint32_t sraw_off = UM_A_BYTES + x_bytes + (WSRC ? UM_RAW_BYTES : 0);
+    const uint32_t sraw_bytes = p.xsrc ? (uint32_t)Rp * 256u : 0u;                   // fp32 [Rp][64] slice of the residual sum
+    const uint32_t stage_bytes = sraw_off + sraw_bytes;                              // [A | X | raw nibbles | raw fp32 rows]
     // fp32 reduction buffer behind the ring (peers push into it while this CTA's pipeline may still be running):
     // n_split > 1: [n_split][Rp / n_split][128]; n_split == 1: a [16][128] exchange buffer; legacy: none
     const size_t ring_bytes = (size_t)stages * stage_bytes;
@@ -152,9 +171,12 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + body);
     uint64_t* empty_bar = full_bar + UM_MAX_STAGES;
     uint64_t* raw_bar = empty_bar + UM_MAX_STAGES;
-    uint64_t* tmem_full_bar = raw_bar + UM_MAX_STAGES;
+    uint64_t* sraw_bar = raw_bar + UM_MAX_STAGES;
+    uint64_t* tmem_full_bar = sraw_bar + UM_MAX_STAGES;
     uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
     float* red = reinterpret_cast<float*>(smem + ring_bytes);
+    float* rstd_s = reinterpret_cast<float*>(smem + body + 512);      // [128] (xsrc)
+    uint4* lnw_s = reinterpret_cast<uint4*>(smem + body + 1024);      // this split's slice of the norm weight, <= 16 k-blocks x 128 B (xsrc)
 
     pdl_launch_dependents();                     // the next kernel's launch latency overlaps this whole kernel (it waits before reading)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -169,9 +191,10 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
         if (!WSRC) tma_prefetch_desc(&tmap_w);
         tma_prefetch_desc(&tmap_x);
         for (int i = 0; i < stages; ++i) {
-            mbar_init(&full_bar[i], WSRC ? 1 + 8 : 1);      // producer (tx) [+ 8 dequant warps]
+            mbar_init(&full_bar[i], (WSRC ? 1 + 8 : 1) + (p.xsrc ? (WSRC ? 4 : 8) : 0));      // producer (tx) [+ 8 dequant warps] [+ operand-build warps]
             mbar_init(&empty_bar[i], 1);
             mbar_init(&raw_bar[i], 1);
+            mbar_init(&sraw_bar[i], 1);
         }
         mbar_init(tmem_full_bar, 1);
         mbar_fence_init();
@@ -192,7 +215,36 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
             tma_load_2d(st + UM_A_BYTES / 2, &tmap_w, &full_bar[s], (kb_begin + i) * UM_K, n_b);
         }
     };
-    const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + x_bytes;
+    // xsrc: builder thread bt of n_build turns the staged fp32 rows of every k-block into the swizzled bf16 operand
+    // (bf16: warps 4..11, AWQ: warps 4..7 - the dequant warps sit behind them)
+    const int n_build = WSRC ? 128 : 256;
+    auto build_x = [&](int bt) {
+        named_bar_sync(2, n_build);                          // rstd_s / lnw_s written by warps 4..7
+        const int ch = bt & 7, first = (bt >> 2) & 1;        // lanes 4..7 of each quarter-warp read their second half first: no bank conflicts
+        for (int i = 0; i < nkb; ++i) {
+            const int s = i % stages, round = i / stages;
+            unsigned char* st = smem + (size_t)s * stage_bytes;
+            unsigned char* xdst = st + UM_A_BYTES;
+            const uint4 wraw = lnw_s[i * 8 + ch];
+            mbar_wait(&sraw_bar[s], round & 1);              // (on a wrapped stage this also implies the MMAs that read it last round are done)
+            for (int row = bt >> 3; row < Rp; row += n_build / 8) {
+                const float4* sp = reinterpret_cast<const float4*>(st + sraw_off + row * 256 + ch * 32);   // rows past the end arrive as zeros
+                const float4 u = sp[first], v = sp[first ^ 1];
+                const float4 a = first ? v : u, b = first ? u : v;
+                const float sv[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                float w8[8], o[8];
+                unpack8(wraw, w8);
+                const float rs = rstd_s[row];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) o[e] = bf16_round(sv[e] * rs) * w8[e];
+                *reinterpret_cast<uint4*>(xdst + (row >> 3) * 1024 + (row & 7) * 128 + ((ch ^ (row & 7)) << 4)) = pack8(o);
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive(&full_bar[s]);
+        }
+    };
+    const uint32_t tx = (WSRC ? 0u : (uint32_t)UM_A_BYTES) + (p.xsrc ? 0u : x_bytes);
     const int pre = nkb < stages ? nkb : stages;
     // The first ring of weight tiles goes out before anything else: weights never depend on the previous kernel.  A TMA / bulk
     // copy instruction costs the issuing THREAD several hundred cycles (scripts/probe/bulk_bw.cu), so lane i of warp 0 issues the
@@ -211,15 +263,27 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
 
     if (warp == 0) {
         pdl_wait();
-        if (lane < pre)
-            tma_load_2d(smem + (size_t)lane * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[lane], (kb_begin + lane) * UM_K, rchunk * p.row_chunk);
+        // xsrc: tmap_x describes the fp32 residual sums; the slice lands in the stage's raw area and the build warps turn it into the operand
+        if (lane < pre) {
+            if (p.xsrc) {
+                mbar_expect_tx(&sraw_bar[lane], sraw_bytes);
+                tma_load_2d(smem + (size_t)lane * stage_bytes + sraw_off, &tmap_x, &sraw_bar[lane], (kb_begin + lane) * UM_K, rchunk * p.row_chunk);
+            } else {
+                tma_load_2d(smem + (size_t)lane * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[lane], (kb_begin + lane) * UM_K, rchunk * p.row_chunk);
+            }
+        }
         if (lane == 0) {
             for (int i = pre; i < nkb; ++i) {
                 const int s = i % stages, round = i / stages;
                 mbar_wait(&empty_bar[s], (round & 1) ^ 1);
                 mbar_expect_tx(&full_bar[s], tx);
                 load_w(i, s);
-                tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
+                if (p.xsrc) {
+                    mbar_expect_tx(&sraw_bar[s], sraw_bytes);
+                    tma_load_2d(smem + (size_t)s * stage_bytes + sraw_off, &tmap_x, &sraw_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
+                } else {
+                    tma_load_2d(smem + (size_t)s * stage_bytes + UM_A_BYTES, &tmap_x, &full_bar[s], (kb_begin + i) * UM_K, rchunk * p.row_chunk);
+                }
             }
         }
     } else if (warp == 1) {
@@ -276,11 +340,26 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
             if (lane == 0) mbar_arrive(&full_bar[s]);
         }
     } else if (warp >= 4 && warp < 8) {
+        if (p.xsrc)          // norm weights are constants: fetched before the dependency wait
+            for (int c = threadIdx.x - 128; c < nkb * 8; c += 128) lnw_s[c] = __ldg(reinterpret_cast<const uint4*>(p.ln_w + (size_t)kb_begin * UM_K) + c);
         pdl_wait();
         const int quad = warp & 3;
         const int f = quad * 32 + lane;          // feature row of the tile this thread reads from TMEM
         const int r0 = rchunk * p.row_chunk;
         const int valid = min(Rp, p.rows - r0);  // rows of this chunk that exist
+        if (p.xsrc) {
+            // ---- F2.1 on the way in: these four warps write the normalised activation tile of every k-block straight into the
+            // swizzled operand stage (the layout TMA would have produced: row r at (r >> 3) * 1024 + (r & 7) * 128, 16-byte chunk
+            // c at c ^ (r & 7)).  The row's sum of squares arrives as ssq_tiles partials, added in tile order.
+            const int tt = threadIdx.x - 128;
+            if (tt < Rp) {
+                float ss = 0.f;
+                if (r0 + tt < p.rows)
+                    for (int t8 = 0; t8 < p.ssq_tiles; ++t8) ss += ld_act(p.xssq + (size_t)t8 * p.rows + r0 + tt);
+                rstd_s[tt] = rsqrtf(ss / (float)(p.kb_total * UM_K) + p.eps);
+            }
+            build_x(tt);
+        }
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         if (p.partials != nullptr) {
@@ -353,13 +432,22 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
             }
         }
     }
+    if (!WSRC && warp >= 8 && p.xsrc) build_x((int)threadIdx.x - 128);      // bf16 + xsrc blocks carry four extra builder warps
     tc_fence_before();
     if (p.partials == nullptr && p.n_split > 1) {
+        // EPI_RESID: the residual values of this thread's first item are fetched while the cluster barrier collects the peers
+        uint4 r_pre = make_uint4(0u, 0u, 0u, 0u);
+        if (p.epi == EPI_RESID) {
+            pdl_wait();
+            const int it = (int)threadIdx.x, per = Rp / p.n_split;
+            const int r = rchunk * p.row_chunk + (it >> 4) * p.n_split + split;
+            if (it < per * 16 && r < p.rows) r_pre = ld_act(reinterpret_cast<const uint4*>(p.resid + (size_t)r * p.N + tile * UM_M + (it & 15) * 8));
+        }
         cluster_sync_all();                      // release / acquire: every peer's pushes into this CTA's buffer have landed
         // (per-owner mbarriers with remote arrives + an acquire.cluster wait instead of this barrier measured SLOWER: qkv 5.6 -> 6.0 us,
         //  o 4.0 -> 4.4, down 6.8 -> 7.5 - barrier.cluster is the cheapest cluster-wide rendezvous there is; profiles/r2_notes.md r3b)
         // after the barrier the producer / MMA warps are idle too: the pure store epilogues run on every thread of the block
-        const bool wide = p.epi == EPI_SILU || (p.epi == EPI_STORE && (p.N & 7) == 0);
+        const bool wide = p.epi == EPI_SILU || p.epi == EPI_RESID || (p.epi == EPI_STORE && (p.N & 7) == 0);
         const int nthr = wide ? (int)blockDim.x : 128;
         if (wide || (warp >= 4 && warp < 8)) {
             // The CTA owns rows {r0 + j * n_split + split}.  Item = (row j, 8 adjacent features): two LDS.128 per split, one
@@ -375,6 +463,33 @@ __global__ void __launch_bounds__(WSRC ? 512 : 256, 1) linear_umma_kernel(const 
                     float acc[8];
                     red_sum8(red, p.n_split, per, j, g * 8, acc);
                     *reinterpret_cast<uint4*>(p.y + (size_t)r * p.N + n) = pack8(acc);
+                }
+            } else if (p.epi == EPI_RESID) {
+                // ---- F2.1 on the way out (o / down): residual add, the fp32 sum for the consumer's normalisation and this tile's
+                // share of the row's sum of squares.  16 adjacent lanes hold one row of the tile.
+                for (int it0 = 0; it0 < per * 16; it0 += nthr) {
+                    const int it = it0 + t;
+                    const int j = it >> 4, g = it & 15, r = r0 + j * p.n_split + split, n = tile * UM_M + g * 8;
+                    const bool ok = it < per * 16 && r < p.rows;
+                    float ss = 0.f;
+                    if (ok) {
+                        float acc[8], rv[8];
+                        red_sum8(red, p.n_split, per, j, g * 8, acc);
+                        uint4* rp = reinterpret_cast<uint4*>(p.resid + (size_t)r * p.N + n);
+                        unpack8(it0 == 0 ? r_pre : ld_act(rp), rv);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            acc[e] = bf16_round(acc[e]) + rv[e];
+                            ss += acc[e] * acc[e];
+                        }
+                        *rp = pack8(acc);
+                        float4* sp = reinterpret_cast<float4*>(p.s32 + (size_t)r * p.N + n);
+                        sp[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+                        sp[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+                    }
+#pragma unroll
+                    for (int m = 8; m >= 1; m >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, m);
+                    if (ok && g == 0) p.ssq[(size_t)tile * p.rows + r] = ss;
                 }
             } else if (p.epi == EPI_STORE) {     // N not a multiple of 8 (the 8194-wide speech head): rows are not 16-byte aligned
                 const int n = tile * UM_M + t;
@@ -558,6 +673,19 @@ static int make_tmap(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t o
     return r == CUDA_SUCCESS ? 0 : (int)r;
 }
 
+// fp32 [outer, inner] row-major, box = 64 x box_outer, no swizzle: the residual sums the normalising operand path stages
+static int make_tmap_f32(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, uint32_t box_outer) {
+    auto enc = get_encode_fn();
+    if (!enc) return -1;
+    cuuint64_t gdim[2] = {inner, outer};
+    cuuint64_t gstride[1] = {inner * 4};
+    cuuint32_t box[2] = {UM_K, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)r;
+}
+
 int t3b_make_tmap_bf16(CUtensorMap* m, const void* ptr, uint64_t inner, uint64_t outer, uint32_t box_outer, bool weights) {
     return make_tmap(m, ptr, inner, outer, box_outer, weights);
 }
@@ -585,15 +713,15 @@ int t3b_umma_pick_split(int rows, int N, int K) {
 template <int WSRC>
 static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const UmmaParams& p, int tiles, int chunks, bool cluster,
                            cudaStream_t stream) {
-    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0);
+    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0) + (p.xsrc ? (uint32_t)p.Rp * 256u : 0u);
     const size_t ring = (size_t)p.stages * stage_bytes;
     const size_t red = !cluster ? 0 : (p.n_split > 1 ? (size_t)p.Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
-    const size_t smem = ring + red + 1024 + (3 * UM_MAX_STAGES + 3) * 8;
+    const size_t smem = ring + red + 1024 + 512 + 512 + 2048;
     auto kern = linear_umma_kernel<WSRC>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles, p.n_split, chunks);
-    cfg.blockDim = dim3(WSRC ? 512 : 256);
+    cfg.blockDim = dim3(WSRC ? 512 : (p.xsrc ? 384 : 256));
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[2];
@@ -614,17 +742,27 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
 // epi: EPI_STORE / EPI_SILU (bf16 output only).  awq == NULL: bf16 weights `w` [N, K].
 // stages_cap: ring depth cap (0 = 5); row_chunk_req: rows per thread block (0 = 128 with cluster split-K, 256 without).
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
-                               int n_split, int epi, int stages_cap, int row_chunk_req, PfArgs pf, int w_wait, cudaStream_t stream) {
+                               int n_split, int epi, int stages_cap, int row_chunk_req, PfArgs pf, int w_wait, cudaStream_t stream,
+                               const UmmaFuse* fuse) {
     T3B_CHECK_SHAPE(K % UM_K == 0 && K >= UM_K, "umma: K %d must be a multiple of 64", K);
     T3B_CHECK_SHAPE(rows >= 1, "umma: rows %d", rows);
     const int kb_total = K / UM_K;
     const bool legacy = partials != nullptr && n_split > 1;
     T3B_CHECK_ARG(n_split >= 1 && n_split <= kb_total, "umma: n_split %d not in [1, %d]", n_split, kb_total);
     T3B_CHECK_ARG(legacy || y != nullptr, "umma: y is null");
-    T3B_CHECK_ARG(x != nullptr, "umma: x is null");
+    T3B_CHECK_ARG(x != nullptr || (fuse && fuse->xs32), "umma: x is null");
     T3B_CHECK_ARG(legacy || n_split == 1 || n_split == 2 || n_split == 4 || n_split == 8, "umma: cluster split-K %d must be 1, 2, 4 or 8", n_split);
     T3B_CHECK_ARG(!(legacy && epi != EPI_STORE), "umma: fused epilogues need the bf16 output mode");
     T3B_CHECK_ARG(epi == EPI_STORE || epi == EPI_SILU, "umma: unknown epilogue %d", epi);
+    const bool f_out = fuse && fuse->resid, f_in = fuse && fuse->xs32;
+    if (f_out) {
+        T3B_CHECK_ARG(!legacy && n_split > 1 && epi == EPI_STORE && N % UM_M == 0 && rows <= 128 && fuse->s32 && fuse->ssq,
+                      "umma: the residual epilogue needs cluster split-K, <= 128 rows and N %d a multiple of 128", N);
+        epi = EPI_RESID;
+    }
+    if (f_in)
+        T3B_CHECK_ARG(!legacy && rows <= 128 && fuse->xssq && fuse->ln_w && fuse->ssq_tiles >= 1,
+                      "umma: the normalising operand path needs <= 128 rows and the producer's sums");
     if (epi == EPI_SILU) T3B_CHECK_SHAPE(N % 128 == 0, "umma: gate_up N %d must be a multiple of 128", N);
     if (awq) {
         T3B_CHECK_SHAPE(N % 128 == 0 && K % 128 == 0, "umma: AWQ needs N %d and K %d to be multiples of 128", N, K);
@@ -655,9 +793,11 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     p.rows = rows; p.N = N; p.kb_total = kb_total; p.n_split = n_split; p.Rp = Rp; p.row_chunk = row_chunk; p.epi = epi;
     p.pf = pf;
     p.w_wait = w_wait;
+    if (f_out) { p.resid = (bf16*)fuse->resid; p.s32 = fuse->s32; p.ssq = fuse->ssq; }
+    if (f_in) { p.xsrc = 1; p.xs32 = fuse->xs32; p.xssq = fuse->xssq; p.ln_w = (const bf16*)fuse->ln_w; p.eps = fuse->eps; p.ssq_tiles = fuse->ssq_tiles; }
     p.tmem_cols = 32;
     while ((int)p.tmem_cols < Rp) p.tmem_cols <<= 1;
-    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u + (awq ? UM_RAW_BYTES : 0);
+    const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)Rp * 128u + (awq ? UM_RAW_BYTES : 0) + (f_in ? (uint32_t)Rp * 256u : 0u);
     const uint32_t red_b = legacy ? 0u : (n_split > 1 ? (uint32_t)Rp * UM_M * 4u : 16u * UM_M * 4u);
     const uint32_t budget = 220u * 1024u - red_b;
     int stages = (int)(budget / stage_bytes);
@@ -681,7 +821,8 @@ int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t*
     memset(&tw, 0, sizeof(tw));
     int e1 = awq ? 0 : make_tmap(&tw, w, (uint64_t)K, (uint64_t)N, 64, true);
     memset(&tx, 0, sizeof(tx));
-    int e2 = make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
+    int e2 = f_in ? make_tmap_f32(&tx, fuse->xs32, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp)
+                  : make_tmap(&tx, x, (uint64_t)K, (uint64_t)rows, (uint32_t)Rp, false);
     if (e1 || e2) T3B_FAIL(T3B_ERR_CUDA, "umma: cuTensorMapEncodeTiled failed (%d, %d)", e1, e2);
     const int tiles = epi == EPI_SILU ? N / 128 : (N + UM_M - 1) / UM_M;
     if (awq) {

@@ -25,6 +25,19 @@ static inline cudaStream_t t3b_stream(void* s) { return reinterpret_cast<cudaStr
 // projection two launches ahead): the kernel's blocks pull their slices into L2 with bulk prefetches before they wait for their
 // own inputs, so HBM keeps streaming while the dependent chain (wait -> load x -> MMA -> exchange -> store) runs from L2.
 // bytes == 0: nothing.  A hint only - never affects results.
+// F2.1 folded into the tcgen05 projections of the decode chain (linear_umma.cu; rows <= 128, hidden = 8 tiles of 128).
+// resid != nullptr: producer (o / down) - the epilogue adds the residual, rewrites it, and leaves the fp32 sum + per-tile sums of squares.
+// xs32 != nullptr: consumer (qkv / gate_up) - the activation operand is normalised from those on the fly.
+struct UmmaFuse {
+    void* resid;             // bf16 [rows, N]
+    float* s32;              // fp32 [rows, N]
+    float* ssq;              // fp32 [N / 128, rows]
+    const float* xs32;       // fp32 [rows, K]
+    const float* xssq;       // fp32 [ssq_tiles, rows]
+    const void* ln_w;        // bf16 [K]
+    float eps;
+    int ssq_tiles;
+};
 struct PfArgs {
     const unsigned char* p;
     unsigned long long bytes;      // multiple of 16

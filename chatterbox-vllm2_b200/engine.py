@@ -100,7 +100,7 @@ class T3B200Engine:
     def __init__(self, model: T3B200Model, max_num_seqs: int = 32, max_model_len: int = 1200,
                  kv_blocks: Optional[int] = None, check_every: int = 8, prefill_chunk_tokens: int = 8192,
                  use_graphs: bool = True, kv_dtype: str = "bf16", share_prefix: bool = True, grow_steps: int = 32,
-                 admit_batch: Optional[int] = None, admit_wait_steps: int = 16):
+                 admit_batch: Optional[int] = None, admit_wait_steps: int = 16, norm_fusion: Optional[bool] = None):
         self.m = model
         self.dims: T3Dims = model.dims
         self.dev = model.device
@@ -139,7 +139,13 @@ class T3B200Engine:
             team = 8
             while team > 1 and items * team > 148 * 8:
                 team //= 2
-            self.opt = _lib.make_options(gemv_max_rows=0 if max_num_seqs == 1 else -1, attn_team_warps=team)
+            # Same rule for the norms folded into the projections (t3b_options_t.norm_fusion; pays at 16..32 rows): an engine whose
+            # largest step is in that range uses them at every step, any other engine never - ``norm_fusion=True / False`` overrides
+            # (engines of different sizes produce the same tokens only if they agree on it).
+            if norm_fusion is None:
+                norm_fusion = 16 <= 2 * max_num_seqs <= 32
+            self.opt = _lib.make_options(gemv_max_rows=0 if max_num_seqs == 1 else -1, attn_team_warps=team,
+                                         norm_fusion=1 if norm_fusion else -1)
         model.bind(self.kv, self.state)
         # One workspace for the engine's lifetime, sized for its largest launch: captured graphs hold its address, so it must
         # never move (the model's own growable scratch is not used here).
@@ -151,10 +157,15 @@ class T3B200Engine:
 
     def launches_per_step(self, n_slots: int) -> int:
         """Kernels one decode step launches: embed + per layer [norm, qkv, attention(+RoPE+KV write), o, norm,
-        gate_up(+SiLU*mul), down] + final norm + head + sampler (the two norms ride inside the GEMVs at <= 2 rows)."""
+        gate_up(+SiLU*mul), down] + final norm + head + sampler (the two norms ride inside the GEMVs at <= 2 rows and inside the
+        tcgen05 projections at 3..32 rows)."""
         rows = 2 * self._bucket(n_slots)
         gmax = 2 if self.opt.gemv_max_rows == 0 else max(0, min(4, self.opt.gemv_max_rows))
         gemv = rows <= gmax and self.m.quantization is None and not self.opt.gemv_no_norm
+        nf = self.opt.norm_fusion
+        if not gemv and rows <= 32 and (nf > 0 or (nf == 0 and rows >= 9)) and rows > gmax and self.dims.hidden == 1024:
+            # the norms ride inside the tcgen05 projections (csrc/api.cu forward_impl): layer 0's first norm is the only one left
+            return 1 + 1 + self.dims.n_layers * 5 + 3
         return 1 + self.dims.n_layers * (5 if gemv else 7) + 3
 
     def _bucket(self, n_slots: int) -> int:

@@ -156,6 +156,11 @@ typedef struct t3b_options {
                                     L2 (measured: no gain, the chain is latency-bound - profiles/r2_notes.md; default off)       */
     int32_t umma_big_min_rows;   /* bf16 projections without split-K run the persistent double-buffered tcgen05 kernel (csrc/linear_big.cu)
                                     from this many rows on (0 = default 1024: prefill passes and decode batches of >= 512 requests; < 0 = never)                       */
+    int32_t norm_fusion;         /* t3b_decode_step can fold add+RMSNorm into the tcgen05 projections either side of it (5 launches per layer
+                                    instead of 7; up to 32 rows).  0 = where it is measured faster (9..32 rows), 1 = wherever the shapes allow
+                                    (3..32 rows: what an engine picks so that every batch size it runs uses the same arithmetic), -1 = never.
+                                    The folded chain adds a row's sum of squares in a different order than the norm kernel: results agree
+                                    to a bf16 step, not bit for bit                                                                */
 } t3b_options_t;
 
 const char* t3b_last_error(void);

@@ -357,6 +357,37 @@ def test_gemv_norm_fold_equals_separate_norm_launches(L, small_model, rows):
     assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1]))
 
 
+@pytest.mark.parametrize("rows", [6, 16, 18, 32])
+def test_norm_folded_into_projections_matches_separate_norm_launches(L, small_model, rows):
+    """t3b_options_t.norm_fusion: at up to 32 rows the decode chain runs add + RMSNorm inside the o / down epilogues and the
+    qkv / gate_up operand build (5 launches per layer).  The arithmetic is the norm kernel's except for the order in which a row's
+    sum of squares is added (8 tile partials instead of 128 thread partials): rstd may move by one fp32 ulp, so the comparison with
+    the 7-launch chain is 'all but a few elements identical, the rest one or two bf16 steps apart'.  Layer 0's K/V (written before any
+    folded norm) must be bit-identical, the folded chain must be deterministic, and a row's result must not depend on the rows
+    beside it."""
+    m, _ = small_model
+    g = torch.Generator().manual_seed(rows)
+    lens = torch.randint(5, 300, (rows // 2,), generator=g).repeat_interleave(2).tolist()
+    outs = []
+    for mode in (1, -1, 1):
+        kv, st = random_state(SMALL, rows, lens, seed=5)
+        opt = _lib.make_options(gemv_max_rows=-1, norm_fusion=mode)
+        ws = m.workspace(rows)
+        hid = torch.empty(rows, 1024, dtype=torch.bfloat16, device=DEV)
+        _lib.check(L.t3b_decode_step(C.byref(m.c), C.byref(kv.c), C.byref(st.c), None, rows, hid.data_ptr(), ws.data_ptr(), ws.numel(),
+                                     C.byref(opt), sp()))
+        torch.cuda.synchronize()
+        outs.append((hid.clone(), kv.k.clone(), kv.v.clone()))
+    fused, plain, again = outs
+    assert all(torch.equal(a, b) for a, b in zip(fused, again))                       # deterministic
+    assert torch.equal(fused[1][0], plain[1][0]) and torch.equal(fused[2][0], plain[2][0])   # layer 0 K / V
+    hf, hp = fused[0].float(), plain[0].float()
+    assert torch.isfinite(hf).all()
+    same = (hf == hp).float().mean().item()
+    err = (hf - hp).abs().max().item() / hp.abs().max().item()
+    assert same > 0.8 and err < 2 ** -6, (same, err)
+
+
 @pytest.mark.parametrize("rows,chunk,stages", [(64, 32, 0), (64, 16, 3), (100, 48, 4), (64, 64, 2)])
 def test_umma_row_chunk_and_stage_options_do_not_change_results(L, rows, chunk, stages):
     """Row chunking / ring depth only move work between thread blocks: every output element keeps its K order -> bit-identical."""

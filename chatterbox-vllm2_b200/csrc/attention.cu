@@ -734,7 +734,11 @@ static int32_t attn_launch(bool fused, const AttnArgs& a, int kv_dtype, int team
     const int w = at_team_warps(a.n_items, team_warps);
     cudaError_t e;
     if (kv_dtype == T3B_KV_FP8) e = fused ? launch_ring_w<true, 5, 1>(a, w, s) : launch_ring_w<false, 5, 1>(a, w, s);
-    else e = fused ? launch_ring_w<true, 3, 0>(a, w, s) : launch_ring_w<false, 3, 0>(a, w, s);
+    // bf16: 2 pair slots per warp = 131 KB per block.  Bandwidth does not need a third slot (8 warps x 2 x 8 KB in flight per SM =
+    // 19 MB over the chip, more than twice the ~8 MB latency-bandwidth product of HBM), and at 131 KB a
+    // block of the o projection that follows (80 KB) fits on the SM beside it: 64 rows 1.337 -> 1.315 ms/step, 16 rows
+    // 0.982 -> 0.931, no config slower (profiles/r2_notes.md r4j).  fp8: 5 slots of 4.25 KB (measured in round 2).
+    else e = fused ? launch_ring_w<true, 2, 0>(a, w, s) : launch_ring_w<false, 2, 0>(a, w, s);
     T3B_CUDA(e);
     return T3B_OK;
 }

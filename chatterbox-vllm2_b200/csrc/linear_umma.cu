@@ -716,9 +716,10 @@ static int32_t launch_umma(const CUtensorMap& tw, const CUtensorMap& tx, const U
     const uint32_t stage_bytes = UM_A_BYTES + (uint32_t)p.Rp * 128u + (WSRC ? UM_RAW_BYTES : 0) + (p.xsrc ? (uint32_t)p.Rp * 256u : 0u);
     const size_t ring = (size_t)p.stages * stage_bytes;
     const size_t red = !cluster ? 0 : (p.n_split > 1 ? (size_t)p.Rp * UM_M * 4 : (size_t)16 * UM_M * 4);
-    const size_t smem = ring + red + 1024 + 512 + 512 + 2048;
+    const size_t smem = ring + red + 1024 + 512 + (p.xsrc ? 512 + 2048 : 0);      // alignment slack, barriers [, rstd + norm weights]
     auto kern = linear_umma_kernel<WSRC>;
     T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    T3B_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));   // see t3b_launch
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(tiles, p.n_split, chunks);
     cfg.blockDim = dim3(WSRC ? 512 : (p.xsrc ? 384 : 256));

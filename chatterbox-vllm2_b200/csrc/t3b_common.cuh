@@ -57,6 +57,10 @@ int t3b_num_sms();
 template <typename... KArgs, typename... Args>
 static inline cudaError_t t3b_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                                      cudaStream_t stream, Args... args) {
+    // Every kernel of the chain asks for the same L1 / shared-memory split (all shared): kernels with little shared memory would
+    // otherwise prefer L1, and an SM cannot hold blocks of two kernels that want different splits - which is what the programmatic
+    // launches are for (64 rows: 1.351 -> 1.339 ms/step; AWQ 1.527 -> 1.466; profiles/r2_notes.md r4g)
+    cudaFuncSetAttribute((const void*)kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
     cudaLaunchAttribute attr[1];

@@ -116,6 +116,30 @@ def test_configs1_shape_64_rows_vs_golden():
     check_greedy("configs1_64rows_teacher_forced", logits, toks, gold, TOL_30)
 
 
+class _GoldSlice:
+    """The first ``n`` requests of a batch fixture (requests are independent: request i is synthetic_request(i) in every batch)."""
+
+    def __init__(self, gold, n):
+        self._d = {"tokens": gold["tokens"][:n], "margins": gold["margins"][:, :n], "top_idx": gold["top_idx"][:, :n],
+                   "top_val": gold["top_val"][:, :n], "sample_idx": gold["sample_idx"], "sample_val": gold["sample_val"][:, :n]}
+        self.files = list(self._d)
+
+    def __getitem__(self, k):
+        return self._d[k]
+
+
+@pytest.mark.parametrize("n_req", [8, 16])
+def test_folded_norm_chain_16_and_32_rows_vs_golden(n_req):
+    """The decode chain with add + RMSNorm folded into the tcgen05 projections (t3b_options_t.norm_fusion, what an engine of 8..16
+    slots runs) at full depth: the first 8 / 16 requests of the configs[1] fixture, same tolerance as the 7-launch chain."""
+    gold = _GoldSlice(np.load(os.path.join(GOLD, "t3_full_batch32.npz")), n_req)
+    sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=16, ignore_eos=True)
+    m = full_model()
+    assert T3B200Engine(m, max_num_seqs=n_req, max_model_len=256, use_graphs=False).opt.norm_fusion == 1
+    logits, toks = run_teacher_forced(m, n_req, gold["tokens"], sp, max_model_len=256)
+    check_greedy(f"folded_norms_{2 * n_req}rows_teacher_forced", logits, toks, gold, TOL_30)
+
+
 def sampler_on_cuda_logits(logits, forced, seeds, rho=2.0, temperature=0.8, min_p=0.05, top_p=0.8):
     """oracle/sampler_ref.py on the CUDA logits of every step (history = the forced tokens before that step)."""
     T, B, _ = logits.shape

@@ -101,6 +101,7 @@ _PROTOS = {
     "t3b_decode_step": (i32, [C.POINTER(Model), C.POINTER(KV), C.POINTER(State), vp, i32, vp, vp, C.c_size_t, p_opt, vp]),
     "t3b_head_cfg_sample": (i32, [C.POINTER(Model), vp, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, vp,
                                   C.c_size_t, p_opt, vp]),
+    "t3b_head_cfg_sample_static": (i32, [C.POINTER(Model), vp, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, p_opt, vp]),
     "t3b_sample_logits": (i32, [vp, i32, i32, C.POINTER(Sampling), C.POINTER(State), vp, vp]),
     "t3b_cfg_sample_head_logits": (i32, [vp, i32, i32, C.POINTER(Sampling), C.POINTER(State), i32, vp, vp, vp]),
     "t3b_filter_speech_tokens": (i32, [vp, i32, i32, i32, vp, vp, vp]),

@@ -3,6 +3,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "t3b_common.cuh"
 
@@ -421,6 +422,59 @@ extern "C" int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden,
     rc = linear_any(hidden, &m->head, rows, ws.head, nullptr, 0, nullptr, T3B_IMPL_AUTO, T3B_EPI_NONE, resolve(opt), pf_none(), t3b_stream(stream));
     if (rc) return rc;
     return t3b_sampler_launch(ws.head, nullptr, 1, nullptr, m->speech_vocab, rows / 2, sp, st, advance, out_tokens, logits_out,
+                              t3b_stream(stream));
+}
+
+// ------------------------------------------------------------------ no-allocation variant of t3b_head_cfg_sample
+// The head logits of a step (bf16 [rows, speech_vocab], scratch between the head projection and the sampler) live in a file-scope
+// device array instead of a caller-provided workspace, so the call needs no allocation at all.  Every GPU that loads the library
+// holds the array (T3B_STATIC_SCRATCH_BYTES, ~1.03 MiB) until exit.  In host code `g_static_head` is only a stand-in for the
+// symbol, NOT a device address: the address comes from cudaGetSymbolAddress, once per device, with that device current.
+#define T3B_STATIC_SCRATCH_BYTES ((size_t)T3B_STATIC_MAX_ROWS * T3B_STATIC_MAX_VOCAB * 2 + 256)
+static __device__ __align__(256) unsigned char g_static_head[T3B_STATIC_SCRATCH_BYTES];
+
+#define T3B_MAX_DEVICES 64
+static void* g_static_head_ptr[T3B_MAX_DEVICES];      // per device; nullptr = not looked up yet
+static std::mutex g_static_mu;
+
+static int32_t static_head_scratch(void** out) {
+    int dev = -1;
+    T3B_CUDA(cudaGetDevice(&dev));
+    T3B_CHECK_ARG(dev >= 0 && dev < T3B_MAX_DEVICES, "static scratch: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (g_static_head_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_head);
+        if (e != cudaSuccess || p == nullptr)
+            T3B_FAIL(T3B_ERR_CUDA, "static scratch: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        g_static_head_ptr[dev] = p;
+    }
+    *out = g_static_head_ptr[dev];
+    return T3B_OK;
+}
+
+extern "C" int32_t t3b_head_cfg_sample_static(const t3b_model_t* m, const void* hidden, int32_t rows, const t3b_sampling_t* sp,
+                                              const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out,
+                                              const t3b_options_t* opt, void* stream) {
+    int32_t rc = check_model(m);
+    if (rc) return rc;
+    T3B_CHECK_ARG(hidden && sp, "t3b_head_cfg_sample_static: null pointer");
+    T3B_CHECK_ARG(rows >= 0 && rows % 2 == 0, "t3b_head_cfg_sample_static: rows %d must be even", rows);
+    T3B_CHECK_ARG(m->head.kind == T3B_W_BF16, "t3b_head_cfg_sample_static: speech_head must be bf16");
+    T3B_CHECK_ARG(rows <= T3B_STATIC_MAX_ROWS, "t3b_head_cfg_sample_static: rows %d exceed the static scratch (T3B_STATIC_MAX_ROWS = %d); "
+                  "use t3b_head_cfg_sample with a workspace", rows, T3B_STATIC_MAX_ROWS);
+    T3B_CHECK_ARG(m->speech_vocab <= T3B_STATIC_MAX_VOCAB, "t3b_head_cfg_sample_static: speech_vocab %d exceeds the static scratch "
+                  "(T3B_STATIC_MAX_VOCAB = %d); use t3b_head_cfg_sample with a workspace", m->speech_vocab, T3B_STATIC_MAX_VOCAB);
+    T3B_CHECK_ALIGN(hidden);
+    if (rows == 0) return T3B_OK;
+    void* head = nullptr;
+    rc = static_head_scratch(&head);
+    if (rc) return rc;
+    // nothing in the scratch has to start at zero: the projection writes every one of its rows x speech_vocab elements before
+    // the sampler reads them (the array keeps the previous call's logits until then)
+    rc = linear_any(hidden, &m->head, rows, head, nullptr, 0, nullptr, T3B_IMPL_AUTO, T3B_EPI_NONE, resolve(opt), pf_none(), t3b_stream(stream));
+    if (rc) return rc;
+    return t3b_sampler_launch(head, nullptr, 1, nullptr, m->speech_vocab, rows / 2, sp, st, advance, out_tokens, logits_out,
                               t3b_stream(stream));
 }
 

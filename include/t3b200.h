@@ -308,6 +308,25 @@ int32_t t3b_head_cfg_sample(const t3b_model_t* m, const void* hidden, int32_t ro
                             const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out,
                             void* workspace, size_t workspace_bytes, const t3b_options_t* opt, void* stream);
 
+/* t3b_head_cfg_sample without any allocation by anyone.  NO COUNTERPART IN THE REFERENCE: added
+ *     for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ *     forbid it).  Same arguments, outputs and state advance as t3b_head_cfg_sample, minus the workspace: the head logits
+ *     (bf16 [rows, speech_vocab], the scratch between the head projection and the sampler) live in a file-scope
+ *     `static __device__` array inside the library, T3B_STATIC_MAX_ROWS x T3B_STATIC_MAX_VOCAB bf16 + 256 B (~1.03 MiB), which
+ *     every GPU that loads the library holds until the process exits.  The call makes no cudaMalloc / cudaFree and calls no
+ *     allocating library routine; the array's device address is looked up once per device (cudaGetSymbolAddress, with that
+ *     device current - make the first call per device outside graph capture).
+ *     Limits: rows <= T3B_STATIC_MAX_ROWS (32 requests) and m->speech_vocab <= T3B_STATIC_MAX_VOCAB, else T3B_ERR_ARG with a
+ *     message naming the limit.  ALL calls on a device share the one array: it keeps the previous call's logits (nothing needs
+ *     to start at zero - the projection overwrites every element the sampler reads), and two calls that overlap on the GPU
+ *     (different streams, or graph branches without an edge between them) RACE; serialise them or use t3b_head_cfg_sample
+ *     with separate workspaces. */
+#define T3B_STATIC_MAX_ROWS  64
+#define T3B_STATIC_MAX_VOCAB 8448
+int32_t t3b_head_cfg_sample_static(const t3b_model_t* m, const void* hidden, int32_t rows, const t3b_sampling_t* sp,
+                                   const t3b_state_t* st, int32_t advance, int32_t* out_tokens, float* logits_out,
+                                   const t3b_options_t* opt, void* stream);
+
 /* S1..S4 alone on caller-provided combined fp32 logits [n_req, vocab] (parity tests of the sampler). */
 int32_t t3b_sample_logits(const float* logits, int32_t n_req, int32_t vocab, const t3b_sampling_t* sp,
                           const t3b_state_t* st, int32_t* out_tokens, void* stream);

@@ -242,6 +242,8 @@ def build_engine(batch, dev, sd=None, max_model_len=MAX_MODEL_LEN, quant=None, k
     for kv in [t for t in OPT_OVERRIDES.split(",") if t]:
         k, v = kv.split("=")
         setattr(eng.opt, k, int(v))
+    if eng.opt.gemv_mma > 0:
+        m.enable_gemv_mma()
     return m, eng, sd
 
 

@@ -67,16 +67,16 @@ class Sampling(C.Structure):        # t3b_sampling_t
 
 class Options(C.Structure):         # t3b_options_t
     _fields_ = [("gemv_max_rows", i32), ("gemv_no_norm", i32), ("umma_stages", i32), ("umma_row_chunk", i32),
-                ("umma_split", i32 * 4), ("attn_team_warps", i32), ("weight_prefetch", i32), ("umma_big_min_rows", i32), ("norm_fusion", i32)]
+                ("umma_split", i32 * 4), ("attn_team_warps", i32), ("weight_prefetch", i32), ("umma_big_min_rows", i32), ("norm_fusion", i32), ("gemv_mma", i32)]
 
 
 p_opt = C.POINTER(Options)
 
 
 def make_options(gemv_max_rows=0, gemv_no_norm=0, umma_stages=0, umma_row_chunk=0, umma_split=(0, 0, 0, 0), attn_team_warps=0,
-                 weight_prefetch=0, umma_big_min_rows=0, norm_fusion=0) -> Options:
+                 weight_prefetch=0, umma_big_min_rows=0, norm_fusion=0, gemv_mma=0) -> Options:
     return Options(gemv_max_rows, gemv_no_norm, umma_stages, umma_row_chunk, (i32 * 4)(*umma_split), attn_team_warps, weight_prefetch,
-                   umma_big_min_rows, norm_fusion)
+                   umma_big_min_rows, norm_fusion, gemv_mma)
 
 _PROTOS = {
     "t3b_last_error": (C.c_char_p, []),
@@ -89,6 +89,8 @@ _PROTOS = {
     "t3b_linear_bf16": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, p_opt, vp]),
     "t3b_linear_awq": (i32, [vp, C.POINTER(Linear), i32, vp, vp, i32, p_i32, i32, i32, p_opt, vp]),
     "t3b_repack_weights_awq": (i32, [vp, vp, vp, i32, i32, i32, vp, vp, vp, vp]),
+    "t3b_gemv_frag_bytes": (C.c_size_t, [i32, i32, i32]),
+    "t3b_repack_weights_gemv": (i32, [vp, i32, i32, i32, vp, vp]),
     "t3b_attn_decode_fused": (i32, [vp, i32, vp, vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, p_opt, vp]),
     "t3b_rope_kv_write": (i32, [vp, vp, i32, i32, vp, vp, vp, vp, i32, vp, i32, vp, vp, i32, i32, vp, vp]),
     "t3b_paged_attn_decode": (i32, [vp, i32, vp, vp, vp, i32, vp, vp, i32, i32, vp, p_opt, vp]),

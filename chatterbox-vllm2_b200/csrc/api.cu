@@ -9,7 +9,10 @@
 
 // implemented in the kernel translation units
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
-                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf);
+                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf, const void* wf);
+bool t3b_gemv_mma_ok(int N, int K, int mode);
+size_t t3b_gemv_frag_bytes_impl(int N, int K, int gate_up);
+int32_t t3b_gemv_frag_launch(const void* w, int N, int K, int gate_up, void* out, cudaStream_t s);
 int32_t t3b_linear_umma_launch(const void* x, const void* w, const t3b_linear_t* awq, int rows, int N, int K, void* y, float* partials,
                                int n_split, int epi, int stages_cap, int row_chunk, PfArgs pf, int w_wait, cudaStream_t s,
                                const UmmaFuse* fuse);
@@ -32,6 +35,7 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
 #define NORM_FUSE_MAX_ROWS 32         // decode steps of 3..32 rows run F2.1 inside the projections (measured: 1.157 -> 1.076 ms/step at 32 rows;
                                       // at 64 rows the operand build costs what the two launches saved: 1.351 -> 1.369, profiles/r2_notes.md r4)
 #define AWQ_DEQUANT_MIN_ROWS 256      // from here on AWQ layers are dequantised once per layer into a bf16 scratch (vllm awq.py:276-281 does the same)
+#define GEMV_MMA_DEFAULT 0            // t3b_options_t.gemv_mma = 0
 #define GEMV_MAX_ROWS_DEFAULT 2       // measured: 4 rows run 0.87 ms/step on the tcgen05 path, 0.96 on the GEMV (profiles/r02_notes.md)
 static thread_local char g_err[512] = "";
 
@@ -108,18 +112,20 @@ extern "C" size_t t3b_workspace_bytes(const t3b_model_t* m, int32_t max_rows) {
 }
 
 struct Opt {
-    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch, w_wait, big_min_rows, norm_fuse;
+    int gemv_max_rows, gemv_norm, stages, row_chunk, split[4], attn_team, prefetch, w_wait, big_min_rows, norm_fuse, gemv_mma;
 };
 static Opt resolve(const t3b_options_t* o) {
-    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0, 1024, 1};      // norm_fuse: 0 never, 1 where faster, 2 wherever possible
+    Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0, 1024, 1, GEMV_MMA_DEFAULT};      // norm_fuse: 0 never, 1 where faster, 2 wherever possible
     if (o) {
-        if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > 4 ? 4 : o->gemv_max_rows);
+        if (o->gemv_mma != 0) r.gemv_mma = o->gemv_mma > 0 ? 1 : 0;
+        const int cap = r.gemv_mma ? 8 : 4;
+        if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > cap ? cap : o->gemv_max_rows);
         r.gemv_norm = o->gemv_no_norm ? 0 : 1;
         r.stages = o->umma_stages > 0 ? o->umma_stages : 0;
         r.row_chunk = o->umma_row_chunk > 0 ? o->umma_row_chunk : 0;
         for (int i = 0; i < 4; ++i) r.split[i] = o->umma_split[i] > 0 ? o->umma_split[i] : 0;
         r.attn_team = o->attn_team_warps;
-        r.prefetch = o->weight_prefetch ? 1 : 0;
+        r.prefetch = o->weight_prefetch > 0 ? o->weight_prefetch : 0;
         r.norm_fuse = o->norm_fusion < 0 ? 0 : (o->norm_fusion > 0 ? 2 : 1);
         if (o->umma_big_min_rows != 0) r.big_min_rows = o->umma_big_min_rows < 0 ? 0x7fffffff : o->umma_big_min_rows;
     }
@@ -138,14 +144,17 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     if (rows == 0) { if (n_split_out) *n_split_out = 1; return T3B_OK; }
     const bool awq = w->kind == T3B_W_AWQ;
     T3B_CHECK_ARG(awq || w->kind == T3B_W_BF16, "linear: unknown weight kind %d", w->kind);
-    if (impl == T3B_IMPL_AUTO) impl = (!awq && rows <= o.gemv_max_rows && w->k % 1024 == 0 && w->k <= 8192) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
+    // the SIMT GEMV takes <= 4 rows of any K % 1024 == 0, the tensor-core GEMV <= 8 rows of the model's own K (1024 / 4096)
+    const bool mma = o.gemv_mma && !awq && w->scales != nullptr && t3b_gemv_mma_ok(w->n, w->k, epi);     // scales = the fragment-ordered copy
+    const bool gemv_fits = mma ? rows <= 8 : (rows <= 4 && w->k % 1024 == 0 && w->k <= 8192);
+    if (impl == T3B_IMPL_AUTO) impl = (!awq && rows <= o.gemv_max_rows && gemv_fits) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
     if (impl == T3B_IMPL_GEMV) {
         T3B_CHECK_ARG(fuse == nullptr, "linear: the fused normalisation runs on the tcgen05 kernel only");
         T3B_CHECK_ARG(!awq, "linear: AWQ weights run on the dequant-fused tcgen05 kernel at every row count (no GEMV)");
         T3B_CHECK_ARG(n_split <= 1, "linear: the GEMV path has no split-K (n_split %d)", n_split);
         T3B_CHECK_ARG(y != nullptr, "linear: y is null");
         if (n_split_out) *n_split_out = 1;
-        return t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, epi, s, nullptr, nullptr, nullptr, 0.f, 0, pf);
+        return t3b_linear_gemv_launch(x, w->w, rows, w->n, w->k, y, epi, s, nullptr, nullptr, nullptr, 0.f, 0, pf, mma ? w->scales : nullptr);
     }
     T3B_CHECK_ARG(impl == T3B_IMPL_UMMA, "linear: unknown impl %d", impl);
     const bool legacy = partials != nullptr && n_split > 1;      // explicit request for global fp32 partials
@@ -177,6 +186,15 @@ extern "C" int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t 
     T3B_CHECK_ARG(w->scales && w->zeros, "t3b_linear_awq: scales / zeros are null");
     T3B_CHECK_ARG(epilogue == T3B_EPI_NONE || epilogue == T3B_EPI_SILU_MUL, "t3b_linear_awq: unknown epilogue %d", epilogue);
     return linear_any(x, w, rows, y, partials, n_split, n_split_out, impl, epilogue, resolve(opt), pf_none(), t3b_stream(stream));
+}
+
+extern "C" size_t t3b_gemv_frag_bytes(int32_t n, int32_t k, int32_t gate_up) {
+    return t3b_gemv_mma_ok(n, k, gate_up) ? t3b_gemv_frag_bytes_impl(n, k, gate_up) : 0;
+}
+extern "C" int32_t t3b_repack_weights_gemv(const void* w, int32_t n, int32_t k, int32_t gate_up, void* out, void* stream) {
+    T3B_CHECK_ARG(w && out, "t3b_repack_weights_gemv: null pointer");
+    T3B_CHECK_ALIGN(w); T3B_CHECK_ALIGN(out);
+    return t3b_gemv_frag_launch(w, n, k, gate_up, out, t3b_stream(stream));
 }
 
 // ------------------------------------------------------------------ whole step
@@ -235,35 +253,58 @@ static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void
     // launches ahead into L2 (qkv -> o, attention -> gate_up, o -> down, gate_up -> the next layer's qkv / the speech head), so
     // the weight stream never waits for the dependent chain.  Prefill passes are compute-bound: no prefetch.
     const bool pfo = !prefill && o.prefetch;
-    auto pfw = [&](const t3b_linear_t* w) { return pfo ? pf_linear(w) : pf_none(); };
+    bool frag_pf = false;          // set below: the chain reads the fragment-ordered copies, so those are what gets prefetched
+    auto pfw = [&](const t3b_linear_t* w) {
+        if (!pfo) return pf_none();
+        if (frag_pf && w->kind == T3B_W_BF16 && w->scales != nullptr) {
+            PfArgs a;
+            a.p = static_cast<const unsigned char*>(w->scales);
+            a.bytes = t3b_gemv_frag_bytes_impl(w->n, w->k, 0) & ~15ull;        // same size for a gate_up copy
+            return a;
+        }
+        return pf_linear(w);
+    };
     auto pf_after = [&](int li) { return li + 1 < m->n_layers ? pfw(&m->layers[li + 1].qkv) : pfw(&m->head); };
     auto kpool = [&](int li) { return static_cast<char*>(kv->k) + (size_t)li * kv->layer_stride; };
     auto vpool = [&](int li) { return static_cast<char*>(kv->v) + (size_t)li * kv->layer_stride; };
     // Small batch (rows <= gemv_max_rows, bf16): F2.1 runs in front of the qkv / gate_up GEMVs (each block normalises the <= 4 rows
     // it needs anyway; block 0 writes the residual to the other ping-pong buffer) - 5 launches per layer, bit-identical to the
     // 7-launch path.
+    // tensor-core GEMV (<= 8 rows): every layer carries the fragment-ordered copies of its projections (t3b_repack_weights_gemv)
+    bool small_mma = o.gemv_mma && t3b_gemv_mma_ok(2 * m->ffn, D, 1);
+    for (int li = 0; small_mma && li < m->n_layers; ++li)
+        small_mma = m->layers[li].qkv.kind == T3B_W_BF16 && m->layers[li].gate_up.kind == T3B_W_BF16 && m->layers[li].qkv.scales != nullptr &&
+                    m->layers[li].gate_up.scales != nullptr;
     const bool small = !prefill && n_tok <= o.gemv_max_rows && o.gemv_norm && D == 1024 && m->layers[0].qkv.kind == T3B_W_BF16 &&
-                       m->layers[0].gate_up.kind == T3B_W_BF16 && m->ffn % 1024 == 0;
+                       m->layers[0].gate_up.kind == T3B_W_BF16 && m->ffn % 1024 == 0 && (small_mma || n_tok <= 4);
     if (small) {
+        frag_pf = small_mma;
         char* rcur = ws.resid;
         char* roth = ws.resid2;
         const void* xin = x0;
         for (int li = 0; li < m->n_layers; ++li) {
             const t3b_layer_t* L = &m->layers[li];
             T3B_CHECK_ARG(L->ln1 && L->ln2, "forward: layer %d norm weights are null", li);
-            rc = t3b_linear_gemv_launch(xin, L->qkv.w, n_tok, L->qkv.n, L->qkv.k, ws.qkv, 0, s, rcur, roth, L->ln1, m->rms_eps, li > 0, pfw(&L->o));
+            // weight_prefetch 1: every launch pulls the projection two launches ahead into L2; 2: the same projection of the NEXT layer
+            // (a whole layer ahead; gate_up rides on the attention launch, the speech head on the last layer's qkv)
+            const bool far = o.prefetch >= 2;
+            const t3b_layer_t* Ln = li + 1 < m->n_layers ? &m->layers[li + 1] : nullptr;
+            auto nxt = [&](const t3b_linear_t* w) { return w ? pfw(w) : pf_none(); };
+            rc = t3b_linear_gemv_launch(xin, L->qkv.w, n_tok, L->qkv.n, L->qkv.k, ws.qkv, 0, s, rcur, roth, L->ln1, m->rms_eps, li > 0,
+                                        far ? (Ln ? pfw(&Ln->qkv) : pfw(&m->head)) : pfw(&L->o), small_mma ? L->qkv.scales : nullptr);
             if (rc) return rc;
             { char* t = rcur; rcur = roth; roth = t; }
             rc = t3b_attn_fused_launch(ws.qkv, n_tok, tok_idx, rope_pos, m->rope_cos_sin, m->max_pos, block_tables, max_blocks, kpool(li),
-                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, pfw(&L->gate_up), row_order, s);
+                                       vpool(li), H, kv->dtype, ws.attn, o.attn_team, far ? nxt(Ln ? &Ln->gate_up : nullptr) : pfw(&L->gate_up),
+                                       row_order, s);
             if (rc) return rc;
-            rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE, pfw(&L->down));
+            rc = lin(ws.attn, &L->o, ws.lin, T3B_EPI_NONE, far ? nxt(Ln ? &Ln->o : nullptr) : pfw(&L->down));
             if (rc) return rc;
             rc = t3b_linear_gemv_launch(ws.lin, L->gate_up.w, n_tok, L->gate_up.n, L->gate_up.k, ws.act, 1, s, rcur, roth, L->ln2, m->rms_eps, 1,
-                                        pf_after(li));
+                                        far ? pf_none() : pf_after(li), small_mma ? L->gate_up.scales : nullptr);
             if (rc) return rc;
             { char* t = rcur; rcur = roth; roth = t; }
-            rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE, pf_none());
+            rc = lin(ws.act, &L->down, ws.lin, T3B_EPI_NONE, far ? nxt(Ln ? &Ln->down : nullptr) : pf_none());
             if (rc) return rc;
             xin = ws.lin;
         }

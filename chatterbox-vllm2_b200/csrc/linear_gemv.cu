@@ -219,18 +219,213 @@ static cudaError_t dispatch_gemv_r(const void* x, const void* w, int rows, int N
     return launch_gemv<R, 1, 4, 0>(x, w, rows, N, K, y, s, nz, pf);
 }
 
+// ------------------------------------------------------------------ rows <= 8 on the tensor cores (t3b_options_t.gemv_mma)
+// The SIMT kernel above spends 2 R + 1 ALU instructions per 8 weight bytes: gate_up is issue-bound from R = 2 on (4.2 us with
+// L2-resident weights, scripts/probe/gemv_probe.py) and R = 8 would be four times that.  Here a warp holds a 16-feature x 32 * STEPS
+// slice of W as mma.sync.m16n8k16 A fragments loaded STRAIGHT from global memory, before the dependency wait: lane (g, t) =
+// (lane >> 2, lane & 3) holds 16 bytes of feature g and of feature g + 8 at k = 32 s + 8 t per step s.  Read from the nn.Linear
+// layout that is 16 rows x 64 bytes per load instruction (measured: qkv 4.3 us vs 2.5 for the SIMT kernel on HBM-resident weights,
+// profiles/r5d_gemv_probe.log), so the kernel reads a copy of W in fragment order (t3b_repack_weights_gemv, 512 contiguous bytes
+// per load instruction; t3b_linear_t.scales of a bf16 projection).  The k order inside an MMA is
+// permuted (k 2t, 2t+1, 2t+8, 2t+9 of the instruction <- 8t + {0,1,2,3} / 8t + {4,5,6,7} of the slice), which a dot product does not
+// see as long as the B fragment (the activations, 8 rows = the n dimension, from padded shared memory) uses the same permutation.
+// The WARPS warps of a block split K; their 16 x 8 fp32 partials meet in shared memory and are summed in warp order
+// (deterministic, independent of the row count: a request's numbers do not depend on how many rows ride along).
+// MODE 1 (gate_up): tile rows 0..7 = gate features, 8..15 = the matching up features, so a thread owns both halves of a SiLU * mul.
+// TPB = 16-feature tiles per block (2 for gate_up: half as many blocks re-run the fused normalisation).
+__device__ __forceinline__ void gemv_mma16816(float* c, uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+template <int STEPS, int WARPS, int TPB, int MODE>
+__global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16* __restrict__ x, const uint4* __restrict__ wf, int rows, int N,
+                                                                     bf16* __restrict__ y, const GemvNorm nz, const PfArgs pf) {
+    constexpr int K = STEPS * 32 * WARPS, K8 = K / 8;
+    constexpr int XROW = K * 2 + 64;                               // bytes per activation row: +64 keeps the B-fragment loads conflict-free
+    __shared__ float s_red[8][4];
+    extern __shared__ __align__(16) unsigned char smem_mm[];
+    unsigned char* xs = smem_mm;                                    // [rows][XROW]
+    float* part = reinterpret_cast<float*>(smem_mm + (size_t)rows * XROW);      // [WARPS][TPB][128]
+    pdl_launch_dependents();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
+    const int n_out = (MODE == 1) ? N / 2 : N;
+    const int kb = warp * STEPS * 32 + t * 8;                       // this lane's first k (of the activations; the weights come pre-ordered)
+    uint4 wlo[TPB][STEPS], whi[TPB][STEPS];
+#pragma unroll
+    for (int tl = 0; tl < TPB; ++tl) {
+        // fragment-ordered copy (gemv_frag_kernel): [tile][k-step of 32][lo | hi][lane] x 16 bytes - a warp's load is 512 contiguous
+        // bytes, a warp's slice STEPS KB, a block's tile 32 K bytes
+        const uint4* p = wf + ((size_t)(blockIdx.x * TPB + tl) * (K / 32) + warp * STEPS) * 64 + lane;
+#pragma unroll
+        for (int st = 0; st < STEPS; ++st) { wlo[tl][st] = ldg_stream(p + st * 64); whi[tl][st] = ldg_stream(p + st * 64 + 32); }
+    }
+    if (threadIdx.x == 0) pf_slice(pf, blockIdx.x, gridDim.x);      // behind this block's own weight loads: a later launch's weights -> L2
+    uint4 nwraw = make_uint4(0, 0, 0, 0);
+    if (nz.norm_w != nullptr) nwraw = __ldg(reinterpret_cast<const uint4*>(nz.norm_w) + (threadIdx.x & 127));     // before the wait: constant
+    pdl_wait();
+    if (nz.norm_w != nullptr) {
+        // F2.1 in front (K == 1024, 256 threads): threads [128 h, 128 h + 128) take rows h, h + 2, h + 4, h + 6 - per row the arithmetic
+        // and summation order of add_rmsnorm_kernel<1> (128 threads x 8 elements, warp sums, (s0 + s1) + (s2 + s3))
+        const int h = threadIdx.x >> 7, i = threadIdx.x & 127, wq = (threadIdx.x >> 5) & 3;
+        float xv[4][8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int r = h + 2 * q;
+            float ss = 0.f;
+            if (r < rows) {
+                unpack8(ld_act(reinterpret_cast<const uint4*>(x) + (size_t)r * K8 + i), xv[q]);
+                if (nz.has_res) {
+                    float rv[8];
+                    unpack8(ld_act(reinterpret_cast<const uint4*>(nz.res_in) + (size_t)r * K8 + i), rv);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) xv[q][e] += rv[e];
+                }
+                if (blockIdx.x == 0) reinterpret_cast<uint4*>(nz.res_out)[(size_t)r * K8 + i] = pack8(xv[q]);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) ss += xv[q][e] * xv[q][e];
+            }
+            ss = warp_sum(ss);
+            if (lane == 0) s_red[r][wq] = ss;
+        }
+        __syncthreads();
+        float wv8[8];
+        unpack8(nwraw, wv8);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int r = h + 2 * q;
+            if (r < rows) {
+                const float tot = (s_red[r][0] + s_red[r][1]) + (s_red[r][2] + s_red[r][3]);
+                const float rstd = rsqrtf(tot / (float)K + nz.eps);
+                float o[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) o[e] = bf16_round(xv[q][e] * rstd) * wv8[e];
+                *reinterpret_cast<uint4*>(xs + (size_t)r * XROW + i * 16) = pack8(o);
+            }
+        }
+    } else {
+        for (int i = threadIdx.x; i < rows * K8; i += WARPS * 32) {
+            const int r = i / K8, col = i - r * K8;
+            *reinterpret_cast<uint4*>(xs + (size_t)r * XROW + col * 16) = ld_act(reinterpret_cast<const uint4*>(x) + i);
+        }
+    }
+    __syncthreads();
+
+    float c[TPB][4];
+#pragma unroll
+    for (int tl = 0; tl < TPB; ++tl) c[tl][0] = c[tl][1] = c[tl][2] = c[tl][3] = 0.f;
+    const unsigned char* xrow = xs + (size_t)g * XROW + (size_t)kb * 2;      // activation row g = column g of the B operand
+#pragma unroll
+    for (int st = 0; st < STEPS; ++st) {
+        uint4 xb = make_uint4(0, 0, 0, 0);
+        if (g < rows) xb = *reinterpret_cast<const uint4*>(xrow + st * 64);
+#pragma unroll
+        for (int tl = 0; tl < TPB; ++tl) {
+            gemv_mma16816(c[tl], wlo[tl][st].x, whi[tl][st].x, wlo[tl][st].y, whi[tl][st].y, xb.x, xb.y);
+            gemv_mma16816(c[tl], wlo[tl][st].z, whi[tl][st].z, wlo[tl][st].w, whi[tl][st].w, xb.z, xb.w);
+        }
+    }
+    // c[0..3] = (feature g, rows 2t / 2t+1), (feature g + 8, rows 2t / 2t+1): slot (g * 4 + t) * 4 + j of the warp's partial tile
+#pragma unroll
+    for (int tl = 0; tl < TPB; ++tl)
+        *reinterpret_cast<float4*>(part + ((size_t)(warp * TPB + tl) * 32 + lane) * 4) = make_float4(c[tl][0], c[tl][1], c[tl][2], c[tl][3]);
+    __syncthreads();
+    if (MODE == 1) {
+        // thread -> (tile, row, gate feature f): 8 adjacent features of a row are adjacent in y
+        for (int i = threadIdx.x; i < TPB * 64; i += WARPS * 32) {
+            const int tl = i >> 6, r = (i >> 3) & 7, f = i & 7;
+            if (r >= rows) continue;
+            const int slot = ((f * 4 + (r >> 1)) * 4) + (r & 1);
+            float gs = 0.f, us = 0.f;
+#pragma unroll
+            for (int wp = 0; wp < WARPS; ++wp) {
+                gs += part[(size_t)(wp * TPB + tl) * 128 + slot];
+                us += part[(size_t)(wp * TPB + tl) * 128 + slot + 2];
+            }
+            const float gg = bf16_round(gs), u = bf16_round(us);
+            y[(size_t)r * n_out + (blockIdx.x * TPB + tl) * 8 + f] = __float2bfloat16_rn(bf16_round(gg / (1.0f + expf(-gg))) * u);
+        }
+    } else {
+        for (int i = threadIdx.x; i < TPB * 128; i += WARPS * 32) {
+            const int tl = i >> 7, r = (i >> 4) & 7, f = i & 15;
+            const int n = (blockIdx.x * TPB + tl) * 16 + f;
+            if (r >= rows || n >= N) continue;
+            const int slot = (((f & 7) * 4 + (r >> 1)) * 4) + (f >> 3) * 2 + (r & 1);
+            float a = 0.f;
+#pragma unroll
+            for (int wp = 0; wp < WARPS; ++wp) a += part[(size_t)(wp * TPB + tl) * 128 + slot];
+            y[(size_t)r * N + n] = __float2bfloat16_rn(a);
+        }
+    }
+}
+
+template <int STEPS, int WARPS, int TPB, int MODE>
+static cudaError_t launch_gemv_mma(const void* x, const void* wf, int rows, int N, void* y, cudaStream_t s, const GemvNorm& nz,
+                                   const PfArgs& pf) {
+    constexpr int K = STEPS * 32 * WARPS;
+    const int tiles = MODE == 1 ? N / 16 : (N + 15) / 16;
+    const size_t smem = (size_t)rows * (K * 2 + 64) + (size_t)WARPS * TPB * 512;
+    auto kern = linear_gemv_mma_kernel<STEPS, WARPS, TPB, MODE>;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    return t3b_launch(kern, dim3(tiles / TPB), dim3(WARPS * 32), smem, s, (const bf16*)x, (const uint4*)wf, rows, N, (bf16*)y, nz, pf);
+}
+
+// shapes of the tensor-core GEMV: K = 1024 (8 warps x 4 steps) or 4096 (16 warps x 8 steps); gate_up needs N / 2 % 16 == 0
+bool t3b_gemv_mma_ok(int N, int K, int mode) {
+    if (K == 1024) return mode ? (N % 32 == 0) : true;
+    return K == 4096 && mode == 0;
+}
+
+// W bf16 [N, K] (nn.Linear) -> the fragment order of linear_gemv_mma_kernel: out[tile][ks][half][lane] (16 bytes each) =
+// W[row(tile, lane >> 2, half)][32 ks + 8 (lane & 3) .. + 8); rows past N (the 8194-wide head) repeat row N - 1 (never stored).
+__global__ void gemv_frag_kernel(const uint4* __restrict__ w, int N, int K, int gate_up, uint4* __restrict__ out, size_t total) {
+    const int ksteps = K / 32;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int lane = (int)(i & 31), half = (int)((i >> 5) & 1);
+        const size_t rest = i >> 6;
+        const int ks = (int)(rest % (size_t)ksteps), tile = (int)(rest / (size_t)ksteps);
+        const int g = lane >> 2, t = lane & 3;
+        int row = gate_up ? (half ? N / 2 + tile * 8 + g : tile * 8 + g) : tile * 16 + g + 8 * half;
+        row = min(row, N - 1);
+        out[i] = w[((size_t)row * K + ks * 32 + t * 8) / 8];
+    }
+}
+size_t t3b_gemv_frag_bytes_impl(int N, int K, int gate_up) {
+    const size_t tiles = gate_up ? (size_t)N / 16 : ((size_t)N + 15) / 16;
+    return tiles * 16 * (size_t)K * 2;
+}
+int32_t t3b_gemv_frag_launch(const void* w, int N, int K, int gate_up, void* out, cudaStream_t s) {
+    T3B_CHECK_SHAPE(t3b_gemv_mma_ok(N, K, gate_up), "gemv repack: N %d K %d gate_up %d is not a shape of the tensor-core GEMV", N, K, gate_up);
+    const size_t total = t3b_gemv_frag_bytes_impl(N, K, gate_up) / 16;
+    gemv_frag_kernel<<<1184, 256, 0, s>>>((const uint4*)w, N, K, gate_up, (uint4*)out, total);
+    T3B_LAUNCH_CHECK();
+    return T3B_OK;
+}
+
 // mode: 0 = y[rows, N]; 1 = gate_up with fused SiLU*mul -> y[rows, N/2]
 int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, int K, void* y, int mode, cudaStream_t s,
-                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf) {
+                               const void* res_in, void* res_out, const void* norm_w, float eps, int has_res, PfArgs pf, const void* wf) {
     GemvNorm nz = {(const bf16*)res_in, (bf16*)res_out, (const bf16*)norm_w, eps, has_res};
     if (norm_w != nullptr) {
         T3B_CHECK_SHAPE(K == 1024, "gemv: the fused norm needs K == 1024 (got %d)", K);
         T3B_CHECK_ARG(res_out != nullptr && (!has_res || res_in != nullptr) && res_in != res_out, "gemv: fused norm needs res_out != res_in");
     }
-    T3B_CHECK_SHAPE(rows >= 1 && rows <= 4, "gemv: rows %d not in [1,4]", rows);
-    T3B_CHECK_SHAPE(K % 1024 == 0 && K <= 8192, "gemv: K %d must be a multiple of 1024 (<= 8192)", K);
     T3B_CHECK_SHAPE(mode == 0 || N % 4 == 0, "gemv: gate_up N %d", N);
     cudaError_t e;
+    if (wf != nullptr) {        // tensor-core GEMV on the fragment-ordered copy of w
+        T3B_CHECK_SHAPE(t3b_gemv_mma_ok(N, K, mode), "gemv (tensor-core): N %d K %d", N, K);
+        T3B_CHECK_SHAPE(rows >= 1 && rows <= 8, "gemv (tensor-core): rows %d not in [1,8]", rows);
+        if (K == 4096) e = launch_gemv_mma<8, 16, 1, 0>(x, wf, rows, N, y, s, nz, pf);
+        else if (mode) e = launch_gemv_mma<4, 8, 2, 1>(x, wf, rows, N, y, s, nz, pf);
+        else e = launch_gemv_mma<4, 8, 1, 0>(x, wf, rows, N, y, s, nz, pf);
+        T3B_CUDA(e);
+        return T3B_OK;
+    }
+    T3B_CHECK_SHAPE(rows >= 1 && rows <= 4, "gemv: rows %d not in [1,4]", rows);
+    T3B_CHECK_SHAPE(K % 1024 == 0 && K <= 8192, "gemv: K %d must be a multiple of 1024 (<= 8192)", K);
     if (rows == 1) e = mode ? dispatch_gemv_r<1, 1>(x, w, rows, N, K, y, s, nz, pf) : dispatch_gemv_r<1, 0>(x, w, rows, N, K, y, s, nz, pf);
     else if (rows == 2) e = mode ? dispatch_gemv_r<2, 1>(x, w, rows, N, K, y, s, nz, pf) : dispatch_gemv_r<2, 0>(x, w, rows, N, K, y, s, nz, pf);
     else e = mode ? dispatch_gemv_r<4, 1>(x, w, rows, N, K, y, s, nz, pf) : dispatch_gemv_r<4, 0>(x, w, rows, N, K, y, s, nz, pf);

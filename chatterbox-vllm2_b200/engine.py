@@ -25,6 +25,7 @@ from . import _lib
 from .constants import CONDITIONING_SIZE, KV_BLOCK, SPEECH_TOKEN_OFFSET, T3Dims
 from .model import (START_SPEECH_TOKEN, STOP_SPEECH_TOKEN, DecodeState, KVPool, SamplingTensors, T3B200Model)
 
+GEMV_MMA_MAX_SEQS = 4            # engines of up to this many requests (<= 8 CFG rows) run the tensor-core GEMV chain by default
 SHARED_PREFIX_BLOCKS = (CONDITIONING_SIZE // KV_BLOCK)          # 2 blocks = positions 0..31 of the 34-row conditioning prefix
 
 
@@ -100,7 +101,8 @@ class T3B200Engine:
     def __init__(self, model: T3B200Model, max_num_seqs: int = 32, max_model_len: int = 1200,
                  kv_blocks: Optional[int] = None, check_every: int = 8, prefill_chunk_tokens: int = 8192,
                  use_graphs: bool = True, kv_dtype: str = "bf16", share_prefix: bool = True, grow_steps: int = 32,
-                 admit_batch: Optional[int] = None, admit_wait_steps: int = 16, norm_fusion: Optional[bool] = None):
+                 admit_batch: Optional[int] = None, admit_wait_steps: int = 16, norm_fusion: Optional[bool] = None,
+                 gemv_mma: Optional[bool] = None):
         self.m = model
         self.dims: T3Dims = model.dims
         self.dev = model.device
@@ -144,8 +146,16 @@ class T3B200Engine:
             # (engines of different sizes produce the same tokens only if they agree on it).
             if norm_fusion is None:
                 norm_fusion = 16 <= 2 * max_num_seqs <= 32
-            self.opt = _lib.make_options(gemv_max_rows=0 if max_num_seqs == 1 else -1, attn_team_warps=team,
-                                         norm_fusion=1 if norm_fusion else -1)
+            # Engines of up to 4 requests (<= 8 CFG rows, bf16): the tensor-core GEMV chain (t3b_options_t.gemv_mma, 5 launches per
+            # layer) at every live-row count, on fragment-ordered copies of the weights made here once (+1 GB), every launch pulling
+            # the next layer's copy of its projection into L2 (1 request 0.57 -> 0.50 ms/step, 2 requests 0.87 -> 0.57, 4 requests
+            # 0.91 -> 0.70; profiles/r2_notes.md r5).  ``gemv_mma=False`` keeps the SIMT GEMV (1 request) / tcgen05 (2..4) chain.
+            if gemv_mma is None:
+                gemv_mma = max_num_seqs <= GEMV_MMA_MAX_SEQS
+            gemv_mma = bool(gemv_mma) and 2 * max_num_seqs <= 8 and model.enable_gemv_mma()
+            self.opt = _lib.make_options(gemv_max_rows=8 if gemv_mma else (0 if max_num_seqs == 1 else -1), attn_team_warps=team,
+                                         norm_fusion=1 if norm_fusion else -1, gemv_mma=1 if gemv_mma else -1,
+                                         weight_prefetch=2 if gemv_mma else 0)
         model.bind(self.kv, self.state)
         # One workspace for the engine's lifetime, sized for its largest launch: captured graphs hold its address, so it must
         # never move (the model's own growable scratch is not used here).
@@ -160,7 +170,7 @@ class T3B200Engine:
         gate_up(+SiLU*mul), down] + final norm + head + sampler (the two norms ride inside the GEMVs at <= 2 rows and inside the
         tcgen05 projections at 3..32 rows)."""
         rows = 2 * self._bucket(n_slots)
-        gmax = 2 if self.opt.gemv_max_rows == 0 else max(0, min(4, self.opt.gemv_max_rows))
+        gmax = 2 if self.opt.gemv_max_rows == 0 else max(0, min(8 if self.opt.gemv_mma > 0 else 4, self.opt.gemv_max_rows))
         gemv = rows <= gmax and self.m.quantization is None and not self.opt.gemv_no_norm
         nf = self.opt.norm_fusion
         if not gemv and rows <= 32 and (nf > 0 or (nf == 0 and rows >= 9)) and rows > gmax and self.dims.hidden == 1024:

@@ -237,6 +237,7 @@ class T3B200Model:
         bf = lambda t: t.detach().to(device=dev, dtype=torch.bfloat16).contiguous()
         need = lambda k: raw[k] if k in raw else (_ for _ in ()).throw(KeyError(f"load_weights: missing {k}"))
         layers = (_lib.Layer * d.n_layers)()
+        self._gemv_frag = False
         for i in range(d.n_layers):
             p = f"tfmr.layers.{i}."
             qkv = bf(torch.cat([need(p + "self_attn.q_proj.weight"), need(p + "self_attn.k_proj.weight"),
@@ -291,6 +292,29 @@ class T3B200Model:
         k, n = qweight.shape[0], qweight.shape[1] * 8
         q = repack(qweight, qzeros, scales, self.device, gate_up=(name == "gate_up"))
         setattr(self._layers[layer], name, self._awq_struct(f"{layer}.{name}", q, n, k, name == "gate_up"))
+
+    def enable_gemv_mma(self) -> bool:
+        """Fragment-ordered copies of the bf16 projections and the speech head (t3b_repack_weights_gemv) for the tensor-core GEMV
+        of decode steps of <= 8 rows (t3b_options_t.gemv_mma): a second copy of the weights (+1.0 GB for T3; a step still streams
+        one copy), made once.  False (nothing done) for quantised models and shapes the kernel does not take."""
+        L = self._require()
+        if self.quantization is not None:
+            return False
+        if getattr(self, "_gemv_frag", False):
+            return True
+        d = self.dims
+        jobs = [(f"{i}.{nm}", getattr(self._layers[i], nm), nm == "gate_up") for i in range(d.n_layers) for nm in ("qkv", "o", "gate_up", "down")]
+        jobs.append(("head", self.c.head, False))
+        if any(L.t3b_gemv_frag_bytes(lin.n, lin.k, int(gu)) == 0 for _, lin, gu in jobs):
+            return False
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        for key, lin, gu in jobs:
+            out = torch.empty(L.t3b_gemv_frag_bytes(lin.n, lin.k, int(gu)), dtype=torch.uint8, device=self.device)
+            _lib.check(L.t3b_repack_weights_gemv(self.w[key].data_ptr(), lin.n, lin.k, int(gu), out.data_ptr(), stream), "t3b_repack_weights_gemv")
+            self.w["frag." + key] = out
+            lin.scales = out.data_ptr()
+        self._gemv_frag = True
+        return True
 
     def weight_bytes(self) -> int:
         """Bytes streamed from HBM per decode step (layers + final norm + head)."""

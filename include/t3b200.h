@@ -70,7 +70,8 @@ typedef struct t3b_linear {
     int32_t kind;                /* T3B_W_* */
     int32_t n, k;                /* out features, in features */
     const void* w;               /* bf16 [n,k]  |  AWQ repacked nibbles */
-    const void* scales;          /* AWQ: bf16 [k/128, n]          (else NULL) */
+    const void* scales;          /* AWQ: bf16 [k/128, n].  bf16: NULL, or the copy of w in the fragment order of the tensor-core GEMV
+                                    (t3b_repack_weights_gemv) - with it and t3b_options_t.gemv_mma, <= 8 rows run that kernel   */
     const void* zeros;           /* AWQ: uint8 [k/128, n]         (else NULL) */
     int32_t flags;               /* T3B_LIN_* */
 } t3b_linear_t;
@@ -146,14 +147,16 @@ typedef struct t3b_sampling {    /* per-request device arrays [B]; tts.py:455-46
 /* Launch-shape knobs of the decode path (NULL / 0 fields = the library's measured defaults).  Everything that used to be an
  * environment variable inside the library is an explicit argument here. */
 typedef struct t3b_options {
-    int32_t gemv_max_rows;       /* bf16 projections use the SIMT GEMV up to this many rows (0 = default 2, max 4; -1 = never) */
+    int32_t gemv_max_rows;       /* bf16 projections use the GEMV kernels up to this many rows (0 = default 2, max 4 - 8 with gemv_mma; -1 = never) */
     int32_t gemv_no_norm;        /* 1 = keep add+RMSNorm as separate launches at GEMV row counts (default: folded in)     */
     int32_t umma_stages;         /* tcgen05 GEMM: shared-memory ring depth cap (0 = default 5)                             */
     int32_t umma_row_chunk;      /* tcgen05 GEMM: CFG rows per thread block, multiple of 16 (0 = default)                  */
     int32_t umma_split[4];       /* cluster split-K of the qkv / o / gate_up / down projections (0 = automatic)            */
     int32_t attn_team_warps;     /* decode attention: warps that share one (row, head) item: 1, 2, 4 or 8 (0 = by item count) */
     int32_t weight_prefetch;     /* 1 = every launch of t3b_decode_step pulls the weights of the projection two launches ahead into
-                                    L2 (measured: no gain, the chain is latency-bound - profiles/r2_notes.md; default off)       */
+                                    L2; 2 (GEMV chains only) = the same projection of the NEXT layer, a whole layer ahead.  No gain where
+                                    the chain is latency-bound (tcgen05 / SIMT chains, profiles/r2_notes.md); the tensor-core GEMV chain
+                                    gains 3-5 % (what an engine of <= 4 requests sets).  Default off                                */
     int32_t umma_big_min_rows;   /* bf16 projections without split-K run the persistent double-buffered tcgen05 kernel (csrc/linear_big.cu)
                                     from this many rows on (0 = default 1024: prefill passes and decode batches of >= 512 requests; < 0 = never)                       */
     int32_t norm_fusion;         /* t3b_decode_step can fold add+RMSNorm into the tcgen05 projections either side of it (5 launches per layer
@@ -161,6 +164,10 @@ typedef struct t3b_options {
                                     (3..32 rows: what an engine picks so that every batch size it runs uses the same arithmetic), -1 = never.
                                     The folded chain adds a row's sum of squares in a different order than the norm kernel: results agree
                                     to a bf16 step, not bit for bit                                                                */
+    int32_t gemv_mma;            /* 1 = the GEMV row counts run on the tensor cores (mma.sync m16n8k16 on weight fragments loaded straight
+                                    from global memory, csrc/linear_gemv.cu) for every bf16 projection that carries its fragment-ordered
+                                    copy (t3b_linear_t.scales): up to 8 rows (gemv_max_rows may then be up to 8), K = 1024 or 4096.  fp32 accumulation in another order than the SIMT GEMV: results agree to a bf16 step.
+                                    0 = library default, -1 = the SIMT kernel                                                        */
 } t3b_options_t;
 
 const char* t3b_last_error(void);
@@ -217,6 +224,14 @@ int32_t t3b_linear_awq(const void* x, const t3b_linear_t* w, int32_t rows, void*
 int32_t t3b_repack_weights_awq(const int32_t* qweight, const int32_t* qzeros, const void* scales_fp16,
                                int32_t n, int32_t k, int32_t gate_up_interleave, void* w_out, void* zeros_out,
                                void* scales_out, void* stream);
+
+/* Small-batch layout of a bf16 projection (no counterpart in the reference: vLLM keeps nn.Linear layout): w bf16 [n, k] -> out,
+ * t3b_gemv_frag_bytes(n, k, gate_up) bytes (0 = shape not supported: k must be 1024 or 4096, gate_up needs k = 1024 and n % 32 == 0),
+ * in the order the tensor-core GEMV reads its mma.sync A fragments ([16-feature tile][k step of 32][lo | hi][lane] x 16 bytes;
+ * gate_up != 0: a tile = 8 gate features + the 8 matching up features, for the T3B_EPI_SILU_MUL epilogue).  One-off, at load; the
+ * pointer goes into t3b_linear_t.scales of the bf16 projection. */
+size_t  t3b_gemv_frag_bytes(int32_t n, int32_t k, int32_t gate_up);
+int32_t t3b_repack_weights_gemv(const void* w, int32_t n, int32_t k, int32_t gate_up, void* out, void* stream);
 
 /* F2.3 + KV write  (rotary_embedding/common.py:144-174, llama3 table; reshape_and_cache of
  *     llama.py:231): qkv as bf16 [n_tok, 3*hidden] or split-K partials.  Token j belongs to KV row

@@ -1,0 +1,26 @@
+#!/bin/bash
+# A/B of t3b_options_t.gemv_mma (tensor-core GEMV for <= 8 rows) at 1..4 requests:
+# the bit-exactness tests first, then bench.py device-resident ms/step per setting.  Everything lands in gpurun_out/$TAG_*.
+TAG=${TAG:-ab}
+O=gpurun_out
+mkdir -p $O
+timeout 600 python -m pytest tests/test_gpu_round2.py tests/test_gpu_kernels.py -m gpu -x -q -k "gemv" --timeout 300 > $O/${TAG}_pytest.log 2>&1; echo "pytest exit $?"
+tail -4 $O/${TAG}_pytest.log
+run() {  # name, batch, opts
+  timeout 300 python bench.py --batch $2 --steps 100 --warmup 5 --no-cpu-baseline --no-breakdown --sweep '' --opt "$3" > $O/${TAG}_$1.json 2> $O/${TAG}_$1.err
+  echo "$1 exit $?"
+  python - <<PY
+import json
+try:
+    d = json.loads(open("$O/${TAG}_$1.json").read().strip().splitlines()[-1])
+    print("$1", "ms/step", round(d["ms_per_step"], 4), "tokens/s", round(d["value"]), "e2e", round(d["e2e"]["value"]), "step frac", round(d["step_roofline"]["frac"], 3))
+except Exception as e:
+    print("$1 no bench line:", e)
+PY
+}
+run b1_mma_pf1 1 "gemv_mma=1,weight_prefetch=1"
+run b1_mma_pf2 1 "gemv_mma=1,weight_prefetch=2"
+run b2_mma_pf2 2 "gemv_max_rows=8,gemv_mma=1,weight_prefetch=2"
+run b4_mma_pf1 4 "gemv_max_rows=8,gemv_mma=1,weight_prefetch=1"
+run b4_mma_pf2 4 "gemv_max_rows=8,gemv_mma=1,weight_prefetch=2"
+run b1_reg_pf2 1 "weight_prefetch=2"

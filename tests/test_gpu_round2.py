@@ -357,6 +357,40 @@ def test_gemv_norm_fold_equals_separate_norm_launches(L, small_model, rows):
     assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1]))
 
 
+@pytest.mark.parametrize("rows", [2, 4, 6, 8])
+def test_gemv_mma_decode_chain_matches_tcgen05_chain(L, small_model, rows):
+    """t3b_options_t.gemv_mma: the 5-launch GEMV chain on the tensor cores (<= 8 rows, add + RMSNorm in front of qkv / gate_up) against
+    the 7-launch tcgen05 chain.  Both accumulate in fp32, in different orders: layer 0's K / V come out of one projection (all but a
+    few elements identical, the rest one bf16 step apart), the hidden state after the small model's layers agrees to a few bf16
+    steps; the chain is deterministic, and a request's rows do not depend on the rows beside them (rows 0..1 alone == rows 0..1 of
+    the batch, bit for bit)."""
+    m, _ = small_model
+    assert m.enable_gemv_mma()
+    g = torch.Generator().manual_seed(rows)
+    lens = torch.randint(5, 300, (rows // 2,), generator=g).repeat_interleave(2).tolist()
+    outs = []
+    for mode in ("mma", "umma", "mma", "mma2"):
+        n = 2 if mode == "mma2" else rows
+        kv, st = random_state(SMALL, rows, lens, seed=5)
+        opt = _lib.make_options(gemv_max_rows=-1, norm_fusion=-1) if mode == "umma" else _lib.make_options(gemv_max_rows=8, gemv_mma=1)
+        ws = m.workspace(rows)
+        hid = torch.zeros(rows, 1024, dtype=torch.bfloat16, device=DEV)
+        _lib.check(L.t3b_decode_step(C.byref(m.c), C.byref(kv.c), C.byref(st.c), None, n, hid.data_ptr(), ws.data_ptr(), ws.numel(),
+                                     C.byref(opt), sp()))
+        torch.cuda.synchronize()
+        outs.append((hid.clone(), kv.k.clone(), kv.v.clone()))
+    mma, umma, again, alone = outs
+    assert all(torch.equal(a, b) for a, b in zip(mma, again))                          # deterministic
+    assert torch.equal(alone[0][:2], mma[0][:2])                                       # independent of the rows beside it
+    hf, hp = mma[0].float(), umma[0].float()
+    assert torch.isfinite(hf).all()
+    k0m, k0u = mma[1][0].float(), umma[1][0].float()                                   # layer 0 of the pool (viewed as raw bf16)
+    assert (k0m == k0u).float().mean().item() > 0.99
+    same = (hf == hp).float().mean().item()
+    err = (hf - hp).abs().max().item() / hp.abs().max().item()
+    assert same > 0.4 and err < 2 ** -5, (same, err)
+
+
 @pytest.mark.parametrize("rows", [6, 16, 18, 32])
 def test_norm_folded_into_projections_matches_separate_norm_launches(L, small_model, rows):
     """t3b_options_t.norm_fusion: at up to 32 rows the decode chain runs add + RMSNorm inside the o / down epilogues and the

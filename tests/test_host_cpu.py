@@ -206,3 +206,39 @@ def test_vllm_plugin_registers_architecture_and_s3gen_filter():
         assert callable(getattr(vllm_plugin.T3B200ForVllm, hook))
     ids = [SPEECH_TOKEN_OFFSET + t for t in (0, 5, 6560, 6561, 6562, 8193)] + [17, 2499]
     assert vllm_plugin.speech_tokens_for_s3gen(ids) == [0, 5, 6560]
+
+
+def test_gemv_weight_loads_stay_in_front_of_the_dependency_wait():
+    """The GEMV kernels request their whole weight slice BEFORE griddepcontrol.wait (weights never depend on the previous kernel).
+    ptxas is free to hoist the wait above ``ld.global.nc`` loads - it did so in one build of the tensor-core GEMV, which cost 0.9 us
+    per launch (profiles/r2_notes.md r5) - and only the control flow between the loads and the wait keeps the order.  Guard it in
+    the shipped binary: in every GEMV kernel the first ACQBULK (the wait) comes after all of the kernel's streaming weight loads
+    (LDG.E.NA = ld.global.nc.L1::no_allocate)."""
+    import re
+    import shutil
+    import subprocess
+    from chatterbox_vllm2_b200 import _lib
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    so = _lib.lib_path() if hasattr(_lib, "lib_path") else os.path.join(ROOT, "chatterbox-vllm2_b200", "csrc", "libt3b200.so")
+    sass = subprocess.run([cuobjdump, "-sass", so], capture_output=True, text=True, check=True).stdout
+    fn, seen = None, {}
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            fn = m.group(1) if "linear_gemv" in m.group(1) else None
+            if fn:
+                seen[fn] = [0, 0, False]          # weight loads before the wait, after it, wait seen
+            continue
+        if fn is None:
+            continue
+        if "ACQBULK" in line:
+            seen[fn][2] = True
+        elif "LDG.E.NA" in line:
+            seen[fn][1 if seen[fn][2] else 0] += 1
+    assert len(seen) >= 30, len(seen)
+    for fn, (pre, post, wait) in seen.items():
+        assert wait and pre >= 2, (fn, pre, post)
+        if "mma" in fn or fn.endswith("Lb1EEvPK13__nv_bfloat16S2_iiiPS0_8GemvNorm6PfArgs"):
+            assert post == 0, (fn, pre, post)      # single-shot kernels: the whole slice is requested before the wait

@@ -18,9 +18,10 @@ except Exception as e:
     print("$1 no bench line:", e)
 PY
 }
-run b1_mma_pf1 1 "gemv_mma=1,weight_prefetch=1"
-run b1_mma_pf2 1 "gemv_mma=1,weight_prefetch=2"
-run b2_mma_pf2 2 "gemv_max_rows=8,gemv_mma=1,weight_prefetch=2"
-run b4_mma_pf1 4 "gemv_max_rows=8,gemv_mma=1,weight_prefetch=1"
-run b4_mma_pf2 4 "gemv_max_rows=8,gemv_mma=1,weight_prefetch=2"
-run b1_reg_pf2 1 "weight_prefetch=2"
+OLD="gemv_mma=-1,gemv_max_rows=-1,weight_prefetch=0"
+run b1_old 1 "gemv_mma=-1,gemv_max_rows=0,weight_prefetch=0"
+run b1_mma 1 ""
+run b2_old 2 "$OLD"
+run b2_mma 2 ""
+run b4_old 4 "$OLD"
+run b4_mma 4 ""

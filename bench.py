@@ -369,7 +369,7 @@ def kernel_breakdown(m, eng, B, ctx):
     def lin(name, xin, yout, epi=0):
         def f(li):
             w = getattr(auto[li], name)
-            _lib.check(lin_fn(xin.data_ptr(), C.byref(w), R, yout.data_ptr(), None, 0, C.byref(ns), 0, epi, m._opt(), cur["s"]), name)
+            _lib.check(lin_fn(xin.data_ptr(), C.byref(w), R, yout.data_ptr(), None, 0, C.byref(ns), 0, epi, C.byref(eng.opt), cur["s"]), name)
         return f
 
     def attn_f(li):

@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
 #pragma unroll 1
     for (int i = pn; i < S; ++i) produce();
     AT_STAMP(2);
-    if (warp == AT_NW - 1 && lane == 1) pf_slice(a.pf, (int)blockIdx.x, G);      // behind the first ring fill
+    if (warp == AT_NW - 1) pf_slice_warp(a.pf, (int)blockIdx.x, G, lane);      // behind the first ring fill, one piece per lane
     if (FUSED) pdl_wait();
     AT_STAMP(3);
     const float kScale = 0.125f * 1.4426950408889634f;   // head_dim^-0.5 * log2(e)

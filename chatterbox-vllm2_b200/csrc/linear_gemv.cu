@@ -260,7 +260,9 @@ __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16*
 #pragma unroll
         for (int st = 0; st < STEPS; ++st) { wlo[tl][st] = ldg_stream(p + st * 64); whi[tl][st] = ldg_stream(p + st * 64 + 32); }
     }
-    if (threadIdx.x == 0) pf_slice(pf, blockIdx.x, gridDim.x);      // behind this block's own weight loads: a later launch's weights -> L2
+    // behind this block's own weight loads: a later launch's weights -> L2, one piece per lane of the last warp.  (This branch also keeps
+    // ptxas from hoisting the dependency wait above the weight loads - see the guard in tests/test_host_cpu.py.)
+    if (warp == WARPS - 1) pf_slice_warp(pf, blockIdx.x, gridDim.x, lane);
     uint4 nwraw = make_uint4(0, 0, 0, 0);
     if (nz.norm_w != nullptr) nwraw = __ldg(reinterpret_cast<const uint4*>(nz.norm_w) + (threadIdx.x & 127));     // before the wait: constant
     pdl_wait();

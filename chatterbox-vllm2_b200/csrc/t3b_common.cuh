@@ -176,6 +176,16 @@ __device__ __forceinline__ void pf_slice(const PfArgs pf, int cta, int ncta) {
     const unsigned long long e = a + per < pf.bytes ? a + per : pf.bytes;
     for (; a < e; a += 16384ull) l2_prefetch_bulk(pf.p + a, (uint32_t)(e - a < 16384ull ? e - a : 16384ull));
 }
+// the same slice, issued by a whole WARP: lane i takes pieces i, i + 32, ... - a bulk instruction costs the issuing thread several
+// hundred cycles (scripts/probe/bulk_bw.cu), 32 lanes issue theirs in one warp instruction; call with all 32 lanes
+__device__ __forceinline__ void pf_slice_warp(const PfArgs pf, int cta, int ncta, int lane) {
+    if (pf.bytes == 0) return;
+    const unsigned long long per = ((pf.bytes + ncta - 1) / ncta + 4095ull) & ~4095ull;
+    const unsigned long long a0 = per * (unsigned long long)cta;
+    const unsigned long long e = a0 + per < pf.bytes ? a0 + per : pf.bytes;
+    for (unsigned long long a = a0 + 16384ull * lane; a < e; a += 16384ull * 32)
+        l2_prefetch_bulk(pf.p + a, (uint32_t)(e - a < 16384ull ? e - a : 16384ull));
+}
 // 1-D bulk copy with an L2 evict-first hint: data read once per step (K/V) must not push the prefetched weights out of L2
 __device__ __forceinline__ uint64_t l2_policy_evict_first() {
     uint64_t pol;

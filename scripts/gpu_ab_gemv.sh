@@ -18,10 +18,11 @@ except Exception as e:
     print("$1 no bench line:", e)
 PY
 }
-OLD="gemv_mma=-1,gemv_max_rows=-1,weight_prefetch=0"
-run b1_old 1 "gemv_mma=-1,gemv_max_rows=0,weight_prefetch=0"
-run b1_mma 1 ""
-run b2_old 2 "$OLD"
-run b2_mma 2 ""
-run b4_old 4 "$OLD"
-run b4_mma 4 ""
+run b1_pf2 1 ""
+run b1_pf3 1 "weight_prefetch=3"
+run b1_pf1 1 "weight_prefetch=1"
+run b2_pf2 2 ""
+run b4_pf2 4 ""
+run b4_pf3 4 "weight_prefetch=3"
+run b32_pf0 32 ""
+run b32_pf1 32 "weight_prefetch=1"

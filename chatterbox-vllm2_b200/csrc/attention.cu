@@ -61,10 +61,17 @@ __device__ unsigned long long* g_attn_trace = nullptr;
 extern "C" int32_t t3b_debug_set_attn_trace(unsigned long long* buf) {
     return cudaMemcpyToSymbol(g_attn_trace, &buf, sizeof(buf)) == cudaSuccess ? 0 : -4;
 }
-#define AT_STAMP(i) do { if (g_attn_trace && threadIdx.x == 0) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
-                         g_attn_trace[(size_t)blockIdx.x * 8 + (i)] = t_; } } while (0)
+// the buffer pointer is read ONCE per kernel (AT_TRACE_INIT): a stamp that loads it first would show - and add - an L2 round trip
+#define AT_TRACE_INIT unsigned long long* const at_tr_ = threadIdx.x == 0 ? g_attn_trace : nullptr
+#define AT_STAMP(i) do { if (at_tr_) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); \
+                         at_tr_[(size_t)blockIdx.x * 16 + (i)] = t_; } } while (0)
+// stamp that cannot be scheduled before `val` is available
+#define AT_STAMP_DEP(i, val) do { if (at_tr_) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_) : "f"(val)); \
+                                  at_tr_[(size_t)blockIdx.x * 16 + (i)] = t_; } } while (0)
 #else
+#define AT_TRACE_INIT do { } while (0)
 #define AT_STAMP(i) do { } while (0)
+#define AT_STAMP_DEP(i, val) do { } while (0)
 #endif
 
 template <int KVT> struct KvFmt;
@@ -193,6 +200,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
     int* s_tok = s_pos + AT_CAP;                                                           // [AT_CAP] token (= row of the step) of the item
 
     pdl_launch_dependents();       // the next kernel's launch overlaps this one (it waits before reading)
+    AT_TRACE_INIT;
     AT_STAMP(0);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int team = warp / W, wt = warp - team * W;      // team = the warps that share one item
@@ -314,24 +322,32 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[e] = 0.f;
         unpack8(hq, qf);
+        if (k == 0) AT_STAMP_DEP(5, qf[0]);                 // q of the first item has arrived
         if (FUSED) {
             float kf[8], cs[8], sn[8], vf[8];
             unpack8(hk, kf); unpack8(hcs, cs); unpack8(hsn, sn); unpack8(hv, vf);
-            const bool hi = c >= 4;                           // lanes c < 4 hold x1 (dims 0..31), c >= 4 hold x2
+            // o1 = x1*cos - x2*sin ; o2 = x2*cos + x1*sin, every product and the sum rounded to bf16.  Lanes c < 4 hold x1 (dims 0..31),
+            // c >= 4 hold x2: the partner's value comes by shuffle and the sign rides on the (exactly negated) second product.  All
+            // shuffles of the head are issued before any of the arithmetic: as one loop per element the compiler funnelled them through one
+            // register - 16 shuffle -> round -> round -> add chains back to back, 1.8 us of a 4.2 us launch at small batch (r5p trace).
+            const float sg = c >= 4 ? 1.f : -1.f;
+            float qp[8], kp[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-                const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4);
-                // o1 = x1*cos - x2*sin ; o2 = x2*cos + x1*sin, every product and the sum rounded to bf16
-                qf[e] = hi ? bf16_round(bf16_round(qf[e] * cs[e]) + bf16_round(qp * sn[e])) : bf16_round(bf16_round(qf[e] * cs[e]) - bf16_round(qp * sn[e]));
+            for (int e = 0; e < 8; ++e) qp[e] = __shfl_xor_sync(0xffffffffu, qf[e], 4);
+            if (wt == 0) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) kp[e] = __shfl_xor_sync(0xffffffffu, kf[e], 4);
             }
+#pragma unroll
+            for (int e = 0; e < 8; ++e) qf[e] = bf16_round(bf16_round(qf[e] * cs[e]) + sg * bf16_round(qp[e] * sn[e]));
+            if (k == 0) AT_STAMP_DEP(8, qf[0] + qf[7]);
             if (wt == 0) {
                 // the new token: rotated, stored for the following steps, and attended to straight from registers
 #pragma unroll
-                for (int e = 0; e < 8; ++e) {
-                    const float kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
-                    kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
-                }
+                for (int e = 0; e < 8; ++e) kf[e] = bf16_round(bf16_round(kf[e] * cs[e]) + sg * bf16_round(kp[e] * sn[e]));
+                if (k == 0) AT_STAMP_DEP(9, kf[0] + kf[7]);
                 const size_t sl = ((size_t)hblk * H + h) * SLICE;
+                if (k == 0) AT_STAMP_DEP(10, (float)sl);
                 if (KVT == 1) {
                     float ka = 0.f, va = 0.f;
 #pragma unroll
@@ -363,6 +379,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
                 d += __shfl_xor_sync(0xffffffffu, d, 2);
                 d += __shfl_xor_sync(0xffffffffu, d, 4);
                 m = d * kScale;
+                if (k == 0) AT_STAMP_DEP(11, m);
                 l = lane == 0 ? 1.f : 0.f;
 #pragma unroll
                 for (int e = 0; e < 8; ++e) acc[e] = t4 == 0 ? vf[e] : 0.f;
@@ -370,6 +387,7 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
         }
 #pragma unroll
         for (int e = 0; e < 8; ++e) qf[e] *= kScale;
+        if (k == 0) AT_STAMP_DEP(2, qf[0] + m);            // head of the first item done (trace builds: overwrites ring_issued)
         load_head(k + 1);                                  // in flight while this item's pairs are processed
 
 #pragma unroll 1
@@ -377,7 +395,6 @@ __global__ void __launch_bounds__(AT_NW * 32, AT_CTAS) attn_ring_kernel(const At
             const int slot = cn % S;
             mbar_wait(&my_full[slot], (uint32_t)((cn / S) & 1));
             if (cn == 0) AT_STAMP(4);
-            if (cn == S) AT_STAMP(5);
             const unsigned char* sl = my_ring + (size_t)slot * PAIR;
             const bool two = pr * 2 + 1 < n_pages;         // warp-uniform
             attn_pair<KVT>(sl, sl + SLICE, sl + 2 * SLICE, sl + 3 * SLICE, two, pr * 32, nc, qf, lane, m, l, acc);

@@ -4,7 +4,7 @@
 TAG=${TAG:-ab}
 O=gpurun_out
 mkdir -p $O
-timeout 600 python -m pytest tests/test_gpu_round2.py tests/test_gpu_kernels.py -m gpu -x -q -k "gemv" --timeout 300 > $O/${TAG}_pytest.log 2>&1; echo "pytest exit $?"
+timeout 600 python -m pytest tests/test_gpu_round2.py tests/test_gpu_kernels.py -m gpu -x -q -k "gemv or attn or attention or decode or rope or row_order" --timeout 300 > $O/${TAG}_pytest.log 2>&1; echo "pytest exit $?"
 tail -4 $O/${TAG}_pytest.log
 run() {  # name, batch, opts
   timeout 300 python bench.py --batch $2 --steps 100 --warmup 5 --no-cpu-baseline --no-breakdown --sweep '' --opt "$3" > $O/${TAG}_$1.json 2> $O/${TAG}_$1.err
@@ -18,11 +18,8 @@ except Exception as e:
     print("$1 no bench line:", e)
 PY
 }
-run b1_pf2 1 ""
-run b1_pf3 1 "weight_prefetch=3"
-run b1_pf1 1 "weight_prefetch=1"
-run b2_pf2 2 ""
-run b4_pf2 4 ""
-run b4_pf3 4 "weight_prefetch=3"
-run b32_pf0 32 ""
-run b32_pf1 32 "weight_prefetch=1"
+run b1 1 ""
+run b4 4 ""
+run b16 16 ""
+run b32 32 ""
+run b128 128 ""

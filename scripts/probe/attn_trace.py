@@ -15,7 +15,7 @@ OUT = os.path.join(ROOT, "scripts", "probe", "bin", "libt3b200_trace.so")
 
 
 def build():
-    srcs = ["api.cu", "elementwise.cu", "attention.cu", "linear_gemv.cu", "linear_umma.cu", "sampler.cu"]
+    srcs = ["api.cu", "elementwise.cu", "attention.cu", "linear_gemv.cu", "linear_umma.cu", "linear_big.cu", "sampler.cu"]
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
     subprocess.check_call(["nvcc", "-shared", "-o", OUT, "-DT3B_ATTN_TRACE", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17",
                            "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-cudart", "static"] + [os.path.join(CS, s) for s in srcs])
@@ -48,7 +48,7 @@ def main():
     out = torch.empty(R, 1024, dtype=torch.bfloat16, device=dev)
     from chatterbox_vllm2_b200.model import llama3_rope_table
     rope = llama3_rope_table(d).to(device=dev, dtype=torch.bfloat16).contiguous()
-    trace = torch.zeros(4, 148, 8, dtype=torch.int64, device=dev)
+    trace = torch.zeros(4, 148, 16, dtype=torch.int64, device=dev)
     s = torch.cuda.current_stream().cuda_stream
     only_attn = "--attn-only" in sys.argv
     for rep in range(4):
@@ -63,7 +63,7 @@ def main():
     t = trace[3].cpu().double()
     t = t[t[:, 0] > 0]
     t0 = t[:, 0].min()
-    names = ["start", "meta_done", "ring_issued", "wait_done", "first_pair", "pair_S", "item0_done", "end"]
+    names = ["start", "meta_done", "head_done", "wait_done", "first_pair", "q_arrived", "item0_done", "end", "q_rotated", "k_rotated", "hblk_arrived", "new_token_dot"]
     print(f"rows {R} context {ctx}: {t.shape[0]} CTAs of the last launch, ns after the earliest CTA start (min / median / max)")
     for i, n in enumerate(names):
         c = t[:, i] - t0

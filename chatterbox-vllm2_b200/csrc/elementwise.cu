@@ -235,12 +235,16 @@ __global__ void __launch_bounds__(512) rope_kv_write_vec_kernel(const bf16* __re
     const uint4 vraw = ld_act(reinterpret_cast<const uint4*>(src + 2 * hidden));
     unpack8(__ldg(reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + (c & 3) * 8)), cs);
     unpack8(__ldg(reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * 64 + 32 + (c & 3) * 8)), sn);
-    const bool hi = c >= 4;
+    // all shuffles first, the sign of the second product by an exact +-1 (same arithmetic as the decode attention's item head, where one
+    // shuffle -> round chain per element measured 1.8 us per launch: profiles/r2_notes.md r5p)
+    const float sg = c >= 4 ? 1.f : -1.f;
+    float qp[8], kp[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { qp[e] = __shfl_xor_sync(0xffffffffu, qf[e], 4); kp[e] = __shfl_xor_sync(0xffffffffu, kf[e], 4); }
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-        const float qp = __shfl_xor_sync(0xffffffffu, qf[e], 4), kp = __shfl_xor_sync(0xffffffffu, kf[e], 4);
-        qf[e] = hi ? bf16_round(bf16_round(qf[e] * cs[e]) + bf16_round(qp * sn[e])) : bf16_round(bf16_round(qf[e] * cs[e]) - bf16_round(qp * sn[e]));
-        kf[e] = hi ? bf16_round(bf16_round(kf[e] * cs[e]) + bf16_round(kp * sn[e])) : bf16_round(bf16_round(kf[e] * cs[e]) - bf16_round(kp * sn[e]));
+        qf[e] = bf16_round(bf16_round(qf[e] * cs[e]) + sg * bf16_round(qp[e] * sn[e]));
+        kf[e] = bf16_round(bf16_round(kf[e] * cs[e]) + sg * bf16_round(kp[e] * sn[e]));
     }
     *reinterpret_cast<uint4*>(q_out + (size_t)t * hidden + h * 64 + c * 8) = pack8(qf);
     if (KVT == 1) {

@@ -270,25 +270,44 @@ __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16*
         // F2.1 in front (K == 1024, 256 threads): threads [128 h, 128 h + 128) take rows h, h + 2, h + 4, h + 6 - per row the arithmetic
         // and summation order of add_rmsnorm_kernel<1> (128 threads x 8 elements, warp sums, (s0 + s1) + (s2 + s3))
         const int h = threadIdx.x >> 7, i = threadIdx.x & 127, wq = (threadIdx.x >> 5) & 3;
-        float xv[4][8];
+        // every load of the up to four rows goes out first: written as one loop per row, the store of the updated residual (which
+        // may alias the inputs as far as the compiler knows) pinned each row's loads behind the previous row's store - four L2 round
+        // trips back to back at 8 rows (profiles/r2_notes.md r5r); the four warp reductions are interleaved for the same reason
+        uint4 xr[4], rr[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
             const int r = h + 2 * q;
-            float ss = 0.f;
+            xr[q] = rr[q] = make_uint4(0, 0, 0, 0);
             if (r < rows) {
-                unpack8(ld_act(reinterpret_cast<const uint4*>(x) + (size_t)r * K8 + i), xv[q]);
-                if (nz.has_res) {
-                    float rv[8];
-                    unpack8(ld_act(reinterpret_cast<const uint4*>(nz.res_in) + (size_t)r * K8 + i), rv);
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) xv[q][e] += rv[e];
-                }
-                if (blockIdx.x == 0) reinterpret_cast<uint4*>(nz.res_out)[(size_t)r * K8 + i] = pack8(xv[q]);
-#pragma unroll
-                for (int e = 0; e < 8; ++e) ss += xv[q][e] * xv[q][e];
+                xr[q] = ld_act(reinterpret_cast<const uint4*>(x) + (size_t)r * K8 + i);
+                if (nz.has_res) rr[q] = ld_act(reinterpret_cast<const uint4*>(nz.res_in) + (size_t)r * K8 + i);
             }
-            ss = warp_sum(ss);
-            if (lane == 0) s_red[r][wq] = ss;
+        }
+        float xv[4][8], ss[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float rv[8];
+            unpack8(xr[q], xv[q]);
+            unpack8(rr[q], rv);
+            ss[q] = 0.f;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+                if (nz.has_res) xv[q][e] += rv[e];
+                ss[q] += xv[q][e] * xv[q][e];
+            }
+        }
+        if (blockIdx.x == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (h + 2 * q < rows) reinterpret_cast<uint4*>(nz.res_out)[(size_t)(h + 2 * q) * K8 + i] = pack8(xv[q]);
+        }
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1)
+#pragma unroll
+            for (int q = 0; q < 4; ++q) ss[q] += __shfl_xor_sync(0xffffffffu, ss[q], o);
+        if (lane == 0) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) s_red[h + 2 * q][wq] = ss[q];
         }
         __syncthreads();
         float wv8[8];

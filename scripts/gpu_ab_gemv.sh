@@ -19,7 +19,6 @@ except Exception as e:
 PY
 }
 run b1 1 ""
+run b2 2 ""
+run b3 3 ""
 run b4 4 ""
-run b16 16 ""
-run b32 32 ""
-run b128 128 ""

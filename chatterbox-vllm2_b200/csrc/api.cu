@@ -92,7 +92,7 @@ Workspace carve(const t3b_model_t* m, int rows, void* base) {
     w.act = take(R * F * 2);
     w.lin = take(R * D * 2);
     w.head = take(R * V * 2 + 64);
-    w.resid2 = take((R < 4 ? R : 4) * D * 2);    // ping-pong residual of the small-batch path (rows <= 4)
+    w.resid2 = take((R < 16 ? R : 16) * D * 2);  // ping-pong residual of the GEMV chains (rows <= 16)
     // bf16 copy of ONE layer's projections for AWQ models at large row counts
     const bool awq_big = m->layers && m->layers[0].qkv.kind == T3B_W_AWQ && rows >= AWQ_DEQUANT_MIN_ROWS;
     w.deq = take(awq_big ? (3 * D * D + D * D + 2 * F * D + D * F) * 2 : 0);
@@ -118,7 +118,7 @@ static Opt resolve(const t3b_options_t* o) {
     Opt r = {GEMV_MAX_ROWS_DEFAULT, 1, 0, 0, {0, 0, 0, 0}, 0, 0, 0, 1024, 1, GEMV_MMA_DEFAULT};      // norm_fuse: 0 never, 1 where faster, 2 wherever possible
     if (o) {
         if (o->gemv_mma != 0) r.gemv_mma = o->gemv_mma > 0 ? 1 : 0;
-        const int cap = r.gemv_mma ? 8 : 4;
+        const int cap = r.gemv_mma ? 16 : 4;
         if (o->gemv_max_rows != 0) r.gemv_max_rows = o->gemv_max_rows < 0 ? 0 : (o->gemv_max_rows > cap ? cap : o->gemv_max_rows);
         r.gemv_norm = o->gemv_no_norm ? 0 : 1;
         r.stages = o->umma_stages > 0 ? o->umma_stages : 0;
@@ -146,7 +146,7 @@ static int32_t linear_any(const void* x, const t3b_linear_t* w, int rows, void* 
     T3B_CHECK_ARG(awq || w->kind == T3B_W_BF16, "linear: unknown weight kind %d", w->kind);
     // the SIMT GEMV takes <= 4 rows of any K % 1024 == 0, the tensor-core GEMV <= 8 rows of the model's own K (1024 / 4096)
     const bool mma = o.gemv_mma && !awq && w->scales != nullptr && t3b_gemv_mma_ok(w->n, w->k, epi);     // scales = the fragment-ordered copy
-    const bool gemv_fits = mma ? rows <= 8 : (rows <= 4 && w->k % 1024 == 0 && w->k <= 8192);
+    const bool gemv_fits = mma ? rows <= 16 : (rows <= 4 && w->k % 1024 == 0 && w->k <= 8192);
     if (impl == T3B_IMPL_AUTO) impl = (!awq && rows <= o.gemv_max_rows && gemv_fits) ? T3B_IMPL_GEMV : T3B_IMPL_UMMA;
     if (impl == T3B_IMPL_GEMV) {
         T3B_CHECK_ARG(fuse == nullptr, "linear: the fused normalisation runs on the tcgen05 kernel only");

@@ -238,7 +238,7 @@ __device__ __forceinline__ void gemv_mma16816(float* c, uint32_t a0, uint32_t a1
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-template <int STEPS, int WARPS, int TPB, int MODE>
+template <int STEPS, int WARPS, int TPB, int NT, int MODE>
 __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16* __restrict__ x, const uint4* __restrict__ wf, int rows, int N,
                                                                      bf16* __restrict__ y, const GemvNorm nz, const PfArgs pf) {
     constexpr int K = STEPS * 32 * WARPS, K8 = K / 8;
@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16*
     __shared__ float s_red[8][4];
     extern __shared__ __align__(16) unsigned char smem_mm[];
     unsigned char* xs = smem_mm;                                    // [rows][XROW]
-    float* part = reinterpret_cast<float*>(smem_mm + (size_t)rows * XROW);      // [WARPS][TPB][128]
+    float* part = reinterpret_cast<float*>(smem_mm + (size_t)rows * XROW);      // [WARPS][TPB][NT][128]
     pdl_launch_dependents();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, g = lane >> 2, t = lane & 3;
     const int n_out = (MODE == 1) ? N / 2 : N;
@@ -270,13 +270,16 @@ __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16*
         // F2.1 in front (K == 1024, 256 threads): threads [128 h, 128 h + 128) take rows h, h + 2, h + 4, h + 6 - per row the arithmetic
         // and summation order of add_rmsnorm_kernel<1> (128 threads x 8 elements, warp sums, (s0 + s1) + (s2 + s3))
         const int h = threadIdx.x >> 7, i = threadIdx.x & 127, wq = (threadIdx.x >> 5) & 3;
+        float wv8[8];
+        unpack8(nwraw, wv8);
+        auto stage_group = [&](const int r0) {
         // every load of the up to four rows goes out first: written as one loop per row, the store of the updated residual (which
         // may alias the inputs as far as the compiler knows) pinned each row's loads behind the previous row's store - four L2 round
         // trips back to back at 8 rows (profiles/r2_notes.md r5r); the four warp reductions are interleaved for the same reason
         uint4 xr[4], rr[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const int r = h + 2 * q;
+            const int r = r0 + h + 2 * q;
             xr[q] = rr[q] = make_uint4(0, 0, 0, 0);
             if (r < rows) {
                 xr[q] = ld_act(reinterpret_cast<const uint4*>(x) + (size_t)r * K8 + i);
@@ -299,7 +302,7 @@ __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16*
         if (blockIdx.x == 0) {
 #pragma unroll
             for (int q = 0; q < 4; ++q)
-                if (h + 2 * q < rows) reinterpret_cast<uint4*>(nz.res_out)[(size_t)(h + 2 * q) * K8 + i] = pack8(xv[q]);
+                if (r0 + h + 2 * q < rows) reinterpret_cast<uint4*>(nz.res_out)[(size_t)(r0 + h + 2 * q) * K8 + i] = pack8(xv[q]);
         }
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1)
@@ -310,19 +313,24 @@ __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16*
             for (int q = 0; q < 4; ++q) s_red[h + 2 * q][wq] = ss[q];
         }
         __syncthreads();
-        float wv8[8];
-        unpack8(nwraw, wv8);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const int r = h + 2 * q;
+            const int r = r0 + h + 2 * q;
             if (r < rows) {
-                const float tot = (s_red[r][0] + s_red[r][1]) + (s_red[r][2] + s_red[r][3]);
+                const float* sr = s_red[h + 2 * q];
+                const float tot = (sr[0] + sr[1]) + (sr[2] + sr[3]);
                 const float rstd = rsqrtf(tot / (float)K + nz.eps);
                 float o[8];
 #pragma unroll
                 for (int e = 0; e < 8; ++e) o[e] = bf16_round(xv[q][e] * rstd) * wv8[e];
                 *reinterpret_cast<uint4*>(xs + (size_t)r * XROW + i * 16) = pack8(o);
             }
+        }
+        };
+        stage_group(0);
+        if (NT > 1 && rows > 8) {                                   // NT = 2: a second group of up to 8 rows
+            __syncthreads();                                        // s_red of the first group has been read
+            stage_group(8);
         }
     } else {
         for (int i = threadIdx.x; i < rows * K8; i += WARPS * 32) {
@@ -332,61 +340,74 @@ __global__ void __launch_bounds__(WARPS * 32) linear_gemv_mma_kernel(const bf16*
     }
     __syncthreads();
 
-    float c[TPB][4];
-#pragma unroll
-    for (int tl = 0; tl < TPB; ++tl) c[tl][0] = c[tl][1] = c[tl][2] = c[tl][3] = 0.f;
-    const unsigned char* xrow = xs + (size_t)g * XROW + (size_t)kb * 2;      // activation row g = column g of the B operand
-#pragma unroll
-    for (int st = 0; st < STEPS; ++st) {
-        uint4 xb = make_uint4(0, 0, 0, 0);
-        if (g < rows) xb = *reinterpret_cast<const uint4*>(xrow + st * 64);
-#pragma unroll
-        for (int tl = 0; tl < TPB; ++tl) {
-            gemv_mma16816(c[tl], wlo[tl][st].x, whi[tl][st].x, wlo[tl][st].y, whi[tl][st].y, xb.x, xb.y);
-            gemv_mma16816(c[tl], wlo[tl][st].z, whi[tl][st].z, wlo[tl][st].w, whi[tl][st].w, xb.z, xb.w);
-        }
-    }
-    // c[0..3] = (feature g, rows 2t / 2t+1), (feature g + 8, rows 2t / 2t+1): slot (g * 4 + t) * 4 + j of the warp's partial tile
+    float c[TPB][NT][4];
 #pragma unroll
     for (int tl = 0; tl < TPB; ++tl)
-        *reinterpret_cast<float4*>(part + ((size_t)(warp * TPB + tl) * 32 + lane) * 4) = make_float4(c[tl][0], c[tl][1], c[tl][2], c[tl][3]);
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) c[tl][nt][0] = c[tl][nt][1] = c[tl][nt][2] = c[tl][nt][3] = 0.f;
+    const unsigned char* xrow = xs + (size_t)g * XROW + (size_t)kb * 2;      // activation row 8 nt + g = column g of B operand nt
+#pragma unroll
+    for (int st = 0; st < STEPS; ++st) {
+        uint4 xb[NT];
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            xb[nt] = make_uint4(0, 0, 0, 0);
+            if (nt * 8 + g < rows) xb[nt] = *reinterpret_cast<const uint4*>(xrow + (size_t)nt * 8 * XROW + st * 64);
+        }
+#pragma unroll
+        for (int tl = 0; tl < TPB; ++tl)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) {
+                gemv_mma16816(c[tl][nt], wlo[tl][st].x, whi[tl][st].x, wlo[tl][st].y, whi[tl][st].y, xb[nt].x, xb[nt].y);
+                gemv_mma16816(c[tl][nt], wlo[tl][st].z, whi[tl][st].z, wlo[tl][st].w, whi[tl][st].w, xb[nt].z, xb[nt].w);
+            }
+    }
+    // c[0..3] = (feature g, rows 2t / 2t+1), (feature g + 8, rows 2t / 2t+1) of row group nt: slot (g * 4 + t) * 4 + j of a partial tile
+#pragma unroll
+    for (int tl = 0; tl < TPB; ++tl)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+            *reinterpret_cast<float4*>(part + ((size_t)((warp * TPB + tl) * NT + nt) * 32 + lane) * 4) =
+                make_float4(c[tl][nt][0], c[tl][nt][1], c[tl][nt][2], c[tl][nt][3]);
     __syncthreads();
     if (MODE == 1) {
         // thread -> (tile, row, gate feature f): 8 adjacent features of a row are adjacent in y
-        for (int i = threadIdx.x; i < TPB * 64; i += WARPS * 32) {
-            const int tl = i >> 6, r = (i >> 3) & 7, f = i & 7;
+        for (int i = threadIdx.x; i < TPB * NT * 64; i += WARPS * 32) {
+            const int f = i & 7, r = (i >> 3) % (8 * NT), tl = i / (64 * NT);
             if (r >= rows) continue;
-            const int slot = ((f * 4 + (r >> 1)) * 4) + (r & 1);
+            const int nt = r >> 3, rr = r & 7;
+            const int slot = ((f * 4 + (rr >> 1)) * 4) + (rr & 1);
             float gs = 0.f, us = 0.f;
 #pragma unroll
             for (int wp = 0; wp < WARPS; ++wp) {
-                gs += part[(size_t)(wp * TPB + tl) * 128 + slot];
-                us += part[(size_t)(wp * TPB + tl) * 128 + slot + 2];
+                gs += part[(size_t)((wp * TPB + tl) * NT + nt) * 128 + slot];
+                us += part[(size_t)((wp * TPB + tl) * NT + nt) * 128 + slot + 2];
             }
             const float gg = bf16_round(gs), u = bf16_round(us);
             y[(size_t)r * n_out + (blockIdx.x * TPB + tl) * 8 + f] = __float2bfloat16_rn(bf16_round(gg / (1.0f + expf(-gg))) * u);
         }
     } else {
-        for (int i = threadIdx.x; i < TPB * 128; i += WARPS * 32) {
-            const int tl = i >> 7, r = (i >> 4) & 7, f = i & 15;
+        for (int i = threadIdx.x; i < TPB * NT * 128; i += WARPS * 32) {
+            const int f = i & 15, r = (i >> 4) % (8 * NT), tl = i / (128 * NT);
             const int n = (blockIdx.x * TPB + tl) * 16 + f;
             if (r >= rows || n >= N) continue;
-            const int slot = (((f & 7) * 4 + (r >> 1)) * 4) + (f >> 3) * 2 + (r & 1);
+            const int nt = r >> 3, rr = r & 7;
+            const int slot = (((f & 7) * 4 + (rr >> 1)) * 4) + (f >> 3) * 2 + (rr & 1);
             float a = 0.f;
 #pragma unroll
-            for (int wp = 0; wp < WARPS; ++wp) a += part[(size_t)(wp * TPB + tl) * 128 + slot];
+            for (int wp = 0; wp < WARPS; ++wp) a += part[(size_t)((wp * TPB + tl) * NT + nt) * 128 + slot];
             y[(size_t)r * N + n] = __float2bfloat16_rn(a);
         }
     }
 }
 
-template <int STEPS, int WARPS, int TPB, int MODE>
+template <int STEPS, int WARPS, int TPB, int NT, int MODE>
 static cudaError_t launch_gemv_mma(const void* x, const void* wf, int rows, int N, void* y, cudaStream_t s, const GemvNorm& nz,
                                    const PfArgs& pf) {
     constexpr int K = STEPS * 32 * WARPS;
     const int tiles = MODE == 1 ? N / 16 : (N + 15) / 16;
-    const size_t smem = (size_t)rows * (K * 2 + 64) + (size_t)WARPS * TPB * 512;
-    auto kern = linear_gemv_mma_kernel<STEPS, WARPS, TPB, MODE>;
+    const size_t smem = (size_t)rows * (K * 2 + 64) + (size_t)WARPS * TPB * NT * 512;
+    auto kern = linear_gemv_mma_kernel<STEPS, WARPS, TPB, NT, MODE>;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -438,10 +459,16 @@ int32_t t3b_linear_gemv_launch(const void* x, const void* w, int rows, int N, in
     cudaError_t e;
     if (wf != nullptr) {        // tensor-core GEMV on the fragment-ordered copy of w
         T3B_CHECK_SHAPE(t3b_gemv_mma_ok(N, K, mode), "gemv (tensor-core): N %d K %d", N, K);
-        T3B_CHECK_SHAPE(rows >= 1 && rows <= 8, "gemv (tensor-core): rows %d not in [1,8]", rows);
-        if (K == 4096) e = launch_gemv_mma<8, 16, 1, 0>(x, wf, rows, N, y, s, nz, pf);
-        else if (mode) e = launch_gemv_mma<4, 8, 2, 1>(x, wf, rows, N, y, s, nz, pf);
-        else e = launch_gemv_mma<4, 8, 1, 0>(x, wf, rows, N, y, s, nz, pf);
+        T3B_CHECK_SHAPE(rows >= 1 && rows <= 16, "gemv (tensor-core): rows %d not in [1,16]", rows);
+        if (rows <= 8) {
+            if (K == 4096) e = launch_gemv_mma<8, 16, 1, 1, 0>(x, wf, rows, N, y, s, nz, pf);
+            else if (mode) e = launch_gemv_mma<4, 8, 2, 1, 1>(x, wf, rows, N, y, s, nz, pf);
+            else e = launch_gemv_mma<4, 8, 1, 1, 0>(x, wf, rows, N, y, s, nz, pf);
+        } else {             // 9..16 rows: two 8-row B operands per weight fragment (a row's numbers are the same in both shapes)
+            if (K == 4096) e = launch_gemv_mma<8, 16, 1, 2, 0>(x, wf, rows, N, y, s, nz, pf);
+            else if (mode) e = launch_gemv_mma<4, 8, 2, 2, 1>(x, wf, rows, N, y, s, nz, pf);
+            else e = launch_gemv_mma<4, 8, 1, 2, 0>(x, wf, rows, N, y, s, nz, pf);
+        }
         T3B_CUDA(e);
         return T3B_OK;
     }

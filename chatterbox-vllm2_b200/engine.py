@@ -25,7 +25,7 @@ from . import _lib
 from .constants import CONDITIONING_SIZE, KV_BLOCK, SPEECH_TOKEN_OFFSET, T3Dims
 from .model import (START_SPEECH_TOKEN, STOP_SPEECH_TOKEN, DecodeState, KVPool, SamplingTensors, T3B200Model)
 
-GEMV_MMA_MAX_SEQS = 4            # engines of up to this many requests (<= 8 CFG rows) run the tensor-core GEMV chain by default
+GEMV_MMA_MAX_SEQS = 8            # engines of up to this many requests (<= 16 CFG rows) run the tensor-core GEMV chain by default
 SHARED_PREFIX_BLOCKS = (CONDITIONING_SIZE // KV_BLOCK)          # 2 blocks = positions 0..31 of the 34-row conditioning prefix
 
 
@@ -152,8 +152,8 @@ class T3B200Engine:
             # 0.91 -> 0.70; profiles/r2_notes.md r5).  ``gemv_mma=False`` keeps the SIMT GEMV (1 request) / tcgen05 (2..4) chain.
             if gemv_mma is None:
                 gemv_mma = max_num_seqs <= GEMV_MMA_MAX_SEQS
-            gemv_mma = bool(gemv_mma) and 2 * max_num_seqs <= 8 and model.enable_gemv_mma()
-            self.opt = _lib.make_options(gemv_max_rows=8 if gemv_mma else (0 if max_num_seqs == 1 else -1), attn_team_warps=team,
+            gemv_mma = bool(gemv_mma) and 2 * max_num_seqs <= 16 and model.enable_gemv_mma()
+            self.opt = _lib.make_options(gemv_max_rows=16 if gemv_mma else (0 if max_num_seqs == 1 else -1), attn_team_warps=team,
                                          norm_fusion=1 if norm_fusion else -1, gemv_mma=1 if gemv_mma else -1,
                                          weight_prefetch=2 if gemv_mma else 0)
         model.bind(self.kv, self.state)
@@ -170,7 +170,7 @@ class T3B200Engine:
         gate_up(+SiLU*mul), down] + final norm + head + sampler (the two norms ride inside the GEMVs at <= 2 rows and inside the
         tcgen05 projections at 3..32 rows)."""
         rows = 2 * self._bucket(n_slots)
-        gmax = 2 if self.opt.gemv_max_rows == 0 else max(0, min(8 if self.opt.gemv_mma > 0 else 4, self.opt.gemv_max_rows))
+        gmax = 2 if self.opt.gemv_max_rows == 0 else max(0, min(16 if self.opt.gemv_mma > 0 else 4, self.opt.gemv_max_rows))
         gemv = rows <= gmax and self.m.quantization is None and not self.opt.gemv_no_norm
         nf = self.opt.norm_fusion
         if not gemv and rows <= 32 and (nf > 0 or (nf == 0 and rows >= 9)) and rows > gmax and self.dims.hidden == 1024:

@@ -71,7 +71,7 @@ typedef struct t3b_linear {
     int32_t n, k;                /* out features, in features */
     const void* w;               /* bf16 [n,k]  |  AWQ repacked nibbles */
     const void* scales;          /* AWQ: bf16 [k/128, n].  bf16: NULL, or the copy of w in the fragment order of the tensor-core GEMV
-                                    (t3b_repack_weights_gemv) - with it and t3b_options_t.gemv_mma, <= 8 rows run that kernel   */
+                                    (t3b_repack_weights_gemv) - with it and t3b_options_t.gemv_mma, <= 16 rows run that kernel   */
     const void* zeros;           /* AWQ: uint8 [k/128, n]         (else NULL) */
     int32_t flags;               /* T3B_LIN_* */
 } t3b_linear_t;
@@ -147,7 +147,7 @@ typedef struct t3b_sampling {    /* per-request device arrays [B]; tts.py:455-46
 /* Launch-shape knobs of the decode path (NULL / 0 fields = the library's measured defaults).  Everything that used to be an
  * environment variable inside the library is an explicit argument here. */
 typedef struct t3b_options {
-    int32_t gemv_max_rows;       /* bf16 projections use the GEMV kernels up to this many rows (0 = default 2, max 4 - 8 with gemv_mma; -1 = never) */
+    int32_t gemv_max_rows;       /* bf16 projections use the GEMV kernels up to this many rows (0 = default 2, max 4 - 16 with gemv_mma; -1 = never) */
     int32_t gemv_no_norm;        /* 1 = keep add+RMSNorm as separate launches at GEMV row counts (default: folded in)     */
     int32_t umma_stages;         /* tcgen05 GEMM: shared-memory ring depth cap (0 = default 5)                             */
     int32_t umma_row_chunk;      /* tcgen05 GEMM: CFG rows per thread block, multiple of 16 (0 = default)                  */
@@ -166,7 +166,7 @@ typedef struct t3b_options {
                                     to a bf16 step, not bit for bit                                                                */
     int32_t gemv_mma;            /* 1 = the GEMV row counts run on the tensor cores (mma.sync m16n8k16 on weight fragments loaded straight
                                     from global memory, csrc/linear_gemv.cu) for every bf16 projection that carries its fragment-ordered
-                                    copy (t3b_linear_t.scales): up to 8 rows (gemv_max_rows may then be up to 8), K = 1024 or 4096.  fp32 accumulation in another order than the SIMT GEMV: results agree to a bf16 step.
+                                    copy (t3b_linear_t.scales): up to 16 rows (gemv_max_rows may then be up to 16), K = 1024 or 4096.  fp32 accumulation in another order than the SIMT GEMV: results agree to a bf16 step.
                                     0 = library default, -1 = the SIMT kernel                                                        */
 } t3b_options_t;
 

@@ -150,16 +150,22 @@ def test_engine_graph_replay_equals_eager_and_is_batch_invariant():
         assert runs[0] == runs[1], "CUDA-graph replay must reproduce the eager launches bit for bit"
         assert runs[0] == runs[2], "continuous batching (3 slots, 6 requests) must not change any request's tokens"
         assert runs[0] == runs[3], "batched admission (refill when 2 slots are free or after 5 steps) must not change any request's tokens"
-    # Engines of <= 4 slots on their default chain (tensor-core GEMV at every live-row count, 2..8 rows): a request's tokens do not
-    # depend on the engine size, the other requests beside it, or graph replay.
-    runs = []
-    for kw in (dict(max_num_seqs=4, use_graphs=False), dict(max_num_seqs=4, use_graphs=True), dict(max_num_seqs=3, use_graphs=True, check_every=5),
-               dict(max_num_seqs=2, use_graphs=True), dict(max_num_seqs=1, use_graphs=True)):
-        eng = T3B200Engine(m, max_model_len=128, **kw)
-        assert eng.opt.gemv_mma == 1 and eng.opt.gemv_max_rows == 8
-        runs.append([o.outputs[0].token_ids for o in eng.generate(prompts, sp)])
-        del eng
-    assert all(r == runs[0] for r in runs[1:]), "tensor-core GEMV engines of 1..4 slots must agree bit for bit"
+    # Engines of <= 8 slots on their default chain (tensor-core GEMV at every live-row count, 2..16 rows): a request's tokens do not
+    # depend on the engine size, the other requests beside it, or graph replay - among engines that share the attention team size
+    # (8 warps per item up to 4 slots, 4 warps at 5..9 slots: the order in which an item's online-softmax states are merged).
+    for group in ((dict(max_num_seqs=4, use_graphs=False), dict(max_num_seqs=4, use_graphs=True), dict(max_num_seqs=3, use_graphs=True, check_every=5),
+                   dict(max_num_seqs=2, use_graphs=True), dict(max_num_seqs=1, use_graphs=True)),
+                  (dict(max_num_seqs=8, use_graphs=False), dict(max_num_seqs=8, use_graphs=True),
+                   dict(max_num_seqs=6, use_graphs=True, admit_batch=2, admit_wait_steps=5), dict(max_num_seqs=5, use_graphs=True))):
+        runs, teams = [], set()
+        for kw in group:
+            eng = T3B200Engine(m, max_model_len=128, **kw)
+            assert eng.opt.gemv_mma == 1 and eng.opt.gemv_max_rows == 16
+            teams.add(eng.opt.attn_team_warps)
+            runs.append([o.outputs[0].token_ids for o in eng.generate(prompts, sp)])
+            del eng
+        assert len(teams) == 1
+        assert all(r == runs[0] for r in runs[1:]), "tensor-core GEMV engines that share the attention team size must agree bit for bit"
 
 
 def test_engine_sampled_stream_vs_golden():

@@ -221,17 +221,17 @@ def _gemv_frag(L, wd, N, K, gate_up):
     return out
 
 
-@pytest.mark.parametrize("rows", [1, 2, 3, 5, 8])
+@pytest.mark.parametrize("rows", [1, 2, 3, 5, 8, 9, 13, 16])
 @pytest.mark.parametrize("N,K", [(3072, 1024), (1024, 1024), (1024, 4096), (8194, 1024), (48, 1024)])
 def test_linear_gemv_mma(L, rows, N, K):
-    """t3b_options_t.gemv_mma: the tensor-core GEMV (<= 8 rows, weight fragments straight from global memory, split-K over the warps
+    """t3b_options_t.gemv_mma: the tensor-core GEMV (<= 16 rows, weight fragments straight from global memory, split-K over the warps
     of a block) against the fp32 matmul, every projection shape of the model incl. the 8194-wide head (last tile: 2 features);
     a row's numbers do not depend on how many rows ride along (row r alone == row r of the batch)."""
     g = torch.Generator().manual_seed(N + K + rows)
     x = torch.randn(rows, K, generator=g).bfloat16()
     w = (torch.randn(N, K, generator=g) * K ** -0.5).bfloat16()
     xd, wd = bf(x), bf(w)
-    opt = _lib.make_options(gemv_max_rows=8, gemv_mma=1)
+    opt = _lib.make_options(gemv_max_rows=16, gemv_mma=1)
     frag = _gemv_frag(L, wd, N, K, 0)
     lin = _lib.Linear(_lib.T3B_W_BF16, N, K, wd.data_ptr(), frag.data_ptr(), None)
     y = torch.full((rows, N), float("nan"), dtype=torch.bfloat16, device=DEV)
@@ -241,13 +241,13 @@ def test_linear_gemv_mma(L, rows, N, K):
     last = xd[rows - 1:].contiguous()
     _lib.check(L.t3b_linear_bf16(last.data_ptr(), C.byref(lin), 1, y1.data_ptr(), None, 1, None, _lib.T3B_IMPL_GEMV, 0, C.byref(opt), sp()))
     assert torch.equal(y1[0], y[rows - 1])
-    # AUTO: rows <= gemv_max_rows take it too, 9 rows fall through to the tcgen05 kernel
+    # AUTO: rows <= gemv_max_rows take it too
     ns = C.c_int32(-1)
     _lib.check(L.t3b_linear_bf16(xd.data_ptr(), C.byref(lin), rows, y.data_ptr(), None, 0, C.byref(ns), _lib.T3B_IMPL_AUTO, 0, C.byref(opt), sp()))
     assert ns.value == 1
 
 
-@pytest.mark.parametrize("rows", [1, 2, 4, 7, 8])
+@pytest.mark.parametrize("rows", [1, 2, 4, 7, 8, 10, 16])
 def test_linear_gemv_mma_gate_up_silu(L, rows):
     """gate_up on the tensor-core GEMV: tile rows 0..7 = gate, 8..15 = up, SiLU * mul with the reference's bf16 roundings."""
     g = torch.Generator().manual_seed(rows)
@@ -255,7 +255,7 @@ def test_linear_gemv_mma_gate_up_silu(L, rows):
     x = torch.randn(rows, K, generator=g).bfloat16()
     w = (torch.randn(2 * F, K, generator=g) * K ** -0.5).bfloat16()
     xd, wd = bf(x), bf(w)
-    opt = _lib.make_options(gemv_max_rows=8, gemv_mma=1)
+    opt = _lib.make_options(gemv_max_rows=16, gemv_mma=1)
     act = torch.full((rows, F), float("nan"), dtype=torch.bfloat16, device=DEV)
     frag = _gemv_frag(L, wd, 2 * F, K, 1)
     lin = _lib.Linear(_lib.T3B_W_BF16, 2 * F, K, wd.data_ptr(), frag.data_ptr(), None)

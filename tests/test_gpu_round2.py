@@ -357,9 +357,9 @@ def test_gemv_norm_fold_equals_separate_norm_launches(L, small_model, rows):
     assert all(torch.equal(a, b) for a, b in zip(outs[0], outs[1]))
 
 
-@pytest.mark.parametrize("rows", [2, 4, 6, 8])
+@pytest.mark.parametrize("rows", [2, 4, 6, 8, 12, 16])
 def test_gemv_mma_decode_chain_matches_tcgen05_chain(L, small_model, rows):
-    """t3b_options_t.gemv_mma: the 5-launch GEMV chain on the tensor cores (<= 8 rows, add + RMSNorm in front of qkv / gate_up) against
+    """t3b_options_t.gemv_mma: the 5-launch GEMV chain on the tensor cores (<= 16 rows, add + RMSNorm in front of qkv / gate_up) against
     the 7-launch tcgen05 chain.  Both accumulate in fp32, in different orders: layer 0's K / V come out of one projection (all but a
     few elements identical, the rest one bf16 step apart), the hidden state after the small model's layers agrees to a few bf16
     steps; the chain is deterministic, and a request's rows do not depend on the rows beside them (rows 0..1 alone == rows 0..1 of
@@ -372,7 +372,7 @@ def test_gemv_mma_decode_chain_matches_tcgen05_chain(L, small_model, rows):
     for mode in ("mma", "umma", "mma", "mma2"):
         n = 2 if mode == "mma2" else rows
         kv, st = random_state(SMALL, rows, lens, seed=5)
-        opt = _lib.make_options(gemv_max_rows=-1, norm_fusion=-1) if mode == "umma" else _lib.make_options(gemv_max_rows=8, gemv_mma=1)
+        opt = _lib.make_options(gemv_max_rows=-1, norm_fusion=-1, attn_team_warps=4) if mode == "umma" else _lib.make_options(gemv_max_rows=16, gemv_mma=1, attn_team_warps=4)
         ws = m.workspace(rows)
         hid = torch.zeros(rows, 1024, dtype=torch.bfloat16, device=DEV)
         _lib.check(L.t3b_decode_step(C.byref(m.c), C.byref(kv.c), C.byref(st.c), None, n, hid.data_ptr(), ws.data_ptr(), ws.numel(),

@@ -53,7 +53,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=32, help="requests per GPU (CFG rows = 2x)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-breakdown", action="store_true")
-    ap.add_argument("--sweep", default="1,awq256,cfg4", help="extra points for the 'sweep' key: N = N bf16 requests greedy; awqN = configs[2] "
+    ap.add_argument("--sweep", default="1,8,awq256,cfg4", help="extra points for the 'sweep' key: N = N bf16 requests greedy; awqN = configs[2] "
                                                              "(AWQ W4A16, sampling); cfg4 = configs[3] (128 requests at context ~1000); fp8N = N "
                                                              "requests on an FP8 KV pool; '' = none")
     ap.add_argument("--workload", default="cfg2", choices=["cfg2", "cfg5"], help="cfg2 = BASELINE.json configs[1] (default); cfg5 = "

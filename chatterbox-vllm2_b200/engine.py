@@ -146,10 +146,10 @@ class T3B200Engine:
             # (engines of different sizes produce the same tokens only if they agree on it).
             if norm_fusion is None:
                 norm_fusion = 16 <= 2 * max_num_seqs <= 32
-            # Engines of up to 4 requests (<= 8 CFG rows, bf16): the tensor-core GEMV chain (t3b_options_t.gemv_mma, 5 launches per
+            # Engines of up to 8 requests (<= 16 CFG rows, bf16): the tensor-core GEMV chain (t3b_options_t.gemv_mma, 5 launches per
             # layer) at every live-row count, on fragment-ordered copies of the weights made here once (+1 GB), every launch pulling
-            # the next layer's copy of its projection into L2 (1 request 0.57 -> 0.50 ms/step, 2 requests 0.87 -> 0.57, 4 requests
-            # 0.91 -> 0.70; profiles/r2_notes.md r5).  ``gemv_mma=False`` keeps the SIMT GEMV (1 request) / tcgen05 (2..4) chain.
+            # the next layer's copy of its projection into L2 (1 request 0.57 -> 0.44 ms/step, 2 requests 0.87 -> 0.48, 4 requests
+            # 0.91 -> 0.56, 8 requests 0.94 -> 0.80; profiles/r2_notes.md r5).  ``gemv_mma=False`` keeps the SIMT GEMV (1 request) / tcgen05 (2..8) chain.
             if gemv_mma is None:
                 gemv_mma = max_num_seqs <= GEMV_MMA_MAX_SEQS
             gemv_mma = bool(gemv_mma) and 2 * max_num_seqs <= 16 and model.enable_gemv_mma()

@@ -18,10 +18,7 @@ except Exception as e:
     print("$1 no bench line:", e)
 PY
 }
-OLD="gemv_mma=-1,gemv_max_rows=-1,weight_prefetch=0"
-run b5_old 5 "$OLD"
-run b5_mma 5 ""
-run b6_mma 6 ""
-run b8_old 8 "$OLD"
-run b8_mma 8 ""
-run b4_mma 4 ""
+run b5 5 ""
+run b6 6 ""
+run b8 8 ""
+run b2 2 ""

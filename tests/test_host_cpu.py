@@ -242,3 +242,33 @@ def test_gemv_weight_loads_stay_in_front_of_the_dependency_wait():
         assert wait and pre >= 2, (fn, pre, post)
         if "mma" in fn or fn.endswith("Lb1EEvPK13__nv_bfloat16S2_iiiPS0_8GemvNorm6PfArgs"):
             assert post == 0, (fn, pre, post)      # single-shot kernels: the whole slice is requested before the wait
+
+
+def test_ctypes_mirrors_match_the_header_layout(tmp_path):
+    """The Python host side mirrors the C structs of include/t3b200.h field by field (chatterbox_vllm2_b200/_lib.py).  Compile a
+    C program against the header with gcc and compare sizeof / offsetof of the last field of every struct with the ctypes
+    mirrors - a field added on one side only would shift every argument behind it."""
+    import ctypes as C
+    import shutil
+    import subprocess
+    from chatterbox_vllm2_b200 import _lib
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("gcc not available")
+    pairs = [("t3b_linear_t", _lib.Linear, "flags"), ("t3b_layer_t", _lib.Layer, "ln2"), ("t3b_model_t", _lib.Model, None),
+             ("t3b_kv_t", _lib.KV, None), ("t3b_state_t", _lib.State, "row_order"), ("t3b_sampling_t", _lib.Sampling, "combine"),
+             ("t3b_options_t", _lib.Options, "gemv_mma")]
+    lines = ["#include <stdio.h>", "#include <stddef.h>", '#include "t3b200.h"', "int main(void) {"]
+    for cname, _, last in pairs:
+        lines.append(f'  printf("{cname} %zu %zu\\n", sizeof({cname}), ' + (f"offsetof({cname}, {last})" if last else "(size_t)0") + ");")
+    lines += ["  return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.run([gcc, "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()
+    got = {out[i]: (int(out[i + 1]), int(out[i + 2])) for i in range(0, len(out), 3)}
+    for cname, mirror, last in pairs:
+        assert got[cname][0] == C.sizeof(mirror), (cname, got[cname][0], C.sizeof(mirror))
+        if last:
+            assert got[cname][1] == getattr(mirror, last).offset, (cname, last)

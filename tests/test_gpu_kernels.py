@@ -221,6 +221,19 @@ def _gemv_frag(L, wd, N, K, gate_up):
     return out
 
 
+@pytest.mark.parametrize("N,K,gate_up", [(3072, 1024, 0), (8192, 1024, 1), (1024, 4096, 0), (8194, 1024, 0), (48, 1024, 0)])
+def test_gemv_frag_repack_matches_oracle_layout(L, N, K, gate_up):
+    """t3b_repack_weights_gemv against the numpy restatement of the fragment order (oracle/gemv_frag_ref.py, whose dot products are
+    checked against x @ W.T on the CPU): bit for bit, incl. the padded last tile of the 8194-wide head and the gate | up tiles."""
+    from oracle import gemv_frag_ref
+    g = torch.Generator().manual_seed(N + K)
+    w = (torch.randn(N, K, generator=g) * K ** -0.5).bfloat16()
+    wd = bf(w)
+    got = _gemv_frag(L, wd, N, K, gate_up).cpu().numpy().view(np.uint16)
+    want = gemv_frag_ref.frag_order(w.view(torch.int16).numpy().view(np.uint16), bool(gate_up)).reshape(-1)
+    assert got.shape == want.shape and np.array_equal(got, want)
+
+
 @pytest.mark.parametrize("rows", [1, 2, 3, 5, 8, 9, 13, 16])
 @pytest.mark.parametrize("N,K", [(3072, 1024), (1024, 1024), (1024, 4096), (8194, 1024), (48, 1024)])
 def test_linear_gemv_mma(L, rows, N, K):

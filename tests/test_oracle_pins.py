@@ -198,3 +198,16 @@ def test_decode_embedding_and_cfg_semantics():
     c, u = orc.prefill_embeds(cond.float(), ids)
     assert c.shape == (34 + 5 + 1, 1024) and torch.equal(c[:34], u[:34]) and torch.equal(c[-1], u[-1])
     assert u[34:39].abs().sum() == 0
+
+
+def test_gemv_fragment_order_forms_the_matmul():
+    """oracle/gemv_frag_ref.py: the fragment-ordered weight copy of the tensor-core GEMV, with the k permutation of its mma.sync
+    operands, pairs every W[n][k] with x[r][k] - plain projections (incl. a last tile that is only partly valid, like the 8194-wide
+    head) and gate_up tiles (8 gate + the 8 matching up features).  The GPU test compares t3b_repack_weights_gemv with this layout."""
+    from oracle import gemv_frag_ref as gf
+    rng = np.random.default_rng(0)
+    for N, K, gu in ((48, 64, False), (50, 128, False), (64, 64, True), (130, 1024, False), (96, 4096, False)):
+        w, x = rng.standard_normal((N, K)), rng.standard_normal((5, K))
+        f = gf.frag_order(w, gu)
+        assert f.shape == ((N // 16 if gu else (N + 15) // 16), K // 32, 2, 32, 8)
+        assert np.abs(gf.mma_emulate(f, x, N, gu) - x @ w.T).max() < 1e-10

@@ -44,13 +44,13 @@ def full_model(quant=None):
     return _MODELS[quant]
 
 
-def run_teacher_forced(m, n_req, forced, sps, max_model_len):
+def run_teacher_forced(m, n_req, forced, sps, max_model_len, **engine_kw):
     """forced [B, T] (the fixture's tokens).  Returns CUDA combined logits [T, B, V] (step 0 = NaN: the first token comes out of
     install()'s prefill) and the tokens the CUDA sampler chose [B, T]."""
     B, T = forced.shape
     assert B == n_req
     prompts = [synthetic_request(i, FULL, n_text=64) for i in range(B)]
-    eng = T3B200Engine(m, max_num_seqs=B, max_model_len=max_model_len, use_graphs=False)
+    eng = T3B200Engine(m, max_num_seqs=B, max_model_len=max_model_len, use_graphs=False, **engine_kw)
     st = eng.state
     logits = torch.empty(T, B, FULL.speech_vocab, dtype=torch.float32, device=DEV)
     toks = torch.empty(T, B, dtype=torch.int32, device=DEV)
@@ -135,9 +135,28 @@ def test_folded_norm_chain_16_and_32_rows_vs_golden(n_req):
     gold = _GoldSlice(np.load(os.path.join(GOLD, "t3_full_batch32.npz")), n_req)
     sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=16, ignore_eos=True)
     m = full_model()
-    assert T3B200Engine(m, max_num_seqs=n_req, max_model_len=256, use_graphs=False).opt.norm_fusion == 1
-    logits, toks = run_teacher_forced(m, n_req, gold["tokens"], sp, max_model_len=256)
+    # gemv_mma=False: an engine of 8 slots would otherwise run the tensor-core GEMV chain (next test); the folded chain at 16 rows is
+    # what a 9..16-slot engine runs when 8 of its requests are live
+    probe = T3B200Engine(m, max_num_seqs=n_req, max_model_len=256, use_graphs=False, gemv_mma=False)
+    assert probe.opt.norm_fusion == 1 and probe.opt.gemv_mma != 1
+    del probe
+    logits, toks = run_teacher_forced(m, n_req, gold["tokens"], sp, max_model_len=256, gemv_mma=False)
     check_greedy(f"folded_norms_{2 * n_req}rows_teacher_forced", logits, toks, gold, TOL_30)
+
+
+@pytest.mark.parametrize("n_req", [4, 8])
+def test_gemv_mma_chain_8_and_16_rows_vs_golden(n_req):
+    """The tensor-core GEMV chain (t3b_options_t.gemv_mma, what an engine of <= 8 slots runs: fragment-ordered weight copies,
+    mma.sync, fused norms, one / two 8-row B operands) at full depth: the first 4 / 8 requests of the configs[1] fixture, same
+    tolerance as the other chains."""
+    gold = _GoldSlice(np.load(os.path.join(GOLD, "t3_full_batch32.npz")), n_req)
+    sp = SamplingParams(temperature=0.0, repetition_penalty=2.0, max_tokens=16, ignore_eos=True)
+    m = full_model()
+    probe = T3B200Engine(m, max_num_seqs=n_req, max_model_len=256, use_graphs=False)
+    assert probe.opt.gemv_mma == 1 and probe.opt.gemv_max_rows == 16
+    del probe
+    logits, toks = run_teacher_forced(m, n_req, gold["tokens"], sp, max_model_len=256)
+    check_greedy(f"gemv_mma_{2 * n_req}rows_teacher_forced", logits, toks, gold, TOL_30)
 
 
 def sampler_on_cuda_logits(logits, forced, seeds, rho=2.0, temperature=0.8, min_p=0.05, top_p=0.8):

@@ -36,7 +36,7 @@ int32_t t3b_paged_attn_launch(const void* q, int n_tok, const int32_t* tok_row, 
                                       // at 64 rows the operand build costs what the two launches saved: 1.351 -> 1.369, profiles/r2_notes.md r4)
 #define AWQ_DEQUANT_MIN_ROWS 256      // from here on AWQ layers are dequantised once per layer into a bf16 scratch (vllm awq.py:276-281 does the same)
 #define GEMV_MMA_DEFAULT 0            // t3b_options_t.gemv_mma = 0
-#define GEMV_MAX_ROWS_DEFAULT 2       // measured: 4 rows run 0.87 ms/step on the tcgen05 path, 0.96 on the GEMV (profiles/r02_notes.md)
+#define GEMV_MAX_ROWS_DEFAULT 2       // library default without options; engines fix their own (16 with the tensor-core GEMV chain)
 static thread_local char g_err[512] = "";
 
 void t3b_set_error(const char* fmt, ...) {
@@ -226,7 +226,8 @@ struct PrefillSeqs {          // sequences of a multi-token pass (t3b_prefill_at
 // F2: the 30-layer stack over n_tok tokens (decode: one token per CFG row; prefill: the whole prompt of
 // each new row, causal through tok_idx).  x0 = bf16 [n_tok, hidden] input embeddings.
 // Decode layer = 7 launches: add+norm, qkv GEMM, attention (RoPE + KV write fused), o GEMM, add+norm,
-// gate_up GEMM (SiLU*mul epilogue), down GEMM; at GEMV row counts the two add+norms run inside the qkv / gate_up GEMVs (5 launches).
+// gate_up GEMM (SiLU*mul epilogue), down GEMM; at GEMV row counts (SIMT <= 4 rows, tensor cores <= 16 rows) the two add+norms run
+// inside the qkv / gate_up GEMVs (5 launches), at <= 32 rows on the tcgen05 kernel inside the projections (5 launches).
 static int32_t forward_impl(const t3b_model_t* m, const t3b_kv_t* kv, const void* x0, int n_tok, const int32_t* tok_row,
                             const int32_t* tok_idx, const int32_t* rope_pos, const int32_t* block_tables, int max_blocks,
                             const PrefillSeqs* ps, void* hidden_out, const Workspace& ws, const Opt& o, void* stream,

@@ -1,5 +1,8 @@
-// F2.2 / F2.5 / F2.6 / C1 at small batch (rows <= 4): SIMT GEMV, HBM-bound.
+// F2.2 / F2.5 / F2.6 / C1 at small batch.  Two kernels: the SIMT GEMV below (rows <= 4, reads the nn.Linear layout; what a model
+// without fragment-ordered weight copies runs) and the tensor-core GEMV further down (rows <= 16, linear_gemv_mma_kernel: what engines
+// of <= 8 requests run).
 //
+// SIMT kernel:
 // Each warp owns FPW output features and streams their weight rows with 128-bit non-allocating
 // loads, FPW*KSTEP loads (16) in flight per lane; the activations (<= 4 rows) sit in shared memory
 // as bf16 and are read conflict-free.  fp32 accumulate, one warp-shuffle tree per output, bf16
